@@ -1,0 +1,125 @@
+"""ctypes loader for libgeot_b200.so (include/geot_b200.h) — stream, device and error plumbing.
+
+PyTorch is used for device memory and streams only.  There is NO fallback: if the CUDA library is
+missing or a call fails this raises; nothing here (or anywhere in geot_b200/) imports oracle/.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, "_C", "libgeot_b200.so")
+_lib = None
+
+GEOT_FPS_CAP512 = 1
+GEOT_FPS_MAGSKIP = 2
+GEOT_FPS_FORCE_GENERIC = 4
+
+_vp, _i, _f, _i64, _sz = C.c_void_p, C.c_int, C.c_float, C.c_int64, C.c_size_t
+
+# name -> argtypes (every function returns int unless listed in _RESTYPES)
+_SIGNATURES = {
+    "geot_abi_version": [],
+    "geot_last_error": [],
+    "geot_launch_count": [],
+    "geot_furthest_point_sampling": [_i, _i, _i, _vp, _vp, _vp, _i, _vp],
+    "geot_furthestsampling": [_i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
+    "geot_ball_query": [_i, _i, _i, _f, _i, _vp, _vp, _vp, _vp],
+    "geot_ballquery_offset": [_i, _i, _f, _i, _vp, _vp, _vp, _vp, _vp, _vp],
+    "geot_knnquery_workspace_bytes": [_i],
+    "geot_knnquery": [_i, _i, _i, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _sz, _vp],
+    "geot_group_points": [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp],
+    "geot_gather_points": [_i, _i, _i, _i, _vp, _vp, _vp, _vp],
+    "geot_scatter_plan_bytes": [_i, _i, _i64],
+    "geot_scatter_plan_build": [_i, _i, _i64, _vp, _vp, _sz, _vp],
+    "geot_group_points_grad": [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp],
+    "geot_gather_points_grad": [_i, _i, _i, _i, _vp, _vp, _vp, _vp],
+    "geot_three_nn": [_i, _i, _i, _vp, _vp, _vp, _vp, _vp],
+    "geot_three_interpolate": [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp],
+    "geot_three_interpolate_grad": [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp],
+    "geot_grouping_forward": [_i, _i, _i, _vp, _vp, _vp, _vp],
+    "geot_grouping_backward": [_i, _i, _i, _i, _vp, _vp, _vp, _vp],
+    "geot_interpolation_forward": [_i, _i, _i, _vp, _vp, _vp, _vp, _vp],
+    "geot_interpolation_backward": [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp],
+    "geot_subtraction_forward": [_i, _i, _i, _vp, _vp, _vp, _vp, _vp],
+    "geot_subtraction_backward": [_i, _i, _i, _vp, _vp, _vp, _vp, _vp],
+    "geot_aggregation_forward": [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp],
+    "geot_aggregation_backward": [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
+}
+_RESTYPES = {
+    "geot_last_error": C.c_char_p,
+    "geot_launch_count": C.c_uint64,
+    "geot_scatter_plan_bytes": _sz,
+    "geot_knnquery_workspace_bytes": _sz,
+}
+
+
+class GeotError(RuntimeError):
+    pass
+
+
+def build(verbose: bool = False) -> str:
+    """Compile every kernel for sm_100a into geot_b200/_C/libgeot_b200.so (nvcc, no torch headers)."""
+    r = subprocess.run(["make", "-C", os.path.join(_HERE, "csrc"), "-j8"], capture_output=True, text=True)
+    if r.returncode != 0:
+        raise GeotError("building libgeot_b200.so failed:\n" + r.stdout[-4000:] + r.stderr[-4000:])
+    if verbose:
+        print(r.stdout[-2000:])
+    return SO_PATH
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(SO_PATH):
+            raise GeotError(
+                f"{SO_PATH} is missing: the geot_b200 ops have no CPU or PyTorch fallback. "
+                "Build it with `python -c 'import __graft_entry__ as g; g.build()'` or `make -C geot_b200/csrc`.")
+        L = C.CDLL(SO_PATH)
+        for name, argtypes in _SIGNATURES.items():
+            fn = getattr(L, name)  # AttributeError here = header/library mismatch: fail loudly
+            fn.argtypes = argtypes
+            fn.restype = _RESTYPES.get(name, C.c_int)
+        _lib = L
+    return _lib
+
+
+def launch_count() -> int:
+    return int(lib().geot_launch_count())
+
+
+def ptr(t):
+    """Device pointer of a tensor (None -> NULL)."""
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def stream_ptr():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def check_cuda(*tensors):
+    """Every tensor must live on one CUDA device and be contiguous; returns that device."""
+    dev = None
+    for t in tensors:
+        if t is None:
+            continue
+        if not t.is_cuda:
+            raise GeotError("geot_b200 ops are CUDA-only (sm_100a); got a CPU tensor — there is no CPU fallback")
+        if not t.is_contiguous():
+            raise GeotError("geot_b200 ops need contiguous tensors (the reference asserts the same, group.py:88-89)")
+        if dev is None:
+            dev = t.device
+        elif t.device != dev:
+            raise GeotError(f"tensors on different devices: {dev} vs {t.device}")
+    return dev
+
+
+def call(name, *args):
+    rc = getattr(lib(), name)(*args)
+    if rc != 0:
+        msg = lib().geot_last_error()
+        raise GeotError(f"{name} failed ({rc}): {msg.decode() if msg else ''}")

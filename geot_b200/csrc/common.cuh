@@ -1,0 +1,61 @@
+// geot_b200/csrc/common.cuh — shared helpers for the sm_100a kernels behind include/geot_b200.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <cmath>
+#include "../../include/geot_b200.h"
+
+#define GEOT_API extern "C" __attribute__((visibility("default")))
+
+namespace geot {
+
+void set_error(const char* fmt, ...);
+
+// Launch-error plumbing: the reference exit(-1)s on a failed launch (sampling_gpu.cu:255-259);
+// the C ABI returns a code and keeps a per-thread message instead.
+inline int check_launch(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("%s: %s", what, cudaGetErrorString(e));
+    return GEOT_ERR_CUDA;
+  }
+  return GEOT_OK;
+}
+
+#define GEOT_REQUIRE(cond, ...)          \
+  do {                                   \
+    if (!(cond)) {                       \
+      ::geot::set_error(__VA_ARGS__);    \
+      return GEOT_ERR_INVALID;           \
+    }                                    \
+  } while (0)
+
+inline cudaStream_t as_stream(geot_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
+
+// The reference's block-size rule (cuda_utils.h:10-14): largest power of two <= n, capped.
+// It decides the FPS tie order, so it is reproduced with the same double-log expression.
+inline int ref_opt_n_threads(int work_size, int cap) {
+  const int pow_2 = (int)(std::log(static_cast<double>(work_size)) / std::log(2.0));
+  int v = 1 << pow_2;
+  if (v > cap) v = cap;
+  if (v < 1) v = 1;
+  return v;
+}
+
+// Squared distance in the evaluation order nvcc gives the reference kernels on sm_100
+// (FMUL dy*dy ; FFMA dx*dx+. ; FFMA dz*dz+.) — explicit _rn intrinsics are never re-contracted.
+__device__ __forceinline__ float dist2_ref(float ax, float ay, float az, float bx, float by, float bz) {
+  const float dx = __fsub_rn(ax, bx), dy = __fsub_rn(ay, by), dz = __fsub_rn(az, bz);
+  return __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
+}
+
+__device__ __forceinline__ unsigned lanemask_lt() {
+  unsigned m;
+  asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+  return m;
+}
+
+constexpr int kNumSMs = 148;  // B200
+
+}  // namespace geot

@@ -1,0 +1,294 @@
+// geot_b200/csrc/group.cu — grouping / gather (channel-major, batched) and the deterministic
+// scatter plan used by every backward pass.
+//
+// Replaces
+//   openpoints/cpp/pointnet2_batch/src/group_points_gpu.cu:53-72 (fwd), :14-31 (bwd, atomicAdd :30)
+//   openpoints/cpp/pointnet2_batch/src/sampling_gpu.cu:15-31 (gather fwd), :53-70 (bwd, atomicAdd :69)
+//   pointnet2/_ext_src/src/group_points_gpu.cu:11-31,46-67 and sampling_gpu.cu:11-23,37-50 (same results)
+//
+// Forward: HBM-bound on the (B,C,M,ns) write.  The reference launches one thread per output element
+// and one grid row per channel, so idx is re-read C times and every access is 4 bytes.  Here a thread
+// owns 4 consecutive (j,s) entries: one int4 idx load kept in registers across a chunk of channels,
+// four cached 4-byte gathers per channel (a (N) feature row is L1/L2 resident) and one 16-byte
+// streaming store; 64-bit flat offsets throughout.
+//
+// Backward: the reference scatter-adds with float atomics (run-to-run different sums).  Here a
+// "scatter plan" — CSR of source positions by target, sources in ascending order — is built once per
+// idx with integer atomics + a stable ranking pass (bit-reproducible), and each target sums its
+// sources in that fixed order.
+#include "common.cuh"
+
+namespace geot {
+
+void count_launch(int n);
+
+constexpr int kGroupCCH = 16;  // channels per thread in the forward gather
+
+// VEC = 4: E % 4 == 0 and 16-byte aligned idx/out.  grid (ceil(E/VEC/256), ceil(C/CCH), B).
+template <int VEC>
+__global__ void __launch_bounds__(256)
+group_points_kernel(int C, int N, int64_t E, const float* __restrict__ points,
+                    const int* __restrict__ idx, float* __restrict__ out) {
+  const int b = blockIdx.z;
+  const int c0 = blockIdx.y * kGroupCCH;
+  const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // entry group
+  if (g * VEC >= E) return;
+  const int c1 = min(C, c0 + kGroupCCH);
+  if (VEC == 4) {
+    const int4 id = __ldg(reinterpret_cast<const int4*>(idx + (int64_t)b * E) + g);
+    for (int c = c0; c < c1; c++) {
+      const float* __restrict__ row = points + ((int64_t)b * C + c) * N;
+      float4 o;
+      o.x = __ldg(row + id.x); o.y = __ldg(row + id.y); o.z = __ldg(row + id.z); o.w = __ldg(row + id.w);
+      __stcs(reinterpret_cast<float4*>(out + ((int64_t)b * C + c) * E) + g, o);
+    }
+  } else {
+    const int id = __ldg(idx + (int64_t)b * E + g);
+    for (int c = c0; c < c1; c++) {
+      const float* __restrict__ row = points + ((int64_t)b * C + c) * N;
+      __stcs(out + ((int64_t)b * C + c) * E + g, __ldg(row + id));
+    }
+  }
+}
+
+static int launch_group(int B, int C, int N, int64_t E, const float* points, const int* idx, float* out,
+                        cudaStream_t s, const char* what) {
+  if (B == 0 || C == 0 || E == 0) return GEOT_OK;
+  GEOT_REQUIRE(points && idx && out, "%s: NULL pointer", what);
+  GEOT_REQUIRE(B <= 65535 && (C + kGroupCCH - 1) / kGroupCCH <= 65535, "%s: B or C exceeds grid limits", what);
+  const bool vec = (E % 4 == 0) && (((uintptr_t)idx & 15) == 0) && (((uintptr_t)out & 15) == 0);
+  if (vec) {
+    dim3 grid((unsigned)((E / 4 + 255) / 256), (C + kGroupCCH - 1) / kGroupCCH, B);
+    group_points_kernel<4><<<grid, 256, 0, s>>>(C, N, E, points, idx, out);
+  } else {
+    dim3 grid((unsigned)((E + 255) / 256), (C + kGroupCCH - 1) / kGroupCCH, B);
+    group_points_kernel<1><<<grid, 256, 0, s>>>(C, N, E, points, idx, out);
+  }
+  count_launch(1);
+  return check_launch(what);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Scatter plan:  idx (B,E) -> row_ptr (B,N+1), perm (B,E)   [workspace = row_ptr | perm]
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+plan_count_kernel(int N, int64_t E, const int* __restrict__ idx, int* __restrict__ row_ptr) {
+  const int b = blockIdx.y;
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= E) return;
+  const int k = idx[(int64_t)b * E + e];
+  if ((unsigned)k < (unsigned)N) atomicAdd(row_ptr + (int64_t)b * (N + 1) + k + 1, 1);  // integer: order-free
+}
+
+// In-place inclusive scan of each (N+1)-row (counts were stored shifted by one => exclusive offsets).
+__global__ void __launch_bounds__(1024)
+plan_scan_kernel(int N, int* __restrict__ row_ptr) {
+  __shared__ int s_warp[32];
+  __shared__ int s_carry;
+  int* row = row_ptr + (int64_t)blockIdx.x * (N + 1);
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  if (t == 0) s_carry = 0;
+  __syncthreads();
+  for (int base = 0; base <= N; base += 1024) {
+    const int i = base + t;
+    int v = (i <= N) ? row[i] : 0;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int u = __shfl_up_sync(0xffffffffu, v, o);
+      if (lane >= o) v += u;
+    }
+    if (lane == 31) s_warp[warp] = v;
+    __syncthreads();
+    int w = s_warp[lane];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int u = __shfl_up_sync(0xffffffffu, w, o);
+      if (lane >= o) w += u;
+    }
+    const int warp_prefix = __shfl_sync(0xffffffffu, w, max(warp - 1, 0));
+    const int carry = s_carry;
+    v += carry + (warp ? warp_prefix : 0);
+    if (i <= N) row[i] = v;
+    __syncthreads();
+    if (t == 1023) s_carry = v;
+    __syncthreads();
+  }
+}
+
+// Stable fill.  Each warp owns a range of kPlanR target keys and walks ALL entries of its cloud in
+// order; running per-key counters live in shared memory and are touched by that warp only, so the
+// position of every source inside its target's segment is its arrival order: bit-reproducible.
+constexpr int kPlanR = 64;
+__global__ void __launch_bounds__(1024)
+plan_fill_kernel(int N, int64_t E, const int* __restrict__ idx, const int* __restrict__ row_ptr,
+                 int* __restrict__ perm) {
+  __shared__ int s_cnt[32][kPlanR];
+  const int b = blockIdx.y;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int lo = (blockIdx.x * 32 + warp) * kPlanR;
+  for (int i = lane; i < kPlanR; i += 32) s_cnt[warp][i] = 0;
+  __syncwarp();
+  if (lo >= N) return;
+  const int* __restrict__ src = idx + (int64_t)b * E;
+  const int* __restrict__ rp = row_ptr + (int64_t)b * (N + 1);
+  int* __restrict__ dst = perm + (int64_t)b * E;
+  for (int64_t e0 = 0; e0 < E; e0 += 32) {
+    const int64_t e = e0 + lane;
+    const int k = (e < E) ? __ldg(src + e) : -1;
+    const bool mine = (unsigned)(k - lo) < (unsigned)kPlanR && k < N;
+    if (!__any_sync(0xffffffffu, mine)) continue;
+    const unsigned grp = __match_any_sync(0xffffffffu, mine ? k : (int)(0x80000000u | lane));
+    int base = 0;
+    if (mine) base = s_cnt[warp][k - lo];
+    __syncwarp();
+    if (mine && lane == __ffs(grp) - 1) s_cnt[warp][k - lo] = base + __popc(grp);
+    __syncwarp();
+    if (mine) dst[rp[k] + base + __popc(grp & lanemask_lt())] = (int)e;
+  }
+}
+
+struct PlanView {
+  const int* row_ptr;
+  const int* perm;
+};
+static inline size_t plan_rowptr_bytes(int B, int N) {
+  size_t b = (size_t)B * (N + 1) * sizeof(int);
+  return (b + 255) & ~(size_t)255;
+}
+static inline PlanView plan_view(const void* plan, int B, int N) {
+  PlanView v;
+  v.row_ptr = reinterpret_cast<const int*>(plan);
+  v.perm = reinterpret_cast<const int*>(reinterpret_cast<const char*>(plan) + plan_rowptr_bytes(B, N));
+  return v;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Deterministic segmented reduction (channel-major):  dst[b,c,t] = sum_{p in seg(b,t)} g[b,c,perm[p]/DIV] (* w[b,perm[p]])
+// DIV = 1: group/gather grads.  DIV = 3, weighted: three_interpolate grad.
+// One thread per target, kSegCCH channels at a time, sources in plan (ascending) order.
+// ---------------------------------------------------------------------------------------------
+constexpr int kSegCCH = 8;
+template <int DIV, bool WEIGHTED>
+__global__ void __launch_bounds__(256)
+seg_reduce_cmajor_kernel(int C, int N, int64_t E, const float* __restrict__ g,
+                         const float* __restrict__ w, const int* __restrict__ row_ptr,
+                         const int* __restrict__ perm, float* __restrict__ dst) {
+  const int b = blockIdx.z;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= N) return;
+  const int c0 = blockIdx.y * kSegCCH;
+  const int nc = min(kSegCCH, C - c0);
+  const int64_t Eg = E / DIV;
+  const int* __restrict__ rp = row_ptr + (int64_t)b * (N + 1);
+  const int* __restrict__ pm = perm + (int64_t)b * E;
+  const float* __restrict__ gb = g + ((int64_t)b * C + c0) * Eg;
+  const int s = rp[t], e = rp[t + 1];
+  float acc[kSegCCH];
+#pragma unroll
+  for (int i = 0; i < kSegCCH; i++) acc[i] = 0.f;
+  for (int p = s; p < e; p++) {
+    const int src = __ldg(pm + p);
+    const int64_t pos = DIV == 1 ? src : src / DIV;
+    const float wt = WEIGHTED ? __ldg(w + (int64_t)b * E + src) : 1.f;
+#pragma unroll
+    for (int i = 0; i < kSegCCH; i++) {
+      if (i < nc) {
+        const float v = __ldg(gb + (int64_t)i * Eg + pos);
+        acc[i] = __fadd_rn(acc[i], WEIGHTED ? __fmul_rn(v, wt) : v);
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < kSegCCH; i++)
+    if (i < nc) dst[((int64_t)b * C + c0 + i) * N + t] = acc[i];
+}
+
+template <int DIV, bool WEIGHTED>
+static int launch_seg_reduce(int B, int C, int N, int64_t E, const float* g, const float* w,
+                             const void* plan, float* dst, cudaStream_t s, const char* what) {
+  if (B == 0 || C == 0 || N == 0) return GEOT_OK;
+  GEOT_REQUIRE(g && plan && dst, "%s: NULL pointer", what);
+  GEOT_REQUIRE(B <= 65535 && (C + kSegCCH - 1) / kSegCCH <= 65535, "%s: B or C exceeds grid limits", what);
+  const PlanView pv = plan_view(plan, B, N);
+  dim3 grid((N + 255) / 256, (C + kSegCCH - 1) / kSegCCH, B);
+  seg_reduce_cmajor_kernel<DIV, WEIGHTED><<<grid, 256, 0, s>>>(C, N, E, g, w, pv.row_ptr, pv.perm, dst);
+  count_launch(1);
+  return check_launch(what);
+}
+
+// used by interp.cu
+int three_interpolate_grad_impl(int B, int C, int n, int m, const float* grad_out, const float* weight,
+                                const void* plan, float* grad_points, cudaStream_t s) {
+  return launch_seg_reduce<3, true>(B, C, m, (int64_t)3 * n, grad_out, weight, plan, grad_points, s,
+                                    "three_interpolate_grad");
+}
+
+}  // namespace geot
+
+using namespace geot;
+
+GEOT_API int geot_group_points(int B, int C, int N, int M, int nsample, const float* points,
+                               const int* idx, float* out, geot_stream_t stream) {
+  GEOT_REQUIRE(B >= 0 && C >= 0 && N >= 0 && M >= 0 && nsample >= 0, "group_points: bad sizes");
+  return launch_group(B, C, N, (int64_t)M * nsample, points, idx, out, as_stream(stream), "group_points");
+}
+
+GEOT_API int geot_gather_points(int B, int C, int N, int M, const float* points, const int* idx,
+                                float* out, geot_stream_t stream) {
+  GEOT_REQUIRE(B >= 0 && C >= 0 && N >= 0 && M >= 0, "gather_points: bad sizes");
+  return launch_group(B, C, N, (int64_t)M, points, idx, out, as_stream(stream), "gather_points");
+}
+
+GEOT_API size_t geot_scatter_plan_bytes(int B, int N, int64_t E) {
+  if (B < 0 || N < 0 || E < 0) return 0;
+  return plan_rowptr_bytes(B, N) + (size_t)B * (size_t)E * sizeof(int);
+}
+
+GEOT_API int geot_scatter_plan_build(int B, int N, int64_t E, const int* idx, void* plan,
+                                     size_t plan_bytes, geot_stream_t stream) {
+  GEOT_REQUIRE(B >= 0 && N >= 0 && E >= 0, "scatter_plan_build: bad sizes");
+  if (B == 0) return GEOT_OK;
+  GEOT_REQUIRE(plan != nullptr && (E == 0 || idx != nullptr), "scatter_plan_build: NULL pointer");
+  GEOT_REQUIRE(B <= 65535, "scatter_plan_build: B exceeds grid limits");
+  if (plan_bytes < geot_scatter_plan_bytes(B, N, E)) {
+    set_error("scatter_plan_build: workspace %zu < %zu bytes", plan_bytes, geot_scatter_plan_bytes(B, N, E));
+    return GEOT_ERR_WORKSPACE;
+  }
+  cudaStream_t s = as_stream(stream);
+  int* row_ptr = reinterpret_cast<int*>(plan);
+  int* perm = reinterpret_cast<int*>(reinterpret_cast<char*>(plan) + plan_rowptr_bytes(B, N));
+  cudaError_t err = cudaMemsetAsync(row_ptr, 0, (size_t)B * (N + 1) * sizeof(int), s);
+  if (err != cudaSuccess) { set_error("scatter_plan_build: memset: %s", cudaGetErrorString(err)); return GEOT_ERR_CUDA; }
+  if (E > 0) {
+    dim3 gc((unsigned)((E + 255) / 256), B);
+    plan_count_kernel<<<gc, 256, 0, s>>>(N, E, idx, row_ptr);
+    count_launch(1);
+    int rc = check_launch("plan_count_kernel");
+    if (rc) return rc;
+  }
+  plan_scan_kernel<<<B, 1024, 0, s>>>(N, row_ptr);
+  count_launch(1);
+  int rc = check_launch("plan_scan_kernel");
+  if (rc) return rc;
+  if (E > 0 && N > 0) {
+    dim3 gf((N + 32 * kPlanR - 1) / (32 * kPlanR), B);
+    plan_fill_kernel<<<gf, 1024, 0, s>>>(N, E, idx, row_ptr, perm);
+    count_launch(1);
+    rc = check_launch("plan_fill_kernel");
+  }
+  return rc;
+}
+
+GEOT_API int geot_group_points_grad(int B, int C, int N, int M, int nsample, const float* grad_out,
+                                    const void* plan, float* grad_points, geot_stream_t stream) {
+  GEOT_REQUIRE(B >= 0 && C >= 0 && N >= 0 && M >= 0 && nsample >= 0, "group_points_grad: bad sizes");
+  return launch_seg_reduce<1, false>(B, C, N, (int64_t)M * nsample, grad_out, nullptr, plan, grad_points,
+                                     as_stream(stream), "group_points_grad");
+}
+
+GEOT_API int geot_gather_points_grad(int B, int C, int N, int M, const float* grad_out, const void* plan,
+                                     float* grad_points, geot_stream_t stream) {
+  GEOT_REQUIRE(B >= 0 && C >= 0 && N >= 0 && M >= 0, "gather_points_grad: bad sizes");
+  return launch_seg_reduce<1, false>(B, C, N, (int64_t)M, grad_out, nullptr, plan, grad_points,
+                                     as_stream(stream), "gather_points_grad");
+}

@@ -1,0 +1,318 @@
+"""Tensor-level entry points: allocate outputs with torch, enqueue the sm_100a kernels through the C ABI.
+
+One function per C-ABI entry point of include/geot_b200.h.  These are what the API mirrors
+(layers.py, pointops.py, pointnet2_utils.py) and the pybind-shaped facades (backends.py) call.
+No CPU path, no PyTorch re-implementation: a missing library or a CPU tensor raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import call, check_cuda, ptr, stream_ptr
+
+_i32 = torch.int32
+_f32 = torch.float32
+
+
+def _as_f32(t):
+    return t if t.dtype == _f32 else t.float()
+
+
+def _as_i32(t):
+    return t if t.dtype == _i32 else t.int()
+
+
+# --------------------------------------------------------------------------------------------------
+# sampling
+# --------------------------------------------------------------------------------------------------
+def furthest_point_sampling(xyz, npoint, flags=0, temp=None, out=None):
+    """xyz (B,N,3) fp32 -> idx (B,npoint) int32.  flags: _lib.GEOT_FPS_* (which reference kernel to match)."""
+    dev = check_cuda(xyz, temp, out)
+    B, N, _ = xyz.shape
+    with torch.cuda.device(dev):
+        if out is None:
+            out = torch.empty((B, npoint), dtype=_i32, device=dev)
+        needs_temp = N > 16384 or (flags & _lib.GEOT_FPS_FORCE_GENERIC)
+        if temp is None and needs_temp:
+            temp = torch.full((B, N), 1e10, dtype=_f32, device=dev)
+        call("geot_furthest_point_sampling", B, N, npoint, ptr(xyz), ptr(temp), ptr(out), flags, stream_ptr())
+    return out
+
+
+def furthestsampling(xyz, offset, new_offset, weights=None, n_max=None, m_total=None, tmp=None, out=None, flags=0):
+    """Offset-format FPS: xyz (n,3), cumulative int32 offset/new_offset (b) -> GLOBAL idx (m_total)."""
+    dev = check_cuda(xyz, offset, new_offset, weights, tmp, out)
+    n, b = xyz.shape[0], offset.shape[0]
+    with torch.cuda.device(dev):
+        if n_max is None or m_total is None:
+            # one host sync, like the reference's own Python (pointops.py:69-72 reads offset on the host)
+            o = offset.cpu()
+            seg = torch.diff(o, prepend=o.new_zeros(1))
+            n_max = int(seg.max()) if n_max is None else n_max
+            m_total = int(new_offset[-1]) if m_total is None else m_total
+        if out is None:
+            out = torch.empty((m_total,), dtype=_i32, device=dev)
+        if tmp is None and (weights is not None or n_max > 16384 or (flags & _lib.GEOT_FPS_FORCE_GENERIC)):
+            tmp = torch.full((n,), 1e10, dtype=_f32, device=dev)
+        call("geot_furthestsampling", b, n_max, ptr(xyz), ptr(offset), ptr(new_offset), ptr(weights), ptr(tmp), ptr(out), flags, stream_ptr())
+    return out
+
+
+# --------------------------------------------------------------------------------------------------
+# neighbour search
+# --------------------------------------------------------------------------------------------------
+def ball_query(new_xyz, xyz, radius, nsample, out=None):
+    """new_xyz (B,M,3), xyz (B,N,3) -> idx (B,M,nsample) int32."""
+    dev = check_cuda(new_xyz, xyz, out)
+    B, N, _ = xyz.shape
+    M = new_xyz.shape[1]
+    with torch.cuda.device(dev):
+        if out is None:
+            out = torch.empty((B, M, nsample), dtype=_i32, device=dev)
+        call("geot_ball_query", B, N, M, float(radius), nsample, ptr(new_xyz), ptr(xyz), ptr(out), stream_ptr())
+    return out
+
+
+def ballquery_offset(radius, nsample, xyz, new_xyz, offset, new_offset, out=None):
+    dev = check_cuda(xyz, new_xyz, offset, new_offset, out)
+    m, b = new_xyz.shape[0], offset.shape[0]
+    with torch.cuda.device(dev):
+        if out is None:
+            out = torch.empty((m, nsample), dtype=_i32, device=dev)
+        call("geot_ballquery_offset", b, m, float(radius), nsample, ptr(xyz), ptr(new_xyz), ptr(offset), ptr(new_offset), ptr(out), stream_ptr())
+    return out
+
+
+def knnquery(nsample, xyz, new_xyz, offset=None, new_offset=None, n_per=0, m_per=None, idx=None, dist2=None):
+    """k nearest in the same segment: GLOBAL int32 idx (m,k), SQUARED dist2 (m,k), ascending.
+
+    offset/new_offset given: offset format (ragged).  Otherwise batched: xyz is (b*n_per,3) and
+    new_xyz (b*m_per,3)."""
+    dev = check_cuda(xyz, new_xyz, offset, new_offset, idx, dist2)
+    m = new_xyz.shape[0]
+    with torch.cuda.device(dev):
+        if offset is not None:
+            b = offset.shape[0]
+            if m_per is None:
+                m_per = m if b == 1 else int(torch.diff(new_offset, prepend=new_offset.new_zeros(1)).max())
+        else:
+            b = m // m_per
+        if idx is None:
+            idx = torch.empty((m, nsample), dtype=_i32, device=dev)
+        if dist2 is None:
+            dist2 = torch.empty((m, nsample), dtype=_f32, device=dev)
+        ws_bytes = int(_lib.lib().geot_knnquery_workspace_bytes(m))
+        ws = torch.empty((max(ws_bytes, 1),), dtype=torch.uint8, device=dev)
+        call("geot_knnquery", b, m, nsample, ptr(xyz), ptr(new_xyz), ptr(offset), ptr(new_offset), n_per, max(m_per, 1), ptr(idx), ptr(dist2), ptr(ws), ws_bytes, stream_ptr())
+    return idx, dist2
+
+
+# --------------------------------------------------------------------------------------------------
+# grouping / gather
+# --------------------------------------------------------------------------------------------------
+def group_points(points, idx, out=None):
+    """points (B,C,N), idx (B,M,ns) -> (B,C,M,ns)."""
+    dev = check_cuda(points, idx, out)
+    B, Cc, N = points.shape
+    _, M, ns = idx.shape
+    with torch.cuda.device(dev):
+        if out is None:
+            out = torch.empty((B, Cc, M, ns), dtype=_f32, device=dev)
+        call("geot_group_points", B, Cc, N, M, ns, ptr(points), ptr(idx), ptr(out), stream_ptr())
+    return out
+
+
+def gather_points(points, idx, out=None):
+    """points (B,C,N), idx (B,M) -> (B,C,M)."""
+    dev = check_cuda(points, idx, out)
+    B, Cc, N = points.shape
+    M = idx.shape[1]
+    with torch.cuda.device(dev):
+        if out is None:
+            out = torch.empty((B, Cc, M), dtype=_f32, device=dev)
+        call("geot_gather_points", B, Cc, N, M, ptr(points), ptr(idx), ptr(out), stream_ptr())
+    return out
+
+
+class ScatterPlan:
+    """Deterministic scatter-add plan (CSR of source positions by target) for one idx tensor.
+
+    Built lazily on the first backward that needs it and cached on the idx tensor's autograd context,
+    so e.g. the xyz- and feature-grouping of one QueryAndGroup share it."""
+
+    def __init__(self, idx, B, N):
+        dev = check_cuda(idx)
+        self.B, self.N = B, N
+        self.E = idx.numel() // max(B, 1)
+        with torch.cuda.device(dev):
+            nbytes = int(_lib.lib().geot_scatter_plan_bytes(B, N, self.E))
+            self.ws = torch.empty((max(nbytes, 1),), dtype=torch.uint8, device=dev)
+            call("geot_scatter_plan_build", B, N, self.E, ptr(idx), ptr(self.ws), nbytes, stream_ptr())
+
+    @property
+    def ptr(self):
+        return ptr(self.ws)
+
+    def row_ptr(self):
+        return self.ws[: self.B * (self.N + 1) * 4].view(_i32).view(self.B, self.N + 1)
+
+    def perm(self):
+        off = (self.B * (self.N + 1) * 4 + 255) // 256 * 256
+        return self.ws[off: off + self.B * self.E * 4].view(_i32).view(self.B, self.E)
+
+
+def group_points_grad(grad_out, plan, N, out=None):
+    """grad_out (B,C,M,ns) -> grad_points (B,C,N), fixed summation order."""
+    dev = check_cuda(grad_out, out)
+    B, Cc, M, ns = grad_out.shape
+    with torch.cuda.device(dev):
+        if out is None:
+            out = torch.empty((B, Cc, N), dtype=_f32, device=dev)
+        call("geot_group_points_grad", B, Cc, N, M, ns, ptr(grad_out), plan.ptr, ptr(out), stream_ptr())
+    return out
+
+
+def gather_points_grad(grad_out, plan, N, out=None):
+    dev = check_cuda(grad_out, out)
+    B, Cc, M = grad_out.shape
+    with torch.cuda.device(dev):
+        if out is None:
+            out = torch.empty((B, Cc, N), dtype=_f32, device=dev)
+        call("geot_gather_points_grad", B, Cc, N, M, ptr(grad_out), plan.ptr, ptr(out), stream_ptr())
+    return out
+
+
+# --------------------------------------------------------------------------------------------------
+# three_nn / three_interpolate
+# --------------------------------------------------------------------------------------------------
+def three_nn(unknown, known, dist2=None, idx=None):
+    """unknown (B,n,3), known (B,m,3) -> SQUARED dist2 (B,n,3), idx (B,n,3) int32."""
+    dev = check_cuda(unknown, known, dist2, idx)
+    B, n, _ = unknown.shape
+    m = known.shape[1]
+    with torch.cuda.device(dev):
+        if dist2 is None:
+            dist2 = torch.empty((B, n, 3), dtype=_f32, device=dev)
+        if idx is None:
+            idx = torch.empty((B, n, 3), dtype=_i32, device=dev)
+        call("geot_three_nn", B, n, m, ptr(unknown), ptr(known), ptr(dist2), ptr(idx), stream_ptr())
+    return dist2, idx
+
+
+def three_interpolate(points, idx, weight, out=None):
+    """points (B,C,m), idx/weight (B,n,3) -> (B,C,n)."""
+    dev = check_cuda(points, idx, weight, out)
+    B, Cc, m = points.shape
+    n = idx.shape[1]
+    with torch.cuda.device(dev):
+        if out is None:
+            out = torch.empty((B, Cc, n), dtype=_f32, device=dev)
+        call("geot_three_interpolate", B, Cc, m, n, ptr(points), ptr(idx), ptr(weight), ptr(out), stream_ptr())
+    return out
+
+
+def three_interpolate_grad(grad_out, weight, plan, m, out=None):
+    dev = check_cuda(grad_out, weight, out)
+    B, Cc, n = grad_out.shape
+    with torch.cuda.device(dev):
+        if out is None:
+            out = torch.empty((B, Cc, m), dtype=_f32, device=dev)
+        call("geot_three_interpolate_grad", B, Cc, n, m, ptr(grad_out), ptr(weight), plan.ptr, ptr(out), stream_ptr())
+    return out
+
+
+# --------------------------------------------------------------------------------------------------
+# offset-format (channel-last) ops
+# --------------------------------------------------------------------------------------------------
+def grouping_forward(input, idx, out=None):
+    dev = check_cuda(input, idx, out)
+    m, ns = idx.shape
+    c = input.shape[1]
+    with torch.cuda.device(dev):
+        if out is None:
+            out = torch.empty((m, ns, c), dtype=_f32, device=dev)
+        call("geot_grouping_forward", m, ns, c, ptr(input), ptr(idx), ptr(out), stream_ptr())
+    return out
+
+
+def grouping_backward(grad_output, plan, n, out=None):
+    dev = check_cuda(grad_output, out)
+    m, ns, c = grad_output.shape
+    with torch.cuda.device(dev):
+        if out is None:
+            out = torch.empty((n, c), dtype=_f32, device=dev)
+        call("geot_grouping_backward", m, ns, c, n, ptr(grad_output), plan.ptr, ptr(out), stream_ptr())
+    return out
+
+
+def interpolation_forward(input, idx, weight, out=None):
+    dev = check_cuda(input, idx, weight, out)
+    n, k = idx.shape
+    c = input.shape[1]
+    with torch.cuda.device(dev):
+        if out is None:
+            out = torch.empty((n, c), dtype=_f32, device=dev)
+        call("geot_interpolation_forward", n, c, k, ptr(input), ptr(idx), ptr(weight), ptr(out), stream_ptr())
+    return out
+
+
+def interpolation_backward(grad_output, weight, plan, m, k, out=None):
+    dev = check_cuda(grad_output, weight, out)
+    n, c = grad_output.shape
+    with torch.cuda.device(dev):
+        if out is None:
+            out = torch.empty((m, c), dtype=_f32, device=dev)
+        call("geot_interpolation_backward", n, c, k, m, ptr(grad_output), ptr(weight), plan.ptr, ptr(out), stream_ptr())
+    return out
+
+
+def subtraction_forward(input1, input2, idx, out=None):
+    dev = check_cuda(input1, input2, idx, out)
+    n, ns = idx.shape
+    c = input1.shape[1]
+    with torch.cuda.device(dev):
+        if out is None:
+            out = torch.empty((n, ns, c), dtype=_f32, device=dev)
+        call("geot_subtraction_forward", n, ns, c, ptr(input1), ptr(input2), ptr(idx), ptr(out), stream_ptr())
+    return out
+
+
+def subtraction_backward(grad_output, plan, g1=None, g2=None):
+    dev = check_cuda(grad_output, g1, g2)
+    n, ns, c = grad_output.shape
+    with torch.cuda.device(dev):
+        if g1 is None:
+            g1 = torch.empty((n, c), dtype=_f32, device=dev)
+        if g2 is None:
+            g2 = torch.empty((n, c), dtype=_f32, device=dev)
+        call("geot_subtraction_backward", n, ns, c, ptr(grad_output), plan.ptr, ptr(g1), ptr(g2), stream_ptr())
+    return g1, g2
+
+
+def aggregation_forward(input, position, weight, idx, out=None):
+    dev = check_cuda(input, position, weight, idx, out)
+    n, ns, c = position.shape
+    w_c = weight.shape[2]
+    with torch.cuda.device(dev):
+        if out is None:
+            out = torch.empty((n, c), dtype=_f32, device=dev)
+        call("geot_aggregation_forward", n, ns, c, w_c, ptr(input), ptr(position), ptr(weight), ptr(idx), ptr(out), stream_ptr())
+    return out
+
+
+def aggregation_backward(input, position, weight, idx, grad_output, plan, gi=None, gp=None, gw=None):
+    dev = check_cuda(input, position, weight, idx, grad_output, gi, gp, gw)
+    n, ns, c = position.shape
+    w_c = weight.shape[2]
+    with torch.cuda.device(dev):
+        if gi is None:
+            gi = torch.empty((n, c), dtype=_f32, device=dev)
+        if gp is None:
+            gp = torch.empty((n, ns, c), dtype=_f32, device=dev)
+        if gw is None:
+            gw = torch.empty((n, ns, w_c), dtype=_f32, device=dev)
+        call("geot_aggregation_backward", n, ns, c, w_c, ptr(input), ptr(position), ptr(weight), ptr(idx), ptr(grad_output), plan.ptr, ptr(gi), ptr(gp), ptr(gw), stream_ptr())
+    return gi, gp, gw

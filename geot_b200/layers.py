@@ -1,0 +1,325 @@
+"""Mirror of the reference's batched op API (openpoints/models/layers/{subsample,group,upsampling,knn}.py).
+
+Same names, argument order, dtypes, shapes and autograd contracts as the reference so that code
+written against `openpoints.models.layers` runs unchanged on top of the sm_100a kernels:
+  furthest_point_sample  subsample.py:76-105      gather_operation   subsample.py:108-144 / group.py:140-174
+  ball_query             group.py:177-203         grouping_operation group.py:76-117
+  three_nn               upsampling.py:11-40      three_interpolate  upsampling.py:43-89
+  three_interpolation    upsampling.py:92-102     knn_point / KNN    knn.py:7-61, group.py:12-28
+  QueryAndGroup / KNNGroup / GroupAll / create_grouper   group.py:206-352
+Differences, all deliberate: outputs are allocated on the inputs' device (the reference uses the
+current device, subsample.py:93-94); backward passes are deterministic; CPU tensors raise.
+"""
+from __future__ import annotations
+
+import copy
+from typing import Tuple
+
+import torch
+import torch.nn as nn
+from torch.autograd import Function
+
+from . import functional as F_
+
+
+class FurthestPointSampling(Function):
+    @staticmethod
+    def forward(ctx, xyz: torch.Tensor, npoint: int) -> torch.Tensor:
+        """xyz (B,N,3) -> idx (B,npoint) int32; same indices as furthest_point_sampling_wrapper."""
+        assert xyz.is_contiguous()
+        out = F_.furthest_point_sampling(xyz, npoint, flags=0)
+        ctx.mark_non_differentiable(out)
+        return out
+
+    @staticmethod
+    def backward(ctx, a=None):
+        return None, None
+
+
+furthest_point_sample = FurthestPointSampling.apply
+
+
+class GatherOperation(Function):
+    @staticmethod
+    def forward(ctx, features: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+        """features (B,C,N), idx (B,npoint) int32 -> (B,C,npoint)."""
+        assert features.is_contiguous()
+        assert idx.is_contiguous()
+        _, C, N = features.size()
+        ctx.for_backwards = (idx, C, N)
+        return F_.gather_points(features, idx)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        idx, C, N = ctx.for_backwards
+        plan = F_.ScatterPlan(idx, idx.shape[0], N)
+        return F_.gather_points_grad(grad_out.contiguous(), plan, N), None
+
+
+gather_operation = GatherOperation.apply
+
+
+def fps(data, number):
+    """subsample.py:148-156: data (B,N,C) -> sampled rows (B,number,C)."""
+    fps_idx = furthest_point_sample(data[:, :, :3].contiguous(), number)
+    return torch.gather(data, 1, fps_idx.unsqueeze(-1).long().expand(-1, -1, data.shape[-1]))
+
+
+class _PlanCache:
+    """One scatter plan per idx tensor, shared by every grouping_operation that used it."""
+
+    def __init__(self):
+        self.plan = None
+
+
+class GroupingOperation(Function):
+    @staticmethod
+    @torch.amp.custom_fwd(device_type="cuda", cast_inputs=torch.float32)
+    def forward(ctx, features: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+        """features (B,C,N), idx (B,npoint,nsample) int32 -> (B,C,npoint,nsample)."""
+        assert features.is_contiguous()
+        assert idx.is_contiguous()
+        N = features.size(2)
+        cache = getattr(idx, "_geot_plan_cache", None)
+        if cache is None:
+            cache = _PlanCache()
+            try:
+                idx._geot_plan_cache = cache
+            except Exception:  # tensor subclasses that refuse attributes: no sharing, still correct
+                pass
+        ctx.for_backwards = (idx, N, cache)
+        return F_.group_points(features, idx)
+
+    @staticmethod
+    def backward(ctx, grad_out: torch.Tensor):
+        idx, N, cache = ctx.for_backwards
+        if cache.plan is None or cache.plan.N != N:
+            cache.plan = F_.ScatterPlan(idx, idx.shape[0], N)
+        return F_.group_points_grad(grad_out.contiguous(), cache.plan, N), None
+
+
+grouping_operation = GroupingOperation.apply
+
+
+def torch_grouping_operation(features, idx):
+    """group.py:120-137 (pure torch, kept because utils/insT_loss.py imports the name)."""
+    all_idx = idx.reshape(idx.shape[0], -1)
+    all_idx = all_idx.unsqueeze(1).repeat(1, features.shape[1], 1)
+    grouped_features = features.gather(2, all_idx)
+    return grouped_features.reshape(idx.shape[0], features.shape[1], idx.shape[1], idx.shape[2])
+
+
+class BallQuery(Function):
+    @staticmethod
+    def forward(ctx, radius: float, nsample: int, xyz: torch.Tensor, new_xyz: torch.Tensor) -> torch.Tensor:
+        """xyz (B,N,3) points, new_xyz (B,npoint,3) ball centres -> idx (B,npoint,nsample) int32."""
+        assert new_xyz.is_contiguous()
+        assert xyz.is_contiguous()
+        idx = F_.ball_query(new_xyz, xyz, radius, nsample)
+        ctx.mark_non_differentiable(idx)
+        return idx
+
+    @staticmethod
+    def backward(ctx, a=None):
+        return None, None, None, None
+
+
+ball_query = BallQuery.apply
+
+
+class ThreeNN(Function):
+    @staticmethod
+    def forward(ctx, unknown: torch.Tensor, known: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+        """unknown (B,n,3), known (B,m,3) -> (dist (B,n,3) = sqrt(d2), idx (B,n,3) int32)."""
+        assert unknown.is_contiguous()
+        assert known.is_contiguous()
+        dist2, idx = F_.three_nn(unknown, known)
+        dist = torch.sqrt(dist2)
+        ctx.mark_non_differentiable(dist, idx)
+        return dist, idx
+
+    @staticmethod
+    def backward(ctx, a=None, b=None):
+        return None, None
+
+
+three_nn = ThreeNN.apply
+
+
+class ThreeInterpolate(Function):
+    @staticmethod
+    @torch.amp.custom_fwd(device_type="cuda", cast_inputs=torch.float32)
+    def forward(ctx, features: torch.Tensor, idx: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
+        """features (B,C,m), idx/weight (B,n,3) -> (B,C,n)."""
+        assert features.is_contiguous()
+        assert idx.is_contiguous()
+        assert weight.is_contiguous()
+        m = features.size(2)
+        ctx.three_interpolate_for_backward = (idx, weight, m)
+        return F_.three_interpolate(features, idx, weight)
+
+    @staticmethod
+    def backward(ctx, grad_out: torch.Tensor):
+        idx, weight, m = ctx.three_interpolate_for_backward
+        plan = F_.ScatterPlan(idx, idx.shape[0], m)
+        return F_.three_interpolate_grad(grad_out.contiguous(), weight, plan, m), None, None
+
+
+three_interpolate = ThreeInterpolate.apply
+
+
+def three_interpolation(unknown_xyz, known_xyz, know_feat):
+    """upsampling.py:92-102: three_nn -> inverse-distance weights -> three_interpolate."""
+    dist, idx = three_nn(unknown_xyz, known_xyz)
+    dist_recip = 1.0 / (dist + 1e-8)
+    norm = torch.sum(dist_recip, dim=2, keepdim=True)
+    weight = dist_recip / norm
+    return three_interpolate(know_feat, idx, weight)
+
+
+# --------------------------------------------------------------------------------------------------
+# kNN (knn.py:7-61, group.py:12-28).  The reference builds a dense (B,M,N) torch.cdist matrix and
+# runs topk over it (2 GB at B=2, N=16000).  For 3-D points the sm_100a kNN kernel gives the same
+# neighbours without the matrix; distances are sqrt(d2) of the kernel's fp32 d2 (cdist's matmul
+# expansion differs in the last bits, and topk's tie order is unspecified — SURVEY.md §7.3-8 — so the
+# contract is "same neighbour sets / loss values", not bit-equal indices).  Other feature widths keep
+# the reference's own torch expression (it is pure torch in the reference too).
+# --------------------------------------------------------------------------------------------------
+def _knn3d(k, query, support):
+    B, M, _ = query.shape
+    N = support.shape[1]
+    q = query.contiguous().float().view(-1, 3)
+    s = support.contiguous().float().view(-1, 3)
+    idx, d2 = F_.knnquery(k, s, q, None, None, n_per=N, m_per=M)
+    base = (torch.arange(B, device=idx.device, dtype=torch.int32) * N).view(B, 1, 1)
+    return torch.sqrt(d2).view(B, M, k), (idx.view(B, M, k) - base)
+
+
+@torch.no_grad()
+def knn_point(k, query, support=None):
+    """knn.py:7-20 -> (dist (B,M,k), idx (B,M,k) int64), ascending."""
+    if support is None:
+        support = query
+    if query.shape[-1] == 3 and query.is_cuda and k <= 127:
+        dist, idx = _knn3d(k, query, support)
+        return dist, idx.long()
+    dist = torch.cdist(query, support)
+    k_dist = dist.topk(k=k, dim=-1, largest=False, sorted=True)
+    return k_dist.values, k_dist.indices
+
+
+class KNN(nn.Module):
+    """knn.py:23-61 (query, support) -> (dist, idx int32 (B,M,k)).  `farthest=True` keeps the torch path."""
+
+    def __init__(self, neighbors, farthest=False, sorted=True, **kwargs):
+        super().__init__()
+        self.neighbors = neighbors
+        self.farthest = farthest
+        self.sorted = sorted
+
+    @torch.no_grad()
+    def forward(self, query, support=None):
+        if support is None:
+            support = query
+        if not self.farthest and query.shape[-1] == 3 and query.is_cuda and self.neighbors <= 127:
+            return _knn3d(self.neighbors, query, support)
+        dist = torch.cdist(query, support)
+        k_dist = dist.topk(k=self.neighbors, dim=-1, largest=self.farthest, sorted=self.sorted)
+        return k_dist.values, k_dist.indices.int()
+
+
+class GroupKNN(nn.Module):
+    """group.py:12-28 `KNN(neighbors)(support, query)` -> (dist (B,k,M)-shaped values, idx (B,M,k) int32)."""
+
+    def __init__(self, neighbors, transpose_mode=True):
+        super().__init__()
+        self.neighbors = neighbors
+
+    @torch.no_grad()
+    def forward(self, support, query):
+        if query.shape[-1] == 3 and query.is_cuda and self.neighbors <= 127:
+            dist, idx = _knn3d(self.neighbors, query, support)
+            return dist.transpose(1, 2).contiguous(), idx.contiguous()
+        dist = torch.cdist(support, query)
+        k_dist = dist.topk(k=self.neighbors, dim=1, largest=False)
+        return k_dist.values, k_dist.indices.transpose(1, 2).contiguous().int()
+
+
+class QueryAndGroup(nn.Module):
+    """group.py:206-255: ball_query -> group xyz -> subtract centre (-> /radius) -> group features."""
+
+    def __init__(self, radius: float, nsample: int, relative_xyz=True, normalize_dp=False,
+                 normalize_by_std=False, normalize_by_allstd=False, normalize_by_allstd2=False,
+                 return_only_idx=False, **kwargs):
+        super().__init__()
+        self.radius, self.nsample = radius, nsample
+        self.normalize_dp = normalize_dp
+        self.normalize_by_std = normalize_by_std
+        self.normalize_by_allstd = normalize_by_allstd
+        self.normalize_by_allstd2 = normalize_by_allstd2
+        assert self.normalize_dp + self.normalize_by_std + self.normalize_by_allstd < 2
+        self.relative_xyz = relative_xyz
+        self.return_only_idx = return_only_idx
+
+    def forward(self, query_xyz, support_xyz, features=None):
+        idx = ball_query(self.radius, self.nsample, support_xyz, query_xyz)
+        if self.return_only_idx:
+            return idx
+        xyz_trans = support_xyz.transpose(1, 2).contiguous()
+        grouped_xyz = grouping_operation(xyz_trans, idx)  # (B,3,npoint,nsample)
+        if self.relative_xyz:
+            grouped_xyz = grouped_xyz - query_xyz.transpose(1, 2).unsqueeze(-1)
+            if self.normalize_dp:
+                grouped_xyz /= self.radius
+        grouped_features = grouping_operation(features, idx) if features is not None else None
+        return grouped_xyz, grouped_features
+
+
+class GroupAll(nn.Module):
+    """group.py:258-272."""
+
+    def forward(self, new_xyz, xyz, features=None):
+        grouped_xyz = xyz.transpose(1, 2).unsqueeze(2)
+        grouped_features = features.unsqueeze(2) if features is not None else None
+        return grouped_xyz, grouped_features
+
+
+class KNNGroup(nn.Module):
+    """group.py:275-320."""
+
+    def __init__(self, nsample: int, relative_xyz=True, normalize_dp=False, return_only_idx=False, **kwargs):
+        super().__init__()
+        self.nsample = nsample
+        self.knn = GroupKNN(nsample, transpose_mode=True)
+        self.relative_xyz = relative_xyz
+        self.normalize_dp = normalize_dp
+        self.return_only_idx = return_only_idx
+
+    def forward(self, query_xyz, support_xyz, features=None):
+        _, idx = self.knn(support_xyz, query_xyz)
+        if self.return_only_idx:
+            return idx
+        idx = idx.int()
+        xyz_trans = support_xyz.transpose(1, 2).contiguous()
+        grouped_xyz = grouping_operation(xyz_trans, idx)
+        if self.relative_xyz:
+            grouped_xyz -= query_xyz.transpose(1, 2).unsqueeze(-1)
+        if self.normalize_dp:
+            grouped_xyz /= torch.amax(torch.sqrt(torch.sum(grouped_xyz ** 2, dim=1)), dim=(1, 2)).view(-1, 1, 1, 1)
+        if features is not None:
+            return grouped_xyz, grouping_operation(features, idx)
+        return grouped_xyz, None
+
+
+def create_grouper(group_args):
+    """group.py:338-352."""
+    group_args_copy = copy.deepcopy(group_args)
+    method = group_args_copy.pop('NAME', 'ballquery')
+    radius = group_args_copy.pop('radius', 0.1)
+    nsample = group_args_copy.pop('nsample', 20)
+    if nsample is not None:
+        if method == 'ballquery':
+            return QueryAndGroup(radius, nsample, **group_args_copy)
+        elif method == 'knn':
+            return KNNGroup(nsample, **group_args_copy)
+    return GroupAll()

@@ -1,0 +1,189 @@
+/*
+ * include/geot_b200.h — C ABI of libgeot_b200.so: B200 (sm_100a) kernels for GeoT's point-cloud
+ * sampling / grouping / interpolation hot path and its per-point transition-matrix path.
+ *
+ * This is the drop-in boundary.  The reference binds these ops through three pybind11 modules
+ * (paths relative to the reference root):
+ *   pointnet2_batch_cuda   openpoints/cpp/pointnet2_batch/src/pointnet2_api.cpp:10-24
+ *   pointops_cuda          pointops/src/pointops_api.cpp:8-12, openpoints/cpp/pointops/src/pointops_api.cpp:13-25
+ *   pointnet2._ext         pointnet2/_ext_src/src/bindings.cpp:9-21
+ * Each entry point below names the reference callable it replaces.  INTEGRATION.md shows the
+ * reference-side stub (ctypes / pybind) a maintainer would add.
+ *
+ * Conventions (all entry points):
+ *   - every pointer is a DEVICE pointer on the current CUDA device; the caller owns all memory
+ *     (outputs and workspaces) — nothing is allocated, freed or synchronised inside;
+ *   - work is enqueued on `stream` (a cudaStream_t passed as void*; NULL = legacy default stream);
+ *   - returns GEOT_OK (0) or a negative GEOT_ERR_* code; geot_last_error() gives the message for
+ *     the calling thread.  Nothing calls exit() (the reference does: sampling_gpu.cu:255-259);
+ *   - tensors are contiguous fp32 / int32 in the reference's layouts; 64-bit flat indexing inside
+ *     (the reference's int32 products overflow past 2^31 elements, group_points_gpu.cu:68-69);
+ *   - index results are bit-exact with the reference kernels; value results match to 1e-5 relative;
+ *     backward passes are deterministic (fixed summation order) where the reference uses float atomics.
+ */
+#ifndef GEOT_B200_H
+#define GEOT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* geot_stream_t; /* cudaStream_t */
+
+#define GEOT_OK 0
+#define GEOT_ERR_INVALID (-1)     /* bad argument (NULL pointer, negative size, unsupported k ...) */
+#define GEOT_ERR_CUDA (-2)        /* a CUDA launch / runtime call failed */
+#define GEOT_ERR_WORKSPACE (-3)   /* workspace missing or too small */
+
+/* Library introspection. */
+int geot_abi_version(void);
+const char* geot_last_error(void);
+/* Number of kernels this library has launched from the calling process (bench.py's gpu_launches). */
+uint64_t geot_launch_count(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * Furthest point sampling.
+ * flags select which of the reference's three kernels is reproduced bit-for-bit:
+ *   0                         pointnet2_batch  furthest_point_sampling_wrapper   (sampling.cpp:39-48,
+ *                             sampling_gpu.cu:101-216): first index 0, tie order of a 1024-thread tree
+ *   GEOT_FPS_CAP512|MAGSKIP   pointnet2._ext furthest_point_sampling (pointnet2/_ext_src/src/
+ *                             sampling_gpu.cu:73-176): 512-thread tree, points with |p|^2 <= 1e-3 skipped
+ * `temp` mirrors the reference's caller-made (B,N) scratch pre-filled with 1e10.  The fast path keeps
+ * the running min-distances on chip and never touches it (may be NULL); the large-N fallback uses it
+ * as scratch and then requires it, pre-filled with 1e10 exactly like the reference.
+ * --------------------------------------------------------------------------------------------- */
+#define GEOT_FPS_CAP512 1
+#define GEOT_FPS_MAGSKIP 2
+#define GEOT_FPS_FORCE_GENERIC 4 /* testing: take the large-N fallback regardless of N */
+
+/* replaces pointnet2_batch_cuda.furthest_point_sampling_wrapper(B,N,M,xyz,temp,idx) and
+ * pointnet2._ext.furthest_point_sampling(points, nsamples).  xyz (B,N,3) -> idx (B,M) int32. */
+int geot_furthest_point_sampling(int B, int N, int M, const float* xyz, float* temp, int* idx,
+                                 int flags, geot_stream_t stream);
+
+/* replaces pointops_cuda.furthestsampling_cuda(b,n_max,xyz,offset,new_offset,tmp,idx) and, with
+ * weights != NULL, furthestsampling_weights_cuda (pointops/src/sampling/sampling_cuda_kernel.cu:15-129,
+ * :175-307).  xyz (n,3); offset/new_offset cumulative int32 (b) on the DEVICE; idx (new_offset[b-1])
+ * receives GLOBAL indices.  n_max (largest segment) picks the tie rule exactly like the reference;
+ * m_max = largest number of samples of any segment (host-known, sizes nothing but validation).
+ * tmp (n) pre-filled 1e10: used only by the fallback / weighted path, may be NULL otherwise. */
+int geot_furthestsampling(int b, int n_max, const float* xyz, const int* offset,
+                          const int* new_offset, const float* weights, float* tmp, int* idx,
+                          int flags, geot_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Ball query.  replaces pointnet2_batch_cuda.ball_query_wrapper(B,N,M,radius,nsample,new_xyz,xyz,idx)
+ * (ball_query.cpp:29-39, ball_query_gpu.cu:15-51) and pointnet2._ext.ball_query(new_xyz,xyz,radius,nsample).
+ * new_xyz (B,M,3), xyz (B,N,3) -> idx (B,M,nsample): first nsample indices k (ascending) with
+ * d2 < radius*radius, remaining slots = first hit, rows with no hit all 0.  Unlike the reference the
+ * kernel writes every slot itself (no caller zero-fill needed).
+ * --------------------------------------------------------------------------------------------- */
+int geot_ball_query(int B, int N, int M, float radius, int nsample, const float* new_xyz,
+                    const float* xyz, int* idx, geot_stream_t stream);
+
+/* replaces pointops_cuda.ballquery_cuda(m,radius,nsample,xyz,new_xyz,offset,new_offset,idx)
+ * (openpoints/cpp/pointops/src/ballquery/ballquery_cuda_kernel.cu:26-78).  b = number of segments. */
+int geot_ballquery_offset(int b, int m, float radius, int nsample, const float* xyz,
+                          const float* new_xyz, const int* offset, const int* new_offset, int* idx,
+                          geot_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * kNN query.  replaces pointops_cuda.knnquery_cuda(m,nsample,xyz,new_xyz,offset,new_offset,idx,dist2)
+ * (pointops/src/knnquery/knnquery_cuda_kernel.cu:65-108).  Global int32 indices, ascending d2;
+ * exact-tie cases reproduce the reference's heap order.  b = number of segments, 1 <= nsample <= 1000.
+ * With offset == new_offset == NULL the inputs are batched: b clouds of n_per xyz points and m_per
+ * queries each (the layout of pointops.knn / knn_cuda.KNN / knn_point), indices stay GLOBAL.
+ * In the offset layout m_per must be an upper bound of the queries of any one segment (m always is).
+ * workspace: geot_knnquery_workspace_bytes(m) bytes of scratch (per-query tie flags).
+ * --------------------------------------------------------------------------------------------- */
+size_t geot_knnquery_workspace_bytes(int m);
+int geot_knnquery(int b, int m, int nsample, const float* xyz, const float* new_xyz,
+                  const int* offset, const int* new_offset, int n_per, int m_per, int* idx,
+                  float* dist2, void* workspace, size_t workspace_bytes, geot_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Grouping / gather (channel-major, batched).
+ * --------------------------------------------------------------------------------------------- */
+/* replaces pointnet2_batch_cuda.group_points_wrapper(B,C,N,M,ns,points,idx,out) (group_points_gpu.cu:53-72)
+ * and pointnet2._ext.group_points.  points (B,C,N), idx (B,M,ns) -> out (B,C,M,ns). */
+int geot_group_points(int B, int C, int N, int M, int nsample, const float* points, const int* idx,
+                      float* out, geot_stream_t stream);
+/* replaces pointnet2_batch_cuda.gather_points_wrapper(B,C,N,M,points,idx,out) (sampling_gpu.cu:15-31)
+ * and pointnet2._ext.gather_points.  points (B,C,N), idx (B,M) -> out (B,C,M). */
+int geot_gather_points(int B, int C, int N, int M, const float* points, const int* idx, float* out,
+                       geot_stream_t stream);
+
+/* Deterministic scatter-add plan shared by every backward pass that the reference does with float
+ * atomics: a CSR of source positions grouped by target, in ascending source order.
+ *   idx (B,E) int32 with values in [0,N)  ->  row_ptr (B,N+1) int32, perm (B,E) int32.
+ * Workspace layout: [row_ptr | perm]; query the size first.  Reusable across channels and calls that
+ * share idx (e.g. the xyz and feature grouping of one QueryAndGroup). */
+size_t geot_scatter_plan_bytes(int B, int N, int64_t E);
+int geot_scatter_plan_build(int B, int N, int64_t E, const int* idx, void* plan, size_t plan_bytes,
+                            geot_stream_t stream);
+
+/* replaces pointnet2_batch_cuda.group_points_grad_wrapper(B,C,N,M,ns,grad_out,idx,grad_points)
+ * (group_points_gpu.cu:14-31, atomicAdd :30) and pointnet2._ext.group_points_grad.
+ * grad_out (B,C,M,ns) -> grad_points (B,C,N), every element written (no caller zero-fill needed).
+ * plan = geot_scatter_plan_build(B,N,M*ns,idx). */
+int geot_group_points_grad(int B, int C, int N, int M, int nsample, const float* grad_out,
+                           const void* plan, float* grad_points, geot_stream_t stream);
+/* replaces pointnet2_batch_cuda.gather_points_grad_wrapper (sampling_gpu.cu:53-70). plan over E = M. */
+int geot_gather_points_grad(int B, int C, int N, int M, const float* grad_out, const void* plan,
+                            float* grad_points, geot_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * three_nn / three_interpolate (batched).
+ * --------------------------------------------------------------------------------------------- */
+/* replaces pointnet2_batch_cuda.three_nn_wrapper(B,n,m,unknown,known,dist2,idx) (interpolate_gpu.cu:16-59)
+ * and pointnet2._ext.three_nn.  unknown (B,n,3), known (B,m,3) -> dist2 (B,n,3) SQUARED, idx (B,n,3). */
+int geot_three_nn(int B, int n, int m, const float* unknown, const float* known, float* dist2,
+                  int* idx, geot_stream_t stream);
+/* replaces three_interpolate_wrapper(B,C,m,n,points,idx,weight,out) (interpolate_gpu.cu:84-104). */
+int geot_three_interpolate(int B, int C, int m, int n, const float* points, const int* idx,
+                           const float* weight, float* out, geot_stream_t stream);
+/* replaces three_interpolate_grad_wrapper(B,C,n,m,grad_out,idx,weight,grad_points)
+ * (interpolate_gpu.cu:127-149, 3 atomicAdds).  plan = geot_scatter_plan_build(B, m, 3*n, idx). */
+int geot_three_interpolate_grad(int B, int C, int n, int m, const float* grad_out, const float* weight,
+                                const void* plan, float* grad_points, geot_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Offset-format (channel-last) ops of pointops_cuda (openpoints/cpp/pointops/src).
+ * --------------------------------------------------------------------------------------------- */
+/* grouping_forward_cuda(m,nsample,c,input,idx,output)  grouping/grouping_cuda_kernel.cu:5-14 */
+int geot_grouping_forward(int m, int nsample, int c, const float* input, const int* idx,
+                          float* output, geot_stream_t stream);
+/* grouping_backward_cuda (:16-25, atomicAdd).  n = rows of grad_input; plan over (B=1, N=n, E=m*nsample). */
+int geot_grouping_backward(int m, int nsample, int c, int n, const float* grad_output,
+                           const void* plan, float* grad_input, geot_stream_t stream);
+/* interpolation_forward_cuda(n,c,k,input,idx,weight,output)  interpolation/interpolation_cuda_kernel.cu:5-18.
+ * Writes output (the reference accumulates into a caller-zeroed buffer; same values). */
+int geot_interpolation_forward(int n, int c, int k, const float* input, const int* idx,
+                               const float* weight, float* output, geot_stream_t stream);
+/* interpolation_backward_cuda (:20-33).  m = rows of grad_input; plan over (1, m, n*k). */
+int geot_interpolation_backward(int n, int c, int k, int m, const float* grad_output,
+                                const float* weight, const void* plan, float* grad_input,
+                                geot_stream_t stream);
+/* subtraction_forward_cuda / subtraction_backward_cuda  subtraction/subtraction_cuda_kernel.cu:5-30.
+ * plan over (1, n, n*nsample). */
+int geot_subtraction_forward(int n, int nsample, int c, const float* input1, const float* input2,
+                             const int* idx, float* output, geot_stream_t stream);
+int geot_subtraction_backward(int n, int nsample, int c, const float* grad_output, const void* plan,
+                              float* grad_input1, float* grad_input2, geot_stream_t stream);
+/* aggregation_forward_cuda / aggregation_backward_cuda  aggregation/aggregation_cuda_kernel.cu:5-39.
+ * plan over (1, n, n*nsample). */
+int geot_aggregation_forward(int n, int nsample, int c, int w_c, const float* input,
+                             const float* position, const float* weight, const int* idx,
+                             float* output, geot_stream_t stream);
+int geot_aggregation_backward(int n, int nsample, int c, int w_c, const float* input,
+                              const float* position, const float* weight, const int* idx,
+                              const float* grad_output, const void* plan, float* grad_input,
+                              float* grad_position, float* grad_weight, geot_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GEOT_B200_H */

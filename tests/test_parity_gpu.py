@@ -1,0 +1,224 @@
+"""Parity proper: the sm_100a kernels, called through the C ABI (geot_b200.functional -> libgeot_b200.so),
+against the CPU oracle on the same seeded inputs.  Bit-exact for indices / copies; 1e-5 relative for
+interpolated values and gradients (north_star tolerance)."""
+import numpy as np
+import pytest
+import torch
+
+from geot_b200 import _lib, synth
+from geot_b200 import functional as F
+
+pytestmark = pytest.mark.gpu
+RTOL, ATOL = 1e-5, 1e-6
+
+
+def cu(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def clouds(kind, B, N, seed=0):
+    if kind == "tooth":
+        return synth.tooth_batch(B, N, first_cloud=seed)
+    return np.stack([synth.adversarial_cloud(N, 100 + seed + i, kind) for i in range(B)])
+
+
+FPS_CASES = [("tooth", 2, 16384, 1024), ("tooth", 3, 4096, 512), ("tooth", 2, 1000, 100), ("tooth", 2, 5000, 300),
+             ("tooth", 1, 16000, 512), ("quant", 2, 6000, 700), ("dup", 2, 3000, 900), ("origin", 2, 9000, 400),
+             ("tooth", 2, 37, 37), ("tooth", 1, 1, 1), ("quant", 1, 12289, 64)]
+
+
+@pytest.mark.parametrize("kind,B,N,M", FPS_CASES)
+@pytest.mark.parametrize("variant", ["batch", "ext"])
+def test_fps_batched(cuda, oracle, kind, B, N, M, variant):
+    xyz = clouds(kind, B, N)
+    flags = 0 if variant == "batch" else (_lib.GEOT_FPS_CAP512 | _lib.GEOT_FPS_MAGSKIP)
+    exp = oracle.furthest_point_sample(xyz, M, cap=1024 if variant == "batch" else 512, mag_skip=variant == "ext")
+    got = F.furthest_point_sampling(cu(xyz), M, flags=flags).cpu().numpy()
+    assert np.array_equal(got, exp)
+    got = F.furthest_point_sampling(cu(xyz), M, flags=flags | _lib.GEOT_FPS_FORCE_GENERIC).cpu().numpy()
+    assert np.array_equal(got, exp), "generic fallback kernel"
+
+
+def test_fps_large_n_uses_fallback(cuda, oracle):
+    xyz = clouds("tooth", 2, 20000)
+    assert np.array_equal(F.furthest_point_sampling(cu(xyz), 200).cpu().numpy(), oracle.furthest_point_sample(xyz, 200))
+
+
+def test_fps_more_samples_than_points(cuda, oracle):
+    xyz = clouds("tooth", 2, 50)
+    assert np.array_equal(F.furthest_point_sampling(cu(xyz), 80).cpu().numpy(), oracle.furthest_point_sample(xyz, 80))
+
+
+@pytest.mark.parametrize("weighted", [False, True])
+def test_fps_offset_ragged(cuda, oracle, weighted):
+    sizes, ms = [5000, 1200, 16384, 333], [300, 100, 1024, 333]
+    xyz = np.concatenate([synth.tooth_cloud(n, 50 + i) for i, n in enumerate(sizes)])
+    off, noff = np.cumsum(sizes).astype(np.int32), np.cumsum(ms).astype(np.int32)
+    w = np.random.default_rng(1).random(xyz.shape[0]).astype(np.float32) if weighted else None
+    if weighted:
+        w[::7] = 0.0  # exercises max(w, 1e-12)
+    exp = oracle.furthestsampling(xyz, off, noff, w)
+    got = F.furthestsampling(cu(xyz), cu(off), cu(noff), weights=cu(w) if weighted else None).cpu().numpy()
+    assert np.array_equal(got, exp)
+
+
+BALL_CASES = [("tooth", 2, 16384, 1024, 0.1, 32), ("tooth", 2, 4099, 257, 0.2, 64), ("tooth", 3, 1000, 64, 0.05, 16),
+              ("quant", 2, 5000, 300, 0.125, 48), ("dup", 1, 2000, 100, 0.1, 8), ("tooth", 1, 30, 5, 0.5, 40)]
+
+
+@pytest.mark.parametrize("kind,B,N,M,r,ns", BALL_CASES)
+def test_ball_query(cuda, oracle, kind, B, N, M, r, ns):
+    xyz = clouds(kind, B, N)
+    q = xyz[:, np.random.default_rng(2).choice(N, M, replace=False)].copy()
+    q[:, -1] += 9.0  # an empty ball -> all-zero row
+    exp = oracle.ball_query(r, ns, xyz, q)
+    out = torch.full((B, M, ns), -7, dtype=torch.int32, device="cuda")  # every slot must be written
+    got = F.ball_query(cu(q), cu(xyz), r, ns, out=out).cpu().numpy()
+    assert np.array_equal(got, exp)
+    assert not exp[:, -1].any()
+
+
+def test_ball_query_offset(cuda, oracle):
+    sizes, ms = [3000, 700, 5001], [100, 33, 250]
+    xyz = np.concatenate([synth.tooth_cloud(n, 60 + i) for i, n in enumerate(sizes)])
+    off, noff = np.cumsum(sizes).astype(np.int32), np.cumsum(ms).astype(np.int32)
+    starts = np.concatenate([[0], off[:-1]])
+    q = np.concatenate([xyz[s:s + m] for s, m in zip(starts, ms)])
+    exp = oracle.ballquery(0.15, 24, xyz, q, off, noff)
+    got = F.ballquery_offset(0.15, 24, cu(xyz), cu(q), cu(off), cu(noff)).cpu().numpy()
+    assert np.array_equal(got, exp)
+
+
+@pytest.mark.parametrize("kind", ["tooth", "dup", "quant"])
+@pytest.mark.parametrize("k", [1, 3, 16, 31, 32, 64, 100, 130])
+def test_knnquery_offset(cuda, oracle, kind, k):
+    sizes, ms = [4000, 900, 2500, 40], [300, 200, 257, 40]
+    xyz = np.concatenate([clouds(kind, 1, n, seed=i)[0] for i, n in enumerate(sizes)])
+    off, noff = np.cumsum(sizes).astype(np.int32), np.cumsum(ms).astype(np.int32)
+    starts = np.concatenate([[0], off[:-1]])
+    q = np.concatenate([xyz[s:s + m] + (0 if kind != "tooth" else 1e-3) for s, m in zip(starts, ms)]).astype(np.float32)
+    ei, _, ed2 = oracle.knnquery(k, xyz, q, off, noff)
+    gi, gd2 = F.knnquery(k, cu(xyz), cu(q), cu(off), cu(noff))
+    assert np.array_equal(gd2.cpu().numpy(), ed2)
+    assert np.array_equal(gi.cpu().numpy(), ei)
+
+
+def test_knnquery_batched_layout(cuda, oracle):
+    b, n, m, k = 3, 2048, 512, 16
+    xyz = clouds("tooth", b, n)
+    q = xyz[:, :m] + np.float32(2e-3)
+    off = (np.arange(1, b + 1) * n).astype(np.int32)
+    noff = (np.arange(1, b + 1) * m).astype(np.int32)
+    ei, _, ed2 = oracle.knnquery(k, xyz.reshape(-1, 3), q.reshape(-1, 3), off, noff)
+    gi, gd2 = F.knnquery(k, cu(xyz.reshape(-1, 3)), cu(q.reshape(-1, 3)), None, None, n_per=n, m_per=m)
+    assert np.array_equal(gi.cpu().numpy(), ei) and np.array_equal(gd2.cpu().numpy(), ed2)
+
+
+GROUP_CASES = [(2, 3, 16384, 1024, 32), (2, 64, 4096, 256, 32), (1, 5, 1000, 33, 7), (3, 17, 500, 64, 16), (1, 1, 10, 1, 1)]
+
+
+@pytest.mark.parametrize("B,C,N,M,ns", GROUP_CASES)
+def test_group_points_fwd_bwd(cuda, oracle, B, C, N, M, ns):
+    rng = np.random.default_rng(5)
+    feat = rng.standard_normal((B, C, N)).astype(np.float32)
+    idx = rng.integers(0, N, (B, M, ns)).astype(np.int32)
+    idx[:, 0, :] = idx[:, 0, :1]  # a padded row: one target hit ns times
+    out = F.group_points(cu(feat), cu(idx)).cpu().numpy()
+    assert np.array_equal(out, oracle.grouping_operation(feat, idx))
+    g = rng.standard_normal((B, C, M, ns)).astype(np.float32)
+    plan = F.ScatterPlan(cu(idx), B, N)
+    got = F.group_points_grad(cu(g), plan, N)
+    np.testing.assert_allclose(got.cpu().numpy(), oracle.grouping_operation_grad(g, idx, N), rtol=RTOL, atol=ATOL)
+    again = F.group_points_grad(cu(g), F.ScatterPlan(cu(idx), B, N), N)
+    assert torch.equal(got, again), "backward must be bit-reproducible"
+
+
+def test_scatter_plan_is_stable_csr(cuda):
+    rng = np.random.default_rng(6)
+    B, N, E = 3, 777, 5000
+    idx = rng.integers(0, N, (B, E)).astype(np.int32)
+    idx[0, :2000] = 5  # one very long segment
+    plan = F.ScatterPlan(cu(idx), B, N)
+    rp, pm = plan.row_ptr().cpu().numpy(), plan.perm().cpu().numpy()
+    for b in range(B):
+        order = np.argsort(idx[b], kind="stable")
+        assert np.array_equal(pm[b], order.astype(np.int32))
+        assert np.array_equal(rp[b], np.concatenate([[0], np.cumsum(np.bincount(idx[b], minlength=N))]))
+
+
+@pytest.mark.parametrize("B,C,N,M", [(2, 3, 16384, 1024), (2, 67, 999, 130), (1, 4, 8, 8)])
+def test_gather_points_fwd_bwd(cuda, oracle, B, C, N, M):
+    rng = np.random.default_rng(7)
+    feat = rng.standard_normal((B, C, N)).astype(np.float32)
+    idx = rng.integers(0, N, (B, M)).astype(np.int32)
+    assert np.array_equal(F.gather_points(cu(feat), cu(idx)).cpu().numpy(), oracle.gather_operation(feat, idx))
+    g = rng.standard_normal((B, C, M)).astype(np.float32)
+    got = F.gather_points_grad(cu(g), F.ScatterPlan(cu(idx), B, N), N).cpu().numpy()
+    np.testing.assert_allclose(got, oracle.gather_operation_grad(g, idx, N), rtol=RTOL, atol=ATOL)
+
+
+@pytest.mark.parametrize("kind,B,n,m", [("tooth", 2, 4096, 512), ("tooth", 2, 16000, 8192), ("quant", 2, 3000, 700),
+                                         ("dup", 1, 1000, 300), ("tooth", 2, 100, 2), ("tooth", 1, 513, 1)])
+def test_three_nn(cuda, oracle, kind, B, n, m):
+    unknown = clouds(kind, B, n)
+    known = unknown[:, np.random.default_rng(8).choice(n, m, replace=False)].copy() if m <= n else clouds(kind, B, m, 3)
+    _, ei, ed2 = oracle.three_nn(unknown, known)
+    gd2, gi = F.three_nn(cu(unknown), cu(known))
+    assert np.array_equal(gi.cpu().numpy(), ei)
+    assert np.array_equal(gd2.cpu().numpy(), ed2)
+
+
+@pytest.mark.parametrize("B,C,m,n", [(2, 384, 512, 4096), (2, 16, 8192, 16000), (1, 3, 5, 9)])
+def test_three_interpolate_fwd_bwd(cuda, oracle, B, C, m, n):
+    rng = np.random.default_rng(9)
+    feat = rng.standard_normal((B, C, m)).astype(np.float32)
+    idx = rng.integers(0, m, (B, n, 3)).astype(np.int32)
+    w = rng.random((B, n, 3)).astype(np.float32)
+    w /= w.sum(-1, keepdims=True)
+    out = F.three_interpolate(cu(feat), cu(idx), cu(w)).cpu().numpy()
+    np.testing.assert_allclose(out, oracle.three_interpolate(feat, idx, w), rtol=RTOL, atol=ATOL)
+    g = rng.standard_normal((B, C, n)).astype(np.float32)
+    got = F.three_interpolate_grad(cu(g), cu(w), F.ScatterPlan(cu(idx), B, m), m)
+    np.testing.assert_allclose(got.cpu().numpy(), oracle.three_interpolate_grad(g, idx, w, m), rtol=RTOL, atol=2e-6)
+    assert torch.equal(got, F.three_interpolate_grad(cu(g), cu(w), F.ScatterPlan(cu(idx), B, m), m))
+
+
+@pytest.mark.parametrize("c", [32, 7])
+def test_offset_channel_last_ops(cuda, oracle, c):
+    rng = np.random.default_rng(10)
+    n, m, ns, k = 3000, 1200, 16, 3
+    inp = rng.standard_normal((n, c)).astype(np.float32)
+    idx = rng.integers(0, n, (m, ns)).astype(np.int32)
+    assert np.array_equal(F.grouping_forward(cu(inp), cu(idx)).cpu().numpy(), oracle.grouping(inp, idx))
+    g = rng.standard_normal((m, ns, c)).astype(np.float32)
+    got = F.grouping_backward(cu(g), F.ScatterPlan(cu(idx), 1, n), n).cpu().numpy()
+    np.testing.assert_allclose(got, oracle.grouping_grad(g, idx, n), rtol=RTOL, atol=ATOL)
+    ik = rng.integers(0, n, (m, k)).astype(np.int32)
+    w = rng.random((m, k)).astype(np.float32)
+    np.testing.assert_allclose(F.interpolation_forward(cu(inp), cu(ik), cu(w)).cpu().numpy(),
+                               oracle.interpolation_forward(inp, ik, w), rtol=RTOL, atol=ATOL)
+    go = rng.standard_normal((m, c)).astype(np.float32)
+    got = F.interpolation_backward(cu(go), cu(w), F.ScatterPlan(cu(ik), 1, n), n, k).cpu().numpy()
+    np.testing.assert_allclose(got, oracle.interpolation_backward(go, ik, w, n), rtol=RTOL, atol=ATOL)
+    # subtraction / aggregation
+    idn = rng.integers(0, n, (n, ns)).astype(np.int32)
+    in2 = rng.standard_normal((n, c)).astype(np.float32)
+    assert np.array_equal(F.subtraction_forward(cu(inp), cu(in2), cu(idn)).cpu().numpy(), oracle.subtraction_forward(inp, in2, idn))
+    gs = rng.standard_normal((n, ns, c)).astype(np.float32)
+    plan = F.ScatterPlan(cu(idn), 1, n)
+    g1, g2 = F.subtraction_backward(cu(gs), plan)
+    e1, e2 = oracle.subtraction_backward(idn, gs)
+    np.testing.assert_allclose(g1.cpu().numpy(), e1, rtol=RTOL, atol=5e-6)
+    np.testing.assert_allclose(g2.cpu().numpy(), e2, rtol=RTOL, atol=5e-6)
+    if c % 4 == 0:
+        wc = c // 4
+        pos = rng.standard_normal((n, ns, c)).astype(np.float32)
+        wt = rng.standard_normal((n, ns, wc)).astype(np.float32)
+        np.testing.assert_allclose(F.aggregation_forward(cu(inp), cu(pos), cu(wt), cu(idn)).cpu().numpy(),
+                                   oracle.aggregation_forward(inp, pos, wt, idn), rtol=1e-4, atol=1e-5)
+        ga = rng.standard_normal((n, c)).astype(np.float32)
+        gi, gp, gw = F.aggregation_backward(cu(inp), cu(pos), cu(wt), cu(idn), cu(ga), plan)
+        ei, ep, ew = oracle.aggregation_backward(inp, pos, wt, idn, ga)
+        np.testing.assert_allclose(gi.cpu().numpy(), ei, rtol=1e-4, atol=1e-5)
+        assert np.array_equal(gp.cpu().numpy(), ep)
+        np.testing.assert_allclose(gw.cpu().numpy(), ew, rtol=1e-4, atol=1e-5)
