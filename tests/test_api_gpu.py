@@ -65,10 +65,11 @@ def test_knn_group_and_knn_point(cuda):
     xyz = cu(synth.tooth_batch(2, 2048))
     q = xyz[:, :300].contiguous() + 1e-3
     d, i = layers.knn_point(9, q, xyz)
-    dist = torch.cdist(q, xyz)
+    # exact-difference cdist: the default matmul expansion loses ~1e-7 absolute on d2, i.e. 5e-5 on d near 1e-3
+    dist = torch.cdist(q, xyz, compute_mode="donot_use_mm_for_euclid_dist")
     td, ti = dist.topk(9, dim=-1, largest=False, sorted=True)
     assert i.dtype == torch.int64 and torch.equal(i, ti)
-    torch.testing.assert_close(d, td, rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(d, td, rtol=1e-5, atol=1e-7)
     dp, fj = layers.KNNGroup(9)(q, xyz, xyz.transpose(1, 2).contiguous())
     assert dp.shape == (2, 3, 300, 9) and torch.equal(fj - q.transpose(1, 2).unsqueeze(-1), dp)
     d2, i2 = layers.KNN(9)(q, xyz)
@@ -80,11 +81,13 @@ def test_three_interpolation_composite_and_grad(cuda):
     known = xyz[:, ::8].contiguous()
     feat = torch.randn(2, 32, known.shape[1], device="cuda", requires_grad=True)
     out = layers.three_interpolation(xyz, known, feat)
-    d = torch.cdist(xyz, known)
+    # known is a subset of xyz, so exact-zero distances occur: use the exact-difference cdist (the matmul
+    # expansion turns those zeros into ~1e-4 and the 1/(d+1e-8) weights change completely)
+    d = torch.cdist(xyz, known, compute_mode="donot_use_mm_for_euclid_dist")
     td, ti = d.topk(3, dim=-1, largest=False)
     w = 1.0 / (td + 1e-8); w = w / w.sum(-1, keepdim=True)
     exp = sum(torch.gather(feat, 2, ti[..., k].unsqueeze(1).expand(-1, 32, -1)) * w[..., k].unsqueeze(1) for k in range(3))
-    torch.testing.assert_close(out, exp, rtol=1e-3, atol=1e-4)  # cdist's matmul distances differ in the last bits
+    torch.testing.assert_close(out, exp, rtol=1e-4, atol=1e-5)
     go = torch.randn_like(out)
     out.backward(go)
     g1 = feat.grad.clone(); feat.grad = None
