@@ -1,0 +1,77 @@
+"""oracle/transition_ref.py against fixtures produced by the REFERENCE'S OWN code (tests/golden/
+make_transition_golden.py ran transformer.py / insT_loss.py / train.py statements on CPU)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import transition_ref as R
+
+G = np.load(os.path.join(os.path.dirname(__file__), "golden", "transition_golden.npz"))
+
+
+def t(name):
+    return torch.from_numpy(G[name])
+
+
+CASES = ["C17", "C33", "C5"]
+
+
+@pytest.mark.parametrize("tag", CASES)
+def test_sig_t_mean_forward_and_grads(tag):
+    W = t(f"{tag}_W").requires_grad_(True)
+    x = t(f"{tag}_x").requires_grad_(True)
+    insT = R.sig_t_mean_forward(x, t(f"{tag}_cm"), W)
+    torch.testing.assert_close(insT, t(f"{tag}_insT"), rtol=1e-6, atol=1e-7)
+    gW, gx = torch.autograd.grad(insT, [W, x], t(f"{tag}_go"))
+    torch.testing.assert_close(gW, t(f"{tag}_gW"), rtol=1e-4, atol=1e-6)
+    torch.testing.assert_close(gx, t(f"{tag}_gx"), rtol=1e-4, atol=1e-6)
+    torch.testing.assert_close(R.sig_t_forward(t(f"{tag}_x"), t(f"{tag}_sigt_W")), t(f"{tag}_sigt_T"), rtol=1e-6, atol=1e-7)
+
+
+@pytest.mark.parametrize("tag", CASES)
+def test_transition_apply(tag):
+    logits = t(f"{tag}_logits").requires_grad_(True)
+    insT = t(f"{tag}_insT").requires_grad_(True)
+    out = R.transition_apply(logits, t(f"{tag}_ema_t_corr"), insT, 0.9)
+    torch.testing.assert_close(out, t(f"{tag}_corr"), rtol=1e-6, atol=1e-7)
+    gl, gi = torch.autograd.grad(out, [logits, insT], t(f"{tag}_go2"))
+    torch.testing.assert_close(gl, t(f"{tag}_g_logits"), rtol=1e-5, atol=1e-7)
+    torch.testing.assert_close(gi, t(f"{tag}_g_insT_apply"), rtol=1e-5, atol=1e-7)
+
+
+@pytest.mark.parametrize("tag", CASES)
+def test_manifold_losses(tag):
+    k = int(G[f"{tag}_k"])
+    insT = t(f"{tag}_insT").requires_grad_(True)
+    pos, labels = t(f"{tag}_pos"), t(f"{tag}_labels")
+    # default neighbours (the reference's own knn_point) and pinned neighbours must both reproduce it
+    for idx in (None, t(f"{tag}_idx3")):
+        l3 = R.threeD_space_loss(pos, labels, insT, k, sigma=0.5, idx=idx)
+        torch.testing.assert_close(l3, t(f"{tag}_loss3"), rtol=1e-6, atol=1e-9)
+        g3, = torch.autograd.grad(l3, insT)
+        torch.testing.assert_close(g3, t(f"{tag}_g_insT_loss3"), rtol=1e-5, atol=1e-9)
+    lf = R.feature_space_loss(t(f"{tag}_logits"), labels, insT, k, sigma=2.0, idx=t(f"{tag}_idxf"))
+    torch.testing.assert_close(lf, t(f"{tag}_lossf"), rtol=1e-5, atol=1e-9)
+    gf, = torch.autograd.grad(lf, insT)
+    torch.testing.assert_close(gf, t(f"{tag}_g_insT_lossf"), rtol=1e-5, atol=1e-9)
+    C = insT.shape[1]
+    torch.testing.assert_close(R.identity_loss(insT.detach(), torch.eye(C).unsqueeze(0)), t(f"{tag}_loss_id"), rtol=1e-6, atol=1e-9)
+
+
+def test_class_statistics():
+    tag = "C17"
+    assert R.LABEL_PROJ_17 == G[f"{tag}_label_proj"].tolist()
+    assert R.LABEL_PROJ_33[:17] == R.LABEL_PROJ_17 and sorted(R.LABEL_PROJ_33) == list(range(33))
+    class_T, best_v, best_i = R.class_T_pick(t(f"{tag}_pred_u"))
+    assert torch.equal(class_T, t(f"{tag}_class_T"))
+    corr, ema = R.class_T_step(class_T, t(f"{tag}_ema_t_in"), t(f"{tag}_sigma"), R.LABEL_PROJ_17, 0.999, 0.999)
+    torch.testing.assert_close(corr, t(f"{tag}_ema_t_corr_out"), rtol=1e-6, atol=1e-8)
+    torch.testing.assert_close(ema, t(f"{tag}_ema_t_out"), rtol=1e-6, atol=1e-8)
+    C = class_T.shape[0]
+    cm, cn = torch.zeros((C, C)), torch.zeros((C,))
+    for _ in range(2):
+        R.mean_feature_update(cm, cn, t(f"{tag}_mf_probs"), t(f"{tag}_mf_target"))
+    torch.testing.assert_close(cm, t(f"{tag}_mf_cm"), rtol=1e-6, atol=1e-8)
+    assert torch.equal(cn, t(f"{tag}_mf_cnum"))
