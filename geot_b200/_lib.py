@@ -49,12 +49,29 @@ _SIGNATURES = {
     "geot_subtraction_backward": [_i, _i, _i, _vp, _vp, _vp, _vp, _vp],
     "geot_aggregation_forward": [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp],
     "geot_aggregation_backward": [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
+    "geot_sigt_workspace_bytes": [_i],
+    "geot_sigt_forward": [_i, _i, _i, _vp, _vp, _i, _vp, _vp, _vp, _sz, _vp],
+    "geot_sigt_backward_workspace_bytes": [_i, _i, _i],
+    "geot_sigt_backward": [_i, _i, _i, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _sz, _vp],
+    "geot_transition_apply_forward": [_i, _i, _i, _vp, _vp, _vp, _f, _vp, _vp],
+    "geot_transition_apply_backward": [_i, _i, _i, _vp, _vp, _vp, _f, _vp, _vp, _vp, _vp],
+    "geot_manifold_workspace_bytes": [_i64],
+    "geot_manifold_loss_forward": [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _f, _i, _vp, _vp, _vp, _sz, _vp],
+    "geot_manifold_loss_backward": [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
+    "geot_class_pick_workspace_bytes": [_i],
+    "geot_class_pick": [_i, _i, _i, _vp, _vp, _vp, _vp, _vp, _sz, _vp],
+    "geot_class_t_step": [_i, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp],
+    "geot_mean_feature_update": [_i64, _i, _vp, _vp, _vp, _vp, _vp, _sz, _vp],
 }
 _RESTYPES = {
     "geot_last_error": C.c_char_p,
     "geot_launch_count": C.c_uint64,
     "geot_scatter_plan_bytes": _sz,
     "geot_knnquery_workspace_bytes": _sz,
+    "geot_sigt_workspace_bytes": _sz,
+    "geot_sigt_backward_workspace_bytes": _sz,
+    "geot_manifold_workspace_bytes": _sz,
+    "geot_class_pick_workspace_bytes": _sz,
 }
 
 

@@ -316,3 +316,122 @@ def aggregation_backward(input, position, weight, idx, grad_output, plan, gi=Non
             gw = torch.empty((n, ns, w_c), dtype=_f32, device=dev)
         call("geot_aggregation_backward", n, ns, c, w_c, ptr(input), ptr(position), ptr(weight), ptr(idx), ptr(grad_output), plan.ptr, ptr(gi), ptr(gp), ptr(gw), stream_ptr())
     return gi, gp, gw
+
+
+# --------------------------------------------------------------------------------------------------
+# instance-dependent transition-matrix path
+# --------------------------------------------------------------------------------------------------
+def _ws(nbytes, dev):
+    return torch.empty((max(int(nbytes), 1),), dtype=torch.uint8, device=dev)
+
+
+def sigt_forward(x, W, cm=None, out=None):
+    """x (B,C,N), W (C,C,2C) with cm (C,C) [sig_t_mean] or W (C*C,C) with cm None [sig_t] -> insT (B*N,C,C)."""
+    dev = check_cuda(x, W, cm, out)
+    B, Cc, N = x.shape
+    stride = 2 * Cc if cm is not None else Cc
+    with torch.cuda.device(dev):
+        if out is None:
+            out = torch.empty((B * N, Cc, Cc), dtype=_f32, device=dev)
+        nb = int(_lib.lib().geot_sigt_workspace_bytes(Cc))
+        ws = _ws(nb, dev)
+        call("geot_sigt_forward", B, Cc, N, ptr(x), ptr(W), stride, ptr(cm), ptr(out), ptr(ws), nb, stream_ptr())
+    return out
+
+
+def sigt_backward(x, W, cm, grad_insT):
+    """-> (grad_W like W, g_raw (B*N, C*C) gradient w.r.t. the pre-clamp products)."""
+    dev = check_cuda(x, W, cm, grad_insT)
+    B, Cc, N = x.shape
+    stride = 2 * Cc if cm is not None else Cc
+    with torch.cuda.device(dev):
+        grad_W = torch.empty_like(W)
+        g_raw = torch.empty((B * N, Cc * Cc), dtype=_f32, device=dev)
+        nb = int(_lib.lib().geot_sigt_backward_workspace_bytes(B, Cc, N))
+        ws = _ws(nb, dev)
+        call("geot_sigt_backward", B, Cc, N, ptr(x), ptr(W), stride, ptr(cm), ptr(grad_insT), ptr(g_raw), ptr(grad_W), ptr(ws), nb, stream_ptr())
+    return grad_W, g_raw
+
+
+def transition_apply_forward(logits, ema_t, insT, lam, out=None):
+    """logits (B,C,N), ema_t (C,C), insT (B*N,C,C) -> corrected logits (B,C,N)."""
+    dev = check_cuda(logits, ema_t, insT, out)
+    B, Cc, N = logits.shape
+    with torch.cuda.device(dev):
+        if out is None:
+            out = torch.empty_like(logits)
+        call("geot_transition_apply_forward", B, Cc, N, ptr(logits), ptr(ema_t), ptr(insT), float(lam), ptr(out), stream_ptr())
+    return out
+
+
+def transition_apply_backward(logits, ema_t, insT, lam, grad_out, need_logits=True, need_insT=True):
+    dev = check_cuda(logits, ema_t, insT, grad_out)
+    B, Cc, N = logits.shape
+    with torch.cuda.device(dev):
+        gl = torch.empty_like(logits) if need_logits else None
+        gi = torch.empty_like(insT) if need_insT else None
+        call("geot_transition_apply_backward", B, Cc, N, ptr(logits), ptr(ema_t), ptr(insT), float(lam), ptr(grad_out), ptr(gl), ptr(gi), stream_ptr())
+    return gl, gi
+
+
+MANIFOLD_3D, MANIFOLD_FEATURE = 0, 1
+
+
+def manifold_loss_forward(points, labels, insT, idx, sigma, mode):
+    """points (B,N,D), labels (B,N) int64, insT (B*N,C,C), idx (B,N,k) int32 local -> (loss (1,), coef (B*N,k))."""
+    dev = check_cuda(points, labels, insT, idx)
+    B, N, D = points.shape
+    Cc, k = insT.shape[1], idx.shape[2]
+    with torch.cuda.device(dev):
+        coef = torch.empty((B * N, k), dtype=_f32, device=dev)
+        loss = torch.empty((1,), dtype=_f32, device=dev)
+        nb = int(_lib.lib().geot_manifold_workspace_bytes(B * N))
+        ws = _ws(nb, dev)
+        call("geot_manifold_loss_forward", B, N, D, Cc, k, ptr(points), ptr(labels), ptr(insT), ptr(idx), float(sigma), mode, ptr(coef), ptr(loss), ptr(ws), nb, stream_ptr())
+    return loss, coef
+
+
+def manifold_loss_backward(insT, idx, coef, plan, grad_loss):
+    dev = check_cuda(insT, idx, coef, grad_loss)
+    B, N, k = idx.shape
+    Cc = insT.shape[1]
+    with torch.cuda.device(dev):
+        g = torch.empty_like(insT)
+        call("geot_manifold_loss_backward", B, N, Cc, k, ptr(insT), ptr(idx), ptr(coef), plan.ptr, ptr(grad_loss), ptr(g), stream_ptr())
+    return g
+
+
+def class_pick(pred_u):
+    """pred_u (B,C,N) softmax -> class_T (C,C), best_val (C), best_idx (C) int64 (flat b*N+n)."""
+    dev = check_cuda(pred_u)
+    B, Cc, N = pred_u.shape
+    with torch.cuda.device(dev):
+        class_T = torch.empty((Cc, Cc), dtype=_f32, device=dev)
+        best_v = torch.empty((Cc,), dtype=_f32, device=dev)
+        best_i = torch.empty((Cc,), dtype=torch.int64, device=dev)
+        nb = int(_lib.lib().geot_class_pick_workspace_bytes(Cc))
+        ws = _ws(nb, dev)
+        call("geot_class_pick", B, Cc, N, ptr(pred_u), ptr(class_T), ptr(best_v), ptr(best_i), ptr(ws), nb, stream_ptr())
+    return class_T, best_v, best_i
+
+
+def class_t_step(class_T, ema_t, sigma, label_proj, geo_lambda, ema_decay):
+    """-> (ema_t_corr, new ema_t); label_proj int32 (C) on the device."""
+    dev = check_cuda(class_T, ema_t, sigma, label_proj)
+    Cc = class_T.shape[0]
+    with torch.cuda.device(dev):
+        corr = torch.empty_like(class_T)
+        ema_out = torch.empty_like(class_T)
+        call("geot_class_t_step", Cc, ptr(class_T), ptr(ema_t), ptr(sigma), ptr(label_proj), float(geo_lambda), float(ema_decay), ptr(corr), ptr(ema_out), stream_ptr())
+    return corr, ema_out
+
+
+def mean_feature_update(probs, target, cm, c_num):
+    """In-place running class-mean update (train.py:884-895 semantics); probs (BN,C), target (BN) int64."""
+    dev = check_cuda(probs, target, cm, c_num)
+    BN, Cc = probs.shape
+    with torch.cuda.device(dev):
+        nb = max(int(_lib.lib().geot_class_pick_workspace_bytes(Cc)), 512)
+        ws = _ws(nb, dev)
+        call("geot_mean_feature_update", BN, Cc, ptr(probs), ptr(target), ptr(cm), ptr(c_num), ptr(ws), nb, stream_ptr())
+    return cm, c_num

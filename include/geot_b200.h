@@ -183,6 +183,78 @@ int geot_aggregation_backward(int n, int nsample, int c, int w_c, const float* i
                               const float* grad_output, const void* plan, float* grad_input,
                               float* grad_position, float* grad_weight, geot_stream_t stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Instance-dependent transition-matrix path (GeoT's noisy-pseudo-label loss).
+ * All tensors fp32 unless noted; C = number of classes (2 <= C <= 64).
+ * --------------------------------------------------------------------------------------------- */
+/* replaces sig_t_mean.forward (openpoints/models/backbone/transformer.py:1120-1131, a Python loop of C
+ * Linear(2C->C) calls + clamp + F.normalize) and, with cm == NULL, sig_t.forward (:1089-1097).
+ *   x (B,C,N) class probabilities; W: sig_t_mean (C, C, 2C) = stacked fc[kk].weight, w_row_stride = 2C;
+ *   sig_t (C*C, C) = fc.weight, w_row_stride = C; cm (C,C) or NULL  ->  insT (B*N, C, C).
+ * workspace: geot_sigt_workspace_bytes(C) (the point-independent bias W[:, :, C:] . cm). */
+size_t geot_sigt_workspace_bytes(int C);
+int geot_sigt_forward(int B, int C, int N, const float* x, const float* W, int w_row_stride,
+                      const float* cm, float* insT, void* workspace, size_t workspace_bytes,
+                      geot_stream_t stream);
+/* backward of the above w.r.t. W (autograd of transformer.py:1123-1129): grad_insT (B*N,C,C) ->
+ * grad_W (same shape as W; every element written).  g_raw (B*N, C*C) receives the gradient w.r.t. the
+ * pre-clamp products (the caller may derive grad_x = g_raw @ W[:, :, :C] from it; the reference call site
+ * detaches x, train.py:548).  Deterministic: fixed-order two-stage reduction over points. */
+size_t geot_sigt_backward_workspace_bytes(int B, int C, int N);
+int geot_sigt_backward(int B, int C, int N, const float* x, const float* W, int w_row_stride,
+                       const float* cm, const float* grad_insT, float* g_raw, float* grad_W,
+                       void* workspace, size_t workspace_bytes, geot_stream_t stream);
+
+/* replaces train.py:549-552: newT = L1norm_rows(lam*ema_t_corr + (1-lam)*insT); out[b,:,n] = logits[b,:,n] . newT[bN+n]
+ * (blend + F.normalize + bmm + two permutes in one pass over insT).  logits/out (B,C,N). */
+int geot_transition_apply_forward(int B, int C, int N, const float* logits, const float* ema_t,
+                                  const float* insT, float lam, float* out, geot_stream_t stream);
+/* its backward: grad_out (B,C,N) -> grad_logits (B,C,N) and grad_insT (B*N,C,C); either may be NULL. */
+int geot_transition_apply_backward(int B, int C, int N, const float* logits, const float* ema_t,
+                                   const float* insT, float lam, const float* grad_out,
+                                   float* grad_logits, float* grad_insT, geot_stream_t stream);
+
+/* replaces threeD_space_loss.forward / feature_space_loss.forward after their kNN (utils/insT_loss.py:72-110,
+ * :22-58): k rounds of index_select + cat growing (BN,k,C,C) tensors become one gather pass.
+ *   points (B*N, D) positions (D=3) or logits (D=C); labels (B*N) int64; insT (B*N, C*C);
+ *   idx (B,N,k) int32 LOCAL neighbour indices (self excluded); mode GEOT_MANIFOLD_3D: w in {0,1}*exp, per point
+ *   sum(w*Td)/(sum(w)+1e-3), mean over points; GEOT_MANIFOLD_FEATURE: w in {-1,+1}*exp, mean over points*k.
+ * Outputs: coef (B*N,k) = d loss_point / d Tdist (kept for the backward), loss (1 float, device).
+ * workspace: geot_manifold_workspace_bytes(B*N). */
+#define GEOT_MANIFOLD_3D 0
+#define GEOT_MANIFOLD_FEATURE 1
+size_t geot_manifold_workspace_bytes(int64_t BN);
+int geot_manifold_loss_forward(int B, int N, int D, int C, int k, const float* points,
+                               const int64_t* labels, const float* insT, const int* idx, float sigma,
+                               int mode, float* coef, float* loss, void* workspace,
+                               size_t workspace_bytes, geot_stream_t stream);
+/* backward w.r.t. insT (weights are detached in the reference, insT_loss.py:106-108): grad_insT (B*N,C*C),
+ * every element written, fixed summation order.  plan = geot_scatter_plan_build(B, N, N*k, idx);
+ * grad_loss: 1 float on the device (upstream gradient of the scalar loss). */
+int geot_manifold_loss_backward(int B, int N, int C, int k, const float* insT, const int* idx,
+                                const float* coef, const void* plan, const float* grad_loss,
+                                float* grad_insT, geot_stream_t stream);
+
+/* replaces the per-class loop train.py:509-526 (filter_outlier off): for every class cc the FIRST point in
+ * (b,n) order with the largest pred_u[b,cc,n]; class_T[cc] = pred_u[b,:,n].  best_val (C), best_idx (C) int64
+ * flat b*N+n are returned so ranks can combine their picks (arg-max over ranks, then a row broadcast).
+ * workspace: geot_class_pick_workspace_bytes(C). */
+size_t geot_class_pick_workspace_bytes(int C);
+int geot_class_pick(int B, int C, int N, const float* pred_u, float* class_T, float* best_val,
+                    int64_t* best_idx, void* workspace, size_t workspace_bytes, geot_stream_t stream);
+/* replaces train.py:507,528-545,556-557 (Gaussian geometric prior over label_proj, blend, the reference's
+ * keepdim-less normalisation copied verbatim, EMA): class_T, ema_t (C,C), sigma (C), label_proj (C) int32
+ * -> ema_t_corr (C,C), ema_t_out (C,C; may alias ema_t). */
+int geot_class_t_step(int C, const float* class_T, const float* ema_t, const float* sigma,
+                      const int* label_proj, float geo_lambda, float ema_decay, float* ema_t_corr,
+                      float* ema_t_out, geot_stream_t stream);
+/* replaces the inner loop of cal_mean_feature (train.py:884-895), bug-for-bug (probs[target] indexes rows by
+ * class id): probs (BN,C), target (BN) int64; cm (C,C) and c_num (C) updated in place.
+ * workspace: geot_class_pick_workspace_bytes(C). */
+int geot_mean_feature_update(int64_t BN, int C, const float* probs, const int64_t* target, float* cm,
+                             float* c_num, void* workspace, size_t workspace_bytes,
+                             geot_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,175 @@
+"""Transition-matrix path on the GPU (through the C ABI) against (1) the golden fixtures produced by the
+reference's own Python and (2) oracle/transition_ref.py on seeded inputs at larger sizes.
+Tolerance: 1e-5 relative (north_star, fp32), written per assert."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from geot_b200 import functional as F_
+from geot_b200 import synth, transition as T
+from oracle import transition_ref as R
+
+pytestmark = pytest.mark.gpu
+G = np.load(os.path.join(os.path.dirname(__file__), "golden", "transition_golden.npz"))
+
+
+def t(name, dev="cuda"):
+    return torch.from_numpy(G[name]).to(dev)
+
+
+def close(a, b, rtol=1e-5, atol=1e-7):
+    torch.testing.assert_close(a.cpu(), b.cpu(), rtol=rtol, atol=atol)
+
+
+def rel(a, b):
+    """relative error in the max norm — the north_star's '1e-5 relative' for gradient tensors."""
+    return float((a.double().cpu() - b.double().cpu()).abs().max() / b.double().abs().max().clamp_min(1e-30))
+
+
+@pytest.mark.parametrize("tag", ["C17", "C33", "C5"])
+def test_golden_sig_t_mean_and_apply(cuda, tag):
+    C = G[f"{tag}_cm"].shape[0]
+    mod = T.sig_t_mean(C).cuda()
+    with torch.no_grad():
+        for kk in range(C):
+            mod.fc[kk].weight.copy_(t(f"{tag}_W")[kk])
+    x = t(f"{tag}_x").requires_grad_(True)
+    insT = mod(x, t(f"{tag}_cm"))
+    close(insT, t(f"{tag}_insT"), rtol=1e-5, atol=1e-7)  # entries just above the 1e-5 clamp come from cancelling O(0.1) terms
+    insT.backward(t(f"{tag}_go"))
+    gW = torch.stack([mod.fc[kk].weight.grad for kk in range(C)])
+    assert rel(gW, t(f"{tag}_gW")) < 1e-5
+    assert rel(x.grad, t(f"{tag}_gx")) < 1e-5
+    m2 = T.sig_t(C).cuda()
+    with torch.no_grad():
+        m2.fc.weight.copy_(t(f"{tag}_sigt_W"))
+    close(m2(t(f"{tag}_x")), t(f"{tag}_sigt_T"), rtol=1e-5, atol=1e-7)
+    # train.py:549-552
+    logits = t(f"{tag}_logits").requires_grad_(True)
+    ins = t(f"{tag}_insT").requires_grad_(True)
+    out = T.apply_transition(logits, t(f"{tag}_ema_t_corr"), ins, 0.9)
+    close(out, t(f"{tag}_corr"), rtol=1e-5, atol=1e-6)
+    out.backward(t(f"{tag}_go2"))
+    assert rel(logits.grad, t(f"{tag}_g_logits")) < 1e-5
+    assert rel(ins.grad, t(f"{tag}_g_insT_apply")) < 1e-5
+
+
+@pytest.mark.parametrize("tag", ["C17", "C33", "C5"])
+def test_golden_manifold_losses(cuda, tag):
+    k = int(G[f"{tag}_k"])
+    pos, labels = t(f"{tag}_pos"), t(f"{tag}_labels")
+    ins = t(f"{tag}_insT").requires_grad_(True)
+    l3 = T.threeD_space_loss(k=k, sigma=0.5)(pos, labels, ins, idx=t(f"{tag}_idx3").int().contiguous())
+    close(l3, t(f"{tag}_loss3"), rtol=1e-5, atol=1e-9)
+    l3.backward()
+    assert rel(ins.grad, t(f"{tag}_g_insT_loss3")) < 1e-5
+    # own kNN (sm_100a kernel) must find the same neighbours on this tie-free input
+    ins.grad = None
+    l3b = T.threeD_space_loss(k=k, sigma=0.5)(pos, labels, ins)
+    close(l3b, t(f"{tag}_loss3"), rtol=1e-5, atol=1e-9)
+    ins.grad = None
+    lf = T.feature_space_loss(k=k, sigma=2.0)(t(f"{tag}_logits"), labels, ins, idx=t(f"{tag}_idxf").int().contiguous())
+    close(lf, t(f"{tag}_lossf"), rtol=1e-5, atol=1e-9)
+    lf.backward()
+    assert rel(ins.grad, t(f"{tag}_g_insT_lossf")) < 1e-5
+    C = ins.shape[1]
+    close(T.Idenyity_loss()(ins.detach(), torch.eye(C, device="cuda").unsqueeze(0)), t(f"{tag}_loss_id"), rtol=1e-5, atol=1e-9)
+
+
+def test_golden_class_statistics(cuda):
+    tag = "C17"
+    class_T, best_v, best_i = T.class_T_pick(t(f"{tag}_pred_u"))
+    assert torch.equal(class_T.cpu(), t(f"{tag}_class_T", "cpu"))  # a row copy: bit-exact
+    corr, ema = T.class_T_step(class_T, t(f"{tag}_ema_t_in"), t(f"{tag}_sigma"), T.LABEL_PROJ_17, 0.999, 0.999)
+    close(corr, t(f"{tag}_ema_t_corr_out"), rtol=1e-5, atol=1e-8)
+    close(ema, t(f"{tag}_ema_t_out"), rtol=1e-5, atol=1e-8)
+    C = 17
+    cm, cn = torch.zeros((C, C), device="cuda"), torch.zeros((C,), device="cuda")
+    for _ in range(2):
+        T.mean_feature_update(cm, cn, t(f"{tag}_mf_probs"), t(f"{tag}_mf_target"))
+    close(cm, t(f"{tag}_mf_cm"), rtol=1e-5, atol=1e-8)
+    assert torch.equal(cn.cpu(), t(f"{tag}_mf_cnum", "cpu"))
+
+
+@pytest.mark.parametrize("C,B,N", [(17, 2, 16000), (33, 2, 4096), (33, 3, 1000), (8, 2, 333), (64, 1, 130)])
+def test_oracle_sigt_apply_large(cuda, C, B, N):
+    g = torch.Generator().manual_seed(C * 1000 + N)
+    x = torch.softmax(torch.randn(B, C, N, generator=g) * 3, 1)
+    W = (torch.rand(C, C, 2 * C, generator=g) - 0.5) * (2 / (2 * C) ** 0.5)
+    W[:, :, :C] += torch.eye(C) * 0.5  # some rows saturate the clamp on both sides
+    cm = torch.softmax(torch.randn(C, C, generator=g), 1)
+    go = torch.randn(B * N, C, C, generator=g)
+    Wr = W.clone().requires_grad_(True)
+    ref = R.sig_t_mean_forward(x, cm, Wr)
+    gWr, = torch.autograd.grad(ref, Wr, go)
+    Wc = W.cuda().requires_grad_(True)
+    out = T._SigT.apply(x.cuda(), Wc, cm.cuda())
+    close(out, ref, rtol=1e-5, atol=1e-7)
+    out.backward(go.cuda())
+    assert rel(Wc.grad, gWr) < 1e-5
+    # determinism of the two-stage reduction
+    Wc.grad = None
+    T._SigT.apply(x.cuda(), Wc, cm.cuda()).backward(go.cuda())
+    g1 = Wc.grad.clone(); Wc.grad = None
+    T._SigT.apply(x.cuda(), Wc, cm.cuda()).backward(go.cuda())
+    assert torch.equal(g1, Wc.grad)
+    # apply
+    logits = (torch.randn(B, C, N, generator=g) * 2).requires_grad_(True)
+    ema = torch.softmax(torch.randn(C, C, generator=g) + torch.eye(C) * 4, 1)
+    insT = ref.detach().clone().requires_grad_(True)
+    r2 = R.transition_apply(logits, ema, insT, 0.9)
+    go2 = torch.randn(B, C, N, generator=g)
+    gl, gi = torch.autograd.grad(r2, [logits, insT], go2)
+    lc = logits.detach().cuda().requires_grad_(True)
+    ic = insT.detach().cuda().requires_grad_(True)
+    o2 = T.apply_transition(lc, ema.cuda(), ic, 0.9)
+    close(o2, r2, rtol=1e-5, atol=1e-6)
+    o2.backward(go2.cuda())
+    assert rel(lc.grad, gl) < 1e-5 and rel(ic.grad, gi) < 1e-5
+
+
+@pytest.mark.parametrize("C,B,N,k", [(17, 2, 3000, 32), (33, 2, 1500, 32), (5, 3, 700, 40), (17, 1, 500, 7)])
+def test_oracle_manifold_large(cuda, C, B, N, k):
+    g = torch.Generator().manual_seed(C + N + k)
+    pos = torch.from_numpy(synth.tooth_batch(B, N))
+    labels = torch.randint(0, 4, (B, N), generator=g)
+    insT = torch.softmax(torch.randn(B * N, C, C, generator=g), 2).requires_grad_(True)
+    idx = R.knn_point(k + 1, pos, pos)[1][:, :, 1:]
+    l = R.threeD_space_loss(pos, labels, insT, k, sigma=0.05, idx=idx)
+    gr, = torch.autograd.grad(l, insT)
+    ic = insT.detach().cuda().requires_grad_(True)
+    lc = T.threeD_space_loss(k=k, sigma=0.05)(pos.cuda(), labels.cuda(), ic)  # own kNN
+    close(lc, l, rtol=1e-5, atol=1e-10)
+    lc.backward()
+    assert rel(ic.grad, gr) < 1e-5
+    g1 = ic.grad.clone(); ic.grad = None
+    T.threeD_space_loss(k=k, sigma=0.05)(pos.cuda(), labels.cuda(), ic).backward()
+    assert torch.equal(g1, ic.grad)  # deterministic
+    logits = torch.randn(B, C, N, generator=g)
+    idxf = R.knn_point(k + 1, logits.permute(0, 2, 1).contiguous())[1][:, :, 1:]
+    lf = R.feature_space_loss(logits, labels, insT, k, sigma=1.5, idx=idxf)
+    gf, = torch.autograd.grad(lf, insT)
+    ic.grad = None
+    lfc = T.feature_space_loss(k=k, sigma=1.5)(logits.cuda(), labels.cuda(), ic, idx=idxf.int().cuda().contiguous())
+    close(lfc, lf, rtol=2e-5, atol=1e-9)  # signed sum: cancellation
+    lfc.backward()
+    assert rel(ic.grad, gf) < 1e-5
+
+
+def test_oracle_class_pick_large(cuda):
+    g = torch.Generator().manual_seed(7)
+    B, C, N = 4, 33, 16000
+    pred = torch.softmax(torch.randn(B, C, N, generator=g) * 2, 1)
+    pred[1, 5, 77] = pred[3, 5, 9] = 2.0  # exact tie across clouds: the first in (b,n) order wins
+    ct, bv, bi = R.class_T_pick(pred)
+    ctc, bvc, bic = T.class_T_pick(pred.cuda())
+    assert torch.equal(ctc.cpu(), ct) and torch.equal(bvc.cpu(), bv) and torch.equal(bic.cpu(), bi)
+    assert int(bi[5]) == 1 * N + 77
+    sigma = torch.full((C,), 0.4)
+    ema = torch.softmax(torch.randn(C, C, generator=g) + torch.eye(C) * 5, 1)
+    corr, ema2 = R.class_T_step(ct, ema, sigma, R.LABEL_PROJ_33, 0.999, 0.999)
+    corrc, ema2c = T.class_T_step(ctc, ema.cuda(), sigma.cuda(), T.LABEL_PROJ_33, 0.999, 0.999)
+    close(corrc, corr, rtol=1e-5, atol=1e-8)
+    close(ema2c, ema2, rtol=1e-5, atol=1e-8)
