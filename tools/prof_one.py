@@ -1,0 +1,26 @@
+#!/usr/bin/env python
+"""Dev tool (GPU box): launch ONE op of the bench workload a few times so ncu can capture it.
+usage: python tools/prof_one.py {fps|fps_noprune|ball|group|group3} [B]"""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np, torch
+from geot_b200 import _lib, synth
+from geot_b200 import functional as F
+
+what = sys.argv[1]
+B = int(sys.argv[2]) if len(sys.argv) > 2 else 64
+N, M, NS, C = 16384, 1024, 32, 64
+xyz = torch.from_numpy(synth.tooth_batch(B, N)).cuda()
+feat = torch.randn(B, C, N, device="cuda")
+idx = F.furthest_point_sampling(xyz, M)
+xyz_t = xyz.transpose(1, 2).contiguous()
+centres = F.gather_points(xyz_t, idx).transpose(1, 2).contiguous()
+nbr = F.ball_query(centres, xyz, 0.1, NS)
+torch.cuda.synchronize()
+for _ in range(3):
+    if what == "fps": F.furthest_point_sampling(xyz, M)
+    elif what == "fps_noprune": F.furthest_point_sampling(xyz, M, flags=_lib.GEOT_FPS_NO_PRUNE)
+    elif what == "ball": F.ball_query(centres, xyz, 0.1, NS)
+    elif what == "group": F.group_points(feat, nbr)
+    elif what == "group3": F.group_points(xyz_t, nbr)
+torch.cuda.synchronize()
