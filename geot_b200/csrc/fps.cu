@@ -445,6 +445,345 @@ fps_bucket_kernel(const float* __restrict__ xyz, const int* __restrict__ offset,
 }
 
 // ---------------------------------------------------------------------------------------------
+// Warp-specialised variant of the bucket-pruned kernel (the default): warp 0 is a MANAGER, warps 1..31 are
+// WORKERS.  In fps_bucket_kernel every one of the 32 warps repeats the box test and the 32-slot reduction each
+// round, so the round is issue-bound on redundant work (8 warps per scheduler x ~50 instructions).  Here
+//   * the manager keeps the boxes of all buckets in registers (4 per lane), reads the per-bucket candidate keys,
+//     picks the global winner (2 REDUX), runs the exact box test for all buckets against the new sample and
+//     publishes {sample, active flags}; then bar.arrive(A);
+//   * a worker waits on A, updates only its ACTIVE buckets (min-distances of its points live in its registers),
+//     republishes the candidate of each bucket it touched, then bar.arrive(B); an idle worker issues ~10
+//     instructions per round;
+//   * the manager waits on B.  Two named barriers in producer/consumer form, nobody waits twice.
+// Same exactness argument, same tie order as above.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void bar_sync_named(int id) { asm volatile("bar.sync %0, 1024;" ::"r"(id) : "memory"); }
+__device__ __forceinline__ void bar_arrive_named(int id) { asm volatile("bar.arrive %0, 1024;" ::"r"(id) : "memory"); }
+__device__ __forceinline__ unsigned lds_u8(unsigned a) {
+  unsigned v;
+  asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void sts_u8(unsigned a, unsigned v) { asm volatile("st.shared.u8 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+__device__ __forceinline__ void sts32(unsigned a, unsigned v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+
+template <int NBK>
+struct MgrCfg {
+  static constexpr int NT = 1024, NWK = 31;
+  static constexpr int CHW = (NBK + NWK - 1) / NWK;  // buckets per worker
+  static constexpr int BPL = NBK / 32;               // buckets per manager lane
+  static constexpr int CAP = NBK * 128;
+  static constexpr int PLANE_BYTES = NBK * 512;
+  static constexpr int SORT_BYTES = 4096 * 4 + 2 * CAP + 2 * CAP;  // hist | perm | cell codes
+  static constexpr int R0_BYTES = 3 * PLANE_BYTES > SORT_BYTES ? 3 * PLANE_BYTES : SORT_BYTES;
+  static constexpr int KEY_OFF = R0_BYTES;
+  static constexpr int AUX_OFF = KEY_OFF + NBK * 8;
+  static constexpr int BOX_OFF = AUX_OFF + NBK * 16;
+  static constexpr int ACT_OFF = BOX_OFF + NBK * 24;
+  static constexpr int CTRL_OFF = ACT_OFF + 256;  // 8 flag bytes per worker
+  static constexpr int SMEM_BYTES = CTRL_OFF + 16;
+};
+
+template <int NBK>
+__global__ void __launch_bounds__(1024, 1)
+fps_mgr_kernel(const float* __restrict__ xyz, const int* __restrict__ offset,
+               const int* __restrict__ new_offset, int N, int M, int* __restrict__ idx, int log2bs,
+               int mag_skip) {
+  using Cfg = MgrCfg<NBK>;
+  constexpr int NT = Cfg::NT, NWK = Cfg::NWK, CHW = Cfg::CHW, BPL = Cfg::BPL;
+  extern __shared__ float4 fps_smem[];
+  unsigned char* smem_raw = reinterpret_cast<unsigned char*>(fps_smem);
+  int* hist = reinterpret_cast<int*>(smem_raw);
+  unsigned short* perm = reinterpret_cast<unsigned short*>(smem_raw + 4096 * 4);
+  unsigned short* codes = perm + Cfg::CAP;
+  __shared__ float s_red[6][32];
+  __shared__ int s_scan[32];
+
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  int64_t start_n, start_m;
+  int n, m, idx_base;
+  fps_segment(offset, new_offset, N, M, blockIdx.x, start_n, n, start_m, m, idx_base);
+  if (m <= 0) return;
+  if (n > Cfg::CAP || n <= 0) return;  // caller understated n_max (the Python layer computes it from offset)
+  const int q_count = (n + (1 << log2bs) - 1) >> log2bs;
+  const float* __restrict__ src = xyz + start_n * 3;
+  const float kInf = __int_as_float(0x7f800000);
+
+  // ---- 1. bounding cube of the cloud -> 16^3 cells --------------------------------------------------------
+  float lo[3] = {kInf, kInf, kInf}, hi[3] = {-kInf, -kInf, -kInf};
+#pragma unroll 4
+  for (int k = t; k < n; k += NT) {
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+      const float v = src[(int64_t)k * 3 + a];
+      lo[a] = fminf(lo[a], v); hi[a] = fmaxf(hi[a], v);
+    }
+  }
+#pragma unroll
+  for (int a = 0; a < 3; a++) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      lo[a] = fminf(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], o));
+      hi[a] = fmaxf(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], o));
+    }
+    if (lane == 0) { s_red[a][warp] = lo[a]; s_red[3 + a][warp] = hi[a]; }
+  }
+  for (int i = t; i < 4096; i += NT) hist[i] = 0;
+  __syncthreads();
+  float ext = 0.f;
+#pragma unroll
+  for (int a = 0; a < 3; a++) {
+    float l = s_red[a][lane], h = s_red[3 + a][lane];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      l = fminf(l, __shfl_xor_sync(0xffffffffu, l, o));
+      h = fmaxf(h, __shfl_xor_sync(0xffffffffu, h, o));
+    }
+    lo[a] = l;
+    ext = fmaxf(ext, h - l);
+  }
+  const float scale = (ext > 0.f && ext < kInf) ? 16.0f / ext : 0.f;
+
+  // ---- 2. counting sort by cell: histogram (codes cached), exclusive scan, scatter of the permutation -----------
+#pragma unroll 4
+  for (int k = t; k < n; k += NT) {
+    unsigned code = 0;
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+      const float f = (src[(int64_t)k * 3 + a] - lo[a]) * scale;
+      const int q = min(max(__float2int_rd(f), 0), 15);  // NaN -> 0: partitioning only, never results
+      code |= morton4((unsigned)q) << a;
+    }
+    codes[k] = (unsigned short)code;
+    atomicAdd(&hist[code], 1);
+  }
+  __syncthreads();
+  {
+    constexpr int PER = 4096 / NT;
+    int v[PER], sum = 0;
+#pragma unroll
+    for (int i = 0; i < PER; i++) { v[i] = hist[t * PER + i]; sum += v[i]; }
+    int inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += y;
+    }
+    if (lane == 31) s_scan[warp] = inc;
+    __syncthreads();
+    int wtot = s_scan[lane], winc = wtot;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, winc, o);
+      if (lane >= o) winc += y;
+    }
+    const int wbase = __shfl_sync(0xffffffffu, winc - wtot, warp);
+    int run = wbase + inc - sum;
+#pragma unroll
+    for (int i = 0; i < PER; i++) { hist[t * PER + i] = run; run += v[i]; }
+  }
+  __syncthreads();
+  for (int k = t; k < n; k += NT) perm[atomicAdd(&hist[codes[k]], 1)] = (unsigned short)k;
+  __syncthreads();
+
+  unsigned a_base;  // opaque to the optimiser, or it re-derives the window base (S2UR SR_CgaCtaId) inside the loop
+  asm volatile("mov.u32 %0, %1;" : "=r"(a_base) : "r"(smem_u32(smem_raw)));
+  const unsigned a_key = a_base + Cfg::KEY_OFF, a_aux = a_base + Cfg::AUX_OFF, a_box = a_base + Cfg::BOX_OFF;
+  const unsigned a_act = a_base + Cfg::ACT_OFF, a_ctrl = a_base + Cfg::CTRL_OFF;
+  const int wk = warp - 1;  // worker id (warp 0 = manager)
+  const int rounds = m - 1;
+  const float x0 = src[0], y0 = src[1], z0 = src[2];  // first sample = segment start (sampling_gpu.cu:120-122)
+  if (t == 0) idx[start_m] = idx_base;
+
+  // ---- 3. workers take their buckets: original indices into registers, then coordinates into the planes --------
+  // Running min-distance, registers only.  -1 marks "never a candidate": padding beyond n and, for the
+  // pointnet2/_ext variant, points the reference skips (|p|^2 <= 1e-3, _ext_src sampling_gpu.cu:103-104).
+  float mind[CHW * 4];
+  unsigned kreg[CHW * 2];  // per bucket: 4 original indices (setup), then their 4 reference tie ranks, packed u16
+#pragma unroll
+  for (int c = 0; c < CHW; c++) {
+    const int b = c * NWK + wk;
+    uint2 kk = make_uint2(0u, 0u);
+    if (wk >= 0 && b < NBK) kk = lds64(smem_u32(perm) + 2u * (unsigned)(b * 128 + 4 * lane));
+    kreg[2 * c] = kk.x; kreg[2 * c + 1] = kk.y;
+  }
+  __syncthreads();  // hist / perm / codes are dead from here on; the coordinate planes overwrite them
+#pragma unroll
+  for (int c = 0; c < CHW; c++) {
+    const int b = c * NWK + wk;
+#pragma unroll
+    for (int e = 0; e < 4; e++) mind[c * 4 + e] = -1.0f;
+    if (wk >= 0 && b < NBK) {
+      const int pos0 = b * 128 + 4 * lane;
+      const unsigned ks[4] = {kreg[2 * c] & 0xffffu, kreg[2 * c] >> 16, kreg[2 * c + 1] & 0xffffu, kreg[2 * c + 1] >> 16};
+      float xs[4], ys[4], zs[4];
+      float l3[3] = {kInf, kInf, kInf}, h3[3] = {-kInf, -kInf, -kInf};
+      unsigned r = 0xffffffffu;
+#pragma unroll
+      for (int e = 0; e < 4; e++) {
+        bool live = pos0 + e < n;
+        float x = 0.f, y = 0.f, z = 0.f;
+        if (live) {
+          const int64_t k = ks[e];
+          x = src[k * 3 + 0]; y = src[k * 3 + 1]; z = src[k * 3 + 2];
+          if (mag_skip) {
+            const float mag = __fmaf_rn(z, z, __fmaf_rn(x, x, __fmul_rn(y, y)));
+            live = !((double)mag <= 1e-3);
+          }
+        }
+        xs[e] = x; ys[e] = y; zs[e] = z;
+        if (live) {
+          mind[c * 4 + e] = 1e10f;
+          l3[0] = fminf(l3[0], x); h3[0] = fmaxf(h3[0], x);
+          l3[1] = fminf(l3[1], y); h3[1] = fmaxf(h3[1], y);
+          l3[2] = fminf(l3[2], z); h3[2] = fmaxf(h3[2], z);
+          r = min(r, (tie_rank((int)ks[e], log2bs, q_count) << 2) | (unsigned)e);
+        }
+      }
+      // from here on only the ranks are needed (n <= 16384: rank < 2^15); the manager un-ranks the winner
+      kreg[2 * c] = tie_rank((int)ks[0], log2bs, q_count) | (tie_rank((int)ks[1], log2bs, q_count) << 16);
+      kreg[2 * c + 1] = tie_rank((int)ks[2], log2bs, q_count) | (tie_rank((int)ks[3], log2bs, q_count) << 16);
+      const unsigned a_pt = a_base + 16u * (unsigned)(b * 32 + lane);
+      sts128(a_pt, make_float4(xs[0], xs[1], xs[2], xs[3]));
+      sts128(a_pt + Cfg::PLANE_BYTES, make_float4(ys[0], ys[1], ys[2], ys[3]));
+      sts128(a_pt + 2 * Cfg::PLANE_BYTES, make_float4(zs[0], zs[1], zs[2], zs[3]));
+#pragma unroll
+      for (int a = 0; a < 3; a++) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          l3[a] = fminf(l3[a], __shfl_xor_sync(0xffffffffu, l3[a], o));
+          h3[a] = fmaxf(h3[a], __shfl_xor_sync(0xffffffffu, h3[a], o));
+        }
+      }
+      if (lane == 0) {
+        float* bx = reinterpret_cast<float*>(smem_raw + Cfg::BOX_OFF) + b * 6;
+        bx[0] = l3[0]; bx[1] = l3[1]; bx[2] = l3[2]; bx[3] = h3[0]; bx[4] = h3[1]; bx[5] = h3[2];
+      }
+      // all live points start at 1e10: the bucket's first candidate is its live point of least rank
+      const unsigned wr = __reduce_min_sync(0xffffffffu, r);
+      if (wr == 0xffffffffu) {
+        if (lane == 0) sts64(a_key + 8u * b, 0u, (unsigned)__float_as_int(-1.0f));
+      } else if (r == wr) {
+        const int e = (int)(wr & 3u);
+        const float px = e == 0 ? xs[0] : e == 1 ? xs[1] : e == 2 ? xs[2] : xs[3];
+        const float py = e == 0 ? ys[0] : e == 1 ? ys[1] : e == 2 ? ys[2] : ys[3];
+        const float pz = e == 0 ? zs[0] : e == 1 ? zs[1] : e == 2 ? zs[2] : zs[3];
+        sts64(a_key + 8u * b, ((0x00ffffffu - (wr >> 2)) << 7) | (unsigned)b, (unsigned)__float_as_int(1e10f));
+        sts128(a_aux + 16u * b, make_float4(0.f, px, py, pz));
+      }
+    }
+  }
+  if (t < 64) sts32(a_act + 4u * t, 0u);  // flag bytes of buckets that do not exist stay 0
+  __syncthreads();
+  if (rounds <= 0) return;
+
+  if (warp == 0) {
+    // =========================== manager ===========================
+    float box[BPL][6];
+    unsigned a_flag[BPL];  // where worker (b % NWK) reads the active flag of its chunk (b / NWK)
+#pragma unroll
+    for (int i = 0; i < BPL; i++) {
+      const int b = BPL * lane + i;
+#pragma unroll
+      for (int a = 0; a < 6; a++) box[i][a] = lds32f(a_box + 4u * (unsigned)(b * 6 + a));
+      a_flag[i] = a_act + 8u * (unsigned)(b % NWK) + (unsigned)(b / NWK);
+    }
+    int* out = idx + start_m;
+    // publish {sample, per-worker active flags}: exact box test of every bucket against the sample, rounded like
+    // dist2_ref; a bucket's current maximum is the value word of its candidate key
+    auto publish = [&](const float4& smp, const uint2 (&key)[BPL]) {
+#pragma unroll
+      for (int i = 0; i < BPL; i++) {
+        const float gx = fmaxf(fmaxf(__fsub_rn(box[i][0], smp.y), __fsub_rn(smp.y, box[i][3])), 0.f);
+        const float gy = fmaxf(fmaxf(__fsub_rn(box[i][1], smp.z), __fsub_rn(smp.z, box[i][4])), 0.f);
+        const float gz = fmaxf(fmaxf(__fsub_rn(box[i][2], smp.w), __fsub_rn(smp.w, box[i][5])), 0.f);
+        const float lb = __fmaf_rn(gz, gz, __fmaf_rn(gx, gx, __fmul_rn(gy, gy)));
+        sts_u8(a_flag[i], lb < __uint_as_float(key[i].y) ? 1u : 0u);
+      }
+      if (lane == 0) sts128(a_ctrl, smp);
+      bar_arrive_named(1);
+    };
+    // global winner: max value, then max of (~rank | bucket) among the holders
+    auto pick = [&](const uint2 (&key)[BPL], int& ghi, unsigned& glo) {
+      unsigned long long best = ((unsigned long long)(key[0].y ^ 0x80000000u) << 32) | key[0].x;
+#pragma unroll
+      for (int i = 1; i < BPL; i++) {
+        const unsigned long long k64 = ((unsigned long long)(key[i].y ^ 0x80000000u) << 32) | key[i].x;
+        best = k64 > best ? k64 : best;
+      }
+      const int bh = (int)((unsigned)(best >> 32) ^ 0x80000000u);
+      ghi = __reduce_max_sync(0xffffffffu, bh);
+      glo = __reduce_max_sync(0xffffffffu, bh == ghi ? (unsigned)best : 0u);
+    };
+    uint2 key[BPL];
+#pragma unroll
+    for (int i = 0; i < BPL; i++) key[i] = lds64(a_key + 8u * (unsigned)(BPL * lane + i));
+    publish(make_float4(0.f, x0, y0, z0), key);
+    for (int j = 1; j <= rounds; j++) {
+      bar_sync_named(2);  // workers have applied sample j-1
+#pragma unroll
+      for (int i = 0; i < BPL; i++) key[i] = lds64(a_key + 8u * (unsigned)(BPL * lane + i));
+      int ghi;
+      unsigned glo;
+      pick(key, ghi, glo);
+      // no candidate at all (every point skipped): the reference keeps index 0
+      float4 smp = make_float4(0.f, x0, y0, z0);
+      if (ghi >= 0) smp = lds128(a_aux + 16u * (glo & 127u));
+      if (j < rounds) publish(smp, key);
+      // off the critical path: un-rank the winner (rank 0 <-> index 0)
+      if (lane == 0) out[j] = idx_base + (ghi >= 0 ? tie_unrank(0x00ffffffu - (glo >> 7), log2bs, q_count) : 0);
+    }
+  } else {
+    // =========================== workers ===========================
+    const unsigned a_my = a_act + 8u * (unsigned)wk;
+    for (int j = 0; j < rounds; j++) {
+      bar_sync_named(1);  // manager has published the sample and the active flags of round j
+      const uint2 fl = lds64(a_my);  // one flag byte per owned bucket
+      if (fl.x | fl.y) {
+        const float4 smp = lds128(a_ctrl);
+#pragma unroll
+        for (int c = 0; c < CHW; c++) {
+          const unsigned f = c < 4 ? (fl.x >> (8 * c)) & 0xffu : (fl.y >> (8 * (c - 4))) & 0xffu;
+          const int b = c * NWK + wk;
+          if (f && b < NBK) {
+            const unsigned a_pt = a_base + 16u * (unsigned)(b * 32 + lane);
+            const float4 X = lds128(a_pt), Y = lds128(a_pt + Cfg::PLANE_BYTES), Z = lds128(a_pt + 2 * Cfg::PLANE_BYTES);
+            const float xs[4] = {X.x, X.y, X.z, X.w}, ys[4] = {Y.x, Y.y, Y.z, Y.w}, zs[4] = {Z.x, Z.y, Z.z, Z.w};
+            unsigned k01 = kreg[2 * c], k23 = kreg[2 * c + 1];
+            asm volatile("" : "+r"(k01), "+r"(k23));  // keep the unpacking in the loop: hoisted it costs 20 registers
+            const unsigned rk[4] = {((k01 & 0xffffu) << 2) | 0u, ((k01 >> 16) << 2) | 1u,
+                                    ((k23 & 0xffffu) << 2) | 2u, ((k23 >> 16) << 2) | 3u};
+            float cm = -1.0f;
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+              const float d = dist2_ref(xs[e], ys[e], zs[e], smp.y, smp.z, smp.w);
+              const float v = fminf(d, mind[c * 4 + e]);
+              mind[c * 4 + e] = v;
+              cm = fmaxf(cm, v);
+            }
+            // candidates are >= 0 or exactly -1, so the int view of the float bits is order preserving
+            const int wm = __reduce_max_sync(0xffffffffu, __float_as_int(cm));
+            unsigned r = 0xffffffffu;
+#pragma unroll
+            for (int e = 0; e < 4; e++) r = min(r, (__float_as_int(mind[c * 4 + e]) == wm) ? rk[e] : 0xffffffffu);
+            const unsigned wr = __reduce_min_sync(0xffffffffu, r);
+            if (r == wr) {  // exactly one lane: ranks are unique (an active bucket has a live point, so wm >= 0)
+              const int e = (int)(wr & 3u);
+              const float px = e == 0 ? xs[0] : e == 1 ? xs[1] : e == 2 ? xs[2] : xs[3];
+              const float py = e == 0 ? ys[0] : e == 1 ? ys[1] : e == 2 ? ys[2] : ys[3];
+              const float pz = e == 0 ? zs[0] : e == 1 ? zs[1] : e == 2 ? zs[2] : zs[3];
+              sts64(a_key + 8u * b, ((0x00ffffffu - (wr >> 2)) << 7) | (unsigned)b, (unsigned)wm);
+              sts128(a_aux + 16u * b, make_float4(0.f, px, py, pz));
+            }
+          }
+        }
+      }
+      bar_arrive_named(2);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // Fallback: any n, optional weights; min-distances in the caller's temp array (global), like the
 // reference.  64-bit (value, ~rank) keys, shuffle reduction.
 // ---------------------------------------------------------------------------------------------
@@ -543,6 +882,21 @@ static int launch_bucket(int blocks, const float* xyz, const int* offset, const 
   return check_launch("fps_bucket_kernel");
 }
 
+template <int NBK>
+static int launch_mgr(int blocks, const float* xyz, const int* offset, const int* new_offset, int N,
+                      int M, int* idx, int log2bs, int mag_skip, cudaStream_t s) {
+  constexpr int smem = MgrCfg<NBK>::SMEM_BYTES;
+  static bool configured = false;  // per instantiation
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(fps_mgr_kernel<NBK>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) { set_error("fps: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
+    configured = true;
+  }
+  fps_mgr_kernel<NBK><<<blocks, 1024, smem, s>>>(xyz, offset, new_offset, N, M, idx, log2bs, mag_skip);
+  count_launch(1);
+  return check_launch("fps_mgr_kernel");
+}
+
 static int fps_dispatch(int blocks, int n_max, const float* xyz, const int* offset, const int* new_offset,
                         int N, int M, const float* weights, float* temp, int* idx, int flags,
                         cudaStream_t s) {
@@ -550,6 +904,15 @@ static int fps_dispatch(int blocks, int n_max, const float* xyz, const int* offs
   const int log2bs = ilog2(ref_opt_n_threads(n_max, cap));
   const int mag_skip = (flags & GEOT_FPS_MAGSKIP) ? 1 : 0;
   const bool generic = (flags & GEOT_FPS_FORCE_GENERIC) || weights != nullptr || n_max > 4 * 4096;
+  if (!generic && !(flags & (GEOT_FPS_NO_PRUNE | GEOT_FPS_SYMMETRIC))) {
+    const int ch = (n_max + 4095) / 4096;
+    switch (ch) {
+      case 1: return launch_mgr<32>(blocks, xyz, offset, new_offset, N, M, idx, log2bs, mag_skip, s);
+      case 2: return launch_mgr<64>(blocks, xyz, offset, new_offset, N, M, idx, log2bs, mag_skip, s);
+      case 3: return launch_mgr<96>(blocks, xyz, offset, new_offset, N, M, idx, log2bs, mag_skip, s);
+      default: return launch_mgr<128>(blocks, xyz, offset, new_offset, N, M, idx, log2bs, mag_skip, s);
+    }
+  }
   if (!generic && !(flags & GEOT_FPS_NO_PRUNE)) {
     const int ch = (n_max + 4095) / 4096;
     switch (ch) {
