@@ -19,7 +19,6 @@ GEOT_FPS_CAP512 = 1
 GEOT_FPS_MAGSKIP = 2
 GEOT_FPS_FORCE_GENERIC = 4
 GEOT_FPS_NO_PRUNE = 8
-GEOT_FPS_SYMMETRIC = 16
 
 _vp, _i, _f, _i64, _sz = C.c_void_p, C.c_int, C.c_float, C.c_int64, C.c_size_t
 

@@ -149,314 +149,32 @@ fps_smem_kernel(const float* __restrict__ xyz, const int* __restrict__ offset,
 }
 
 // ---------------------------------------------------------------------------------------------
-// Default path: bucket-pruned FPS, one CTA per cloud, n <= NW*CH*128 points.
+// Default path: bucket-pruned, warp-specialised FPS, one CTA per cloud, n <= 16384 points.
 //
 // The M-1 rounds are sequential, but a new sample only lowers the min-distance of points near it.  The cloud
 // is therefore binned once (12-bit Morton cell of the cloud's bounding cube, counting sort in shared memory)
-// into buckets of 128 spatially close points; bucket (c, w) is owned by warp w as its chunk c, 4 points per
-// lane, min-distances in registers.  Lane c of the warp keeps the bucket's bounding box and its current
-// maximum min-distance.  Per round the warp evaluates, for all its buckets at once (one per lane), the
-// distance from the new sample to the box with the SAME rounded operations as dist2_ref; every rounded
-// step is monotone in |gap|, so  box_distance <= d(sample, p)  holds in fp32 for every p in the bucket and a
-// bucket with box_distance >= bucket_max cannot change (fminf(d, mind) == mind): it is skipped, exactly.
-// On tooth clouds ~7 % of the buckets survive the test, so a round is a few dependent LDS/REDUX steps
-// instead of N distance evaluations.  A warp republishes its candidate (value, reference tie rank, index,
-// coordinates) to a 32-slot exchange only when one of its buckets changed; slots are double-buffered by
-// round parity so one __syncthreads per round suffices.  Internal point order never reaches the result:
-// ties are resolved by the reference's rank of the ORIGINAL index.
+// into buckets of 128 spatially close points, 4 points per lane of the owning warp, min-distances in registers.
+// Each bucket has a bounding box and a cached candidate (its current maximum min-distance and who holds it).
+// Per round the distance from the new sample to every box is evaluated with the SAME rounded operations as
+// dist2_ref; every rounded step is monotone in |gap|, so  box_distance <= d(sample, p)  holds in fp32 for every
+// p in the bucket and a bucket with box_distance >= bucket_max cannot change (fminf(d, mind) == mind): it is
+// skipped, exactly.  On tooth clouds ~7 % of the buckets survive the test, so a round is a few dependent
+// LDS/REDUX steps instead of N distance evaluations.  Internal point order never reaches the result: ties are
+// resolved by the reference's rank of the ORIGINAL index.
+//
+// Warp specialisation: warp 0 is a MANAGER, warps 1..31 are WORKERS (if every warp repeated the box test and
+// the winner reduction the round would be issue-bound on redundant work: measured 0.78 ms vs 0.55 ms).
+//   * the manager keeps the boxes of all buckets in registers (4 per lane), reads the per-bucket candidate keys,
+//     picks the global winner (2 REDUX), runs the exact box test for all buckets against the new sample and
+//     publishes {sample, active flags}; then bar.arrive(A);
+//   * a worker waits on A, updates only its ACTIVE buckets, republishes the candidate of each bucket it touched,
+//     then bar.arrive(B); an idle worker issues ~10 instructions per round;
+//   * the manager waits on B.  Two named barriers in producer/consumer form, nobody waits twice.
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ unsigned morton4(unsigned v) {  // 4 bits -> every third bit
   return (v & 1u) | ((v & 2u) << 2) | ((v & 4u) << 4) | ((v & 8u) << 6);
 }
 
-template <int NW, int CH>
-struct BucketCfg {
-  static constexpr int NT = NW * 32;
-  static constexpr int CAP = NT * CH * 4;
-  static constexpr int PLANE_BYTES = NT * CH * 16;
-  static constexpr int HIST_BYTES = 4096 * 4;
-  static constexpr int COORD_BYTES = 3 * PLANE_BYTES > HIST_BYTES ? 3 * PLANE_BYTES : HIST_BYTES;
-  static constexpr int PERM_BYTES = CAP * 2;
-  static constexpr int SLOT_BYTES = 64 * 8 + 64 * 16;
-  static constexpr int SMEM_BYTES = COORD_BYTES + PERM_BYTES + SLOT_BYTES;
-};
-
-template <int NW, int CH>
-__global__ void __launch_bounds__(NW * 32, 1)
-fps_bucket_kernel(const float* __restrict__ xyz, const int* __restrict__ offset,
-                  const int* __restrict__ new_offset, int N, int M, int* __restrict__ idx, int log2bs,
-                  int mag_skip) {
-  using Cfg = BucketCfg<NW, CH>;
-  constexpr int NT = Cfg::NT;
-  extern __shared__ float4 fps_smem[];
-  unsigned char* smem_raw = reinterpret_cast<unsigned char*>(fps_smem);
-  float4* sx4 = reinterpret_cast<float4*>(smem_raw);
-  float4* sy4 = reinterpret_cast<float4*>(smem_raw + Cfg::PLANE_BYTES);
-  float4* sz4 = reinterpret_cast<float4*>(smem_raw + 2 * Cfg::PLANE_BYTES);
-  int* hist = reinterpret_cast<int*>(smem_raw);  // aliases the coordinate planes; dead before they are written
-  unsigned short* perm = reinterpret_cast<unsigned short*>(smem_raw + Cfg::COORD_BYTES);
-  unsigned long long* skey = reinterpret_cast<unsigned long long*>(smem_raw + Cfg::COORD_BYTES + Cfg::PERM_BYTES);
-  float4* saux = reinterpret_cast<float4*>(skey + 64);
-  __shared__ float s_red[6][32];
-  __shared__ int s_scan[32];
-
-  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-  int64_t start_n, start_m;
-  int n, m, idx_base;
-  fps_segment(offset, new_offset, N, M, blockIdx.x, start_n, n, start_m, m, idx_base);
-  if (m <= 0) return;
-  if (n > Cfg::CAP || n <= 0) return;  // caller understated n_max (the Python layer computes it from offset)
-  const int q_count = (n + (1 << log2bs) - 1) >> log2bs;
-  const float* __restrict__ src = xyz + start_n * 3;
-  const float kInf = __int_as_float(0x7f800000);
-
-  // ---- 1. bounding cube of the cloud -> 16^3 cells --------------------------------------------------------
-  float lo[3] = {kInf, kInf, kInf}, hi[3] = {-kInf, -kInf, -kInf};
-  for (int k = t; k < n; k += NT) {
-#pragma unroll
-    for (int a = 0; a < 3; a++) {
-      const float v = src[(int64_t)k * 3 + a];
-      lo[a] = fminf(lo[a], v); hi[a] = fmaxf(hi[a], v);
-    }
-  }
-#pragma unroll
-  for (int a = 0; a < 3; a++) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      lo[a] = fminf(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], o));
-      hi[a] = fmaxf(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], o));
-    }
-    if (lane == 0) { s_red[a][warp] = lo[a]; s_red[3 + a][warp] = hi[a]; }
-  }
-  for (int i = t; i < 4096; i += NT) hist[i] = 0;
-  __syncthreads();
-  float ext = 0.f;
-#pragma unroll
-  for (int a = 0; a < 3; a++) {
-    float l = lane < NW ? s_red[a][lane] : kInf, h = lane < NW ? s_red[3 + a][lane] : -kInf;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      l = fminf(l, __shfl_xor_sync(0xffffffffu, l, o));
-      h = fmaxf(h, __shfl_xor_sync(0xffffffffu, h, o));
-    }
-    lo[a] = l;
-    ext = fmaxf(ext, h - l);
-  }
-  const float scale = (ext > 0.f && ext < kInf) ? 16.0f / ext : 0.f;
-  auto cell_code = [&](int k) -> unsigned {
-    unsigned code = 0;
-#pragma unroll
-    for (int a = 0; a < 3; a++) {
-      const float f = (src[(int64_t)k * 3 + a] - lo[a]) * scale;
-      const int q = min(max(__float2int_rd(f), 0), 15);  // NaN -> 0: partitioning only, never results
-      code |= morton4((unsigned)q) << a;
-    }
-    return code;
-  };
-
-  // ---- 2. counting sort by cell: histogram, exclusive scan, scatter of the permutation ---------------------
-  for (int k = t; k < n; k += NT) atomicAdd(&hist[cell_code(k)], 1);
-  __syncthreads();
-  {
-    constexpr int PER = 4096 / NT;
-    int v[PER], sum = 0;
-#pragma unroll
-    for (int i = 0; i < PER; i++) { v[i] = hist[t * PER + i]; sum += v[i]; }
-    int inc = sum;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int y = __shfl_up_sync(0xffffffffu, inc, o);
-      if (lane >= o) inc += y;
-    }
-    if (lane == 31) s_scan[warp] = inc;
-    __syncthreads();
-    int wtot = lane < NW ? s_scan[lane] : 0, winc = wtot;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int y = __shfl_up_sync(0xffffffffu, winc, o);
-      if (lane >= o) winc += y;
-    }
-    const int wbase = __shfl_sync(0xffffffffu, winc - wtot, warp);
-    int run = wbase + inc - sum;
-#pragma unroll
-    for (int i = 0; i < PER; i++) { hist[t * PER + i] = run; run += v[i]; }
-  }
-  __syncthreads();
-  for (int k = t; k < n; k += NT) perm[atomicAdd(&hist[cell_code(k)], 1)] = (unsigned short)k;
-  __syncthreads();  // hist is dead from here on; the coordinate planes may overwrite it
-
-  // ---- 3. gather the sorted coordinates, per-bucket boxes ------------------------------------------------
-  // Running min-distance, registers only.  -1 marks "never a candidate": padding beyond n and, for the
-  // pointnet2/_ext variant, points the reference skips (|p|^2 <= 1e-3, _ext_src sampling_gpu.cu:103-104).
-  // Lane c of the warp owns the state of the warp's bucket c: box, current max min-distance (bmax), the
-  // reference tie rank of the point that holds it (brank) and that point's sorted position (bpos).
-  float mind[CH * 4];
-  float blo[3] = {kInf, kInf, kInf}, bhi[3] = {-kInf, -kInf, -kInf}, bmax = -1.0f;
-  unsigned brank = 0xffffffffu;
-  int bpos = 0;
-#pragma unroll
-  for (int c = 0; c < CH; c++) {
-    const int pos0 = (c * NW + warp) * 128 + 4 * lane;
-    float xs[4], ys[4], zs[4];
-    float l3[3] = {kInf, kInf, kInf}, h3[3] = {-kInf, -kInf, -kInf};
-    unsigned r = 0xffffffffu;
-    int rp = 0;
-#pragma unroll
-    for (int e = 0; e < 4; e++) {
-      const int pos = pos0 + e;
-      bool live = pos < n;
-      float x = 0.f, y = 0.f, z = 0.f;
-      int k = 0;
-      if (live) {
-        k = perm[pos];
-        x = src[(int64_t)k * 3 + 0]; y = src[(int64_t)k * 3 + 1]; z = src[(int64_t)k * 3 + 2];
-        if (mag_skip) {
-          const float mag = __fmaf_rn(z, z, __fmaf_rn(x, x, __fmul_rn(y, y)));
-          live = !((double)mag <= 1e-3);
-        }
-      }
-      xs[e] = x; ys[e] = y; zs[e] = z;
-      mind[c * 4 + e] = live ? 1e10f : -1.0f;
-      if (live) {
-        l3[0] = fminf(l3[0], x); h3[0] = fmaxf(h3[0], x);
-        l3[1] = fminf(l3[1], y); h3[1] = fmaxf(h3[1], y);
-        l3[2] = fminf(l3[2], z); h3[2] = fmaxf(h3[2], z);
-        const unsigned rr = tie_rank(k, log2bs, q_count);
-        if (rr < r) { r = rr; rp = pos; }
-      }
-    }
-    sx4[c * NT + t] = make_float4(xs[0], xs[1], xs[2], xs[3]);
-    sy4[c * NT + t] = make_float4(ys[0], ys[1], ys[2], ys[3]);
-    sz4[c * NT + t] = make_float4(zs[0], zs[1], zs[2], zs[3]);
-#pragma unroll
-    for (int a = 0; a < 3; a++) {
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        l3[a] = fminf(l3[a], __shfl_xor_sync(0xffffffffu, l3[a], o));
-        h3[a] = fmaxf(h3[a], __shfl_xor_sync(0xffffffffu, h3[a], o));
-      }
-    }
-    // all live points start at 1e10: the bucket's first candidate is its live point of least rank
-    const unsigned wr = __reduce_min_sync(0xffffffffu, r);
-    const unsigned wp = __reduce_max_sync(0xffffffffu, (r == wr) ? (unsigned)rp : 0u);
-    if (lane == c) {
-#pragma unroll
-      for (int a = 0; a < 3; a++) { blo[a] = l3[a]; bhi[a] = h3[a]; }
-      bmax = (wr != 0xffffffffu) ? 1e10f : -1.0f;
-      brank = wr;
-      bpos = (int)wp;
-    }
-  }
-  if (t < 64) {
-    skey[t] = 0x8000000000000000ull;  // below every real key (signed compare of the high word)
-    saux[t] = make_float4(0.f, 0.f, 0.f, 0.f);
-  }
-  float x1 = src[0], y1 = src[1], z1 = src[2];  // first sample = segment start (sampling_gpu.cu:120-122)
-  const float x0 = x1, y0 = y1, z0 = z1;
-  if (t == 0) idx[start_m] = idx_base;
-  __syncthreads();
-
-  // explicit 32-bit shared addresses: keeps the shared-window base out of the round loop
-  unsigned a_base;  // opaque to the optimiser, or it re-derives the window base (S2UR SR_CgaCtaId) inside the loop
-  asm volatile("mov.u32 %0, %1;" : "=r"(a_base) : "r"(smem_u32(smem_raw)));
-  const unsigned a_fx = a_base, a_fy = a_base + Cfg::PLANE_BYTES, a_fz = a_base + 2 * Cfg::PLANE_BYTES;
-  const unsigned a_sx = a_fx + 16u * t, a_sy = a_fy + 16u * t, a_sz = a_fz + 16u * t;
-  const unsigned a_perm = a_base + Cfg::COORD_BYTES;
-  const unsigned a_perm_t = a_perm + 2u * (unsigned)(warp * 128 + 4 * lane);
-  const unsigned a_key = a_perm + Cfg::PERM_BYTES, a_aux = a_key + 64 * 8;
-  const unsigned rank_mask = (1u << log2bs) - 1u;
-  const int brev_shift = 32 - log2bs;
-
-  // ---- 4. the rounds ------------------------------------------------------------------------------------------
-  bool dirty = false;
-  for (int j = 1; j < m; j++) {
-    const unsigned buf = (unsigned)(j & 1) * 32u;
-    // distance from the sample to this lane's bucket box, rounded exactly like dist2_ref
-    const float gx = fmaxf(fmaxf(__fsub_rn(blo[0], x1), __fsub_rn(x1, bhi[0])), 0.f);
-    const float gy = fmaxf(fmaxf(__fsub_rn(blo[1], y1), __fsub_rn(y1, bhi[1])), 0.f);
-    const float gz = fmaxf(fmaxf(__fsub_rn(blo[2], z1), __fsub_rn(z1, bhi[2])), 0.f);
-    const float lb = __fmaf_rn(gz, gz, __fmaf_rn(gx, gx, __fmul_rn(gy, gy)));
-    const unsigned act = __ballot_sync(0xffffffffu, lb < bmax);
-    if (act) {
-#pragma unroll
-      for (int c = 0; c < CH; c++) {
-        if (act & (1u << c)) {
-          const float4 X = lds128(a_sx + c * NT * 16), Y = lds128(a_sy + c * NT * 16), Z = lds128(a_sz + c * NT * 16);
-          const uint2 kk = lds64(a_perm_t + 2u * (unsigned)(c * NW * 128));  // original indices of the 4 points
-          const float xs[4] = {X.x, X.y, X.z, X.w}, ys[4] = {Y.x, Y.y, Y.z, Y.w}, zs[4] = {Z.x, Z.y, Z.z, Z.w};
-          float cm = -1.0f;
-#pragma unroll
-          for (int e = 0; e < 4; e++) {
-            const float d = dist2_ref(xs[e], ys[e], zs[e], x1, y1, z1);
-            const float v = fminf(d, mind[c * 4 + e]);
-            mind[c * 4 + e] = v;
-            cm = fmaxf(cm, v);
-          }
-          // candidates are >= 0 or exactly -1, so the int view of the float bits is order preserving
-          const int wm = __reduce_max_sync(0xffffffffu, __float_as_int(cm));
-          // the bucket's candidate: among the points that hold the max, the reference's tie order
-          const unsigned ks[4] = {kk.x & 0xffffu, kk.x >> 16, kk.y & 0xffffu, kk.y >> 16};
-          unsigned r = 0xffffffffu;
-          int rp = 0;
-#pragma unroll
-          for (int e = 0; e < 4; e++) {
-            const unsigned br = log2bs ? (__brev(ks[e] & rank_mask) >> brev_shift) : 0u;
-            unsigned rr = br * (unsigned)q_count + (ks[e] >> log2bs);
-            rr = (__float_as_int(mind[c * 4 + e]) == wm) ? rr : 0xffffffffu;
-            if (rr < r) { r = rr; rp = e; }
-          }
-          const unsigned wr = __reduce_min_sync(0xffffffffu, r);
-          const unsigned wp = __reduce_max_sync(0xffffffffu, (r == wr) ? (unsigned)(4 * lane + rp) : 0u);
-          if (lane == c) { bmax = __int_as_float(wm); brank = wr; bpos = (c * NW + warp) * 128 + (int)wp; }
-        }
-      }
-      // the warp's candidate = best of its buckets; exactly one lane publishes it
-      const int wmax = __reduce_max_sync(0xffffffffu, __float_as_int(bmax));
-      const unsigned r = (__float_as_int(bmax) == wmax) ? brank : 0xffffffffu;
-      const unsigned wr = __reduce_min_sync(0xffffffffu, r);
-      if (r == wr && wmax >= 0) {
-        const unsigned k = lds_u16(a_perm + 2u * (unsigned)bpos);
-        const float px = lds32f(a_fx + 4u * (unsigned)bpos), py = lds32f(a_fy + 4u * (unsigned)bpos), pz = lds32f(a_fz + 4u * (unsigned)bpos);
-        sts64(a_key + 8u * (buf + warp), ((0x07ffffffu - wr) << 5) | (unsigned)warp, (unsigned)wmax);
-        sts128(a_aux + 16u * (buf + warp), make_float4(__uint_as_float(k), px, py, pz));
-      }
-      dirty = true;
-    } else if (dirty) {
-      if (lane == 0) {
-        const uint2 kv = lds64(a_key + 8u * ((buf ^ 32u) + warp));
-        const float4 av = lds128(a_aux + 16u * ((buf ^ 32u) + warp));
-        sts64(a_key + 8u * (buf + warp), kv.x, kv.y);
-        sts128(a_aux + 16u * (buf + warp), av);
-      }
-      dirty = false;
-    }
-    __syncthreads();
-    const uint2 key = lds64(a_key + 8u * (buf + lane));  // .x = (~rank << 5 | warp), .y = value bits
-    const int ghi = __reduce_max_sync(0xffffffffu, (int)key.y);
-    const unsigned glo = __reduce_max_sync(0xffffffffu, ((int)key.y == ghi) ? key.x : 0u);
-    int old = 0;
-    x1 = x0; y1 = y0; z1 = z0;  // no candidate at all (every point skipped): the reference keeps index 0
-    if (ghi >= 0) {
-      const float4 a = lds128(a_aux + 16u * (buf + (glo & 31u)));
-      old = __float_as_int(a.x); x1 = a.y; y1 = a.z; z1 = a.w;
-    }
-    if (t == 0) idx[start_m + j] = idx_base + old;
-  }
-}
-
-// ---------------------------------------------------------------------------------------------
-// Warp-specialised variant of the bucket-pruned kernel (the default): warp 0 is a MANAGER, warps 1..31 are
-// WORKERS.  In fps_bucket_kernel every one of the 32 warps repeats the box test and the 32-slot reduction each
-// round, so the round is issue-bound on redundant work (8 warps per scheduler x ~50 instructions).  Here
-//   * the manager keeps the boxes of all buckets in registers (4 per lane), reads the per-bucket candidate keys,
-//     picks the global winner (2 REDUX), runs the exact box test for all buckets against the new sample and
-//     publishes {sample, active flags}; then bar.arrive(A);
-//   * a worker waits on A, updates only its ACTIVE buckets (min-distances of its points live in its registers),
-//     republishes the candidate of each bucket it touched, then bar.arrive(B); an idle worker issues ~10
-//     instructions per round;
-//   * the manager waits on B.  Two named barriers in producer/consumer form, nobody waits twice.
-// Same exactness argument, same tie order as above.
-// ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ void bar_sync_named(int id) { asm volatile("bar.sync %0, 1024;" ::"r"(id) : "memory"); }
 __device__ __forceinline__ void bar_arrive_named(int id) { asm volatile("bar.arrive %0, 1024;" ::"r"(id) : "memory"); }
 __device__ __forceinline__ unsigned lds_u8(unsigned a) {
@@ -465,6 +183,7 @@ __device__ __forceinline__ unsigned lds_u8(unsigned a) {
   return v;
 }
 __device__ __forceinline__ void sts_u8(unsigned a, unsigned v) { asm volatile("st.shared.u8 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+__device__ __forceinline__ void sts_u16(unsigned a, unsigned v) { asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "h"((unsigned short)v) : "memory"); }
 __device__ __forceinline__ void sts32(unsigned a, unsigned v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
 
 template <int NBK>
@@ -474,11 +193,9 @@ struct MgrCfg {
   static constexpr int BPL = NBK / 32;               // buckets per manager lane
   static constexpr int CAP = NBK * 128;
   static constexpr int PLANE_BYTES = NBK * 512;
-  static constexpr int SORT_BYTES = 4096 * 4 + 2 * CAP + 2 * CAP;  // hist | perm | cell codes
-  static constexpr int R0_BYTES = 3 * PLANE_BYTES > SORT_BYTES ? 3 * PLANE_BYTES : SORT_BYTES;
-  static constexpr int KEY_OFF = R0_BYTES;
-  static constexpr int AUX_OFF = KEY_OFF + NBK * 8;
-  static constexpr int BOX_OFF = AUX_OFF + NBK * 16;
+  static constexpr int HIST_OFF = 3 * PLANE_BYTES;  // 4096 cell counters (setup only)
+  static constexpr int KEY_OFF = HIST_OFF + 4096 * 4;
+  static constexpr int BOX_OFF = KEY_OFF + NBK * 8;
   static constexpr int ACT_OFF = BOX_OFF + NBK * 24;
   static constexpr int CTRL_OFF = ACT_OFF + 256;  // 8 flag bytes per worker
   static constexpr int SMEM_BYTES = CTRL_OFF + 16;
@@ -493,9 +210,7 @@ fps_mgr_kernel(const float* __restrict__ xyz, const int* __restrict__ offset,
   constexpr int NT = Cfg::NT, NWK = Cfg::NWK, CHW = Cfg::CHW, BPL = Cfg::BPL;
   extern __shared__ float4 fps_smem[];
   unsigned char* smem_raw = reinterpret_cast<unsigned char*>(fps_smem);
-  int* hist = reinterpret_cast<int*>(smem_raw);
-  unsigned short* perm = reinterpret_cast<unsigned short*>(smem_raw + 4096 * 4);
-  unsigned short* codes = perm + Cfg::CAP;
+  int* hist = reinterpret_cast<int*>(smem_raw + Cfg::HIST_OFF);
   __shared__ float s_red[6][32];
   __shared__ int s_scan[32];
 
@@ -509,14 +224,19 @@ fps_mgr_kernel(const float* __restrict__ xyz, const int* __restrict__ offset,
   const float* __restrict__ src = xyz + start_n * 3;
   const float kInf = __int_as_float(0x7f800000);
 
-  // ---- 1. bounding cube of the cloud -> 16^3 cells --------------------------------------------------------
+  // ---- 1. the cloud into registers (one coalesced pass over global memory), bounding cube -> 16^3 cells ----------
+  constexpr int PPT = Cfg::CAP / NT;  // points per thread during setup
+  float px[PPT], py[PPT], pz[PPT];
   float lo[3] = {kInf, kInf, kInf}, hi[3] = {-kInf, -kInf, -kInf};
-#pragma unroll 4
-  for (int k = t; k < n; k += NT) {
 #pragma unroll
-    for (int a = 0; a < 3; a++) {
-      const float v = src[(int64_t)k * 3 + a];
-      lo[a] = fminf(lo[a], v); hi[a] = fmaxf(hi[a], v);
+  for (int i = 0; i < PPT; i++) {
+    const int k = t + i * NT;
+    px[i] = py[i] = pz[i] = 0.f;
+    if (k < n) {
+      px[i] = src[(int64_t)k * 3 + 0]; py[i] = src[(int64_t)k * 3 + 1]; pz[i] = src[(int64_t)k * 3 + 2];
+      lo[0] = fminf(lo[0], px[i]); hi[0] = fmaxf(hi[0], px[i]);
+      lo[1] = fminf(lo[1], py[i]); hi[1] = fmaxf(hi[1], py[i]);
+      lo[2] = fminf(lo[2], pz[i]); hi[2] = fmaxf(hi[2], pz[i]);
     }
   }
 #pragma unroll
@@ -543,20 +263,19 @@ fps_mgr_kernel(const float* __restrict__ xyz, const int* __restrict__ offset,
     ext = fmaxf(ext, h - l);
   }
   const float scale = (ext > 0.f && ext < kInf) ? 16.0f / ext : 0.f;
+  auto cell_code = [&](float x, float y, float z) -> unsigned {  // NaN -> cell 0: partitioning only, never results
+    const int qx = min(max(__float2int_rd((x - lo[0]) * scale), 0), 15);
+    const int qy = min(max(__float2int_rd((y - lo[1]) * scale), 0), 15);
+    const int qz = min(max(__float2int_rd((z - lo[2]) * scale), 0), 15);
+    return morton4((unsigned)qx) | (morton4((unsigned)qy) << 1) | (morton4((unsigned)qz) << 2);
+  };
 
-  // ---- 2. counting sort by cell: histogram (codes cached), exclusive scan, scatter of the permutation -----------
-#pragma unroll 4
-  for (int k = t; k < n; k += NT) {
-    unsigned code = 0;
+  // ---- 2. counting sort by cell: histogram, exclusive scan, then every thread scatters ITS points (still in
+  //         registers) straight to their sorted slots: x and y planes now, z after the ranks have been collected
+  //         (the rank table borrows the z plane) -------------------------------------------------------------------
 #pragma unroll
-    for (int a = 0; a < 3; a++) {
-      const float f = (src[(int64_t)k * 3 + a] - lo[a]) * scale;
-      const int q = min(max(__float2int_rd(f), 0), 15);  // NaN -> 0: partitioning only, never results
-      code |= morton4((unsigned)q) << a;
-    }
-    codes[k] = (unsigned short)code;
-    atomicAdd(&hist[code], 1);
-  }
+  for (int i = 0; i < PPT; i++)
+    if (t + i * NT < n) atomicAdd(&hist[cell_code(px[i], py[i], pz[i])], 1);
   __syncthreads();
   {
     constexpr int PER = 4096 / NT;
@@ -583,31 +302,54 @@ fps_mgr_kernel(const float* __restrict__ xyz, const int* __restrict__ offset,
     for (int i = 0; i < PER; i++) { hist[t * PER + i] = run; run += v[i]; }
   }
   __syncthreads();
-  for (int k = t; k < n; k += NT) perm[atomicAdd(&hist[codes[k]], 1)] = (unsigned short)k;
-  __syncthreads();
 
   unsigned a_base;  // opaque to the optimiser, or it re-derives the window base (S2UR SR_CgaCtaId) inside the loop
   asm volatile("mov.u32 %0, %1;" : "=r"(a_base) : "r"(smem_u32(smem_raw)));
-  const unsigned a_key = a_base + Cfg::KEY_OFF, a_aux = a_base + Cfg::AUX_OFF, a_box = a_base + Cfg::BOX_OFF;
+  const unsigned a_key = a_base + Cfg::KEY_OFF, a_box = a_base + Cfg::BOX_OFF;
   const unsigned a_act = a_base + Cfg::ACT_OFF, a_ctrl = a_base + Cfg::CTRL_OFF;
+  const unsigned a_rank = a_base + 2 * Cfg::PLANE_BYTES;  // u16 rank table, lives in the z plane until z is scattered
   const int wk = warp - 1;  // worker id (warp 0 = manager)
   const int rounds = m - 1;
   const float x0 = src[0], y0 = src[1], z0 = src[2];  // first sample = segment start (sampling_gpu.cu:120-122)
   if (t == 0) idx[start_m] = idx_base;
 
-  // ---- 3. workers take their buckets: original indices into registers, then coordinates into the planes --------
+  unsigned short spos[PPT];
+#pragma unroll
+  for (int i = 0; i < PPT; i++) {
+    const int k = t + i * NT;
+    spos[i] = 0;
+    if (k < n) {
+      const int pos = atomicAdd(&hist[cell_code(px[i], py[i], pz[i])], 1);
+      spos[i] = (unsigned short)pos;
+      sts32(a_base + 4u * pos, __float_as_uint(px[i]));
+      sts32(a_base + Cfg::PLANE_BYTES + 4u * pos, __float_as_uint(py[i]));
+      sts_u16(a_rank + 2u * pos, tie_rank(k, log2bs, q_count));  // n <= 16384: rank < 2^15
+    }
+  }
+  for (int pos = n + t; pos < Cfg::CAP; pos += NT) {  // padding slots
+    sts32(a_base + 4u * pos, 0u);
+    sts32(a_base + Cfg::PLANE_BYTES + 4u * pos, 0u);
+  }
+  __syncthreads();
+
+  // ---- 3. workers take their buckets -----------------------------------------------------------------------------
   // Running min-distance, registers only.  -1 marks "never a candidate": padding beyond n and, for the
   // pointnet2/_ext variant, points the reference skips (|p|^2 <= 1e-3, _ext_src sampling_gpu.cu:103-104).
   float mind[CHW * 4];
-  unsigned kreg[CHW * 2];  // per bucket: 4 original indices (setup), then their 4 reference tie ranks, packed u16
+  unsigned kreg[CHW * 2];  // per bucket: the reference tie ranks of its 4 points, packed u16
 #pragma unroll
   for (int c = 0; c < CHW; c++) {
     const int b = c * NWK + wk;
     uint2 kk = make_uint2(0u, 0u);
-    if (wk >= 0 && b < NBK) kk = lds64(smem_u32(perm) + 2u * (unsigned)(b * 128 + 4 * lane));
+    if (wk >= 0 && b < NBK) kk = lds64(a_rank + 2u * (unsigned)(b * 128 + 4 * lane));
     kreg[2 * c] = kk.x; kreg[2 * c + 1] = kk.y;
   }
-  __syncthreads();  // hist / perm / codes are dead from here on; the coordinate planes overwrite them
+  __syncthreads();  // the rank table is in registers: the z plane may be written
+#pragma unroll
+  for (int i = 0; i < PPT; i++)
+    if (t + i * NT < n) sts32(a_base + 2 * Cfg::PLANE_BYTES + 4u * spos[i], __float_as_uint(pz[i]));
+  for (int pos = n + t; pos < Cfg::CAP; pos += NT) sts32(a_base + 2 * Cfg::PLANE_BYTES + 4u * pos, 0u);
+  __syncthreads();
 #pragma unroll
   for (int c = 0; c < CHW; c++) {
     const int b = c * NWK + wk;
@@ -615,38 +357,27 @@ fps_mgr_kernel(const float* __restrict__ xyz, const int* __restrict__ offset,
     for (int e = 0; e < 4; e++) mind[c * 4 + e] = -1.0f;
     if (wk >= 0 && b < NBK) {
       const int pos0 = b * 128 + 4 * lane;
-      const unsigned ks[4] = {kreg[2 * c] & 0xffffu, kreg[2 * c] >> 16, kreg[2 * c + 1] & 0xffffu, kreg[2 * c + 1] >> 16};
-      float xs[4], ys[4], zs[4];
+      const unsigned a_pt = a_base + 16u * (unsigned)(b * 32 + lane);
+      const float4 X = lds128(a_pt), Y = lds128(a_pt + Cfg::PLANE_BYTES), Z = lds128(a_pt + 2 * Cfg::PLANE_BYTES);
+      const float xs[4] = {X.x, X.y, X.z, X.w}, ys[4] = {Y.x, Y.y, Y.z, Y.w}, zs[4] = {Z.x, Z.y, Z.z, Z.w};
+      const unsigned rk[4] = {kreg[2 * c] & 0xffffu, kreg[2 * c] >> 16, kreg[2 * c + 1] & 0xffffu, kreg[2 * c + 1] >> 16};
       float l3[3] = {kInf, kInf, kInf}, h3[3] = {-kInf, -kInf, -kInf};
       unsigned r = 0xffffffffu;
 #pragma unroll
       for (int e = 0; e < 4; e++) {
         bool live = pos0 + e < n;
-        float x = 0.f, y = 0.f, z = 0.f;
-        if (live) {
-          const int64_t k = ks[e];
-          x = src[k * 3 + 0]; y = src[k * 3 + 1]; z = src[k * 3 + 2];
-          if (mag_skip) {
-            const float mag = __fmaf_rn(z, z, __fmaf_rn(x, x, __fmul_rn(y, y)));
-            live = !((double)mag <= 1e-3);
-          }
+        if (live && mag_skip) {
+          const float mag = __fmaf_rn(zs[e], zs[e], __fmaf_rn(xs[e], xs[e], __fmul_rn(ys[e], ys[e])));
+          live = !((double)mag <= 1e-3);
         }
-        xs[e] = x; ys[e] = y; zs[e] = z;
         if (live) {
           mind[c * 4 + e] = 1e10f;
-          l3[0] = fminf(l3[0], x); h3[0] = fmaxf(h3[0], x);
-          l3[1] = fminf(l3[1], y); h3[1] = fmaxf(h3[1], y);
-          l3[2] = fminf(l3[2], z); h3[2] = fmaxf(h3[2], z);
-          r = min(r, (tie_rank((int)ks[e], log2bs, q_count) << 2) | (unsigned)e);
+          l3[0] = fminf(l3[0], xs[e]); h3[0] = fmaxf(h3[0], xs[e]);
+          l3[1] = fminf(l3[1], ys[e]); h3[1] = fmaxf(h3[1], ys[e]);
+          l3[2] = fminf(l3[2], zs[e]); h3[2] = fmaxf(h3[2], zs[e]);
+          r = min(r, (rk[e] << 2) | (unsigned)e);
         }
       }
-      // from here on only the ranks are needed (n <= 16384: rank < 2^15); the manager un-ranks the winner
-      kreg[2 * c] = tie_rank((int)ks[0], log2bs, q_count) | (tie_rank((int)ks[1], log2bs, q_count) << 16);
-      kreg[2 * c + 1] = tie_rank((int)ks[2], log2bs, q_count) | (tie_rank((int)ks[3], log2bs, q_count) << 16);
-      const unsigned a_pt = a_base + 16u * (unsigned)(b * 32 + lane);
-      sts128(a_pt, make_float4(xs[0], xs[1], xs[2], xs[3]));
-      sts128(a_pt + Cfg::PLANE_BYTES, make_float4(ys[0], ys[1], ys[2], ys[3]));
-      sts128(a_pt + 2 * Cfg::PLANE_BYTES, make_float4(zs[0], zs[1], zs[2], zs[3]));
 #pragma unroll
       for (int a = 0; a < 3; a++) {
 #pragma unroll
@@ -664,12 +395,7 @@ fps_mgr_kernel(const float* __restrict__ xyz, const int* __restrict__ offset,
       if (wr == 0xffffffffu) {
         if (lane == 0) sts64(a_key + 8u * b, 0u, (unsigned)__float_as_int(-1.0f));
       } else if (r == wr) {
-        const int e = (int)(wr & 3u);
-        const float px = e == 0 ? xs[0] : e == 1 ? xs[1] : e == 2 ? xs[2] : xs[3];
-        const float py = e == 0 ? ys[0] : e == 1 ? ys[1] : e == 2 ? ys[2] : ys[3];
-        const float pz = e == 0 ? zs[0] : e == 1 ? zs[1] : e == 2 ? zs[2] : zs[3];
-        sts64(a_key + 8u * b, ((0x00ffffffu - (wr >> 2)) << 7) | (unsigned)b, (unsigned)__float_as_int(1e10f));
-        sts128(a_aux + 16u * b, make_float4(0.f, px, py, pz));
+        sts64(a_key + 8u * b, ((0x7fffu - (wr >> 2)) << 14) | (unsigned)(pos0 + (int)(wr & 3u)), (unsigned)__float_as_int(1e10f));
       }
     }
   }
@@ -691,6 +417,7 @@ fps_mgr_kernel(const float* __restrict__ xyz, const int* __restrict__ offset,
     int* out = idx + start_m;
     // publish {sample, per-worker active flags}: exact box test of every bucket against the sample, rounded like
     // dist2_ref; a bucket's current maximum is the value word of its candidate key
+    // key = {lo: (~rank << 14) | sorted position, hi: value bits}
     auto publish = [&](const float4& smp, const uint2 (&key)[BPL]) {
 #pragma unroll
       for (int i = 0; i < BPL; i++) {
@@ -728,10 +455,13 @@ fps_mgr_kernel(const float* __restrict__ xyz, const int* __restrict__ offset,
       pick(key, ghi, glo);
       // no candidate at all (every point skipped): the reference keeps index 0
       float4 smp = make_float4(0.f, x0, y0, z0);
-      if (ghi >= 0) smp = lds128(a_aux + 16u * (glo & 127u));
+      if (ghi >= 0) {
+        const unsigned a_w = a_base + 4u * (glo & 0x3fffu);  // the winner's coordinates, by sorted position
+        smp.y = lds32f(a_w); smp.z = lds32f(a_w + Cfg::PLANE_BYTES); smp.w = lds32f(a_w + 2 * Cfg::PLANE_BYTES);
+      }
       if (j < rounds) publish(smp, key);
       // off the critical path: un-rank the winner (rank 0 <-> index 0)
-      if (lane == 0) out[j] = idx_base + (ghi >= 0 ? tie_unrank(0x00ffffffu - (glo >> 7), log2bs, q_count) : 0);
+      if (lane == 0) out[j] = idx_base + (ghi >= 0 ? tie_unrank(0x7fffu - (glo >> 14), log2bs, q_count) : 0);
     }
   } else {
     // =========================== workers ===========================
@@ -767,14 +497,8 @@ fps_mgr_kernel(const float* __restrict__ xyz, const int* __restrict__ offset,
 #pragma unroll
             for (int e = 0; e < 4; e++) r = min(r, (__float_as_int(mind[c * 4 + e]) == wm) ? rk[e] : 0xffffffffu);
             const unsigned wr = __reduce_min_sync(0xffffffffu, r);
-            if (r == wr) {  // exactly one lane: ranks are unique (an active bucket has a live point, so wm >= 0)
-              const int e = (int)(wr & 3u);
-              const float px = e == 0 ? xs[0] : e == 1 ? xs[1] : e == 2 ? xs[2] : xs[3];
-              const float py = e == 0 ? ys[0] : e == 1 ? ys[1] : e == 2 ? ys[2] : ys[3];
-              const float pz = e == 0 ? zs[0] : e == 1 ? zs[1] : e == 2 ? zs[2] : zs[3];
-              sts64(a_key + 8u * b, ((0x00ffffffu - (wr >> 2)) << 7) | (unsigned)b, (unsigned)wm);
-              sts128(a_aux + 16u * b, make_float4(0.f, px, py, pz));
-            }
+            // exactly one lane publishes: ranks are unique (an active bucket has a live point, so wm >= 0)
+            if (r == wr) sts64(a_key + 8u * b, ((0x7fffu - (wr >> 2)) << 14) | (unsigned)(b * 128 + 4 * lane) | (wr & 3u), (unsigned)wm);
           }
         }
       }
@@ -867,21 +591,6 @@ static int launch_smem(int blocks, const float* xyz, const int* offset, const in
   return check_launch("fps_smem_kernel");
 }
 
-template <int NW, int CH>
-static int launch_bucket(int blocks, const float* xyz, const int* offset, const int* new_offset, int N,
-                         int M, int* idx, int log2bs, int mag_skip, cudaStream_t s) {
-  constexpr int smem = BucketCfg<NW, CH>::SMEM_BYTES;
-  static bool configured = false;  // per instantiation
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(fps_bucket_kernel<NW, CH>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) { set_error("fps: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
-    configured = true;
-  }
-  fps_bucket_kernel<NW, CH><<<blocks, NW * 32, smem, s>>>(xyz, offset, new_offset, N, M, idx, log2bs, mag_skip);
-  count_launch(1);
-  return check_launch("fps_bucket_kernel");
-}
-
 template <int NBK>
 static int launch_mgr(int blocks, const float* xyz, const int* offset, const int* new_offset, int N,
                       int M, int* idx, int log2bs, int mag_skip, cudaStream_t s) {
@@ -904,22 +613,13 @@ static int fps_dispatch(int blocks, int n_max, const float* xyz, const int* offs
   const int log2bs = ilog2(ref_opt_n_threads(n_max, cap));
   const int mag_skip = (flags & GEOT_FPS_MAGSKIP) ? 1 : 0;
   const bool generic = (flags & GEOT_FPS_FORCE_GENERIC) || weights != nullptr || n_max > 4 * 4096;
-  if (!generic && !(flags & (GEOT_FPS_NO_PRUNE | GEOT_FPS_SYMMETRIC))) {
+  if (!generic && !(flags & GEOT_FPS_NO_PRUNE)) {
     const int ch = (n_max + 4095) / 4096;
     switch (ch) {
       case 1: return launch_mgr<32>(blocks, xyz, offset, new_offset, N, M, idx, log2bs, mag_skip, s);
       case 2: return launch_mgr<64>(blocks, xyz, offset, new_offset, N, M, idx, log2bs, mag_skip, s);
       case 3: return launch_mgr<96>(blocks, xyz, offset, new_offset, N, M, idx, log2bs, mag_skip, s);
       default: return launch_mgr<128>(blocks, xyz, offset, new_offset, N, M, idx, log2bs, mag_skip, s);
-    }
-  }
-  if (!generic && !(flags & GEOT_FPS_NO_PRUNE)) {
-    const int ch = (n_max + 4095) / 4096;
-    switch (ch) {
-      case 1: return launch_bucket<32, 1>(blocks, xyz, offset, new_offset, N, M, idx, log2bs, mag_skip, s);
-      case 2: return launch_bucket<32, 2>(blocks, xyz, offset, new_offset, N, M, idx, log2bs, mag_skip, s);
-      case 3: return launch_bucket<32, 3>(blocks, xyz, offset, new_offset, N, M, idx, log2bs, mag_skip, s);
-      default: return launch_bucket<32, 4>(blocks, xyz, offset, new_offset, N, M, idx, log2bs, mag_skip, s);
     }
   }
   if (!generic) {

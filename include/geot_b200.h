@@ -58,7 +58,6 @@ uint64_t geot_launch_count(void);
 #define GEOT_FPS_CAP512 1
 #define GEOT_FPS_MAGSKIP 2
 #define GEOT_FPS_FORCE_GENERIC 4 /* testing: take the large-N fallback regardless of N */
-#define GEOT_FPS_SYMMETRIC 16    /* testing / A-B timing: the pruned kernel without warp specialisation */
 #define GEOT_FPS_NO_PRUNE 8      /* testing / A-B timing: the un-pruned one-CTA-per-cloud kernel (every round visits every point) */
 
 /* replaces pointnet2_batch_cuda.furthest_point_sampling_wrapper(B,N,M,xyz,temp,idx) and

@@ -22,6 +22,5 @@ for (B, N, M) in [(64, 16384, 1024), (16, 16384, 4096), (6, 16000, 8192), (64, 4
     ok = bool((a == b).all())
     ta = t(lambda: F.furthest_point_sampling(xyz, M))
     tb = t(lambda: F.furthest_point_sampling(xyz, M, flags=_lib.GEOT_FPS_NO_PRUNE))
-    tc = t(lambda: F.furthest_point_sampling(xyz, M, flags=_lib.GEOT_FPS_SYMMETRIC))
     t2 = t(lambda: F.furthest_point_sampling(xyz, 2))
-    print(f"FPS B={B} N={N} M={M}: mgr {ta:.3f} ms  symmetric {tc:.3f}  unpruned {tb:.3f} ms  speedup {tb/ta:.2f}x  equal={ok}  ({(ta-t2)*1e3/(M-2):.3f} us/round, setup(M=2) {t2*1e3:.1f} us)", flush=True)
+    print(f"FPS B={B} N={N} M={M}: mgr {ta:.3f} ms  unpruned {tb:.3f} ms  speedup {tb/ta:.2f}x  equal={ok}  ({(ta-t2)*1e3/(M-2):.3f} us/round, setup(M=2) {t2*1e3:.1f} us)", flush=True)
