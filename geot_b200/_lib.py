@@ -19,6 +19,7 @@ GEOT_FPS_CAP512 = 1
 GEOT_FPS_MAGSKIP = 2
 GEOT_FPS_FORCE_GENERIC = 4
 GEOT_FPS_NO_PRUNE = 8
+GEOT_BQ_FORCE_GRID = 1
 
 _vp, _i, _f, _i64, _sz = C.c_void_p, C.c_int, C.c_float, C.c_int64, C.c_size_t
 
@@ -29,7 +30,8 @@ _SIGNATURES = {
     "geot_launch_count": [],
     "geot_furthest_point_sampling": [_i, _i, _i, _vp, _vp, _vp, _i, _vp],
     "geot_furthestsampling": [_i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
-    "geot_ball_query": [_i, _i, _i, _f, _i, _vp, _vp, _vp, _vp],
+    "geot_ball_query_workspace_bytes": [_i, _i],
+    "geot_ball_query": [_i, _i, _i, _f, _i, _vp, _vp, _vp, _vp, _sz, _i, _vp],
     "geot_ballquery_offset": [_i, _i, _f, _i, _vp, _vp, _vp, _vp, _vp, _vp],
     "geot_knnquery_workspace_bytes": [_i],
     "geot_knnquery": [_i, _i, _i, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _sz, _vp],
@@ -68,6 +70,7 @@ _RESTYPES = {
     "geot_last_error": C.c_char_p,
     "geot_launch_count": C.c_uint64,
     "geot_scatter_plan_bytes": _sz,
+    "geot_ball_query_workspace_bytes": _sz,
     "geot_knnquery_workspace_bytes": _sz,
     "geot_sigt_workspace_bytes": _sz,
     "geot_sigt_backward_workspace_bytes": _sz,

@@ -16,12 +16,29 @@
 // shared memory (cp.async double-buffered tiles, raw AoS: the stride-3 word reads are conflict free),
 // so a cloud tile is fetched from L2 once per 32 queries instead of once per query; the CTA leaves as
 // soon as all of its queries are full.
+//
+// Grid path (used when the caller passes a workspace and the ball is small against the cloud).  The scan
+// above visits points in index order until nsample hits are found: ~N*nsample/H points for H hits in the
+// ball (26-40 % of the cloud at the bench shape).  bq_build_kernel bins each cloud once into a uniform grid
+// of cell size >= 1.001*radius (counting sort in shared memory -> sorted {x,y,z,index} + cell offsets in the
+// workspace); bq_grid_kernel then tests only the 27 cells around the query (9 contiguous runs, ~3 H
+// candidates) with the same dist2_ref, sets one bit per hit in a per-warp bitmap over the point indices, and
+// reads the first nsample set bits back in ascending index order - the reference's "first nsample by index"
+// rule, independent of the order candidates were met.  The 0.1 % cell margin keeps the 27-cell cover
+// conservative under fp32 rounding of the cell arithmetic.  bq_build_kernel decides per cloud which path is
+// cheaper (dense balls finish the index-order scan after a few dozen points) and each kernel skips the
+// clouds of the other.
 #include "common.cuh"
 
 namespace geot {
 
 void count_launch(int n);
 
+struct BqHeader {  // grid path (below): per-cloud header at the start of the cloud's workspace slice
+  int use_grid;
+  int dx, dy, dz;
+  float lox, loy, loz, inv;
+};
 constexpr int kBqTile = 1024;  // points per shared-memory tile (12 KB), two buffers
 
 __device__ __forceinline__ void cp_async4(void* smem, const void* gmem) {
@@ -74,10 +91,12 @@ __device__ __forceinline__ bool ball_scan_tile(const float* __restrict__ s, int 
 // Batched: grid (ceil(M/32), B), 1024 threads; warp w of CTA x handles query 32x + w of cloud y.
 __global__ void __launch_bounds__(1024, 2)
 ball_query_shared_kernel(int N, int M, float radius, int nsample, const float* __restrict__ new_xyz,
-                         const float* __restrict__ xyz, int* __restrict__ idx, int aligned16) {
+                         const float* __restrict__ xyz, int* __restrict__ idx, int aligned16,
+                         const unsigned char* __restrict__ ws, size_t ws_stride) {
   __shared__ __align__(16) float tile[2][kBqTile * 3];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int b = blockIdx.y;
+  if (ws != nullptr && reinterpret_cast<const BqHeader*>(ws + (size_t)b * ws_stride)->use_grid) return;
   const int q = blockIdx.x * 32 + warp;
   const float r2 = __fmul_rn(radius, radius);
   const float* __restrict__ cloud = xyz + (int64_t)b * N * 3;
@@ -113,6 +132,223 @@ ball_query_shared_kernel(int N, int M, float radius, int nsample, const float* _
     const int fill = cnt > 0 ? first : 0;
     for (int l = min(cnt, nsample) + lane; l < nsample; l += 32) row[l] = fill;
   }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Grid path.  Workspace per cloud: [BqHeader | cell_start (kBqMaxCells+1 ints) | sorted float4 (N)].
+// ---------------------------------------------------------------------------------------------
+constexpr int kBqMaxDim = 32;
+constexpr int kBqMaxCells = kBqMaxDim * kBqMaxDim * kBqMaxDim;
+constexpr int kBqMaxN = 65536;  // bitmap = N bits per warp
+
+__host__ __device__ inline size_t bq_cells_bytes() { return (((size_t)(kBqMaxCells + 1) * 4) + 15) & ~(size_t)15; }
+static inline size_t bq_ws_stride(int N) { return 32 + bq_cells_bytes() + (size_t)N * 16; }
+
+__device__ __forceinline__ int bq_cell(float p, float lo, float inv) { return __float2int_rd((p - lo) * inv); }
+
+__global__ void __launch_bounds__(1024, 1)
+bq_build_kernel(int N, float radius, int nsample, const float* __restrict__ xyz, unsigned char* __restrict__ ws,
+                size_t ws_stride, int force_grid) {
+  extern __shared__ int bq_hist[];  // kBqMaxCells counters
+  __shared__ float s_red[6][32];
+  __shared__ int s_scan[32];
+  __shared__ int s_nonempty;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int b = blockIdx.x;
+  const float* __restrict__ src = xyz + (int64_t)b * N * 3;
+  BqHeader* hdr = reinterpret_cast<BqHeader*>(ws + (size_t)b * ws_stride);
+  int* cell_start = reinterpret_cast<int*>(ws + (size_t)b * ws_stride + 32);
+  float4* sorted = reinterpret_cast<float4*>(ws + (size_t)b * ws_stride + 32 + bq_cells_bytes());
+  const float kInf = __int_as_float(0x7f800000);
+
+  float lo[3] = {kInf, kInf, kInf}, hi[3] = {-kInf, -kInf, -kInf};
+#pragma unroll 4
+  for (int k = t; k < N; k += 1024) {
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+      const float v = src[(int64_t)k * 3 + a];
+      lo[a] = fminf(lo[a], v); hi[a] = fmaxf(hi[a], v);
+    }
+  }
+#pragma unroll
+  for (int a = 0; a < 3; a++) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      lo[a] = fminf(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], o));
+      hi[a] = fmaxf(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], o));
+    }
+    if (lane == 0) { s_red[a][warp] = lo[a]; s_red[3 + a][warp] = hi[a]; }
+  }
+  if (t == 0) s_nonempty = 0;
+  __syncthreads();
+  float ext = 0.f;
+#pragma unroll
+  for (int a = 0; a < 3; a++) {
+    float l = s_red[a][lane], h = s_red[3 + a][lane];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      l = fminf(l, __shfl_xor_sync(0xffffffffu, l, o));
+      h = fmaxf(h, __shfl_xor_sync(0xffffffffu, h, o));
+    }
+    lo[a] = l; hi[a] = h;
+    ext = fmaxf(ext, h - l);
+  }
+  // cell edge: a hair more than the radius (fp32-safe 27-cell cover), grown if the cloud would need > 32 cells
+  float cell = fmaxf(radius * 1.001f, ext / 31.5f);
+  const bool ok = (cell > 0.f) && (cell < kInf) && (ext < kInf) && (ext == ext) && N > 0;
+  if (!ok) {  // degenerate input (zero radius, NaN/inf coordinates): index-order scan handles it
+    if (t == 0) hdr->use_grid = 0;
+    return;
+  }
+  const float inv = 1.0f / cell;
+  int dims[3];
+#pragma unroll
+  for (int a = 0; a < 3; a++) dims[a] = min(kBqMaxDim, max(1, bq_cell(hi[a], lo[a], inv) + 1));
+  const int ncell = dims[0] * dims[1] * dims[2];
+  auto code_of = [&](float x, float y, float z) -> int {
+    const int cx = min(max(bq_cell(x, lo[0], inv), 0), dims[0] - 1);
+    const int cy = min(max(bq_cell(y, lo[1], inv), 0), dims[1] - 1);
+    const int cz = min(max(bq_cell(z, lo[2], inv), 0), dims[2] - 1);
+    return (cz * dims[1] + cy) * dims[0] + cx;
+  };
+  for (int i = t; i < ncell; i += 1024) bq_hist[i] = 0;
+  __syncthreads();
+#pragma unroll 4
+  for (int k = t; k < N; k += 1024)
+    atomicAdd(&bq_hist[code_of(src[(int64_t)k * 3], src[(int64_t)k * 3 + 1], src[(int64_t)k * 3 + 2])], 1);
+  __syncthreads();
+  // exclusive scan over ncell counters, 1024 threads x PER consecutive entries
+  {
+    const int PER = (ncell + 1023) / 1024;
+    const int i0 = t * PER;
+    int sum = 0, ne = 0;
+    for (int i = i0; i < min(i0 + PER, ncell); i++) { const int v = bq_hist[i]; sum += v; ne += v > 0; }
+    int inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += y;
+    }
+    ne = __reduce_add_sync(0xffffffffu, ne);
+    if (lane == 31) s_scan[warp] = inc;
+    if (lane == 0 && ne) atomicAdd(&s_nonempty, ne);
+    __syncthreads();
+    int wtot = s_scan[lane], winc = wtot;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, winc, o);
+      if (lane >= o) winc += y;
+    }
+    int run = __shfl_sync(0xffffffffu, winc - wtot, warp) + inc - sum;
+    for (int i = i0; i < min(i0 + PER, ncell); i++) {
+      const int v = bq_hist[i];
+      bq_hist[i] = run;
+      cell_start[i] = run;
+      run += v;
+    }
+    if (t == 0) cell_start[ncell] = N;
+  }
+  __syncthreads();
+#pragma unroll 4
+  for (int k = t; k < N; k += 1024) {
+    const float x = src[(int64_t)k * 3], y = src[(int64_t)k * 3 + 1], z = src[(int64_t)k * 3 + 2];
+    const int pos = atomicAdd(&bq_hist[code_of(x, y, z)], 1);
+    sorted[pos] = make_float4(x, y, z, __int_as_float(k));
+  }
+  if (t == 0) {
+    // cost model (points visited per query): grid ~ 12*occ (27 cells, ~1/3 occupied on a surface) against the
+    // index-order scan ~ N*nsample/H with H ~ 3*occ hits; occ = points per occupied cell
+    const float occ = (float)N / (float)max(s_nonempty, 1);
+    const float grid_cost = 12.f * occ + 64.f;
+    const float scan_cost = (float)N * (float)nsample / fmaxf(3.f * occ, (float)nsample);
+    hdr->use_grid = (force_grid || grid_cost < scan_cost) ? 1 : 0;
+    hdr->dx = dims[0]; hdr->dy = dims[1]; hdr->dz = dims[2];
+    hdr->lox = lo[0]; hdr->loy = lo[1]; hdr->loz = lo[2]; hdr->inv = inv;
+  }
+}
+
+// One warp per query; 8 queries per CTA.  Dynamic smem: 8 bitmaps of wpl*32 words (wpl words per lane, power of 2).
+__global__ void __launch_bounds__(256)
+bq_grid_kernel(int N, int M, float radius, int nsample, const float* __restrict__ new_xyz,
+               const unsigned char* __restrict__ ws, size_t ws_stride, int* __restrict__ idx, int wpl_log2) {
+  extern __shared__ uint4 bq_bitmap[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int b = blockIdx.y;
+  const BqHeader hdr = *reinterpret_cast<const BqHeader*>(ws + (size_t)b * ws_stride);
+  if (!hdr.use_grid) return;
+  const int q = blockIdx.x * 8 + warp;
+  if (q >= M) return;
+  const int* __restrict__ cell_start = reinterpret_cast<const int*>(ws + (size_t)b * ws_stride + 32);
+  const float4* __restrict__ sorted = reinterpret_cast<const float4*>(ws + (size_t)b * ws_stride + 32 + bq_cells_bytes());
+  const int wpl = 1 << wpl_log2, nvec = wpl >> 2;  // uint4 per lane
+  uint4* bm = bq_bitmap + (size_t)warp * nvec * 32;  // bm[j*32 + lane] = words lane*wpl + 4j .. +3
+  unsigned* bmw = reinterpret_cast<unsigned*>(bm);
+  for (int j = 0; j < nvec; j++) bm[j * 32 + lane] = make_uint4(0u, 0u, 0u, 0u);
+
+  const float* qp = new_xyz + ((int64_t)b * M + q) * 3;
+  const float qx = qp[0], qy = qp[1], qz = qp[2];
+  const float r2 = __fmul_rn(radius, radius);
+  const int cx = bq_cell(qx, hdr.lox, hdr.inv), cy = bq_cell(qy, hdr.loy, hdr.inv), cz = bq_cell(qz, hdr.loz, hdr.inv);
+  // lanes 0..8 fetch the 9 runs (3 x-adjacent cells are contiguous in the sorted order) in one round trip
+  int rs = 0, re = 0;
+  if (lane < 9) {
+    const int z = cz + lane / 3 - 1, y = cy + lane % 3 - 1;
+    const int x0 = max(cx - 1, 0), x1 = min(cx + 1, hdr.dx - 1);
+    if (z >= 0 && z < hdr.dz && y >= 0 && y < hdr.dy && x0 <= x1) {
+      const int c0 = (z * hdr.dy + y) * hdr.dx + x0;
+      rs = __ldg(cell_start + c0);
+      re = __ldg(cell_start + c0 + (x1 - x0) + 1);
+    }
+  }
+  __syncwarp();
+#pragma unroll 1
+  for (int r = 0; r < 9; r++) {
+    const int s = __shfl_sync(0xffffffffu, rs, r), e = __shfl_sync(0xffffffffu, re, r);
+    for (int i = s + lane; i < e; i += 32) {
+      const float4 p = __ldg(sorted + i);
+      const float d2 = dist2_ref(qx, qy, qz, p.x, p.y, p.z);
+      if (d2 < r2) {
+        const unsigned k = (unsigned)__float_as_int(p.w), w = k >> 5;
+        const unsigned ln = w >> wpl_log2, rr = w & (unsigned)(wpl - 1);
+        atomicOr(bmw + ((((rr >> 2) << 5) | ln) << 2 | (rr & 3u)), 1u << (k & 31u));
+      }
+    }
+  }
+  __syncwarp();
+  // lane l owns words l*wpl .. l*wpl+wpl-1, i.e. indices ascend with (lane, word, bit): count, scan, emit
+  int cnt = 0;
+  for (int j = 0; j < nvec; j++) {
+    const uint4 v = bm[j * 32 + lane];
+    cnt += __popc(v.x) + __popc(v.y) + __popc(v.z) + __popc(v.w);
+  }
+  int inc = cnt;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int y = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += y;
+  }
+  const int total = __shfl_sync(0xffffffffu, inc, 31);
+  int slot = inc - cnt;
+  int* row = idx + ((int64_t)b * M + q) * nsample;
+  int first = 0x7fffffff;
+  for (int j = 0; j < nvec; j++) {
+    const uint4 v = bm[j * 32 + lane];
+    bm[j * 32 + lane] = make_uint4(0u, 0u, 0u, 0u);
+    const unsigned wd[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+      unsigned word = wd[c];
+      const int base = ((lane << wpl_log2) + 4 * j + c) << 5;
+      if (word && first == 0x7fffffff) first = base + __ffs(word) - 1;
+      while (word && slot < nsample) {
+        row[slot++] = base + __ffs(word) - 1;
+        word &= word - 1;
+      }
+    }
+  }
+  first = __reduce_min_sync(0xffffffffu, first);
+  const int fill = total > 0 ? first : 0;
+  for (int l = min(total, nsample) + lane; l < nsample; l += 32) row[l] = fill;
 }
 
 // Offset format (ragged segments): one warp per query, points straight from global/L2.
@@ -153,15 +389,51 @@ ballquery_offset_kernel(int b, int m, float radius, int nsample, const float* __
 
 using namespace geot;
 
+GEOT_API size_t geot_ball_query_workspace_bytes(int B, int N) {
+  if (B <= 0 || N <= 0 || N > kBqMaxN) return 0;
+  return (size_t)B * bq_ws_stride(N);
+}
+
 GEOT_API int geot_ball_query(int B, int N, int M, float radius, int nsample, const float* new_xyz,
-                             const float* xyz, int* idx, geot_stream_t stream) {
+                             const float* xyz, int* idx, void* workspace, size_t workspace_bytes,
+                             int flags, geot_stream_t stream) {
   GEOT_REQUIRE(B >= 0 && N >= 0 && M >= 0 && nsample >= 0, "ball_query: bad sizes");
   if (B == 0 || M == 0 || nsample == 0) return GEOT_OK;
   GEOT_REQUIRE(new_xyz && xyz && idx, "ball_query: NULL pointer");
   GEOT_REQUIRE(B <= 65535, "ball_query: B=%d exceeds grid.y", B);
+  cudaStream_t s = as_stream(stream);
+  const unsigned char* ws = nullptr;
+  size_t stride = 0;
+  if (workspace != nullptr && N > 0 && N <= kBqMaxN) {
+    stride = bq_ws_stride(N);
+    if (workspace_bytes < (size_t)B * stride) {
+      set_error("ball_query: workspace %zu < %zu bytes", workspace_bytes, (size_t)B * stride);
+      return GEOT_ERR_WORKSPACE;
+    }
+    ws = reinterpret_cast<const unsigned char*>(workspace);
+    static bool configured = false;
+    if (!configured) {
+      cudaError_t e = cudaFuncSetAttribute(bq_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBqMaxCells * 4);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(bq_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * (kBqMaxN / 8));
+      if (e != cudaSuccess) { set_error("ball_query: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
+      configured = true;
+    }
+    bq_build_kernel<<<B, 1024, kBqMaxCells * 4, s>>>(N, radius, nsample, xyz, reinterpret_cast<unsigned char*>(workspace), stride,
+                                                      (flags & GEOT_BQ_FORCE_GRID) ? 1 : 0);
+    count_launch(1);
+    int rc = check_launch("bq_build_kernel");
+    if (rc) return rc;
+    int wpl_log2 = 2;  // words per lane: power of two >= N/1024, at least 4
+    while ((1024 << wpl_log2) < N) wpl_log2++;
+    dim3 gq((M + 7) / 8, B);
+    bq_grid_kernel<<<gq, 256, (size_t)8 * (128u << wpl_log2), s>>>(N, M, radius, nsample, new_xyz, ws, stride, idx, wpl_log2);
+    count_launch(1);
+    rc = check_launch("bq_grid_kernel");
+    if (rc) return rc;
+  }
   const int aligned16 = (((uintptr_t)xyz & 15) == 0) && ((N * 3) % 4 == 0);
   dim3 grid((M + 31) / 32, B);
-  ball_query_shared_kernel<<<grid, 1024, 0, as_stream(stream)>>>(N, M, radius, nsample, new_xyz, xyz, idx, aligned16);
+  ball_query_shared_kernel<<<grid, 1024, 0, s>>>(N, M, radius, nsample, new_xyz, xyz, idx, aligned16, ws, stride);
   count_launch(1);
   return check_launch("ball_query_shared_kernel");
 }

@@ -64,15 +64,21 @@ def furthestsampling(xyz, offset, new_offset, weights=None, n_max=None, m_total=
 # --------------------------------------------------------------------------------------------------
 # neighbour search
 # --------------------------------------------------------------------------------------------------
-def ball_query(new_xyz, xyz, radius, nsample, out=None):
-    """new_xyz (B,M,3), xyz (B,N,3) -> idx (B,M,nsample) int32."""
+def ball_query(new_xyz, xyz, radius, nsample, out=None, workspace=None, use_grid=True, flags=0):
+    """new_xyz (B,M,3), xyz (B,N,3) -> idx (B,M,nsample) int32.  `workspace`: a uint8 tensor of at least
+    geot_ball_query_workspace_bytes(B,N) bytes (allocated here when None); use_grid=False forces the
+    index-order scan for every cloud (same result; testing / A-B timing)."""
     dev = check_cuda(new_xyz, xyz, out)
     B, N, _ = xyz.shape
     M = new_xyz.shape[1]
     with torch.cuda.device(dev):
         if out is None:
             out = torch.empty((B, M, nsample), dtype=_i32, device=dev)
-        call("geot_ball_query", B, N, M, float(radius), nsample, ptr(new_xyz), ptr(xyz), ptr(out), stream_ptr())
+        ws_bytes = int(_lib.lib().geot_ball_query_workspace_bytes(B, N)) if use_grid else 0
+        if ws_bytes and (workspace is None or workspace.numel() < ws_bytes):
+            workspace = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        call("geot_ball_query", B, N, M, float(radius), nsample, ptr(new_xyz), ptr(xyz), ptr(out),
+             ptr(workspace) if ws_bytes else None, ws_bytes, flags, stream_ptr())
     return out
 
 

@@ -81,9 +81,15 @@ int geot_furthestsampling(int b, int n_max, const float* xyz, const int* offset,
  * new_xyz (B,M,3), xyz (B,N,3) -> idx (B,M,nsample): first nsample indices k (ascending) with
  * d2 < radius*radius, remaining slots = first hit, rows with no hit all 0.  Unlike the reference the
  * kernel writes every slot itself (no caller zero-fill needed).
+ * workspace: geot_ball_query_workspace_bytes(B,N) bytes of scratch (uniform-grid binning of each cloud) or
+ * NULL.  With a workspace the library bins the clouds and, per cloud, takes the grid path when the ball is
+ * small against the cloud; without one (or N > 65536) every cloud is scanned in index order.  Same result.
  * --------------------------------------------------------------------------------------------- */
+#define GEOT_BQ_FORCE_GRID 1 /* testing: take the grid path for every cloud, whatever the cost model says */
+size_t geot_ball_query_workspace_bytes(int B, int N);
 int geot_ball_query(int B, int N, int M, float radius, int nsample, const float* new_xyz,
-                    const float* xyz, int* idx, geot_stream_t stream);
+                    const float* xyz, int* idx, void* workspace, size_t workspace_bytes, int flags,
+                    geot_stream_t stream);
 
 /* replaces pointops_cuda.ballquery_cuda(m,radius,nsample,xyz,new_xyz,offset,new_offset,idx)
  * (openpoints/cpp/pointops/src/ballquery/ballquery_cuda_kernel.cu:26-78).  b = number of segments. */

@@ -78,6 +78,25 @@ def test_ball_query(cuda, oracle, kind, B, N, M, r, ns):
     got = F.ball_query(cu(q), cu(xyz), r, ns, out=out).cpu().numpy()
     assert np.array_equal(got, exp)
     assert not exp[:, -1].any()
+    out.fill_(-7)
+    got = F.ball_query(cu(q), cu(xyz), r, ns, out=out, use_grid=False).cpu().numpy()
+    assert np.array_equal(got, exp), "index-order scan"
+    out.fill_(-7)
+    got = F.ball_query(cu(q), cu(xyz), r, ns, out=out, flags=_lib.GEOT_BQ_FORCE_GRID).cpu().numpy()
+    assert np.array_equal(got, exp), "grid path"
+
+
+@pytest.mark.parametrize("r", [0.003, 0.02, 0.1, 0.4, 3.0])
+def test_ball_query_radius_sweep_and_outside_queries(cuda, oracle, r):
+    """tiny radius (grid capped at 32 cells per axis), huge radius (one cell), queries outside the cloud's box."""
+    xyz = clouds("tooth", 2, 8192)
+    rng = np.random.default_rng(5)
+    q = np.concatenate([xyz[:, :200], xyz[:, 200:300] + rng.normal(0, r, (2, 100, 3)).astype(np.float32),
+                        rng.uniform(-2, 2, (2, 100, 3)).astype(np.float32)], 1)
+    exp = oracle.ball_query(r, 32, xyz, q)
+    for flags in (0, _lib.GEOT_BQ_FORCE_GRID):
+        got = F.ball_query(cu(q), cu(xyz), r, 32, flags=flags).cpu().numpy()
+        assert np.array_equal(got, exp), f"flags={flags}"
 
 
 def test_ball_query_offset(cuda, oracle):
