@@ -37,6 +37,7 @@ _SIGNATURES = {
     "geot_knnquery": [_i, _i, _i, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _sz, _vp],
     "geot_group_points": [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp],
     "geot_gather_points": [_i, _i, _i, _i, _vp, _vp, _vp, _vp],
+    "geot_group_points_config": [_i],
     "geot_scatter_plan_bytes": [_i, _i, _i64],
     "geot_scatter_plan_build": [_i, _i, _i64, _vp, _vp, _sz, _vp],
     "geot_group_points_grad": [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp],
@@ -71,6 +72,7 @@ _RESTYPES = {
     "geot_launch_count": C.c_uint64,
     "geot_scatter_plan_bytes": _sz,
     "geot_ball_query_workspace_bytes": _sz,
+    "geot_group_points_config": None,
     "geot_knnquery_workspace_bytes": _sz,
     "geot_sigt_workspace_bytes": _sz,
     "geot_sigt_backward_workspace_bytes": _sz,

@@ -23,6 +23,7 @@ namespace geot {
 void count_launch(int n);
 
 constexpr int kGroupCCH = 16;  // channels per thread in the forward gather
+static bool g_group_force_direct = false;  // testing / A-B timing: geot_group_points_config
 
 // VEC = 4: E % 4 == 0 and 16-byte aligned idx/out.  grid (ceil(E/VEC/256), ceil(C/CCH), B).
 template <int VEC>
@@ -51,12 +52,105 @@ group_points_kernel(int C, int N, int64_t E, const float* __restrict__ points,
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Row-staged forward (the default when a feature row fits shared memory and is re-used: E >= 2N).
+// The gather above pulls a 32-byte sector through L2/L1 for every 4-byte element: at C=64, ns=32 that is
+// 8x the algorithmic source traffic and the kernel sits on the L1/L2 sector rate (42 % of HBM peak).
+// Here one CTA owns one (b, c) row: the row (N floats) is brought into shared memory once by a single
+// bulk async copy (cp.async.bulk, completion on an mbarrier), idx is streamed as int4 (L2 resident: it is
+// shared by the C rows of the cloud), the 4-byte gathers hit shared memory and the output leaves as 16-byte
+// streaming stores.  Up to three CTAs per SM, so one row's load overlaps the neighbours' gather/store phases.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@!p bra WAIT_%=;\n"
+      "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+constexpr int kRowThreads = 512;
+__global__ void __launch_bounds__(kRowThreads)
+group_rows_kernel(int C, int N, int64_t E, const float* __restrict__ points, const int* __restrict__ idx,
+                  float* __restrict__ out) {
+  extern __shared__ __align__(16) float g_row[];
+  __shared__ uint64_t bar;
+  const int t = threadIdx.x;
+  const int c = blockIdx.x, b = blockIdx.y;
+  const int64_t rowi = (int64_t)b * C + c;
+  if (t == 0) {
+    mbar_init(&bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (t == 0) {
+    mbar_expect_tx(&bar, (unsigned)N * 4u);
+    bulk_g2s(g_row, points + rowi * N, (unsigned)N * 4u, &bar);
+  }
+  const int4* __restrict__ idp = reinterpret_cast<const int4*>(idx + (int64_t)b * E);
+  float4* __restrict__ op = reinterpret_cast<float4*>(out + rowi * E);
+  const int64_t n4 = E >> 2;
+  constexpr int U = 4;
+  int4 id[U];
+#pragma unroll
+  for (int u = 0; u < U; u++) {
+    const int64_t g = t + (int64_t)u * kRowThreads;
+    id[u] = g < n4 ? __ldg(idp + g) : make_int4(0, 0, 0, 0);
+  }
+  mbar_wait(&bar, 0);
+  for (int64_t g0 = t; g0 < n4; g0 += (int64_t)U * kRowThreads) {
+    int4 cur[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) cur[u] = id[u];
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int64_t g = g0 + (int64_t)(U + u) * kRowThreads;
+      id[u] = g < n4 ? __ldg(idp + g) : make_int4(0, 0, 0, 0);
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int64_t g = g0 + (int64_t)u * kRowThreads;
+      if (g < n4) {
+        float4 o;
+        o.x = g_row[cur[u].x]; o.y = g_row[cur[u].y]; o.z = g_row[cur[u].z]; o.w = g_row[cur[u].w];
+        __stcs(op + g, o);
+      }
+    }
+  }
+}
+
 static int launch_group(int B, int C, int N, int64_t E, const float* points, const int* idx, float* out,
                         cudaStream_t s, const char* what) {
   if (B == 0 || C == 0 || E == 0) return GEOT_OK;
   GEOT_REQUIRE(points && idx && out, "%s: NULL pointer", what);
   GEOT_REQUIRE(B <= 65535 && (C + kGroupCCH - 1) / kGroupCCH <= 65535, "%s: B or C exceeds grid limits", what);
   const bool vec = (E % 4 == 0) && (((uintptr_t)idx & 15) == 0) && (((uintptr_t)out & 15) == 0);
+  const size_t row_bytes = (size_t)N * 4;
+  if (vec && !g_group_force_direct && E >= 2 * (int64_t)N && N % 4 == 0 && (((uintptr_t)points & 15) == 0) &&
+      row_bytes <= 200 * 1024 && C <= 65535 * 1 && N > 0) {
+    static size_t configured = 0;
+    if (row_bytes > configured) {
+      cudaError_t e = cudaFuncSetAttribute(group_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+      if (e != cudaSuccess) { set_error("%s: cudaFuncSetAttribute: %s", what, cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
+      configured = 200 * 1024;
+    }
+    dim3 grid(C, B);
+    group_rows_kernel<<<grid, kRowThreads, row_bytes, s>>>(C, N, E, points, idx, out);
+    count_launch(1);
+    return check_launch(what);
+  }
   if (vec) {
     dim3 grid((unsigned)((E / 4 + 255) / 256), (C + kGroupCCH - 1) / kGroupCCH, B);
     group_points_kernel<4><<<grid, 256, 0, s>>>(C, N, E, points, idx, out);
@@ -232,6 +326,9 @@ GEOT_API int geot_group_points(int B, int C, int N, int M, int nsample, const fl
   GEOT_REQUIRE(B >= 0 && C >= 0 && N >= 0 && M >= 0 && nsample >= 0, "group_points: bad sizes");
   return launch_group(B, C, N, (int64_t)M * nsample, points, idx, out, as_stream(stream), "group_points");
 }
+
+/* testing / A-B timing: direct != 0 disables the row-staged forward kernel (process-wide). */
+GEOT_API void geot_group_points_config(int direct) { g_group_force_direct = direct != 0; }
 
 GEOT_API int geot_gather_points(int B, int C, int N, int M, const float* points, const int* idx,
                                 float* out, geot_stream_t stream) {

@@ -118,6 +118,9 @@ int geot_knnquery(int b, int m, int nsample, const float* xyz, const float* new_
  * and pointnet2._ext.group_points.  points (B,C,N), idx (B,M,ns) -> out (B,C,M,ns). */
 int geot_group_points(int B, int C, int N, int M, int nsample, const float* points, const int* idx,
                       float* out, geot_stream_t stream);
+/* testing / A-B timing: direct != 0 makes group/gather forward always take the direct L2-gather kernel
+ * instead of the row-staged one (process-wide switch; results are identical). */
+void geot_group_points_config(int direct);
 /* replaces pointnet2_batch_cuda.gather_points_wrapper(B,C,N,M,points,idx,out) (sampling_gpu.cu:15-31)
  * and pointnet2._ext.gather_points.  points (B,C,N), idx (B,M) -> out (B,C,M). */
 int geot_gather_points(int B, int C, int N, int M, const float* points, const int* idx, float* out,

@@ -64,6 +64,23 @@ def test_fps_offset_ragged(cuda, oracle, weighted):
     assert np.array_equal(got, exp)
 
 
+def test_group_points_row_staged_vs_direct(cuda, oracle):
+    """E >= 2N takes the row-staged kernel (cp.async.bulk + smem gather); geot_group_points_config(1) forces the
+    direct L2 gather.  Both must equal the oracle bit for bit."""
+    rng = np.random.default_rng(3)
+    for (B, C, N, M, ns) in [(2, 5, 4096, 512, 32), (1, 3, 16384, 1024, 32), (2, 7, 1024, 256, 16), (1, 2, 50000, 4096, 32)]:
+        feat = rng.standard_normal((B, C, N)).astype(np.float32)
+        idx = rng.integers(0, N, (B, M, ns)).astype(np.int32)
+        exp = oracle.grouping_operation(feat, idx)
+        try:
+            for direct in (0, 1):
+                _lib.lib().geot_group_points_config(direct)
+                got = F.group_points(cu(feat), cu(idx)).cpu().numpy()
+                assert np.array_equal(got, exp), f"direct={direct} shape={(B, C, N, M, ns)}"
+        finally:
+            _lib.lib().geot_group_points_config(0)
+
+
 BALL_CASES = [("tooth", 2, 16384, 1024, 0.1, 32), ("tooth", 2, 4099, 257, 0.2, 64), ("tooth", 3, 1000, 64, 0.05, 16),
               ("quant", 2, 5000, 300, 0.125, 48), ("dup", 1, 2000, 100, 0.1, 8), ("tooth", 1, 30, 5, 0.5, 40)]
 
