@@ -156,11 +156,12 @@ def run_ours(args):
     out_h = [torch.empty((B, M), dtype=i32).pin_memory(), torch.empty((B, M, NS), dtype=i32).pin_memory(),
              torch.empty((B, M, 3), dtype=f32).pin_memory()]
 
+    bq_ws = torch.empty(int(_lib.lib().geot_ball_query_workspace_bytes(B, N)), dtype=torch.uint8, device=dev)
     ops = {
         "fps": lambda: F.furthest_point_sampling(xyz, M, out=fps_idx),
         "gather_centres": lambda: (xyz_t.copy_(xyz.transpose(1, 2)), F.gather_points(xyz_t, fps_idx, out=centres_t),
                                    centres.copy_(centres_t.transpose(1, 2))),
-        "ball_query": lambda: F.ball_query(centres, xyz, RADIUS, NS, out=nbr),
+        "ball_query": lambda: F.ball_query(centres, xyz, RADIUS, NS, out=nbr, workspace=bq_ws),
         "group_xyz": lambda: F.group_points(xyz_t, nbr, out=g_xyz),
         "group_feat": lambda: F.group_points(feat, nbr, out=g_feat),
     }

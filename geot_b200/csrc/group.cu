@@ -16,6 +16,7 @@
 // "scatter plan" — CSR of source positions by target, sources in ascending order — is built once per
 // idx with integer atomics + a stable ranking pass (bit-reproducible), and each target sums its
 // sources in that fixed order.
+#include <algorithm>
 #include "common.cuh"
 
 namespace geot {
@@ -176,7 +177,7 @@ plan_count_kernel(int N, int64_t E, const int* __restrict__ idx, int* __restrict
 
 // In-place inclusive scan of each (N+1)-row (counts were stored shifted by one => exclusive offsets).
 __global__ void __launch_bounds__(1024)
-plan_scan_kernel(int N, int* __restrict__ row_ptr) {
+plan_scan_kernel(int N, int* __restrict__ row_ptr, int* __restrict__ cursor) {
   __shared__ int s_warp[32];
   __shared__ int s_carry;
   int* row = row_ptr + (int64_t)blockIdx.x * (N + 1);
@@ -202,42 +203,116 @@ plan_scan_kernel(int N, int* __restrict__ row_ptr) {
     const int warp_prefix = __shfl_sync(0xffffffffu, w, max(warp - 1, 0));
     const int carry = s_carry;
     v += carry + (warp ? warp_prefix : 0);
-    if (i <= N) row[i] = v;
+    if (i <= N) { row[i] = v; cursor[(int64_t)blockIdx.x * (N + 1) + i] = v; }
     __syncthreads();
     if (t == 1023) s_carry = v;
     __syncthreads();
   }
 }
 
-// Stable fill.  Each warp owns a range of kPlanR target keys and walks ALL entries of its cloud in
-// order; running per-key counters live in shared memory and are touched by that warp only, so the
-// position of every source inside its target's segment is its arrival order: bit-reproducible.
-constexpr int kPlanR = 64;
-__global__ void __launch_bounds__(1024)
-plan_fill_kernel(int N, int64_t E, const int* __restrict__ idx, const int* __restrict__ row_ptr,
-                 int* __restrict__ perm) {
-  __shared__ int s_cnt[32][kPlanR];
+// Fill.  The counting-sort scatter itself uses integer atomics on a cursor copy of row_ptr, so the order of the
+// sources inside a target's segment is arbitrary after it (into the scratch list `tmp`); a second pass puts
+// every segment into ascending source order, which makes the plan - and every sum computed from it - bit
+// reproducible.  Segments are short (mean E/N, a few entries): a thread sorts a segment of up to kPlanSmall
+// entries by insertion in local memory.  Longer segments (the first-hit padding of ball_query, the all-zero
+// rows of empty balls) go to a work list and are sorted by a whole CTA through a bitmap over the source
+// universe [0,E): set one bit per source, read the bits back in order - O(L + E/32), no quadratic case.
+constexpr int kPlanSmall = 64;
+__global__ void __launch_bounds__(256)
+plan_fill_kernel(int N, int64_t E, const int* __restrict__ idx, int* __restrict__ cursor, int* __restrict__ tmp) {
   const int b = blockIdx.y;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int lo = (blockIdx.x * 32 + warp) * kPlanR;
-  for (int i = lane; i < kPlanR; i += 32) s_cnt[warp][i] = 0;
-  __syncwarp();
-  if (lo >= N) return;
-  const int* __restrict__ src = idx + (int64_t)b * E;
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= E) return;
+  const int k = idx[(int64_t)b * E + e];
+  if ((unsigned)k < (unsigned)N) tmp[(int64_t)b * E + atomicAdd(cursor + (int64_t)b * (N + 1) + k, 1)] = (int)e;
+}
+
+__global__ void __launch_bounds__(256)
+plan_sort_small_kernel(int N, int64_t E, const int* __restrict__ row_ptr, const int* __restrict__ tmp,
+                       int* __restrict__ perm, int* __restrict__ heavy_count, int* __restrict__ heavy_list,
+                       int heavy_cap) {
+  const int b = blockIdx.y;
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= N) return;
   const int* __restrict__ rp = row_ptr + (int64_t)b * (N + 1);
-  int* __restrict__ dst = perm + (int64_t)b * E;
-  for (int64_t e0 = 0; e0 < E; e0 += 32) {
-    const int64_t e = e0 + lane;
-    const int k = (e < E) ? __ldg(src + e) : -1;
-    const bool mine = (unsigned)(k - lo) < (unsigned)kPlanR && k < N;
-    if (!__any_sync(0xffffffffu, mine)) continue;
-    const unsigned grp = __match_any_sync(0xffffffffu, mine ? k : (int)(0x80000000u | lane));
-    int base = 0;
-    if (mine) base = s_cnt[warp][k - lo];
-    __syncwarp();
-    if (mine && lane == __ffs(grp) - 1) s_cnt[warp][k - lo] = base + __popc(grp);
-    __syncwarp();
-    if (mine) dst[rp[k] + base + __popc(grp & lanemask_lt())] = (int)e;
+  const int s = rp[k], L = rp[k + 1] - s;
+  if (L <= 0) return;
+  const int* __restrict__ src = tmp + (int64_t)b * E + s;
+  int* __restrict__ dst = perm + (int64_t)b * E + s;
+  if (L == 1) { dst[0] = src[0]; return; }
+  if (L > kPlanSmall) {
+    const int slot = atomicAdd(heavy_count, 1);  // order of the work list does not matter
+    if (slot < heavy_cap) heavy_list[slot] = b * N + k;
+    return;
+  }
+  int v[kPlanSmall];
+  for (int i = 0; i < L; i++) {
+    const int x = src[i];
+    int j = i;
+    while (j > 0 && v[j - 1] > x) { v[j] = v[j - 1]; j--; }
+    v[j] = x;
+  }
+  for (int i = 0; i < L; i++) dst[i] = v[i];
+}
+
+constexpr int kPlanHeavyBits = 1 << 20;  // universe chunk: 1 Mi sources = 128 KB of shared memory
+__global__ void __launch_bounds__(1024, 1)
+plan_sort_heavy_kernel(int N, int64_t E, const int* __restrict__ row_ptr, const int* __restrict__ tmp,
+                       int* __restrict__ perm, const int* __restrict__ heavy_count,
+                       const int* __restrict__ heavy_list, int heavy_cap) {
+  extern __shared__ unsigned plan_bm[];
+  __shared__ int s_warp[32];
+  __shared__ int s_written;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int count = min(*heavy_count, heavy_cap);
+  for (int item = blockIdx.x; item < count; item += gridDim.x) {
+    const int bk = heavy_list[item], b = bk / N, k = bk % N;
+    const int* __restrict__ rp = row_ptr + (int64_t)b * (N + 1);
+    const int s = rp[k], L = rp[k + 1] - s;
+    const int* __restrict__ src = tmp + (int64_t)b * E + s;
+    int* __restrict__ dst = perm + (int64_t)b * E + s;
+    if (t == 0) s_written = 0;
+    for (int64_t u0 = 0; u0 < E; u0 += kPlanHeavyBits) {
+      const int nbits = (int)min((int64_t)kPlanHeavyBits, E - u0);
+      const int nwords = (nbits + 31) >> 5;
+      const int wpt = (nwords + 1023) >> 10;  // words per thread, consecutive: thread order = source order
+      for (int i = t; i < wpt * 1024; i += 1024) plan_bm[i] = 0u;
+      __syncthreads();
+      for (int i = t; i < L; i += 1024) {
+        const int64_t v = (int64_t)src[i] - u0;
+        if (v >= 0 && v < nbits) atomicOr(&plan_bm[v >> 5], 1u << (v & 31));
+      }
+      __syncthreads();
+      int cnt = 0;
+      for (int i = 0; i < wpt; i++) cnt += __popc(plan_bm[t * wpt + i]);
+      int inc = cnt;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int y = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += y;
+      }
+      if (lane == 31) s_warp[warp] = inc;
+      __syncthreads();
+      int w = s_warp[lane], winc = w;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int y = __shfl_up_sync(0xffffffffu, winc, o);
+        if (lane >= o) winc += y;
+      }
+      const int base = s_written + __shfl_sync(0xffffffffu, winc - w, warp) + inc - cnt;
+      const int chunk_total = __shfl_sync(0xffffffffu, winc, 31);
+      int o = base;
+      for (int i = 0; i < wpt; i++) {
+        unsigned word = plan_bm[t * wpt + i];
+        while (word) {
+          dst[o++] = (int)(u0 + (((int64_t)(t * wpt + i)) << 5) + __ffs(word) - 1);
+          word &= word - 1;
+        }
+      }
+      __syncthreads();
+      if (t == 0) s_written += chunk_total;
+      __syncthreads();
+    }
   }
 }
 
@@ -336,9 +411,14 @@ GEOT_API int geot_gather_points(int B, int C, int N, int M, const float* points,
   return launch_group(B, C, N, (int64_t)M, points, idx, out, as_stream(stream), "gather_points");
 }
 
+// Workspace: [row_ptr | perm | cursor | tmp | heavy_count | heavy_list]; consumers read the first two only.
+static inline size_t plan_align(size_t b) { return (b + 255) & ~(size_t)255; }
+static inline int plan_heavy_cap(int B, int64_t E) { return (int)std::min<int64_t>((int64_t)B * (E / kPlanSmall) + 1, 1 << 28); }
 GEOT_API size_t geot_scatter_plan_bytes(int B, int N, int64_t E) {
   if (B < 0 || N < 0 || E < 0) return 0;
-  return plan_rowptr_bytes(B, N) + (size_t)B * (size_t)E * sizeof(int);
+  const size_t perm_b = plan_align((size_t)B * (size_t)E * sizeof(int));
+  return plan_rowptr_bytes(B, N) + perm_b + plan_rowptr_bytes(B, N) + perm_b + 256 +
+         plan_align((size_t)plan_heavy_cap(B, E) * sizeof(int));
 }
 
 GEOT_API int geot_scatter_plan_build(int B, int N, int64_t E, const int* idx, void* plan,
@@ -363,15 +443,34 @@ GEOT_API int geot_scatter_plan_build(int B, int N, int64_t E, const int* idx, vo
     int rc = check_launch("plan_count_kernel");
     if (rc) return rc;
   }
-  plan_scan_kernel<<<B, 1024, 0, s>>>(N, row_ptr);
+  const size_t perm_b = plan_align((size_t)B * (size_t)E * sizeof(int));
+  char* base = reinterpret_cast<char*>(plan) + plan_rowptr_bytes(B, N) + perm_b;
+  int* cursor = reinterpret_cast<int*>(base);
+  int* tmp = reinterpret_cast<int*>(base + plan_rowptr_bytes(B, N));
+  int* heavy_count = reinterpret_cast<int*>(base + plan_rowptr_bytes(B, N) + perm_b);
+  int* heavy_list = heavy_count + 64;
+  const int heavy_cap = plan_heavy_cap(B, E);
+  plan_scan_kernel<<<B, 1024, 0, s>>>(N, row_ptr, cursor);
   count_launch(1);
   int rc = check_launch("plan_scan_kernel");
   if (rc) return rc;
   if (E > 0 && N > 0) {
-    dim3 gf((N + 32 * kPlanR - 1) / (32 * kPlanR), B);
-    plan_fill_kernel<<<gf, 1024, 0, s>>>(N, E, idx, row_ptr, perm);
-    count_launch(1);
-    rc = check_launch("plan_fill_kernel");
+    err = cudaMemsetAsync(heavy_count, 0, sizeof(int), s);
+    if (err != cudaSuccess) { set_error("scatter_plan_build: memset: %s", cudaGetErrorString(err)); return GEOT_ERR_CUDA; }
+    dim3 gf((unsigned)((E + 255) / 256), B);
+    plan_fill_kernel<<<gf, 256, 0, s>>>(N, E, idx, cursor, tmp);
+    dim3 gs((N + 255) / 256, B);
+    plan_sort_small_kernel<<<gs, 256, 0, s>>>(N, E, row_ptr, tmp, perm, heavy_count, heavy_list, heavy_cap);
+    static bool configured = false;
+    if (!configured) {
+      cudaError_t e2 = cudaFuncSetAttribute(plan_sort_heavy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPlanHeavyBits / 8);
+      if (e2 != cudaSuccess) { set_error("scatter_plan_build: cudaFuncSetAttribute: %s", cudaGetErrorString(e2)); return GEOT_ERR_CUDA; }
+      configured = true;
+    }
+    const size_t bm_bytes = (size_t)std::min<int64_t>(kPlanHeavyBits, ((E + 32767) / 32768) * 32768) / 8;
+    plan_sort_heavy_kernel<<<2 * kNumSMs, 1024, bm_bytes, s>>>(N, E, row_ptr, tmp, perm, heavy_count, heavy_list, heavy_cap);
+    count_launch(3);
+    rc = check_launch("plan_fill/sort kernels");
   }
   return rc;
 }

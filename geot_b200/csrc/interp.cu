@@ -16,6 +16,7 @@
 // three_interpolate fwd: HBM-bound on the (B,C,n) write; idx/weight (24 B per target) are loaded once
 // per thread and reused across a chunk of channels, sources come from an L1/L2-resident (m) row.
 // The backward is the deterministic segmented reduction of group.cu over a scatter plan of idx.
+#include <algorithm>
 #include "common.cuh"
 
 namespace geot {
@@ -117,6 +118,70 @@ three_interpolate_kernel(int C, int m, int n, const float* __restrict__ points,
   }
 }
 
+// Row-staged variant (default): one CTA stages G consecutive feature rows of one cloud (G*m floats, one bulk
+// async copy) and produces G x n_tile outputs: idx/weight are read once per target and re-used over the G
+// channels, the 3 gathers per output hit shared memory instead of pulling 32-byte sectors through L1/L2.
+__device__ __forceinline__ void ti_mbar_init(uint64_t* bar) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(bar)) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void ti_bulk_load(void* dst, const void* src, unsigned bytes, uint64_t* bar) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void ti_mbar_wait(uint64_t* bar) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n"
+      "@!p bra WAIT_%=;\n"
+      "}\n" ::"r"(smem_u32(bar)) : "memory");
+}
+
+constexpr int kTiThreads = 512;
+// grid (ceil(n/n_tile), ceil(C/G), B), kTiThreads threads.
+__global__ void __launch_bounds__(kTiThreads)
+three_interpolate_rows_kernel(int C, int m, int n, int G, int n_tile, const float* __restrict__ points,
+                              const int* __restrict__ idx, const float* __restrict__ weight,
+                              float* __restrict__ out) {
+  extern __shared__ __align__(16) float ti_rows[];
+  __shared__ uint64_t bar;
+  const int t = threadIdx.x, b = blockIdx.z;
+  const int c0 = blockIdx.y * G, gc = min(G, C - c0);
+  if (t == 0) {
+    ti_mbar_init(&bar);
+    ti_bulk_load(ti_rows, points + ((int64_t)b * C + c0) * m, (unsigned)gc * (unsigned)m * 4u, &bar);
+  }
+  const int j0 = blockIdx.x * n_tile, j1 = min(n, j0 + n_tile);
+  __syncthreads();  // the barrier init is visible to the waiters
+  int j = j0 + t;
+  int i0 = 0, i1 = 0, i2 = 0;
+  float w0 = 0.f, w1 = 0.f, w2 = 0.f;
+  auto fetch = [&](int jj) {
+    const int* id = idx + ((int64_t)b * n + jj) * 3;
+    const float* w = weight + ((int64_t)b * n + jj) * 3;
+    i0 = __ldg(id); i1 = __ldg(id + 1); i2 = __ldg(id + 2);
+    w0 = __ldg(w); w1 = __ldg(w + 1); w2 = __ldg(w + 2);
+  };
+  if (j < j1) fetch(j);
+  ti_mbar_wait(&bar);
+  for (; j < j1; j += kTiThreads) {
+    const int a0 = i0, a1 = i1, a2 = i2;
+    const float v0 = w0, v1 = w1, v2 = w2;
+    if (j + kTiThreads < j1) fetch(j + kTiThreads);  // next target's indices/weights while this one is computed
+    float* o = out + ((int64_t)b * C + c0) * n + j;
+#pragma unroll 4
+    for (int g = 0; g < gc; g++) {
+      const float* row = ti_rows + g * m;
+      // reference SASS order: FMUL w1*p1 ; FFMA w0*p0 + . ; FFMA w2*p2 + .
+      const float v = __fmaf_rn(v2, row[a2], __fmaf_rn(v0, row[a0], __fmul_rn(v1, row[a1])));
+      __stcs(o + (int64_t)g * n, v);
+    }
+  }
+}
+
 }  // namespace geot
 
 using namespace geot;
@@ -139,6 +204,25 @@ GEOT_API int geot_three_interpolate(int B, int C, int m, int n, const float* poi
   if (B == 0 || C == 0 || n == 0) return GEOT_OK;
   GEOT_REQUIRE(points && idx && weight && out, "three_interpolate: NULL pointer");
   GEOT_REQUIRE(B <= 65535 && (C + kTiCCH - 1) / kTiCCH <= 65535, "three_interpolate: B or C exceeds grid limits");
+  if (m > 0 && m % 4 == 0 && (((uintptr_t)points & 15) == 0) && (size_t)m * 4 <= 96 * 1024 && n >= 2 * m) {
+    int G = (int)std::min<size_t>(16, (64 * 1024) / ((size_t)m * 4));
+    if (G < 1) G = 1;
+    if (G > C) G = C;
+    int n_tile = std::max(4 * m, 2048);
+    if (n_tile > n) n_tile = n;
+    const size_t smem = (size_t)G * m * 4;
+    static bool configured = false;
+    if (!configured) {
+      cudaError_t e = cudaFuncSetAttribute(three_interpolate_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+      if (e != cudaSuccess) { set_error("three_interpolate: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
+      configured = true;
+    }
+    GEOT_REQUIRE((C + G - 1) / G <= 65535, "three_interpolate: C exceeds grid limits");
+    dim3 grid((n + n_tile - 1) / n_tile, (C + G - 1) / G, B);
+    three_interpolate_rows_kernel<<<grid, kTiThreads, smem, as_stream(stream)>>>(C, m, n, G, n_tile, points, idx, weight, out);
+    count_launch(1);
+    return check_launch("three_interpolate_rows_kernel");
+  }
   dim3 grid((n + 255) / 256, (C + kTiCCH - 1) / kTiCCH, B);
   three_interpolate_kernel<<<grid, 256, 0, as_stream(stream)>>>(C, m, n, points, idx, weight, out);
   count_launch(1);

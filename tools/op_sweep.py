@@ -1,0 +1,136 @@
+#!/usr/bin/env python
+"""GPU box: per-op timing of this library against the reference's OWN kernels (oracle/_ref/*.so, compiled
+unchanged from /root/reference) on identical inputs — SURVEY.md §8(a) rows, §8(d) algorithmic bytes.
+
+    python tools/op_sweep.py [--out gpurun_out/op_sweep.json]
+
+Every line: op, shape, ours ms, reference ms, speed-up, algorithmic bytes, achieved GB/s, fraction of the
+measured HBM peak (MEASURED_PEAKS.json).  The backward of the reference accumulates with float atomics into a
+zeroed buffer; its memset is included in its time (ours writes every element, no memset needed).
+CUDA events on the current (= legacy default) stream, 3 warm-ups, 20 timed iterations."""
+import argparse, ctypes as C, json, os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+import numpy as np, torch
+from geot_b200 import _lib, synth
+from geot_b200 import functional as F
+import refgpu
+
+ap = argparse.ArgumentParser(); ap.add_argument("--out", default=None); args = ap.parse_args()
+try:
+    PEAK = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+except Exception:
+    PEAK = 6650.0
+p = lambda t: C.c_void_p(t.data_ptr()) if t is not None else None
+f32 = lambda v: C.c_float(v)
+rows = []
+
+
+def timeit(fn, it=20):
+    for _ in range(3): fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(it): fn()
+    e1.record(); torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / it
+
+
+def report(op, shape, ours, ref, nbytes, check=None):
+    to = timeit(ours)
+    tr = timeit(ref) if ref is not None else None
+    ok = bool(check()) if check is not None else None
+    gbs = nbytes / to / 1e6
+    rows.append({"op": op, "shape": shape, "ours_ms": to, "ref_ms": tr, "speedup": (tr / to) if tr else None,
+                 "algo_bytes": nbytes, "gbs": gbs, "hbm_frac": gbs / PEAK, "match_ref": ok})
+    print(f"{op:28s} {shape:44s} ours {to:8.4f} ms  ref {tr if tr else float('nan'):8.4f} ms  x{(tr / to) if tr else float('nan'):6.2f}  "
+          f"{gbs:7.0f} GB/s ({100 * gbs / PEAK:5.1f}% HBM)  match={ok}", flush=True)
+
+
+R = refgpu.lib("pn2batch") if refgpu.available("pn2batch") else None
+RF = refgpu.lib("pointops_full") if refgpu.available("pointops_full") else None
+RP = refgpu.lib("pointops") if refgpu.available("pointops") else None
+dev = "cuda"
+i32 = torch.int32
+
+# ---------------------------------------------------------------- batched ops at the bench shape and cfg3-like shapes
+for (B, N, M, ns, Cc, r) in [(64, 16384, 1024, 32, 64, 0.1), (16, 16384, 4096, 32, 32, 0.1), (16, 4096, 1024, 64, 128, 0.4)]:
+    tag = f"B={B} N={N} M={M} ns={ns} C={Cc} r={r}"
+    xyz = torch.from_numpy(synth.tooth_batch(B, N)).to(dev)
+    feat = torch.randn(B, Cc, N, device=dev)
+    temp = torch.full((B, N), 1e10, device=dev)
+    idx = torch.empty((B, M), dtype=i32, device=dev); idx_r = torch.empty_like(idx)
+    report("furthest_point_sample", tag, lambda: F.furthest_point_sampling(xyz, M, out=idx),
+           (lambda: (temp.fill_(1e10), R.ref_furthest_point_sampling(B, N, M, p(xyz), p(temp), p(idx_r)))) if R else None,
+           B * (12 * N + 4 * M), lambda: (idx == idx_r).all())
+    xyz_t = xyz.transpose(1, 2).contiguous()
+    cen_t = torch.empty((B, 3, M), device=dev); cen_r = torch.empty_like(cen_t)
+    report("gather_operation fwd", tag + " (C=3)", lambda: F.gather_points(xyz_t, idx, out=cen_t),
+           (lambda: R.ref_gather_points(B, 3, N, M, p(xyz_t), p(idx), p(cen_r))) if R else None,
+           B * (4 * M + 2 * 12 * M), lambda: (cen_t == cen_r).all())
+    centres = cen_t.transpose(1, 2).contiguous()
+    nbr = torch.empty((B, M, ns), dtype=i32, device=dev); nbr_r = torch.zeros_like(nbr)
+    ws = torch.empty(int(_lib.lib().geot_ball_query_workspace_bytes(B, N)), dtype=torch.uint8, device=dev)
+    report("ball_query", tag, lambda: F.ball_query(centres, xyz, r, ns, out=nbr, workspace=ws),
+           (lambda: (nbr_r.zero_(), R.ref_ball_query(B, N, M, f32(r), ns, p(centres), p(xyz), p(nbr_r)))) if R else None,
+           B * (12 * N + 12 * M + 4 * M * ns), lambda: (nbr == nbr_r).all())
+    g = torch.empty((B, Cc, M, ns), device=dev); g_r = torch.empty_like(g)
+    nb_fwd = B * (4 * M * ns + 4 * Cc * N + 4 * Cc * M * ns)
+    report("grouping_operation fwd", tag, lambda: F.group_points(feat, nbr, out=g),
+           (lambda: R.ref_group_points(B, Cc, N, M, ns, p(feat), p(nbr), p(g_r))) if R else None, nb_fwd, lambda: (g == g_r).all())
+    go = torch.randn(B, Cc, M, ns, device=dev)
+    gp = torch.empty((B, Cc, N), device=dev); gp_r = torch.empty_like(gp)
+    plan = F.ScatterPlan(nbr, B, N)
+    report("grouping_operation bwd", tag + " (plan cached)", lambda: F.group_points_grad(go, plan, N, out=gp),
+           (lambda: (gp_r.zero_(), R.ref_group_points_grad(B, Cc, N, M, ns, p(go), p(nbr), p(gp_r)))) if R else None, nb_fwd,
+           lambda: torch.allclose(gp, gp_r, rtol=1e-4, atol=1e-4))
+    report("scatter plan build", tag, lambda: F.ScatterPlan(nbr, B, N), None, B * (4 * M * ns * 3 + 8 * N))
+    # three_nn / three_interpolate: upsample the M sampled points back to N
+    d2 = torch.empty((B, N, 3), device=dev); i3 = torch.empty((B, N, 3), dtype=i32, device=dev)
+    d2_r = torch.empty_like(d2); i3_r = torch.empty_like(i3)
+    report("three_nn", tag + " (n=N, m=M)", lambda: F.three_nn(xyz, centres, dist2=d2, idx=i3),
+           (lambda: R.ref_three_nn(B, N, M, p(xyz), p(centres), p(d2_r), p(i3_r))) if R else None,
+           B * (12 * N + 12 * M + 24 * N), lambda: (i3 == i3_r).all())
+    w = torch.rand(B, N, 3, device=dev); w = w / w.sum(-1, keepdim=True)
+    pts = torch.randn(B, Cc, M, device=dev)
+    o = torch.empty((B, Cc, N), device=dev); o_r = torch.empty_like(o)
+    nb_ti = B * (24 * N + 4 * Cc * M + 4 * Cc * N)
+    report("three_interpolate fwd", tag, lambda: F.three_interpolate(pts, i3, w, out=o),
+           (lambda: R.ref_three_interpolate(B, Cc, M, N, p(pts), p(i3), p(w), p(o_r))) if R else None, nb_ti,
+           lambda: torch.allclose(o, o_r, rtol=1e-5, atol=1e-6))
+    go3 = torch.randn(B, Cc, N, device=dev)
+    gm = torch.empty((B, Cc, M), device=dev); gm_r = torch.empty_like(gm)
+    plan3 = F.ScatterPlan(i3, B, M)
+    report("three_interpolate bwd", tag + " (plan cached)", lambda: F.three_interpolate_grad(go3, w, plan3, M, out=gm),
+           (lambda: (gm_r.zero_(), R.ref_three_interpolate_grad(B, Cc, N, M, p(go3), p(i3), p(w), p(gm_r)))) if R else None, nb_ti,
+           lambda: torch.allclose(gm, gm_r, rtol=1e-4, atol=1e-3))
+    del xyz, feat, g, g_r, go, gp, gp_r, o, o_r, go3, plan, plan3
+    torch.cuda.empty_cache()
+
+# ---------------------------------------------------------------- offset-format ops (Point-Transformer, cfg2 level 0 / 1)
+for (b, n_per, k, c) in [(8, 16384, 16, 32), (8, 4096, 16, 64)]:
+    n = b * n_per
+    tag = f"b={b} n={n} k={k} c={c}"
+    xyz = torch.from_numpy(synth.tooth_batch(b, n_per)).to(dev).reshape(n, 3).contiguous()
+    off = torch.arange(1, b + 1, device=dev, dtype=i32) * n_per
+    idx = torch.empty((n, k), dtype=i32, device=dev); d = torch.empty((n, k), device=dev)
+    idx_r = torch.zeros_like(idx); d_r = torch.zeros_like(d)
+    report("knnquery (offset)", tag, lambda: F.knnquery(k, xyz, xyz, off, off, idx=idx, dist2=d),
+           (lambda: RP.ref_knnquery(n, k, p(xyz), p(xyz), p(off), p(off), p(idx_r), p(d_r))) if RP else None,
+           24 * n + 8 * n * k, lambda: (idx == idx_r).all())
+    x = torch.randn(n, c, device=dev)
+    o = torch.empty((n, k, c), device=dev); o_r = torch.empty_like(o)
+    nb = 4 * n * k + 4 * n * c + 4 * n * k * c
+    report("pointops.grouping fwd", tag, lambda: F.grouping_forward(x, idx, out=o),
+           (lambda: RF.ref_grouping_forward(n, k, c, p(x), p(idx), p(o_r))) if RF else None, nb, lambda: (o == o_r).all())
+    go = torch.randn(n, k, c, device=dev)
+    gi = torch.empty((n, c), device=dev); gi_r = torch.empty_like(gi)
+    plan = F.ScatterPlan(idx.view(1, n, k), 1, n)
+    report("pointops.grouping bwd", tag + " (plan cached)", lambda: F.grouping_backward(go, plan, n, out=gi),
+           (lambda: (gi_r.zero_(), RF.ref_grouping_backward(n, k, c, p(go), p(idx), p(gi_r)))) if RF else None, nb,
+           lambda: torch.allclose(gi, gi_r, rtol=1e-4, atol=1e-3))
+    del x, o, o_r, go, gi, gi_r, plan
+    torch.cuda.empty_cache()
+
+if args.out:
+    json.dump({"hbm_peak_gbs": PEAK, "rows": rows}, open(args.out, "w"), indent=1)
