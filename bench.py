@@ -106,6 +106,7 @@ def run_reference(args):
     from geot_b200 import synth
     from oracle import cpu_ref as oracle
     oracle.load()
+    oracle.set_num_threads(os.cpu_count() or 1)  # torchrun exports OMP_NUM_THREADS=1
     xyz_h = synth.tooth_batch(B, N)
     feat_h = np.random.default_rng(0).standard_normal((B, C, N)).astype(np.float32)
     for _ in range(args.warmup):
@@ -138,7 +139,18 @@ def run_ours(args):
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+        # NCCL prints its version banner to stdout on the first communicator; stdout must carry ONE JSON line
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
 
     # every rank owns B different clouds (weak scaling, sharded by cloud, no data-path collective)
     xyz_h = torch.from_numpy(synth.tooth_batch(B, N, first_cloud=rank * B)).pin_memory()
@@ -269,6 +281,7 @@ def run_ours(args):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         from oracle import cpu_ref as oracle  # checker/baseline leg only; never on the product path
         oracle.load()
+        oracle.set_num_threads(os.cpu_count() or 1)
         xs, fs = xyz_h.numpy(), feat_h.numpy()
         best = 1e30
         for _ in range(3):

@@ -43,6 +43,9 @@ API int oracle_num_threads(void) {
   return 1;
 #endif
 }
+/* torchrun exports OMP_NUM_THREADS=1; the timed CPU baseline asks for all host threads explicitly. */
+API void oracle_set_num_threads(int n) { if (n > 0) omp_set_num_threads(n); }
+
 
 /* openpoints/cpp/pointnet2_batch/src/cuda_utils.h:10-14 (cap 1024);
  * pointnet2/_ext_src/include/cuda_utils.h:15-21 (cap 512). */

@@ -48,6 +48,11 @@ def num_threads() -> int:
     return int(load().oracle_num_threads())
 
 
+def set_num_threads(n: int) -> None:
+    """torchrun exports OMP_NUM_THREADS=1; the timed CPU baseline (bench.py) asks for all host threads."""
+    load().oracle_set_num_threads(C.c_int(int(n)))
+
+
 def opt_n_threads(n: int, cap: int = 1024) -> int:
     """cuda_utils.h:10-14 block-size rule."""
     return int(load().oracle_opt_n_threads(C.c_int(n), C.c_int(cap)))
