@@ -372,6 +372,56 @@ seg_reduce_cmajor_kernel(int C, int N, int64_t E, const float* __restrict__ g,
     if (i < nc) dst[((int64_t)b * C + c0 + i) * N + t] = acc[i];
 }
 
+// Plan-resident variant for the unweighted channel-major backward (grouping_operation grad) when the whole
+// cloud's plan and one gradient row fit shared memory together (E <= 65535):  a CTA keeps the plan of its cloud
+// in shared memory as 16-bit entries (perm: 2 B per source, row_ptr: 2 B per target - half the bytes of the
+// global plan and read from L2 once per kCPC channels instead of once per channel) and pulls the gradient rows
+// g[b,c,:] of its channels through one shared buffer by bulk async copy.  Every gather of the reduction then
+// hits shared memory: no 32-byte L2 sector per 4-byte element, no global latency inside the segment loops.
+// Summation order = plan order (ascending source), exactly as in the direct kernel: same bits.
+constexpr int kCPC = 4;  // channels per CTA
+__global__ void __launch_bounds__(1024, 1)
+seg_reduce_planrow_kernel(int C, int N, int E, const float* __restrict__ g, const int* __restrict__ row_ptr,
+                          const int* __restrict__ perm, float* __restrict__ dst) {
+  extern __shared__ __align__(16) unsigned char pr_smem[];
+  __shared__ uint64_t bar;
+  float* row = reinterpret_cast<float*>(pr_smem);                                  // E floats
+  unsigned short* perm16 = reinterpret_cast<unsigned short*>(pr_smem + (size_t)E * 4);  // E entries
+  unsigned short* rp16 = perm16 + ((E + 7) & ~7);                                  // N + 1 entries
+  const int t = threadIdx.x;
+  const int b = blockIdx.y, c_first = blockIdx.x * kCPC;
+  if (t == 0) {
+    mbar_init(&bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (t == 0) {
+    mbar_expect_tx(&bar, (unsigned)E * 4u);
+    bulk_g2s(row, g + ((int64_t)b * C + c_first) * E, (unsigned)E * 4u, &bar);
+  }
+  const int* __restrict__ pm = perm + (int64_t)b * E;
+  const int* __restrict__ rp = row_ptr + (int64_t)b * (N + 1);
+  for (int i = t; i < E; i += 1024) perm16[i] = (unsigned short)__ldg(pm + i);
+  for (int i = t; i <= N; i += 1024) rp16[i] = (unsigned short)__ldg(rp + i);
+  __syncthreads();
+  const int nc = min(kCPC, C - c_first);
+  for (int ci = 0; ci < nc; ci++) {
+    mbar_wait(&bar, (unsigned)(ci & 1));
+    float* __restrict__ out = dst + ((int64_t)b * C + c_first + ci) * N;
+    for (int k = t; k < N; k += 1024) {
+      const int s0 = rp16[k], e0 = rp16[k + 1];
+      float acc = 0.f;
+      for (int p = s0; p < e0; p++) acc = __fadd_rn(acc, row[perm16[p]]);
+      out[k] = acc;
+    }
+    __syncthreads();  // every thread is done with the row buffer
+    if (t == 0 && ci + 1 < nc) {
+      mbar_expect_tx(&bar, (unsigned)E * 4u);
+      bulk_g2s(row, g + ((int64_t)b * C + c_first + ci + 1) * E, (unsigned)E * 4u, &bar);
+    }
+  }
+}
+
 template <int DIV, bool WEIGHTED>
 static int launch_seg_reduce(int B, int C, int N, int64_t E, const float* g, const float* w,
                              const void* plan, float* dst, cudaStream_t s, const char* what) {
@@ -379,6 +429,21 @@ static int launch_seg_reduce(int B, int C, int N, int64_t E, const float* g, con
   GEOT_REQUIRE(g && plan && dst, "%s: NULL pointer", what);
   GEOT_REQUIRE(B <= 65535 && (C + kSegCCH - 1) / kSegCCH <= 65535, "%s: B or C exceeds grid limits", what);
   const PlanView pv = plan_view(plan, B, N);
+  if (DIV == 1 && !WEIGHTED && !g_group_force_direct && E <= 65535 && E % 4 == 0 && E >= N && (((uintptr_t)g & 15) == 0)) {
+    const size_t smem = (size_t)E * 4 + (size_t)((E + 7) & ~7) * 2 + (size_t)(N + 1) * 2 + 16;
+    if (smem <= 226 * 1024) {
+      static bool configured = false;
+      if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(seg_reduce_planrow_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+        if (e != cudaSuccess) { set_error("%s: cudaFuncSetAttribute: %s", what, cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
+        configured = true;
+      }
+      dim3 grid((C + kCPC - 1) / kCPC, B);
+      seg_reduce_planrow_kernel<<<grid, 1024, smem, s>>>(C, N, (int)E, g, pv.row_ptr, pv.perm, dst);
+      count_launch(1);
+      return check_launch(what);
+    }
+  }
   dim3 grid((N + 255) / 256, (C + kSegCCH - 1) / kSegCCH, B);
   seg_reduce_cmajor_kernel<DIV, WEIGHTED><<<grid, 256, 0, s>>>(C, N, E, g, w, pv.row_ptr, pv.perm, dst);
   count_launch(1);

@@ -81,6 +81,27 @@ def test_group_points_row_staged_vs_direct(cuda, oracle):
             _lib.lib().geot_group_points_config(0)
 
 
+def test_group_points_grad_plan_resident_vs_direct(cuda, oracle):
+    """E <= 65535 takes the plan-resident backward (16-bit plan + gradient row in shared memory); the direct kernel
+    sums in the same plan order, so the two must agree bit for bit; both match the oracle's double sum to 1e-5."""
+    rng = np.random.default_rng(4)
+    for (B, C, N, M, ns) in [(2, 6, 4096, 512, 32), (1, 5, 16384, 1024, 32), (2, 3, 1000, 250, 16)]:
+        idx = rng.integers(0, N, (B, M, ns)).astype(np.int32)
+        idx[:, : M // 8] = idx[:, : M // 8, :1]  # padded rows: long segments for a few targets
+        g = rng.standard_normal((B, C, M, ns)).astype(np.float32)
+        exp = oracle.grouping_operation_grad(g, idx, N)
+        plan = F.ScatterPlan(cu(idx), B, N)
+        res = []
+        try:
+            for direct in (0, 1):
+                _lib.lib().geot_group_points_config(direct)
+                res.append(F.group_points_grad(cu(g), plan, N))
+        finally:
+            _lib.lib().geot_group_points_config(0)
+        assert torch.equal(res[0], res[1])
+        np.testing.assert_allclose(res[0].cpu().numpy(), exp, rtol=RTOL, atol=1e-4)
+
+
 BALL_CASES = [("tooth", 2, 16384, 1024, 0.1, 32), ("tooth", 2, 4099, 257, 0.2, 64), ("tooth", 3, 1000, 64, 0.05, 16),
               ("quant", 2, 5000, 300, 0.125, 48), ("dup", 1, 2000, 100, 0.1, 8), ("tooth", 1, 30, 5, 0.5, 40)]
 

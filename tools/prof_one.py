@@ -16,6 +16,9 @@ idx = F.furthest_point_sampling(xyz, M)
 xyz_t = xyz.transpose(1, 2).contiguous()
 centres = F.gather_points(xyz_t, idx).transpose(1, 2).contiguous()
 nbr = F.ball_query(centres, xyz, 0.1, NS)
+if what == "groupbwd":
+    go = torch.randn(B, C, M, NS, device="cuda")
+    plan = F.ScatterPlan(nbr, B, N)
 torch.cuda.synchronize()
 for _ in range(3):
     if what == "fps": F.furthest_point_sampling(xyz, M)
@@ -23,4 +26,5 @@ for _ in range(3):
     elif what == "ball": F.ball_query(centres, xyz, 0.1, NS)
     elif what == "group": F.group_points(feat, nbr)
     elif what == "group3": F.group_points(xyz_t, nbr)
+    elif what == "groupbwd": F.group_points_grad(go, plan, N)
 torch.cuda.synchronize()
