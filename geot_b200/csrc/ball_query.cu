@@ -256,10 +256,11 @@ bq_build_kernel(int N, float radius, int nsample, const float* __restrict__ xyz,
     sorted[pos] = make_float4(x, y, z, __int_as_float(k));
   }
   if (t == 0) {
-    // cost model (points visited per query): grid ~ 12*occ (27 cells, ~1/3 occupied on a surface) against the
-    // index-order scan ~ N*nsample/H with H ~ 3*occ hits; occ = points per occupied cell
+    // cost model in units of "points visited by the index-order scan" (calibrated on B200, tools/bq_ab.py): the
+    // 27 cells hold ~34*occ candidate slots (occ = points per occupied cell) at ~1.5x the per-point cost of the
+    // scan, plus ~1000 for the bitmap read-back; the scan visits ~N*nsample/H points for H ~ 3*occ hits
     const float occ = (float)N / (float)max(s_nonempty, 1);
-    const float grid_cost = 12.f * occ + 64.f;
+    const float grid_cost = 51.f * occ + 1000.f;
     const float scan_cost = (float)N * (float)nsample / fmaxf(3.f * occ, (float)nsample);
     hdr->use_grid = (force_grid || grid_cost < scan_cost) ? 1 : 0;
     hdr->dx = dims[0]; hdr->dy = dims[1]; hdr->dz = dims[2];
@@ -280,8 +281,9 @@ bq_grid_kernel(int N, int M, float radius, int nsample, const float* __restrict_
   if (q >= M) return;
   const int* __restrict__ cell_start = reinterpret_cast<const int*>(ws + (size_t)b * ws_stride + 32);
   const float4* __restrict__ sorted = reinterpret_cast<const float4*>(ws + (size_t)b * ws_stride + 32 + bq_cells_bytes());
-  const int wpl = 1 << wpl_log2, nvec = wpl >> 2;  // uint4 per lane
-  uint4* bm = bq_bitmap + (size_t)warp * nvec * 32;  // bm[j*32 + lane] = words lane*wpl + 4j .. +3
+  // bitmap over point indices, word w = index >> 5; step j of the read-back covers words 32j .. 32j+31
+  const int wpl = 1 << wpl_log2, nvec = wpl >> 2;  // words per lane, uint4 per lane
+  uint4* bm = bq_bitmap + (size_t)warp * nvec * 32;
   unsigned* bmw = reinterpret_cast<unsigned*>(bm);
   for (int j = 0; j < nvec; j++) bm[j * 32 + lane] = make_uint4(0u, 0u, 0u, 0u);
 
@@ -301,54 +303,50 @@ bq_grid_kernel(int N, int M, float radius, int nsample, const float* __restrict_
     }
   }
   __syncwarp();
+  auto test = [&](const float4& p) {
+    const float d2 = dist2_ref(qx, qy, qz, p.x, p.y, p.z);
+    if (d2 < r2) {
+      const unsigned k = (unsigned)__float_as_int(p.w);
+      atomicOr(bmw + (k >> 5), 1u << (k & 31u));
+    }
+  };
 #pragma unroll 1
   for (int r = 0; r < 9; r++) {
     const int s = __shfl_sync(0xffffffffu, rs, r), e = __shfl_sync(0xffffffffu, re, r);
-    for (int i = s + lane; i < e; i += 32) {
-      const float4 p = __ldg(sorted + i);
-      const float d2 = dist2_ref(qx, qy, qz, p.x, p.y, p.z);
-      if (d2 < r2) {
-        const unsigned k = (unsigned)__float_as_int(p.w), w = k >> 5;
-        const unsigned ln = w >> wpl_log2, rr = w & (unsigned)(wpl - 1);
-        atomicOr(bmw + ((((rr >> 2) << 5) | ln) << 2 | (rr & 3u)), 1u << (k & 31u));
-      }
+    int i = s + lane;
+    for (; i + 32 < e; i += 64) {  // two candidates per lane in flight
+      const float4 p0 = __ldg(sorted + i), p1 = __ldg(sorted + i + 32);
+      test(p0);
+      test(p1);
     }
+    if (i < e) test(__ldg(sorted + i));
   }
   __syncwarp();
-  // lane l owns words l*wpl .. l*wpl+wpl-1, i.e. indices ascend with (lane, word, bit): count, scan, emit
-  int cnt = 0;
-  for (int j = 0; j < nvec; j++) {
-    const uint4 v = bm[j * 32 + lane];
-    cnt += __popc(v.x) + __popc(v.y) + __popc(v.z) + __popc(v.w);
-  }
-  int inc = cnt;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const int y = __shfl_up_sync(0xffffffffu, inc, o);
-    if (lane >= o) inc += y;
-  }
-  const int total = __shfl_sync(0xffffffffu, inc, 31);
-  int slot = inc - cnt;
+  // read the set bits back in ascending index order, 1024 indices per step, until nsample are out
   int* row = idx + ((int64_t)b * M + q) * nsample;
-  int first = 0x7fffffff;
-  for (int j = 0; j < nvec; j++) {
-    const uint4 v = bm[j * 32 + lane];
-    bm[j * 32 + lane] = make_uint4(0u, 0u, 0u, 0u);
-    const unsigned wd[4] = {v.x, v.y, v.z, v.w};
+  int total = 0, first = 0;
+  for (int j = 0; j < wpl && total < nsample; j++) {
+    unsigned word = bmw[j * 32 + lane];
+    const int cnt = __popc(word);
+    int inc = cnt;
 #pragma unroll
-    for (int c = 0; c < 4; c++) {
-      unsigned word = wd[c];
-      const int base = ((lane << wpl_log2) + 4 * j + c) << 5;
-      if (word && first == 0x7fffffff) first = base + __ffs(word) - 1;
-      while (word && slot < nsample) {
-        row[slot++] = base + __ffs(word) - 1;
-        word &= word - 1;
-      }
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += y;
     }
+    int slot = total + inc - cnt;
+    const int base = (j * 32 + lane) << 5;
+    if (total == 0) {  // the very first hit fills the unused slots (ball_query_gpu.cu:38-42)
+      const unsigned have = __ballot_sync(0xffffffffu, word != 0u);
+      if (have) first = __shfl_sync(0xffffffffu, base + __ffs(word) - 1, __ffs(have) - 1);
+    }
+    while (word && slot < nsample) {
+      row[slot++] = base + __ffs(word) - 1;
+      word &= word - 1;
+    }
+    total += __shfl_sync(0xffffffffu, inc, 31);
   }
-  first = __reduce_min_sync(0xffffffffu, first);
-  const int fill = total > 0 ? first : 0;
-  for (int l = min(total, nsample) + lane; l < nsample; l += 32) row[l] = fill;
+  for (int l = min(total, nsample) + lane; l < nsample; l += 32) row[l] = first;
 }
 
 // Offset format (ragged segments): one warp per query, points straight from global/L2.
