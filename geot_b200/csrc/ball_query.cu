@@ -38,7 +38,10 @@ struct BqHeader {  // grid path (below): per-cloud header at the start of the cl
   int use_grid;
   int dx, dy, dz;
   float lox, loy, loz, inv;
+  int nlev, split;  // index levels: points with index < split are binned separately and searched first
+  int pad[6];
 };
+constexpr int kBqHdrBytes = 64;
 constexpr int kBqTile = 1024;  // points per shared-memory tile (12 KB), two buffers
 
 __device__ __forceinline__ void cp_async4(void* smem, const void* gmem) {
@@ -136,13 +139,16 @@ ball_query_shared_kernel(int N, int M, float radius, int nsample, const float* _
 
 // ---------------------------------------------------------------------------------------------
 // Grid path.  Workspace per cloud: [BqHeader | cell_start (kBqMaxCells+1 ints) | sorted float4 (N)].
+// The reference keeps the nsample LOWEST indices in the ball, so when the ball holds several times nsample
+// points only low indices matter: the points are binned in two index levels (index < N/2 first); a query
+// scans the upper level only if the lower one gave fewer than nsample hits.
 // ---------------------------------------------------------------------------------------------
 constexpr int kBqMaxDim = 32;
 constexpr int kBqMaxCells = kBqMaxDim * kBqMaxDim * kBqMaxDim;
 constexpr int kBqMaxN = 65536;  // bitmap = N bits per warp
 
 __host__ __device__ inline size_t bq_cells_bytes() { return (((size_t)(kBqMaxCells + 1) * 4) + 15) & ~(size_t)15; }
-static inline size_t bq_ws_stride(int N) { return 32 + bq_cells_bytes() + (size_t)N * 16; }
+static inline size_t bq_ws_stride(int N) { return kBqHdrBytes + bq_cells_bytes() + (size_t)N * 16; }
 
 __device__ __forceinline__ int bq_cell(float p, float lo, float inv) { return __float2int_rd((p - lo) * inv); }
 
@@ -157,8 +163,8 @@ bq_build_kernel(int N, float radius, int nsample, const float* __restrict__ xyz,
   const int b = blockIdx.x;
   const float* __restrict__ src = xyz + (int64_t)b * N * 3;
   BqHeader* hdr = reinterpret_cast<BqHeader*>(ws + (size_t)b * ws_stride);
-  int* cell_start = reinterpret_cast<int*>(ws + (size_t)b * ws_stride + 32);
-  float4* sorted = reinterpret_cast<float4*>(ws + (size_t)b * ws_stride + 32 + bq_cells_bytes());
+  int* cell_start = reinterpret_cast<int*>(ws + (size_t)b * ws_stride + kBqHdrBytes);
+  float4* sorted = reinterpret_cast<float4*>(ws + (size_t)b * ws_stride + kBqHdrBytes + bq_cells_bytes());
   const float kInf = __int_as_float(0x7f800000);
 
   float lo[3] = {kInf, kInf, kInf}, hi[3] = {-kInf, -kInf, -kInf};
@@ -204,34 +210,41 @@ bq_build_kernel(int N, float radius, int nsample, const float* __restrict__ xyz,
   int dims[3];
 #pragma unroll
   for (int a = 0; a < 3; a++) dims[a] = min(kBqMaxDim, max(1, bq_cell(hi[a], lo[a], inv) + 1));
-  const int ncell = dims[0] * dims[1] * dims[2];
-  auto code_of = [&](float x, float y, float z) -> int {
+  const int ncells1 = dims[0] * dims[1] * dims[2];
+  const int nlev = (2 * ncells1 <= kBqMaxCells && N >= 2048) ? 2 : 1;
+  const int split = nlev == 2 ? ((N / 2 + 31) & ~31) : N;
+  const int ncell = nlev * ncells1;  // sort keys: level-major, then cell
+  auto code_of = [&](float x, float y, float z, int k) -> int {
     const int cx = min(max(bq_cell(x, lo[0], inv), 0), dims[0] - 1);
     const int cy = min(max(bq_cell(y, lo[1], inv), 0), dims[1] - 1);
     const int cz = min(max(bq_cell(z, lo[2], inv), 0), dims[2] - 1);
-    return (cz * dims[1] + cy) * dims[0] + cx;
+    return (k >= split ? ncells1 : 0) + (cz * dims[1] + cy) * dims[0] + cx;
   };
   for (int i = t; i < ncell; i += 1024) bq_hist[i] = 0;
   __syncthreads();
 #pragma unroll 4
   for (int k = t; k < N; k += 1024)
-    atomicAdd(&bq_hist[code_of(src[(int64_t)k * 3], src[(int64_t)k * 3 + 1], src[(int64_t)k * 3 + 2])], 1);
+    atomicAdd(&bq_hist[code_of(src[(int64_t)k * 3], src[(int64_t)k * 3 + 1], src[(int64_t)k * 3 + 2], k)], 1);
   __syncthreads();
+  {  // occupied cells (either level) for the cost model
+    int ne1 = 0;
+    for (int i = t; i < ncells1; i += 1024) ne1 += (bq_hist[i] + (nlev == 2 ? bq_hist[i + ncells1] : 0)) > 0;
+    ne1 = __reduce_add_sync(0xffffffffu, ne1);
+    if (lane == 0 && ne1) atomicAdd(&s_nonempty, ne1);
+  }
   // exclusive scan over ncell counters, 1024 threads x PER consecutive entries
   {
     const int PER = (ncell + 1023) / 1024;
     const int i0 = t * PER;
-    int sum = 0, ne = 0;
-    for (int i = i0; i < min(i0 + PER, ncell); i++) { const int v = bq_hist[i]; sum += v; ne += v > 0; }
+    int sum = 0;
+    for (int i = i0; i < min(i0 + PER, ncell); i++) sum += bq_hist[i];
     int inc = sum;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
       const int y = __shfl_up_sync(0xffffffffu, inc, o);
       if (lane >= o) inc += y;
     }
-    ne = __reduce_add_sync(0xffffffffu, ne);
     if (lane == 31) s_scan[warp] = inc;
-    if (lane == 0 && ne) atomicAdd(&s_nonempty, ne);
     __syncthreads();
     int wtot = s_scan[lane], winc = wtot;
 #pragma unroll
@@ -252,19 +265,22 @@ bq_build_kernel(int N, float radius, int nsample, const float* __restrict__ xyz,
 #pragma unroll 4
   for (int k = t; k < N; k += 1024) {
     const float x = src[(int64_t)k * 3], y = src[(int64_t)k * 3 + 1], z = src[(int64_t)k * 3 + 2];
-    const int pos = atomicAdd(&bq_hist[code_of(x, y, z)], 1);
+    const int pos = atomicAdd(&bq_hist[code_of(x, y, z, k)], 1);
     sorted[pos] = make_float4(x, y, z, __int_as_float(k));
   }
   if (t == 0) {
     // cost model in units of "points visited by the index-order scan" (calibrated on B200, tools/bq_ab.py): the
     // 27 cells hold ~34*occ candidate slots (occ = points per occupied cell) at ~1.5x the per-point cost of the
-    // scan, plus ~1000 for the bitmap read-back; the scan visits ~N*nsample/H points for H ~ 3*occ hits
+    // scan, plus ~600 for the bitmap read-back; the scan visits ~N*nsample/H points for H ~ 3*occ hits
     const float occ = (float)N / (float)max(s_nonempty, 1);
-    const float grid_cost = 51.f * occ + 1000.f;
-    const float scan_cost = (float)N * (float)nsample / fmaxf(3.f * occ, (float)nsample);
+    const float hits = 3.f * occ;
+    const float lower_only = (nlev == 2 && 0.5f * hits >= 1.3f * (float)nsample) ? 0.5f : 1.f;  // upper level rarely needed
+    const float grid_cost = 51.f * occ * lower_only + 600.f;
+    const float scan_cost = (float)N * (float)nsample / fmaxf(hits, (float)nsample);
     hdr->use_grid = (force_grid || grid_cost < scan_cost) ? 1 : 0;
     hdr->dx = dims[0]; hdr->dy = dims[1]; hdr->dz = dims[2];
     hdr->lox = lo[0]; hdr->loy = lo[1]; hdr->loz = lo[2]; hdr->inv = inv;
+    hdr->nlev = nlev; hdr->split = split;
   }
 }
 
@@ -279,8 +295,8 @@ bq_grid_kernel(int N, int M, float radius, int nsample, const float* __restrict_
   if (!hdr.use_grid) return;
   const int q = blockIdx.x * 8 + warp;
   if (q >= M) return;
-  const int* __restrict__ cell_start = reinterpret_cast<const int*>(ws + (size_t)b * ws_stride + 32);
-  const float4* __restrict__ sorted = reinterpret_cast<const float4*>(ws + (size_t)b * ws_stride + 32 + bq_cells_bytes());
+  const int* __restrict__ cell_start = reinterpret_cast<const int*>(ws + (size_t)b * ws_stride + kBqHdrBytes);
+  const float4* __restrict__ sorted = reinterpret_cast<const float4*>(ws + (size_t)b * ws_stride + kBqHdrBytes + bq_cells_bytes());
   // bitmap over point indices, word w = index >> 5; step j of the read-back covers words 32j .. 32j+31
   const int wpl = 1 << wpl_log2, nvec = wpl >> 2;  // words per lane, uint4 per lane
   uint4* bm = bq_bitmap + (size_t)warp * nvec * 32;
@@ -291,15 +307,19 @@ bq_grid_kernel(int N, int M, float radius, int nsample, const float* __restrict_
   const float qx = qp[0], qy = qp[1], qz = qp[2];
   const float r2 = __fmul_rn(radius, radius);
   const int cx = bq_cell(qx, hdr.lox, hdr.inv), cy = bq_cell(qy, hdr.loy, hdr.inv), cz = bq_cell(qz, hdr.loz, hdr.inv);
-  // lanes 0..8 fetch the 9 runs (3 x-adjacent cells are contiguous in the sorted order) in one round trip
+  // lanes 0..8 (lower index level) and 16..24 (upper level) fetch the 9 runs of their level in one round trip
+  // (3 x-adjacent cells are contiguous in the sorted order)
   int rs = 0, re = 0;
-  if (lane < 9) {
-    const int z = cz + lane / 3 - 1, y = cy + lane % 3 - 1;
-    const int x0 = max(cx - 1, 0), x1 = min(cx + 1, hdr.dx - 1);
-    if (z >= 0 && z < hdr.dz && y >= 0 && y < hdr.dy && x0 <= x1) {
-      const int c0 = (z * hdr.dy + y) * hdr.dx + x0;
-      rs = __ldg(cell_start + c0);
-      re = __ldg(cell_start + c0 + (x1 - x0) + 1);
+  {
+    const int l9 = lane & 15, lev = lane >> 4;
+    if (l9 < 9 && lev < hdr.nlev) {
+      const int z = cz + l9 / 3 - 1, y = cy + l9 % 3 - 1;
+      const int x0 = max(cx - 1, 0), x1 = min(cx + 1, hdr.dx - 1);
+      if (z >= 0 && z < hdr.dz && y >= 0 && y < hdr.dy && x0 <= x1) {
+        const int c0 = lev * hdr.dx * hdr.dy * hdr.dz + (z * hdr.dy + y) * hdr.dx + x0;
+        rs = __ldg(cell_start + c0);
+        re = __ldg(cell_start + c0 + (x1 - x0) + 1);
+      }
     }
   }
   __syncwarp();
@@ -310,18 +330,25 @@ bq_grid_kernel(int N, int M, float radius, int nsample, const float* __restrict_
       atomicOr(bmw + (k >> 5), 1u << (k & 31u));
     }
   };
-#pragma unroll 1
-  for (int r = 0; r < 9; r++) {
-    const int s = __shfl_sync(0xffffffffu, rs, r), e = __shfl_sync(0xffffffffu, re, r);
-    int i = s + lane;
-    for (; i + 32 < e; i += 64) {  // two candidates per lane in flight
-      const float4 p0 = __ldg(sorted + i), p1 = __ldg(sorted + i + 32);
-      test(p0);
-      test(p1);
+  for (int lev = 0; lev < hdr.nlev; lev++) {
+    if (lev == 1) {  // upper level only if the lower one left the row short
+      int c0 = 0;
+      for (int j = 0; (j << 10) < hdr.split; j++) c0 += __popc(bmw[j * 32 + lane]);
+      if (__reduce_add_sync(0xffffffffu, c0) >= nsample) break;
     }
-    if (i < e) test(__ldg(sorted + i));
+#pragma unroll 1
+    for (int r = 0; r < 9; r++) {
+      const int s = __shfl_sync(0xffffffffu, rs, r + 16 * lev), e = __shfl_sync(0xffffffffu, re, r + 16 * lev);
+      int i = s + lane;
+      for (; i + 32 < e; i += 64) {  // two candidates per lane in flight
+        const float4 p0 = __ldg(sorted + i), p1 = __ldg(sorted + i + 32);
+        test(p0);
+        test(p1);
+      }
+      if (i < e) test(__ldg(sorted + i));
+    }
+    __syncwarp();
   }
-  __syncwarp();
   // read the set bits back in ascending index order, 1024 indices per step, until nsample are out
   int* row = idx + ((int64_t)b * M + q) * nsample;
   int total = 0, first = 0;
