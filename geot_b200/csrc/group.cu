@@ -82,6 +82,16 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned by
                ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
+// One logical row copy issued as several bulk copies (all completing on the same mbarrier): a single large
+// cp.async.bulk keeps too few lines in flight to pull a 128 KB row at the SM's share of HBM bandwidth.
+__device__ __forceinline__ void bulk_g2s_chunked(float* dst, const float* src, unsigned bytes, uint64_t* bar) {
+  constexpr unsigned kPiece = 8192;
+  mbar_expect_tx(bar, bytes);
+  for (unsigned o = 0; o < bytes; o += kPiece)
+    bulk_g2s(reinterpret_cast<unsigned char*>(dst) + o, reinterpret_cast<const unsigned char*>(src) + o,
+             min(kPiece, bytes - o), bar);
+}
+
 constexpr int kRowThreads = 512;
 __global__ void __launch_bounds__(kRowThreads)
 group_rows_kernel(int C, int N, int64_t E, const float* __restrict__ points, const int* __restrict__ idx,
@@ -97,8 +107,7 @@ group_rows_kernel(int C, int N, int64_t E, const float* __restrict__ points, con
   }
   __syncthreads();
   if (t == 0) {
-    mbar_expect_tx(&bar, (unsigned)N * 4u);
-    bulk_g2s(g_row, points + rowi * N, (unsigned)N * 4u, &bar);
+    bulk_g2s_chunked(g_row, points + rowi * N, (unsigned)N * 4u, &bar);
   }
   const int4* __restrict__ idp = reinterpret_cast<const int4*>(idx + (int64_t)b * E);
   float4* __restrict__ op = reinterpret_cast<float4*>(out + rowi * E);
@@ -375,49 +384,101 @@ seg_reduce_cmajor_kernel(int C, int N, int64_t E, const float* __restrict__ g,
 // Plan-resident variant for the unweighted channel-major backward (grouping_operation grad) when the whole
 // cloud's plan and one gradient row fit shared memory together (E <= 65535):  a CTA keeps the plan of its cloud
 // in shared memory as 16-bit entries (perm: 2 B per source, row_ptr: 2 B per target - half the bytes of the
-// global plan and read from L2 once per kCPC channels instead of once per channel) and pulls the gradient rows
+// global plan and read from L2 once per 4-8 channels instead of once per channel) and pulls the gradient rows
 // g[b,c,:] of its channels through one shared buffer by bulk async copy.  Every gather of the reduction then
 // hits shared memory: no 32-byte L2 sector per 4-byte element, no global latency inside the segment loops.
 // Summation order = plan order (ascending source), exactly as in the direct kernel: same bits.
-constexpr int kCPC = 4;  // channels per CTA
+constexpr int kPrTaskCap = 5456;  // non-empty targets the compact task list can hold (6 bytes each in 32 KB)
 __global__ void __launch_bounds__(1024, 1)
-seg_reduce_planrow_kernel(int C, int N, int E, const float* __restrict__ g, const int* __restrict__ row_ptr,
+seg_reduce_planrow_kernel(int C, int N, int E, int cpc, const float* __restrict__ g, const int* __restrict__ row_ptr,
                           const int* __restrict__ perm, float* __restrict__ dst) {
   extern __shared__ __align__(16) unsigned char pr_smem[];
   __shared__ uint64_t bar;
-  float* row = reinterpret_cast<float*>(pr_smem);                                  // E floats
+  __shared__ int s_bin[64], s_ne;
+  float* row = reinterpret_cast<float*>(pr_smem);                                        // E floats
   unsigned short* perm16 = reinterpret_cast<unsigned short*>(pr_smem + (size_t)E * 4);  // E entries
-  unsigned short* rp16 = perm16 + ((E + 7) & ~7);                                  // N + 1 entries
-  const int t = threadIdx.x;
-  const int b = blockIdx.y, c_first = blockIdx.x * kCPC;
+  // 32 KB that hold EITHER row_ptr as 16-bit (general case) OR the compact task list {target, start, length} of
+  // the non-empty targets ordered by descending length (sparse case, see below)
+  unsigned short* rp16 = perm16 + ((E + 7) & ~7);
+  unsigned short* t_tgt = rp16;
+  unsigned short* t_start = rp16 + kPrTaskCap;
+  unsigned short* t_len = rp16 + 2 * kPrTaskCap;
+  const int t = threadIdx.x, lane = t & 31;
+  const int b = blockIdx.y, c_first = blockIdx.x * cpc;
   if (t == 0) {
     mbar_init(&bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    s_ne = 0;
   }
+  if (t < 64) s_bin[t] = 0;
   __syncthreads();
   if (t == 0) {
-    mbar_expect_tx(&bar, (unsigned)E * 4u);
-    bulk_g2s(row, g + ((int64_t)b * C + c_first) * E, (unsigned)E * 4u, &bar);
+    bulk_g2s_chunked(row, g + ((int64_t)b * C + c_first) * E, (unsigned)E * 4u, &bar);
   }
   const int* __restrict__ pm = perm + (int64_t)b * E;
   const int* __restrict__ rp = row_ptr + (int64_t)b * (N + 1);
   for (int i = t; i < E; i += 1024) perm16[i] = (unsigned short)__ldg(pm + i);
-  for (int i = t; i <= N; i += 1024) rp16[i] = (unsigned short)__ldg(rp + i);
+  // ball_query keeps the LOWEST indices of every ball, so most points are never a neighbour (80 % of the targets
+  // are empty at the bench shape) and the rest have ~10 sources.  When the non-empty targets fit the task list
+  // they are bucketed by segment length (64 bins, longest first): a warp then works on 32 segments of (almost)
+  // equal length - no empty targets, no divergence on the segment loop.
+  for (int k = t; k < N; k += 1024) {
+    const int len = __ldg(rp + k + 1) - __ldg(rp + k);
+    if (len > 0) atomicAdd(&s_bin[63 - min(len, 63)], 1);
+  }
   __syncthreads();
-  const int nc = min(kCPC, C - c_first);
-  for (int ci = 0; ci < nc; ci++) {
-    mbar_wait(&bar, (unsigned)(ci & 1));
-    float* __restrict__ out = dst + ((int64_t)b * C + c_first + ci) * N;
+  if (t < 32) {  // exclusive scan of the 64 bins (bin 0 = longest)
+    const int a0 = s_bin[2 * lane], a1 = s_bin[2 * lane + 1];
+    int inc = a0 + a1;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += y;
+    }
+    s_bin[2 * lane] = inc - a0 - a1;
+    s_bin[2 * lane + 1] = inc - a1;
+    if (lane == 31) s_ne = inc;
+  }
+  __syncthreads();
+  const int ne = s_ne;
+  const bool compact = ne <= kPrTaskCap;
+  if (compact) {
     for (int k = t; k < N; k += 1024) {
-      const int s0 = rp16[k], e0 = rp16[k + 1];
-      float acc = 0.f;
-      for (int p = s0; p < e0; p++) acc = __fadd_rn(acc, row[perm16[p]]);
-      out[k] = acc;
+      const int s0 = __ldg(rp + k), len = __ldg(rp + k + 1) - s0;
+      if (len > 0) {
+        const int pos = atomicAdd(&s_bin[63 - min(len, 63)], 1);  // order inside a bin is free: sums do not depend on it
+        t_tgt[pos] = (unsigned short)k; t_start[pos] = (unsigned short)s0; t_len[pos] = (unsigned short)len;
+      }
+    }
+  } else {
+    for (int i = t; i <= N; i += 1024) rp16[i] = (unsigned short)__ldg(rp + i);
+  }
+  __syncthreads();
+  const int nc = min(cpc, C - c_first);
+  for (int ci = 0; ci < nc; ci++) {
+    float* __restrict__ out = dst + ((int64_t)b * C + c_first + ci) * N;
+    if (compact) {
+      for (int k = t; k < N; k += 1024) out[k] = 0.f;  // empty targets; the others are overwritten below
+      mbar_wait(&bar, (unsigned)(ci & 1));
+      __syncthreads();  // zero fill ordered before the sums of this CTA
+      for (int i = t; i < ne; i += 1024) {
+        const int s0 = t_start[i], e0 = s0 + t_len[i];
+        float acc = 0.f;
+        for (int p = s0; p < e0; p++) acc = __fadd_rn(acc, row[perm16[p]]);
+        out[t_tgt[i]] = acc;
+      }
+    } else {
+      mbar_wait(&bar, (unsigned)(ci & 1));
+      for (int k = t; k < N; k += 1024) {
+        const int s0 = rp16[k], e0 = rp16[k + 1];
+        float acc = 0.f;
+        for (int p = s0; p < e0; p++) acc = __fadd_rn(acc, row[perm16[p]]);
+        out[k] = acc;
+      }
     }
     __syncthreads();  // every thread is done with the row buffer
     if (t == 0 && ci + 1 < nc) {
-      mbar_expect_tx(&bar, (unsigned)E * 4u);
-      bulk_g2s(row, g + ((int64_t)b * C + c_first + ci + 1) * E, (unsigned)E * 4u, &bar);
+      bulk_g2s_chunked(row, g + ((int64_t)b * C + c_first + ci + 1) * E, (unsigned)E * 4u, &bar);
     }
   }
 }
@@ -430,7 +491,7 @@ static int launch_seg_reduce(int B, int C, int N, int64_t E, const float* g, con
   GEOT_REQUIRE(B <= 65535 && (C + kSegCCH - 1) / kSegCCH <= 65535, "%s: B or C exceeds grid limits", what);
   const PlanView pv = plan_view(plan, B, N);
   if (DIV == 1 && !WEIGHTED && !g_group_force_direct && E <= 65535 && E % 4 == 0 && E >= N && (((uintptr_t)g & 15) == 0)) {
-    const size_t smem = (size_t)E * 4 + (size_t)((E + 7) & ~7) * 2 + (size_t)(N + 1) * 2 + 16;
+    const size_t smem = (size_t)E * 4 + (size_t)((E + 7) & ~7) * 2 + std::max((size_t)(N + 1) * 2, (size_t)kPrTaskCap * 6) + 16;
     if (smem <= 226 * 1024) {
       static bool configured = false;
       if (!configured) {
@@ -438,8 +499,17 @@ static int launch_seg_reduce(int B, int C, int N, int64_t E, const float* g, con
         if (e != cudaSuccess) { set_error("%s: cudaFuncSetAttribute: %s", what, cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
         configured = true;
       }
-      dim3 grid((C + kCPC - 1) / kCPC, B);
-      seg_reduce_planrow_kernel<<<grid, 1024, smem, s>>>(C, N, (int)E, g, pv.row_ptr, pv.perm, dst);
+      // channels per CTA: amortise the per-CTA plan setup (~0.8 of a row) without leaving the last wave half empty
+      int cpc = 4;
+      double best = 0.0;
+      for (int k = 4; k <= 8; k++) {
+        const double ctas = (double)B * ((C + k - 1) / k);
+        const double waves = std::ceil(ctas / kNumSMs);
+        const double score = ctas / (waves * kNumSMs) * k / (k + 0.8);
+        if (score > best) { best = score; cpc = k; }
+      }
+      dim3 grid((C + cpc - 1) / cpc, B);
+      seg_reduce_planrow_kernel<<<grid, 1024, smem, s>>>(C, N, (int)E, cpc, g, pv.row_ptr, pv.perm, dst);
       count_launch(1);
       return check_launch(what);
     }

@@ -205,6 +205,19 @@ def test_scatter_plan_is_stable_csr(cuda):
         assert np.array_equal(rp[b], np.concatenate([[0], np.cumsum(np.bincount(idx[b], minlength=N))]))
 
 
+def test_scatter_plan_large_universe_heavy_segments(cuda):
+    """E > 2^20: the CTA bitmap sort of long segments walks the source universe in two chunks."""
+    rng = np.random.default_rng(7)
+    B, N, E = 1, 3000, (1 << 20) + 70001
+    idx = rng.integers(0, N, (B, E)).astype(np.int32)
+    idx[0, rng.random(E) < 0.2] = 0      # ~2e5 sources on target 0
+    idx[0, -5000:] = N - 1               # a long segment made of the highest sources
+    plan = F.ScatterPlan(cu(idx), B, N)
+    rp, pm = plan.row_ptr().cpu().numpy(), plan.perm().cpu().numpy()
+    assert np.array_equal(pm[0], np.argsort(idx[0], kind="stable").astype(np.int32))
+    assert np.array_equal(rp[0], np.concatenate([[0], np.cumsum(np.bincount(idx[0], minlength=N))]))
+
+
 @pytest.mark.parametrize("B,C,N,M", [(2, 3, 16384, 1024), (2, 67, 999, 130), (1, 4, 8, 8)])
 def test_gather_points_fwd_bwd(cuda, oracle, B, C, N, M):
     rng = np.random.default_rng(7)
