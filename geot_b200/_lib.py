@@ -20,6 +20,7 @@ GEOT_FPS_MAGSKIP = 2
 GEOT_FPS_FORCE_GENERIC = 4
 GEOT_FPS_NO_PRUNE = 8
 GEOT_BQ_FORCE_GRID = 1
+GEOT_KNN_NO_GRID = 1
 
 _vp, _i, _f, _i64, _sz = C.c_void_p, C.c_int, C.c_float, C.c_int64, C.c_size_t
 
@@ -33,8 +34,8 @@ _SIGNATURES = {
     "geot_ball_query_workspace_bytes": [_i, _i],
     "geot_ball_query": [_i, _i, _i, _f, _i, _vp, _vp, _vp, _vp, _sz, _i, _vp],
     "geot_ballquery_offset": [_i, _i, _f, _i, _vp, _vp, _vp, _vp, _vp, _vp],
-    "geot_knnquery_workspace_bytes": [_i],
-    "geot_knnquery": [_i, _i, _i, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _sz, _vp],
+    "geot_knnquery_workspace_bytes": [_i, _i, _i],
+    "geot_knnquery": [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _sz, _i, _vp],
     "geot_group_points": [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp],
     "geot_gather_points": [_i, _i, _i, _i, _vp, _vp, _vp, _vp],
     "geot_group_points_config": [_i],

@@ -92,7 +92,7 @@ def ballquery_offset(radius, nsample, xyz, new_xyz, offset, new_offset, out=None
     return out
 
 
-def knnquery(nsample, xyz, new_xyz, offset=None, new_offset=None, n_per=0, m_per=None, idx=None, dist2=None):
+def knnquery(nsample, xyz, new_xyz, offset=None, new_offset=None, n_per=0, m_per=None, idx=None, dist2=None, flags=0):
     """k nearest in the same segment: GLOBAL int32 idx (m,k), SQUARED dist2 (m,k), ascending.
 
     offset/new_offset given: offset format (ragged).  Otherwise batched: xyz is (b*n_per,3) and
@@ -110,9 +110,10 @@ def knnquery(nsample, xyz, new_xyz, offset=None, new_offset=None, n_per=0, m_per
             idx = torch.empty((m, nsample), dtype=_i32, device=dev)
         if dist2 is None:
             dist2 = torch.empty((m, nsample), dtype=_f32, device=dev)
-        ws_bytes = int(_lib.lib().geot_knnquery_workspace_bytes(m))
+        n = xyz.shape[0]
+        ws_bytes = int(_lib.lib().geot_knnquery_workspace_bytes(b, n, m))
         ws = torch.empty((max(ws_bytes, 1),), dtype=torch.uint8, device=dev)
-        call("geot_knnquery", b, m, nsample, ptr(xyz), ptr(new_xyz), ptr(offset), ptr(new_offset), n_per, max(m_per, 1), ptr(idx), ptr(dist2), ptr(ws), ws_bytes, stream_ptr())
+        call("geot_knnquery", b, n, m, nsample, ptr(xyz), ptr(new_xyz), ptr(offset), ptr(new_offset), n_per, max(m_per, 1), ptr(idx), ptr(dist2), ptr(ws), ws_bytes, int(flags), stream_ptr())
     return idx, dist2
 
 

@@ -104,12 +104,16 @@ int geot_ballquery_offset(int b, int m, float radius, int nsample, const float* 
  * With offset == new_offset == NULL the inputs are batched: b clouds of n_per xyz points and m_per
  * queries each (the layout of pointops.knn / knn_cuda.KNN / knn_point), indices stay GLOBAL.
  * In the offset layout m_per must be an upper bound of the queries of any one segment (m always is).
- * workspace: geot_knnquery_workspace_bytes(m) bytes of scratch (per-query tie flags).
+ * n = total number of xyz points (offset[b-1] in the offset layout, b*n_per batched), m = total queries.
+ * workspace: geot_knnquery_workspace_bytes(b, n, m) bytes of scratch (per-query redo flags; for segments
+ * of >= 3072 points a uniform grid per segment: cell table + points sorted by cell).
+ * flags: GEOT_KNN_NO_GRID forces the brute-force scan for every segment (testing / A-B timing; same results).
  * --------------------------------------------------------------------------------------------- */
-size_t geot_knnquery_workspace_bytes(int m);
-int geot_knnquery(int b, int m, int nsample, const float* xyz, const float* new_xyz,
+#define GEOT_KNN_NO_GRID 1
+size_t geot_knnquery_workspace_bytes(int b, int n, int m);
+int geot_knnquery(int b, int n, int m, int nsample, const float* xyz, const float* new_xyz,
                   const int* offset, const int* new_offset, int n_per, int m_per, int* idx,
-                  float* dist2, void* workspace, size_t workspace_bytes, geot_stream_t stream);
+                  float* dist2, void* workspace, size_t workspace_bytes, int flags, geot_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Grouping / gather (channel-major, batched).

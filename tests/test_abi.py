@@ -47,7 +47,7 @@ def test_argument_validation_returns_error_not_exit():
     L = _lib.lib()
     rc = L.geot_furthest_point_sampling(1, 16, 4, None, None, None, 0, None)
     assert rc == -1 and b"NULL" in L.geot_last_error()
-    rc = L.geot_knnquery(1, 4, 0, None, None, None, None, 4, 4, None, None, None, 0, None)
+    rc = L.geot_knnquery(1, 4, 4, 0, None, None, None, None, 4, 4, None, None, None, 0, 0, None)
     assert rc == -1 and b"nsample" in L.geot_last_error()
 
 

@@ -157,9 +157,49 @@ def test_knnquery_offset(cuda, oracle, kind, k):
     starts = np.concatenate([[0], off[:-1]])
     q = np.concatenate([xyz[s:s + m] + (0 if kind != "tooth" else 1e-3) for s, m in zip(starts, ms)]).astype(np.float32)
     ei, _, ed2 = oracle.knnquery(k, xyz, q, off, noff)
-    gi, gd2 = F.knnquery(k, cu(xyz), cu(q), cu(off), cu(noff))
-    assert np.array_equal(gd2.cpu().numpy(), ed2)
-    assert np.array_equal(gi.cpu().numpy(), ei)
+    for flags in (0, _lib.GEOT_KNN_NO_GRID):  # segments 0 and 2 take the grid path unless it is switched off
+        gi, gd2 = F.knnquery(k, cu(xyz), cu(q), cu(off), cu(noff), flags=flags)
+        assert np.array_equal(gd2.cpu().numpy(), ed2)
+        assert np.array_equal(gi.cpu().numpy(), ei)
+
+
+@pytest.mark.parametrize("kind", ["tooth", "uniform", "dup", "quant"])
+@pytest.mark.parametrize("k", [1, 8, 16, 33, 100])
+def test_knnquery_grid_vs_scan(cuda, kind, k):
+    """Grid path (segments >= 2048 points) against the brute-force scan of the same library at sizes the CPU
+    oracle does not finish quickly: self-queries (distance 0), queries off the surface and far outside the
+    bounding box (they fall through both rings and are redone exactly), ragged segment sizes."""
+    rng = np.random.default_rng(k)
+    sizes = [16384, 2048, 7001, 1500]
+    if kind == "uniform":
+        xyz = np.concatenate([rng.random((n, 3), dtype=np.float32) * np.float32(1 + i) for i, n in enumerate(sizes)])
+    else:
+        xyz = np.concatenate([clouds(kind, 1, n, seed=10 + i)[0] for i, n in enumerate(sizes)])
+    off = np.cumsum(sizes).astype(np.int32)
+    q = xyz.copy()
+    q[::7] += rng.normal(0, 0.05, (len(q[::7]), 3)).astype(np.float32)
+    q[5::101] += np.float32(3.0)
+    q[9::211] *= np.float32(-20.0)
+    a_i, a_d = F.knnquery(k, cu(xyz), cu(q), cu(off), cu(off))
+    b_i, b_d = F.knnquery(k, cu(xyz), cu(q), cu(off), cu(off), flags=_lib.GEOT_KNN_NO_GRID)
+    assert torch.equal(a_d, b_d)
+    assert torch.equal(a_i, b_i)
+
+
+def test_knnquery_grid_degenerate_clouds(cuda, oracle):
+    """All points identical / on a line / on a plane: the grid collapses to 1 cell in the flat axes."""
+    n, k = 3000, 9
+    rng = np.random.default_rng(0)
+    same = np.tile(np.float32([0.3, -1.0, 2.0]), (n, 1))
+    line = np.zeros((n, 3), np.float32); line[:, 0] = rng.random(n, dtype=np.float32)
+    plane = rng.random((n, 3), dtype=np.float32); plane[:, 2] = 0.5
+    for xyz in (same, line, plane):
+        off = np.array([n], np.int32)
+        q = xyz[:200] + np.float32(1e-3)
+        noff = np.array([200], np.int32)
+        ei, _, ed2 = oracle.knnquery(k, xyz, q, off, noff)
+        gi, gd2 = F.knnquery(k, cu(xyz), cu(q), cu(off), cu(noff))
+        assert np.array_equal(gd2.cpu().numpy(), ed2) and np.array_equal(gi.cpu().numpy(), ei)
 
 
 def test_knnquery_batched_layout(cuda, oracle):
