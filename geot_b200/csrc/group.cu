@@ -325,6 +325,7 @@ plan_sort_heavy_kernel(int N, int64_t E, const int* __restrict__ row_ptr, const 
   }
 }
 
+static inline size_t plan_align(size_t b) { return (b + 255) & ~(size_t)255; }
 struct PlanView {
   const int* row_ptr;
   const int* perm;
@@ -520,9 +521,142 @@ static int launch_seg_reduce(int B, int C, int N, int64_t E, const float* g, con
   return check_launch(what);
 }
 
+// ---------------------------------------------------------------------------------------------
+// three_interpolate backward, row-resident:  dst[b,c,k] = sum_{p in seg(b,k)} w[b,perm[p]] * g[b,c,perm[p]/3].
+// The direct kernel above gathers g and w per edge from L2 (one 32-byte sector per 4-byte value, ~5 % of HBM
+// peak at the bench shape).  Here (1) the weights are put into plan order once per call (wsort, into the plan
+// workspace's build scratch), so a segment's {perm, w} are two contiguous runs, and (2) a CTA keeps R gradient
+// rows g[b,c..c+R,:] in shared memory (one bulk async copy), walks the m segments with 8 lanes per target
+// - four targets in flight per warp, edges streamed coalesced from L2 once per R channels - and gathers from
+// shared memory.  Per-target sums: lane-strided partial sums then a fixed xor tree, i.e. a fixed order
+// (run-to-run identical); results leave through a shared staging row as coalesced stores.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+plan_wsort_kernel(int64_t E, const float* __restrict__ w, const int* __restrict__ perm, float* __restrict__ wsorted) {
+  const int64_t e = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (e >= E) return;
+  const int64_t base = (int64_t)blockIdx.y * E;
+  wsorted[base + e] = __ldg(w + base + __ldg(perm + base + e));
+}
+
+template <int R>
+__global__ void __launch_bounds__(1024, 1)
+seg_reduce_wrows_kernel(int C, int n, int m, const float* __restrict__ g, const int* __restrict__ row_ptr,
+                        const int* __restrict__ perm, const float* __restrict__ wsorted, float* __restrict__ dst) {
+  extern __shared__ __align__(16) unsigned char wr_smem[];
+  __shared__ uint64_t bar;
+  float* rows = reinterpret_cast<float*>(wr_smem);          // R x n
+  float* outs = rows + (size_t)R * n;                       // R x m
+  int* rp_s = reinterpret_cast<int*>(outs + (size_t)R * m); // m + 1
+  const int t = threadIdx.x;
+  const int b = blockIdx.y, c0 = blockIdx.x * R;
+  const int nc = min(R, C - c0);
+  const int64_t E = (int64_t)3 * n;
+  if (t == 0) {
+    mbar_init(&bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (t == 0) bulk_g2s_chunked(rows, g + ((int64_t)b * C + c0) * n, (unsigned)(nc * n) * 4u, &bar);
+  const int* __restrict__ rp = row_ptr + (int64_t)b * (m + 1);
+  for (int i = t; i <= m; i += 1024) rp_s[i] = __ldg(rp + i);
+  __syncthreads();
+  mbar_wait(&bar, 0);
+  const int* __restrict__ pm = perm + (int64_t)b * E;
+  const float* __restrict__ ws = wsorted + (int64_t)b * E;
+  const int sub = t & 7;
+  for (int k = t >> 3; k < m; k += 128) {
+    const int s0 = rp_s[k], e0 = rp_s[k + 1];
+    float acc[R];
+#pragma unroll
+    for (int r = 0; r < R; r++) acc[r] = 0.f;
+#pragma unroll 2
+    for (int p = s0 + sub; p < e0; p += 8) {
+      const int src = __ldg(pm + p) / 3;
+      const float wt = __ldg(ws + p);
+#pragma unroll
+      for (int r = 0; r < R; r++) acc[r] = __fadd_rn(acc[r], __fmul_rn(rows[(size_t)r * n + src], wt));
+    }
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+      acc[r] = __fadd_rn(acc[r], __shfl_xor_sync(0xffffffffu, acc[r], 4));
+      acc[r] = __fadd_rn(acc[r], __shfl_xor_sync(0xffffffffu, acc[r], 2));
+      acc[r] = __fadd_rn(acc[r], __shfl_xor_sync(0xffffffffu, acc[r], 1));
+    }
+    if (sub == 0) {
+#pragma unroll
+      for (int r = 0; r < R; r++) outs[(size_t)r * m + k] = acc[r];
+    }
+  }
+  __syncthreads();
+  float* __restrict__ out = dst + ((int64_t)b * C + c0) * m;  // nc rows of m floats are contiguous
+  for (int i = t; i < nc * m; i += 1024) out[i] = outs[i];
+}
+
+template <int R>
+static int launch_wrows(int B, int C, int n, int m, size_t smem, const float* g, const PlanView& pv, const float* wsorted,
+                        float* dst, cudaStream_t s) {
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(seg_reduce_wrows_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+    if (e != cudaSuccess) { set_error("three_interpolate_grad: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
+    configured = true;
+  }
+  dim3 grid((C + R - 1) / R, B);
+  seg_reduce_wrows_kernel<R><<<grid, 1024, smem, s>>>(C, n, m, g, pv.row_ptr, pv.perm, wsorted, dst);
+  count_launch(1);
+  return check_launch("seg_reduce_wrows_kernel");
+}
+
+static int three_interpolate_grad_rows(int B, int C, int n, int m, const float* g, const float* w, const void* plan,
+                                       float* dst, cudaStream_t s, bool* taken) {
+  *taken = false;
+  const int64_t E = (int64_t)3 * n;
+  if (g_group_force_direct || n % 4 != 0 || (((uintptr_t)g) & 15) != 0 || n < 1024 || E < m || B > 65535) return GEOT_OK;
+  auto smem_of = [&](int R) { return (size_t)R * n * 4 + (size_t)R * m * 4 + (size_t)(m + 1) * 4 + 16; };
+  // rows per CTA: the edge stream (8 B per edge = 24 B per row element) is re-read once per R channels
+  static const int kR[6] = {1, 2, 3, 4, 6, 8};
+  int R = 0;
+  double best = 0.0;
+  for (int i = 0; i < 6; i++) {
+    const int r = kR[i];
+    if (smem_of(r) > (size_t)226 * 1024 || (r > 1 && r > C)) continue;
+    const double ctas = (double)B * ((C + r - 1) / r);
+    const double eff = ctas / (std::ceil(ctas / kNumSMs) * kNumSMs);
+    const double score = eff / (24.0 / r + 4.0);
+    if (score > best) { best = score; R = r; }
+  }
+  if (R == 0) return GEOT_OK;
+  // plan workspace: [row_ptr | perm | cursor | tmp(B*E ints) | ...]; tmp is scratch of the plan build, reused here
+  const PlanView pv = plan_view(plan, B, m);
+  const size_t perm_b = plan_align((size_t)B * (size_t)E * sizeof(int));
+  float* wsorted = reinterpret_cast<float*>(const_cast<char*>(reinterpret_cast<const char*>(plan)) + plan_rowptr_bytes(B, m) + perm_b + plan_rowptr_bytes(B, m));
+  dim3 gw((unsigned)((E + 255) / 256), B);
+  plan_wsort_kernel<<<gw, 256, 0, s>>>(E, w, pv.perm, wsorted);
+  count_launch(1);
+  int rc = check_launch("plan_wsort_kernel");
+  if (rc) return rc;
+  *taken = true;
+  const size_t smem = smem_of(R);
+  switch (R) {
+    case 1: return launch_wrows<1>(B, C, n, m, smem, g, pv, wsorted, dst, s);
+    case 2: return launch_wrows<2>(B, C, n, m, smem, g, pv, wsorted, dst, s);
+    case 3: return launch_wrows<3>(B, C, n, m, smem, g, pv, wsorted, dst, s);
+    case 4: return launch_wrows<4>(B, C, n, m, smem, g, pv, wsorted, dst, s);
+    case 6: return launch_wrows<6>(B, C, n, m, smem, g, pv, wsorted, dst, s);
+    default: return launch_wrows<8>(B, C, n, m, smem, g, pv, wsorted, dst, s);
+  }
+}
+
 // used by interp.cu
+bool direct_kernels_forced() { return g_group_force_direct; }
 int three_interpolate_grad_impl(int B, int C, int n, int m, const float* grad_out, const float* weight,
                                 const void* plan, float* grad_points, cudaStream_t s) {
+  if (B > 0 && C > 0 && m > 0 && n > 0 && grad_out && plan && grad_points && weight) {
+    bool taken = false;
+    const int rc = three_interpolate_grad_rows(B, C, n, m, grad_out, weight, plan, grad_points, s, &taken);
+    if (rc || taken) return rc;
+  }
   return launch_seg_reduce<3, true>(B, C, m, (int64_t)3 * n, grad_out, weight, plan, grad_points, s,
                                     "three_interpolate_grad");
 }
@@ -547,7 +681,6 @@ GEOT_API int geot_gather_points(int B, int C, int N, int M, const float* points,
 }
 
 // Workspace: [row_ptr | perm | cursor | tmp | heavy_count | heavy_list]; consumers read the first two only.
-static inline size_t plan_align(size_t b) { return (b + 255) & ~(size_t)255; }
 static inline int plan_heavy_cap(int B, int64_t E) { return (int)std::min<int64_t>((int64_t)B * (E / kPlanSmall) + 1, 1 << 28); }
 GEOT_API size_t geot_scatter_plan_bytes(int B, int N, int64_t E) {
   if (B < 0 || N < 0 || E < 0) return 0;

@@ -22,6 +22,7 @@
 namespace geot {
 
 void count_launch(int n);
+bool direct_kernels_forced();  // geot_group_points_config (group.cu)
 int three_interpolate_grad_impl(int B, int C, int n, int m, const float* grad_out, const float* weight,
                                 const void* plan, float* grad_points, cudaStream_t s);
 
@@ -93,6 +94,229 @@ three_nn_kernel(int n, int m, const float* __restrict__ unknown, const float* __
       od[0] = best[u].d1; od[1] = best[u].d2; od[2] = best[u].d3;
       oi[0] = best[u].i1; oi[1] = best[u].i2; oi[2] = best[u].i3;
     }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// three_nn over a uniform grid (default for 64 <= m <= kNgMaxM).  The brute-force kernel above evaluates all m
+// known points per unknown point (n*m distances per cloud).  The known cloud is small (it is the SAMPLED level
+// of a feature-propagation stage), so every CTA bins it into shared memory itself - bounding box, cell size for
+// ~1.5 points per occupied cell (measured, one re-binning if the first guess is off), counting sort of
+// {x, y, z, index} - and each of its 1024 threads then searches the 3x3x3 cells around its unknown point, the
+// 5x5x5 shell if the third-best distance does not yet beat the distance to the searched block's open faces, and
+// the whole cloud otherwise.  Selection is by (distance, index) lexicographic order, which is exactly what the
+// reference's strict-'<' scan in ascending index order produces (interpolate_gpu.cu:44-55), so the result does
+// not depend on the order candidates are visited in: bit-identical idx and dist2, no fallback pass.
+// ---------------------------------------------------------------------------------------------
+constexpr int kNgMaxM = 8192;
+constexpr int kNgMaxDim = 20;
+constexpr int kNgMaxCells = kNgMaxDim * kNgMaxDim * kNgMaxDim;
+constexpr int kNgThreads = 1024;
+
+__device__ __forceinline__ bool lex_lt(float d, int k, float D, int K) { return d < D || (d == D && k < K); }
+__device__ __forceinline__ void top3_push_lex(Top3& t, float d, int k) {
+  if (lex_lt(d, k, t.d3, t.i3)) {
+    if (lex_lt(d, k, t.d1, t.i1)) {
+      t.d3 = t.d2; t.i3 = t.i2; t.d2 = t.d1; t.i2 = t.i1; t.d1 = d; t.i1 = k;
+    } else if (lex_lt(d, k, t.d2, t.i2)) {
+      t.d3 = t.d2; t.i3 = t.i2; t.d2 = d; t.i2 = k;
+    } else {
+      t.d3 = d; t.i3 = k;
+    }
+  }
+}
+__device__ __forceinline__ int ng_cell(float p, float lo, float inv) { return __float2int_rd((p - lo) * inv); }
+
+__global__ void __launch_bounds__(kNgThreads, 1)
+three_nn_grid_kernel(int n, int m, const float* __restrict__ unknown, const float* __restrict__ known,
+                     float* __restrict__ dist2, int* __restrict__ idx) {
+  extern __shared__ __align__(16) unsigned char ng_smem[];
+  __shared__ float s_red[6][32];
+  __shared__ int s_scan[32];
+  __shared__ int s_occupied;
+  float4* sorted = reinterpret_cast<float4*>(ng_smem);               // m entries
+  int* cells = reinterpret_cast<int*>(ng_smem + (size_t)m * 16);     // kNgMaxCells + 1: histogram -> cursor
+  int* cell_start = cells + kNgMaxCells + 1;                         // kNgMaxCells + 1
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int b = blockIdx.y;
+  const float* __restrict__ kn = known + (int64_t)b * m * 3;
+  const float kInf = __int_as_float(0x7f800000);
+
+  // ---- bin the known cloud ----
+  float lo[3] = {kInf, kInf, kInf}, hi[3] = {-kInf, -kInf, -kInf};
+  for (int k = t; k < m; k += kNgThreads) {
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+      const float v = __ldg(kn + (int64_t)k * 3 + a);
+      lo[a] = fminf(lo[a], v); hi[a] = fmaxf(hi[a], v);
+    }
+  }
+#pragma unroll
+  for (int a = 0; a < 3; a++) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      lo[a] = fminf(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], o));
+      hi[a] = fmaxf(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], o));
+    }
+    if (lane == 0) { s_red[a][warp] = lo[a]; s_red[3 + a][warp] = hi[a]; }
+  }
+  __syncthreads();
+  float ext = 0.f;
+#pragma unroll
+  for (int a = 0; a < 3; a++) {
+    float l = s_red[a][lane], h = s_red[3 + a][lane];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      l = fminf(l, __shfl_xor_sync(0xffffffffu, l, o));
+      h = fmaxf(h, __shfl_xor_sync(0xffffffffu, h, o));
+    }
+    lo[a] = l; hi[a] = h;
+    ext = fmaxf(ext, h - l);
+  }
+  // degenerate cloud (all points equal, non-finite coordinates): one cell, every query scans everything
+  const bool flat = !(ext > 0.f) || !(ext < kInf);
+  const float per_cell = 1.5f;
+  int G = flat ? 1 : min(kNgMaxDim, max(2, (int)ceilf(sqrtf((float)m / per_cell))));
+  float cell = 1.f, inv = 0.f;
+  int dims[3] = {1, 1, 1}, ncell = 1;
+  auto code_of = [&](float x, float y, float z) -> int {
+    const int cx = min(max(ng_cell(x, lo[0], inv), 0), dims[0] - 1);
+    const int cy = min(max(ng_cell(y, lo[1], inv), 0), dims[1] - 1);
+    const int cz = min(max(ng_cell(z, lo[2], inv), 0), dims[2] - 1);
+    return (cz * dims[1] + cy) * dims[0] + cx;
+  };
+#pragma unroll 1
+  for (int pass = 0; pass < 2; pass++) {
+    if (!flat) {
+      cell = ext / ((float)G - 0.5f);
+      inv = 1.0f / cell;
+#pragma unroll
+      for (int a = 0; a < 3; a++) dims[a] = min(kNgMaxDim, max(1, ng_cell(hi[a], lo[a], inv) + 1));
+      ncell = dims[0] * dims[1] * dims[2];
+    }
+    if (t == 0) s_occupied = 0;
+    for (int i = t; i < ncell; i += kNgThreads) cells[i] = 0;
+    __syncthreads();
+    for (int k = t; k < m; k += kNgThreads)
+      atomicAdd(&cells[flat ? 0 : code_of(__ldg(kn + (int64_t)k * 3), __ldg(kn + (int64_t)k * 3 + 1), __ldg(kn + (int64_t)k * 3 + 2))], 1);
+    __syncthreads();
+    if (pass == 1 || flat) break;
+    int occ_cnt = 0;
+    for (int i = t; i < ncell; i += kNgThreads) occ_cnt += cells[i] != 0;
+    occ_cnt = __reduce_add_sync(0xffffffffu, occ_cnt);
+    if (lane == 0 && occ_cnt) atomicAdd(&s_occupied, occ_cnt);
+    __syncthreads();
+    const float occ = (float)m / (float)max(s_occupied, 1);
+    __syncthreads();
+    if (occ >= 0.75f * per_cell && occ <= 1.6f * per_cell) break;
+    const int Gn = min(kNgMaxDim, max(2, (int)rintf((float)G * __powf(occ / per_cell, 0.4f))));
+    if (Gn == G) break;
+    G = Gn;
+  }
+  {  // exclusive scan of the histogram -> cell_start, cells becomes the scatter cursor
+    const int PER = (ncell + kNgThreads - 1) / kNgThreads;
+    const int i0 = t * PER;
+    int sum = 0;
+    for (int i = i0; i < min(i0 + PER, ncell); i++) sum += cells[i];
+    int inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += y;
+    }
+    if (lane == 31) s_scan[warp] = inc;
+    __syncthreads();
+    int wtot = s_scan[lane], winc = wtot;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, winc, o);
+      if (lane >= o) winc += y;
+    }
+    int run = __shfl_sync(0xffffffffu, winc - wtot, warp) + inc - sum;
+    for (int i = i0; i < min(i0 + PER, ncell); i++) {
+      const int v = cells[i];
+      cells[i] = run;
+      cell_start[i] = run;
+      run += v;
+    }
+    if (t == 0) cell_start[ncell] = m;
+  }
+  __syncthreads();
+  for (int k = t; k < m; k += kNgThreads) {
+    const float x = __ldg(kn + (int64_t)k * 3), y = __ldg(kn + (int64_t)k * 3 + 1), z = __ldg(kn + (int64_t)k * 3 + 2);
+    sorted[atomicAdd(&cells[flat ? 0 : code_of(x, y, z)], 1)] = make_float4(x, y, z, __int_as_float(k));
+  }
+  __syncthreads();
+  // ---- one unknown point per thread ----
+  for (int i = blockIdx.x * kNgThreads + t; i < n; i += gridDim.x * kNgThreads) {
+  const float* up = unknown + ((int64_t)b * n + i) * 3;
+  const float qx = up[0], qy = up[1], qz = up[2];
+  Top3 best = Top3{kInf, kInf, kInf, 0, 0, 0};
+  auto visit = [&](int p) {
+    const float4 v = sorted[p];
+    top3_push_lex(best, dist2_ref(qx, qy, qz, v.x, v.y, v.z), __float_as_int(v.w));
+  };
+  bool done = false;
+  if (!flat) {
+    const int dx = dims[0], dy = dims[1], dz = dims[2];
+    const float ux = (qx - lo[0]) * inv, uy = (qy - lo[1]) * inv, uz = (qz - lo[2]) * inv;
+    const int cx = (int)fminf(fmaxf(floorf(ux), -4.f), (float)dx + 3.f);
+    const int cy = (int)fminf(fmaxf(floorf(uy), -4.f), (float)dy + 3.f);
+    const int cz = (int)fminf(fmaxf(floorf(uz), -4.f), (float)dz + 3.f);
+    // squared distance below which no point outside the (2R+1)^3 block can lie (cell units, margin for the
+    // fp32 binning arithmetic; faces at the grid boundary have nothing behind them)
+    auto safe_d2 = [&](int R) -> float {
+      float rho = kInf;
+      if (cx - R > 0) rho = fminf(rho, ux - (float)(cx - R));
+      if (cx + R + 1 < dx) rho = fminf(rho, (float)(cx + R + 1) - ux);
+      if (cy - R > 0) rho = fminf(rho, uy - (float)(cy - R));
+      if (cy + R + 1 < dy) rho = fminf(rho, (float)(cy + R + 1) - uy);
+      if (cz - R > 0) rho = fminf(rho, uz - (float)(cz - R));
+      if (cz + R + 1 < dz) rho = fminf(rho, (float)(cz + R + 1) - uz);
+      rho = fmaxf(rho - 2e-4f * (1.f + fabsf(ux) + fabsf(uy) + fabsf(uz)) * 0.03125f - 2e-4f, 0.f) * cell;
+      return rho * rho * 0.9999f;
+    };
+    auto run_of = [&](int xa, int xb, int y, int z, int& p, int& e) {
+      p = 0; e = 0;
+      if (y < 0 || y >= dy || z < 0 || z >= dz) return;
+      xa = max(xa, 0); xb = min(xb, dx - 1);
+      if (xa > xb) return;
+      const int row = (z * dy + y) * dx;
+      p = cell_start[row + xa]; e = cell_start[row + xb + 1];
+    };
+    {  // ring 1: nine x-runs, walked as one flat sequence so a warp's cost is its longest candidate list
+      int r = 0, p = 0, e = 0;
+      for (;;) {
+        if (p < e) { visit(p++); continue; }
+        if (r == 9) break;
+        run_of(cx - 1, cx + 1, cy + r % 3 - 1, cz + r / 3 - 1, p, e);
+        r++;
+      }
+      done = best.d3 < safe_d2(1);
+    }
+    if (!done) {  // ring 2: border rows are full runs, interior rows contribute their two end cells
+      int r = 0, p = 0, e = 0;
+      for (;;) {
+        if (p < e) { visit(p++); continue; }
+        if (r == 50) break;
+        const int row = r >> 1, half = r & 1;
+        const int oy = row % 5 - 2, oz = row / 5 - 2;
+        const bool border = oy == -2 || oy == 2 || oz == -2 || oz == 2;
+        if (border) { if (half == 0) run_of(cx - 2, cx + 2, cy + oy, cz + oz, p, e); }
+        else run_of(half ? cx + 2 : cx - 2, half ? cx + 2 : cx - 2, cy + oy, cz + oz, p, e);
+        r++;
+      }
+      done = best.d3 < safe_d2(2);
+    }
+  }
+  if (!done) {  // far from the known cloud / degenerate grid: every known point
+    best = Top3{kInf, kInf, kInf, 0, 0, 0};
+    for (int p = 0; p < m; p++) visit(p);
+  }
+  float* od = dist2 + ((int64_t)b * n + i) * 3;
+  int* oi = idx + ((int64_t)b * n + i) * 3;
+  od[0] = best.d1; od[1] = best.d2; od[2] = best.d3;
+  oi[0] = best.i1; oi[1] = best.i2; oi[2] = best.i3;
   }
 }
 
@@ -192,6 +416,29 @@ GEOT_API int geot_three_nn(int B, int n, int m, const float* unknown, const floa
   if (B == 0 || n == 0) return GEOT_OK;
   GEOT_REQUIRE(unknown && dist2 && idx && (m == 0 || known), "three_nn: NULL pointer");
   GEOT_REQUIRE(B <= 65535, "three_nn: B exceeds grid limits");
+  if (m >= 64 && m <= kNgMaxM && !direct_kernels_forced()) {
+    const size_t smem = (size_t)m * 16 + (size_t)(kNgMaxCells + 1) * 8;
+    static bool configured = false;
+    if (!configured) {
+      cudaError_t e = cudaFuncSetAttribute(three_nn_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kNgMaxM * 16 + (kNgMaxCells + 1) * 8);
+      if (e != cudaSuccess) { set_error("three_nn: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
+      configured = true;
+    }
+    // CTAs per cloud: every CTA re-bins the known cloud (~4x the cost of one 1024-query sweep), so prefer few
+    // CTAs with several sweeps each, in whole waves of the 148 SMs
+    const int max_cb = (n + kNgThreads - 1) / kNgThreads;
+    int cb = 1;
+    double best_cost = 1e30;
+    for (int k = 1; k <= max_cb; k++) {
+      const double waves = std::ceil((double)k * B / kNumSMs);
+      const double cost = waves * (4.0 + std::ceil((double)n / ((double)k * kNgThreads)));
+      if (cost < best_cost) { best_cost = cost; cb = k; }
+    }
+    dim3 gg(cb, B);
+    three_nn_grid_kernel<<<gg, kNgThreads, smem, as_stream(stream)>>>(n, m, unknown, known, dist2, idx);
+    count_launch(1);
+    return check_launch("three_nn_grid_kernel");
+  }
   dim3 grid((n + kNnThreads * kNnPerThread - 1) / (kNnThreads * kNnPerThread), B);
   three_nn_kernel<<<grid, kNnThreads, 0, as_stream(stream)>>>(n, m, unknown, known, dist2, idx);
   count_launch(1);

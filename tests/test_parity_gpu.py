@@ -280,6 +280,38 @@ def test_three_nn(cuda, oracle, kind, B, n, m):
     assert np.array_equal(gd2.cpu().numpy(), ed2)
 
 
+@pytest.mark.parametrize("kind", ["tooth", "uniform", "dup", "quant", "plane", "same"])
+@pytest.mark.parametrize("B,n,m", [(3, 16384, 1024), (2, 5000, 64), (2, 3001, 8192), (1, 2048, 4097), (2, 700, 333)])
+def test_three_nn_grid_vs_scan(cuda, kind, B, n, m):
+    """Grid search (64 <= m <= 8192) against the brute-force kernel of the same library (exact on its own, see
+    test_three_nn): duplicates and quantised coordinates (ties resolved by index), unknown points far outside the
+    known cloud, flat and single-point known clouds."""
+    rng = np.random.default_rng(n + m)
+    if kind == "uniform":
+        known = rng.random((B, m, 3), dtype=np.float32)
+        unknown = rng.random((B, n, 3), dtype=np.float32) * np.float32(1.2) - np.float32(0.1)
+    elif kind == "plane":
+        known = rng.random((B, m, 3), dtype=np.float32); known[..., 1] = np.float32(0.25)
+        unknown = rng.random((B, n, 3), dtype=np.float32)
+    elif kind == "same":
+        known = np.tile(np.float32([0.5, 0.5, 0.5]), (B, m, 1))
+        unknown = rng.random((B, n, 3), dtype=np.float32)
+    else:
+        big = clouds(kind, B, max(n, m))
+        known = np.ascontiguousarray(big[:, rng.permutation(max(n, m))[:m]])
+        unknown = np.ascontiguousarray(big[:, :n])
+    unknown[:, 3::97] += np.float32(7.0)
+    unknown[:, 5::131] *= np.float32(-3.0)
+    gd, gi = F.three_nn(cu(unknown), cu(known))
+    _lib.lib().geot_group_points_config(1)
+    try:
+        sd, si = F.three_nn(cu(unknown), cu(known))
+    finally:
+        _lib.lib().geot_group_points_config(0)
+    assert torch.equal(gi, si)
+    assert torch.equal(gd, sd)
+
+
 @pytest.mark.parametrize("B,C,m,n", [(2, 384, 512, 4096), (2, 16, 8192, 16000), (1, 3, 5, 9)])
 def test_three_interpolate_fwd_bwd(cuda, oracle, B, C, m, n):
     rng = np.random.default_rng(9)
@@ -293,6 +325,31 @@ def test_three_interpolate_fwd_bwd(cuda, oracle, B, C, m, n):
     got = F.three_interpolate_grad(cu(g), cu(w), F.ScatterPlan(cu(idx), B, m), m)
     np.testing.assert_allclose(got.cpu().numpy(), oracle.three_interpolate_grad(g, idx, w, m), rtol=RTOL, atol=2e-6)
     assert torch.equal(got, F.three_interpolate_grad(cu(g), cu(w), F.ScatterPlan(cu(idx), B, m), m))
+
+
+@pytest.mark.parametrize("B,C,m,n", [(3, 5, 1024, 16384), (2, 64, 700, 4096), (1, 13, 2048, 6002), (2, 7, 4096, 12288)])
+def test_three_interpolate_grad_rows_vs_direct(cuda, oracle, B, C, m, n):
+    """Row-resident backward (gradient rows in shared memory, weights pre-sorted into plan order) against the
+    direct L2-gather kernel and the oracle, on real three_nn indices: skewed segment lengths, targets that no
+    point selects, channel counts that leave a partial last CTA, n % 4 != 0 (falls back to the direct kernel)."""
+    unknown = clouds("tooth", B, n)
+    known = np.ascontiguousarray(unknown[:, :m])
+    known[:, m // 2:] += np.float32(5.0)  # half of the known points are far away: empty segments
+    d2, idx = F.three_nn(cu(unknown), cu(known))
+    w = 1.0 / (d2 + 1e-8)
+    w = (w / w.sum(-1, keepdim=True)).contiguous()
+    g = torch.randn(B, C, n, device="cuda")
+    plan = F.ScatterPlan(idx, B, m)
+    got = F.three_interpolate_grad(g, w, plan, m)
+    _lib.lib().geot_group_points_config(1)
+    try:
+        direct = F.three_interpolate_grad(g, w, plan, m)
+    finally:
+        _lib.lib().geot_group_points_config(0)
+    exp = oracle.three_interpolate_grad(g.cpu().numpy(), idx.cpu().numpy(), w.cpu().numpy(), m)
+    np.testing.assert_allclose(direct.cpu().numpy(), exp, rtol=1e-4, atol=1e-4)
+    np.testing.assert_allclose(got.cpu().numpy(), exp, rtol=1e-4, atol=1e-4)
+    assert torch.equal(got, F.three_interpolate_grad(g, w, plan, m)), "run-to-run identical"
 
 
 @pytest.mark.parametrize("c", [32, 7])
