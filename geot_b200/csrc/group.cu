@@ -570,12 +570,26 @@ seg_reduce_wrows_kernel(int C, int n, int m, const float* __restrict__ g, const 
     float acc[R];
 #pragma unroll
     for (int r = 0; r < R; r++) acc[r] = 0.f;
-#pragma unroll 2
-    for (int p = s0 + sub; p < e0; p += 8) {
-      const int src = __ldg(pm + p) / 3;
-      const float wt = __ldg(ws + p);
+    // up to 64 edges of the segment per round: all 8 {perm, w} pairs of a lane are requested before the first
+    // is used, so a typical segment (~48 edges) costs one L2 round trip instead of one per pair
+    for (int p0 = s0 + sub; p0 < e0; p0 += 64) {
+      int sr[8];
+      float wt[8];
 #pragma unroll
-      for (int r = 0; r < R; r++) acc[r] = __fadd_rn(acc[r], __fmul_rn(rows[(size_t)r * n + src], wt));
+      for (int j = 0; j < 8; j++) {
+        const int p = p0 + 8 * j;
+        const bool ok = p < e0;
+        sr[j] = ok ? __ldg(pm + p) : 0;
+        wt[j] = ok ? __ldg(ws + p) : 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; j++) {
+        if (p0 + 8 * j < e0) {
+          const int src = sr[j] / 3;
+#pragma unroll
+          for (int r = 0; r < R; r++) acc[r] = __fadd_rn(acc[r], __fmul_rn(rows[(size_t)r * n + src], wt[j]));
+        }
+      }
     }
 #pragma unroll
     for (int r = 0; r < R; r++) {

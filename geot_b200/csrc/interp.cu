@@ -98,7 +98,7 @@ three_nn_kernel(int n, int m, const float* __restrict__ unknown, const float* __
 }
 
 // ---------------------------------------------------------------------------------------------
-// three_nn over a uniform grid (default for 64 <= m <= kNgMaxM).  The brute-force kernel above evaluates all m
+// three_nn over a uniform grid (default for 64 <= m <= kNgMaxM = 7168).  The brute-force kernel above evaluates all m
 // known points per unknown point (n*m distances per cloud).  The known cloud is small (it is the SAMPLED level
 // of a feature-propagation stage), so every CTA bins it into shared memory itself - bounding box, cell size for
 // ~1.5 points per occupied cell (measured, one re-binning if the first guess is off), counting sort of
@@ -108,21 +108,18 @@ three_nn_kernel(int n, int m, const float* __restrict__ unknown, const float* __
 // reference's strict-'<' scan in ascending index order produces (interpolate_gpu.cu:44-55), so the result does
 // not depend on the order candidates are visited in: bit-identical idx and dist2, no fallback pass.
 // ---------------------------------------------------------------------------------------------
-constexpr int kNgMaxM = 8192;
-constexpr int kNgMaxDim = 20;
-constexpr int kNgMaxCells = kNgMaxDim * kNgMaxDim * kNgMaxDim;
+constexpr int kNgMaxM = 7168;
+constexpr int kNgMaxDim = 64;      // cells per axis
+constexpr int kNgMaxCells = 8000;  // cells in total (two int tables of this size live in shared memory)
 constexpr int kNgThreads = 1024;
 
 __device__ __forceinline__ bool lex_lt(float d, int k, float D, int K) { return d < D || (d == D && k < K); }
 __device__ __forceinline__ void top3_push_lex(Top3& t, float d, int k) {
-  if (lex_lt(d, k, t.d3, t.i3)) {
-    if (lex_lt(d, k, t.d1, t.i1)) {
-      t.d3 = t.d2; t.i3 = t.i2; t.d2 = t.d1; t.i2 = t.i1; t.d1 = d; t.i1 = k;
-    } else if (lex_lt(d, k, t.d2, t.i2)) {
-      t.d3 = t.d2; t.i3 = t.i2; t.d2 = d; t.i2 = k;
-    } else {
-      t.d3 = d; t.i3 = k;
-    }
+  if (lex_lt(d, k, t.d3, t.i3)) {  // rare after the first few candidates; the body is select-only
+    const bool l1 = lex_lt(d, k, t.d1, t.i1), l2 = lex_lt(d, k, t.d2, t.i2);
+    t.d3 = l2 ? t.d2 : d; t.i3 = l2 ? t.i2 : k;
+    t.d2 = l1 ? t.d1 : (l2 ? d : t.d2); t.i2 = l1 ? t.i1 : (l2 ? k : t.i2);
+    t.d1 = l1 ? d : t.d1; t.i1 = l1 ? k : t.i1;
   }
 }
 __device__ __forceinline__ int ng_cell(float p, float lo, float inv) { return __float2int_rd((p - lo) * inv); }
@@ -137,6 +134,7 @@ three_nn_grid_kernel(int n, int m, const float* __restrict__ unknown, const floa
   float4* sorted = reinterpret_cast<float4*>(ng_smem);               // m entries
   int* cells = reinterpret_cast<int*>(ng_smem + (size_t)m * 16);     // kNgMaxCells + 1: histogram -> cursor
   int* cell_start = cells + kNgMaxCells + 1;                         // kNgMaxCells + 1
+  unsigned* runs = reinterpret_cast<unsigned*>(cell_start + kNgMaxCells + 1);  // 9 x kNgThreads: {start:16 | length:16}
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int b = blockIdx.y;
   const float* __restrict__ kn = known + (int64_t)b * m * 3;
@@ -179,6 +177,7 @@ three_nn_grid_kernel(int n, int m, const float* __restrict__ unknown, const floa
   int G = flat ? 1 : min(kNgMaxDim, max(2, (int)ceilf(sqrtf((float)m / per_cell))));
   float cell = 1.f, inv = 0.f;
   int dims[3] = {1, 1, 1}, ncell = 1;
+  bool capped = false;
   auto code_of = [&](float x, float y, float z) -> int {
     const int cx = min(max(ng_cell(x, lo[0], inv), 0), dims[0] - 1);
     const int cy = min(max(ng_cell(y, lo[1], inv), 0), dims[1] - 1);
@@ -188,11 +187,17 @@ three_nn_grid_kernel(int n, int m, const float* __restrict__ unknown, const floa
 #pragma unroll 1
   for (int pass = 0; pass < 2; pass++) {
     if (!flat) {
-      cell = ext / ((float)G - 0.5f);
-      inv = 1.0f / cell;
+      capped = false;
+      for (;;) {  // G cells along the longest axis; shrink until the whole grid fits the tables
+        cell = ext / ((float)G - 0.5f);
+        inv = 1.0f / cell;
 #pragma unroll
-      for (int a = 0; a < 3; a++) dims[a] = min(kNgMaxDim, max(1, ng_cell(hi[a], lo[a], inv) + 1));
-      ncell = dims[0] * dims[1] * dims[2];
+        for (int a = 0; a < 3; a++) dims[a] = min(kNgMaxDim, max(1, ng_cell(hi[a], lo[a], inv) + 1));
+        ncell = dims[0] * dims[1] * dims[2];
+        if (ncell <= kNgMaxCells || G <= 2) break;
+        G = max(2, min(G - 1, (int)((float)G * cbrtf((float)kNgMaxCells / (float)ncell))));
+        capped = true;
+      }
     }
     if (t == 0) s_occupied = 0;
     for (int i = t; i < ncell; i += kNgThreads) cells[i] = 0;
@@ -210,7 +215,7 @@ three_nn_grid_kernel(int n, int m, const float* __restrict__ unknown, const floa
     __syncthreads();
     if (occ >= 0.75f * per_cell && occ <= 1.6f * per_cell) break;
     const int Gn = min(kNgMaxDim, max(2, (int)rintf((float)G * __powf(occ / per_cell, 0.4f))));
-    if (Gn == G) break;
+    if (Gn == G || (capped && Gn > G)) break;
     G = Gn;
   }
   {  // exclusive scan of the histogram -> cell_start, cells becomes the scatter cursor
@@ -284,13 +289,25 @@ three_nn_grid_kernel(int n, int m, const float* __restrict__ unknown, const floa
       const int row = (z * dy + y) * dx;
       p = cell_start[row + xa]; e = cell_start[row + xb + 1];
     };
-    {  // ring 1: nine x-runs, walked as one flat sequence so a warp's cost is its longest candidate list
+    {  // ring 1: the non-empty x-runs of the 3x3 rows go to a per-thread list in shared memory (converged code),
+       // then they are walked as ONE flat candidate sequence: a warp's cost is its longest list, not the sum
+       // over rows of the longest run
+      int nr = 0;
+#pragma unroll
+      for (int r = 0; r < 9; r++) {
+        int p, e;
+        run_of(cx - 1, cx + 1, cy + r % 3 - 1, cz + r / 3 - 1, p, e);
+        if (e > p) { runs[nr * kNgThreads + t] = ((unsigned)p << 16) | (unsigned)(e - p); nr++; }
+      }
       int r = 0, p = 0, e = 0;
       for (;;) {
-        if (p < e) { visit(p++); continue; }
-        if (r == 9) break;
-        run_of(cx - 1, cx + 1, cy + r % 3 - 1, cz + r / 3 - 1, p, e);
-        r++;
+        if (p >= e) {
+          if (r >= nr) break;
+          const unsigned u = runs[r * kNgThreads + t];
+          r++;
+          p = (int)(u >> 16); e = p + (int)(u & 0xffffu);
+        }
+        visit(p++);
       }
       done = best.d3 < safe_d2(1);
     }
@@ -417,10 +434,10 @@ GEOT_API int geot_three_nn(int B, int n, int m, const float* unknown, const floa
   GEOT_REQUIRE(unknown && dist2 && idx && (m == 0 || known), "three_nn: NULL pointer");
   GEOT_REQUIRE(B <= 65535, "three_nn: B exceeds grid limits");
   if (m >= 64 && m <= kNgMaxM && !direct_kernels_forced()) {
-    const size_t smem = (size_t)m * 16 + (size_t)(kNgMaxCells + 1) * 8;
+    const size_t smem = (size_t)m * 16 + (size_t)(kNgMaxCells + 1) * 8 + (size_t)9 * kNgThreads * 4;
     static bool configured = false;
     if (!configured) {
-      cudaError_t e = cudaFuncSetAttribute(three_nn_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kNgMaxM * 16 + (kNgMaxCells + 1) * 8);
+      cudaError_t e = cudaFuncSetAttribute(three_nn_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kNgMaxM * 16 + (kNgMaxCells + 1) * 8 + 9 * kNgThreads * 4);
       if (e != cudaSuccess) { set_error("three_nn: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
       configured = true;
     }

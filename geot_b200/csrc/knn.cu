@@ -182,8 +182,8 @@ struct KnnGridHeader {
   int pad[7];
 };
 constexpr int kKnnHdrBytes = 64;
-constexpr int kKnnMaxDim = 32;
-constexpr int kKnnMaxCells = kKnnMaxDim * kKnnMaxDim * kKnnMaxDim;
+constexpr int kKnnMaxDim = 256;       // cells per axis
+constexpr int kKnnMaxCells = 32768;   // cells in total (the build keeps the histogram in shared memory)
 constexpr int kKnnGridMinN = 3072;
 __host__ __device__ inline size_t knn_seg_ws_bytes() { return kKnnHdrBytes + (((size_t)(kKnnMaxCells + 1) * 4 + 15) & ~(size_t)15); }
 
@@ -266,11 +266,17 @@ knn_build_kernel(int nsample, float alpha, const float* __restrict__ xyz, const 
   };
 #pragma unroll 1
   for (int pass = 0; pass < 3; pass++) {
-    cell = ext / ((float)G - 0.5f);
-    inv = 1.0f / cell;
+    bool capped = false;
+    for (;;) {  // G cells along the longest axis; shrink until the whole grid fits the cell table
+      cell = ext / ((float)G - 0.5f);
+      inv = 1.0f / cell;
 #pragma unroll
-    for (int a = 0; a < 3; a++) dims[a] = min(kKnnMaxDim, max(1, knn_cell(hi[a], lo[a], inv) + 1));
-    ncell = dims[0] * dims[1] * dims[2];
+      for (int a = 0; a < 3; a++) dims[a] = min(kKnnMaxDim, max(1, knn_cell(hi[a], lo[a], inv) + 1));
+      ncell = dims[0] * dims[1] * dims[2];
+      if (ncell <= kKnnMaxCells || G <= 2) break;
+      G = max(2, min(G - 1, (int)((float)G * cbrtf((float)kKnnMaxCells / (float)ncell))));
+      capped = true;
+    }
     if (t == 0) s_occupied = 0;
     for (int i = t; i < ncell; i += 1024) knn_hist[i] = 0;
     __syncthreads();
@@ -290,7 +296,7 @@ knn_build_kernel(int nsample, float alpha, const float* __restrict__ xyz, const 
     float d = 2.5f;
     if (pass == 1) d = fminf(fmaxf(__logf(occ_prev / occ) / __logf((float)G / (float)G_prev), 1.5f), 3.f);
     const int Gn = min(kKnnMaxDim, max(2, (int)rintf((float)G * __powf(occ / per_cell, 1.f / d))));
-    if (Gn == G) break;
+    if (Gn == G || (capped && Gn > G)) break;
     G_prev = G; occ_prev = occ; G = Gn;
   }
   {
@@ -667,9 +673,11 @@ GEOT_API int geot_knnquery(int b, int n, int m, int nsample, const float* xyz, c
       static float alpha = -1.f;
       if (alpha < 0.f) {  // tuning knob: points per occupied cell = alpha * (k+1)
         const char* e = getenv("GEOT_KNN_ALPHA");
-        alpha = e ? (float)atof(e) : 0.3f;
+        alpha = e ? (float)atof(e) : 0.f;
       }
-      knn_build_kernel<<<b, 1024, smem, s>>>(nsample, alpha, xyz, offset, n_per, seg_grid, base + w.slots, reinterpret_cast<float4*>(base + w.sorted));
+      // measured optimum: ~0.8 (k+1) points per occupied cell at k = 16, less for longer lists (0.4 at 32, 0.3 at 64)
+      const float a = alpha > 0.f ? alpha : fminf(fmaxf(13.f / (float)(nsample + 1), 0.3f), 0.8f);
+      knn_build_kernel<<<b, 1024, smem, s>>>(nsample, a, xyz, offset, n_per, seg_grid, base + w.slots, reinterpret_cast<float4*>(base + w.sorted));
       count_launch(1);
       int rc = check_launch("knn_build_kernel");
       if (rc) return rc;

@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Dev tool (GPU box): launch ONE op of the bench workload a few times so ncu can capture it.
-usage: python tools/prof_one.py {fps|fps_noprune|ball|group|group3} [B]"""
+usage: python tools/prof_one.py {fps|fps_noprune|ball|group|group3|groupbwd|threenn|tibwd|knn} [B]"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
@@ -19,6 +19,15 @@ nbr = F.ball_query(centres, xyz, 0.1, NS)
 if what == "groupbwd":
     go = torch.randn(B, C, M, NS, device="cuda")
     plan = F.ScatterPlan(nbr, B, N)
+if what in ("threenn", "tibwd"):
+    d2, i3 = F.three_nn(xyz, centres)
+    w = 1.0 / (d2 + 1e-8); w = (w / w.sum(-1, keepdim=True)).contiguous()
+    go3 = torch.randn(B, C, N, device="cuda")
+    plan3 = F.ScatterPlan(i3, B, M)
+if what == "knn":
+    kb = 8
+    kx = xyz[:kb].reshape(-1, 3).contiguous()
+    koff = torch.arange(1, kb + 1, device="cuda", dtype=torch.int32) * N
 torch.cuda.synchronize()
 for _ in range(3):
     if what == "fps": F.furthest_point_sampling(xyz, M)
@@ -27,4 +36,7 @@ for _ in range(3):
     elif what == "group": F.group_points(feat, nbr)
     elif what == "group3": F.group_points(xyz_t, nbr)
     elif what == "groupbwd": F.group_points_grad(go, plan, N)
+    elif what == "threenn": F.three_nn(xyz, centres)
+    elif what == "tibwd": F.three_interpolate_grad(go3, w, plan3, M)
+    elif what == "knn": F.knnquery(16, kx, kx, koff, koff, m_per=N)
 torch.cuda.synchronize()
