@@ -21,9 +21,15 @@ for rep in reps:
     r = list(csv.reader(io.StringIO(txt)))
     h, units, v = r[0], r[1], r[2]
     cols = [c for c in WANT if c in h]
+    SCALE = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "ns": 1e-3, "us": 1, "ms": 1e3, "s": 1e6}
+    BASE = {"byte": "byte", "Kbyte": "byte", "Mbyte": "byte", "Gbyte": "byte", "ns": "us", "us": "us", "ms": "us", "s": "us"}
+
+    def norm(c):  # ncu picks a unit per report: bring bytes to bytes and times to microseconds
+        u, x = units[h.index(c)], v[h.index(c)]
+        return str(float(x.replace(",", "")) * SCALE[u]) if u in SCALE else x
     if hdr_out is None:
         hdr_out = cols
-        rows.append(["report", "Kernel Name"] + [f"{c} [{units[h.index(c)]}]" for c in cols])
-    rows.append([rep.split("/")[-1], v[h.index("Kernel Name")]] + [v[h.index(c)] if c in h else "" for c in hdr_out])
+        rows.append(["report", "Kernel Name"] + [f"{c} [{BASE.get(units[h.index(c)], units[h.index(c)])}]" for c in cols])
+    rows.append([rep.split("/")[-1], v[h.index("Kernel Name")]] + [norm(c) if c in h else "" for c in hdr_out])
 csv.writer(open(out, "w")).writerows(rows)
 for r in rows: print(",".join(r)[:400])
