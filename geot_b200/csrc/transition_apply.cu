@@ -21,34 +21,46 @@ constexpr int kApplyThreads = kApplyWarps * 32;
 constexpr int kApplyTile = 32;  // points per CTA tile (4 per warp)
 
 struct ApplySmem {
-  // floats: E[C*C] | lt[C][33] | gt[C][33] | ot[C][33] | per warp { sv[C*Cp] | ca[64] | cb[64] }
-  int C, Cp;
-  __host__ __device__ ApplySmem(int c) : C(c), Cp(c | 1) {}
+  // floats: E[C*C] | lt[C][33] | gt[C][33] | ot[C][33] | per warp { sv[nbuf][C*Cp] | ca[64] | cb[64] }
+  int C, Cp, nbuf;  // nbuf = 2: the next point's matrix is prefetched while this one is used (needs 2 tiles per warp)
+  __host__ __device__ ApplySmem(int c, int nb) : C(c), Cp(c | 1), nbuf(nb) {}
   __host__ __device__ size_t e_off() const { return 0; }
   __host__ __device__ size_t lt_off() const { return ((size_t)C * C + 3) & ~(size_t)3; }
   __host__ __device__ size_t gt_off() const { return lt_off() + (size_t)C * 33; }
   __host__ __device__ size_t ot_off() const { return gt_off() + (size_t)C * 33; }
-  __host__ __device__ size_t warp_off(int w) const { return ot_off() + (size_t)C * 33 + (size_t)w * ((size_t)C * Cp + 128); }
+  __host__ __device__ size_t warp_off(int w) const { return ot_off() + (size_t)C * 33 + (size_t)w * ((size_t)nbuf * C * Cp + 128); }
   __host__ __device__ size_t bytes() const { return warp_off(kApplyWarps) * sizeof(float); }
 };
 
 // BWD == false: computes out.  BWD == true: computes grad_logits and/or grad_insT from grad_out.
 template <bool BWD>
 __global__ void __launch_bounds__(kApplyThreads)
-transition_apply_kernel(int B, int C, int N, const float* __restrict__ logits, const float* __restrict__ ema_t,
+transition_apply_kernel(int B, int C, int N, int nbuf, const float* __restrict__ logits, const float* __restrict__ ema_t,
                         const float* __restrict__ insT, float lam, const float* __restrict__ grad_out,
                         float* __restrict__ out_or_gl, float* __restrict__ grad_insT) {
   extern __shared__ __align__(16) float apply_smem[];
-  const ApplySmem L(C);
+  const ApplySmem L(C, nbuf);
   const int Cp = L.Cp, C2 = C * C;
   float* E_s = apply_smem + L.e_off();    // lam * ema_t
   float* lt = apply_smem + L.lt_off();    // logits tile      [kk][pt]
   float* gt = apply_smem + L.gt_off();    // grad_out tile    [j][pt]            (BWD)
   float* ot = apply_smem + L.ot_off();    // out / grad_logits tile [c][pt]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  float* sv = apply_smem + L.warp_off(warp);
-  float* ca = sv + (size_t)C * Cp;
+  float* svbuf = apply_smem + L.warp_off(warp);  // two T_n buffers: the next point's matrix lands while this one is used
+  float* ca = svbuf + (size_t)nbuf * C * Cp;
   float* cb = ca + 64;
+  // T_n (4*C*C contiguous bytes, only 4-byte aligned for odd C) -> padded [kk][Cp] layout, asynchronously
+  auto prefetch = [&](int64_t g, float* buf) {
+    const float* __restrict__ T = insT + g * C2;
+    int kk = 0, j = lane;
+    while (j >= C) { j -= C; kk++; }
+    for (int f = lane; f < C2; f += 32) {
+      const unsigned dst = (unsigned)__cvta_generic_to_shared(buf + kk * Cp + j);
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(T + f) : "memory");
+      j += 32;
+      while (j >= C) { j -= C; kk++; }
+    }
+  };
   const int64_t BN = (int64_t)B * N;
   const float oml = 1.0f - lam;
 
@@ -57,6 +69,8 @@ transition_apply_kernel(int B, int C, int N, const float* __restrict__ logits, c
   const int64_t ntiles = (BN + kApplyTile - 1) / kApplyTile;
   for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int64_t g0 = tile * kApplyTile;
+    if (nbuf == 2 && g0 + warp < BN) prefetch(g0 + warp, svbuf);  // flies under the tile loads below
+    asm volatile("cp.async.commit_group;" ::: "memory");
     __syncthreads();  // previous tile's ot fully stored; E_s visible on the first pass
     for (int e = threadIdx.x; e < C * kApplyTile; e += kApplyThreads) {
       const int c = e >> 5, pt = e & 31;
@@ -72,15 +86,24 @@ transition_apply_kernel(int B, int C, int N, const float* __restrict__ logits, c
     }
     __syncthreads();
 
-    for (int pt = warp; pt < kApplyTile; pt += kApplyWarps) {
+    for (int pt = warp, it = 0; pt < kApplyTile; pt += kApplyWarps, it++) {
       const int64_t g = g0 + pt;
       if (g >= BN) break;  // warp-uniform
-      const float* __restrict__ T = insT + g * C2;
-      {  // blend: sv[kk][j] = lam*E + (1-lam)*T
+      float* sv = svbuf + (nbuf == 2 ? (size_t)(it & 1) * C * Cp : 0);
+      if (nbuf == 2) {
+        if (pt + kApplyWarps < kApplyTile && g + kApplyWarps < BN) prefetch(g + kApplyWarps, svbuf + (size_t)((it + 1) & 1) * C * Cp);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_group 1;" ::: "memory");  // this point's matrix has landed (own copies; same lane blends them)
+      } else {  // large C: one tile per warp, no overlap
+        prefetch(g, sv);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+      }
+      {  // blend in place: sv[kk][j] = lam*E + (1-lam)*T
         int kk = 0, j = lane;
         while (j >= C) { j -= C; kk++; }
         for (int f = lane; f < C2; f += 32) {
-          sv[kk * Cp + j] = __fmaf_rn(oml, __ldg(T + f), E_s[f]);
+          sv[kk * Cp + j] = __fmaf_rn(oml, sv[kk * Cp + j], E_s[f]);
           j += 32;
           while (j >= C) { j -= C; kk++; }
         }
@@ -142,7 +165,9 @@ transition_apply_kernel(int B, int C, int N, const float* __restrict__ logits, c
 template <bool BWD>
 static int launch_apply(int B, int C, int N, const float* logits, const float* ema_t, const float* insT,
                         float lam, const float* grad_out, float* out_or_gl, float* grad_insT, cudaStream_t s) {
-  const ApplySmem L(C);
+  int nbuf = 2;
+  if (ApplySmem(C, 2).bytes() > (size_t)112 * 1024) nbuf = 1;  // keep two CTAs per SM
+  const ApplySmem L(C, nbuf);
   const size_t smem = L.bytes();
   static size_t configured = 0;
   if (smem > configured) {
@@ -151,10 +176,10 @@ static int launch_apply(int B, int C, int N, const float* logits, const float* e
     configured = smem;
   }
   const int64_t tiles = ((int64_t)B * N + kApplyTile - 1) / kApplyTile;
-  const int per_sm = smem > 110 * 1024 ? 1 : (smem > 72 * 1024 ? 2 : 3);
+  const int per_sm = smem > 110 * 1024 ? 1 : (smem > 72 * 1024 ? 2 : (smem > 54 * 1024 ? 3 : 4));
   const int64_t cap = (int64_t)kNumSMs * per_sm;
   const int grid = (int)(tiles < cap ? tiles : cap);
-  transition_apply_kernel<BWD><<<grid, kApplyThreads, smem, s>>>(B, C, N, logits, ema_t, insT, lam, grad_out, out_or_gl, grad_insT);
+  transition_apply_kernel<BWD><<<grid, kApplyThreads, smem, s>>>(B, C, N, nbuf, logits, ema_t, insT, lam, grad_out, out_or_gl, grad_insT);
   count_launch(1);
   return check_launch(BWD ? "transition_apply_kernel<bwd>" : "transition_apply_kernel<fwd>");
 }

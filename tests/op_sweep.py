@@ -2,7 +2,7 @@
 """GPU box: per-op timing of this library against the reference's OWN kernels (oracle/_ref/*.so, compiled
 unchanged from /root/reference) on identical inputs — SURVEY.md §8(a) rows, §8(d) algorithmic bytes.
 
-    python tools/op_sweep.py [--out gpurun_out/op_sweep.json]
+    python tests/op_sweep.py [--out gpurun_out/op_sweep.json]
 
 Every line: op, shape, ours ms, reference ms, speed-up, algorithmic bytes, achieved GB/s, fraction of the
 measured HBM peak (MEASURED_PEAKS.json).  The backward of the reference accumulates with float atomics into a

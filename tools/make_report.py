@@ -7,7 +7,7 @@ tag = sys.argv[1]
 b = json.load(open(os.path.join(ROOT, "profiles", f"{tag}_bench.json")))
 sw = json.load(open(os.path.join(ROOT, "profiles", f"{tag}_op_sweep.json")))
 L = [f"# Measured on B200 — {tag}", "",
-     "Sources: `profiles/%s_bench.json` (python bench.py), `profiles/%s_op_sweep.json` (python tools/op_sweep.py), "
+     "Sources: `profiles/%s_bench.json` (python bench.py), `profiles/%s_op_sweep.json` (python tests/op_sweep.py), "
      "`profiles/%s_launches_bench.csv` + `profiles/%s_ncu_full_summary.csv` (ncu)." % (tag, tag, tag, tag), "",
      "## Bench line (B=64 x N=16384 per GPU, FPS(1024) + gather + ball_query(0.1, 32) + grouping C=3 + grouping C=64)", "",
      f"* device-resident: **{b['value']/1e6:.0f} M points/s** ({b['ms_per_step']:.3f} ms/step)",
