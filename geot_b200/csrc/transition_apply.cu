@@ -10,11 +10,14 @@
 // from that tile, and the (B,C,N) <-> point-major permutes are folded into a 32-point CTA tile so that
 // logits / grad_out loads and out / grad_logits stores are 128-byte rows.  HBM-bound: 4*C*C bytes per point
 // forward, 8*C*C backward (read insT, write grad_insT); nothing else of that size is materialised.
+#include <algorithm>
 #include "common.cuh"
 
 namespace geot {
 
 void count_launch(int n);
+bool direct_kernels_forced();  // geot_group_points_config (group.cu): A/B switch, also selects the warp-per-point kernel here
+static inline bool apply_force_warp_kernel() { return direct_kernels_forced(); }
 
 constexpr int kApplyWarps = 8;
 constexpr int kApplyThreads = kApplyWarps * 32;
@@ -162,9 +165,227 @@ transition_apply_kernel(int B, int C, int N, int nbuf, const float* __restrict__
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Tile kernel (default for the class counts it is instantiated for: odd C, 16-byte aligned insT).
+// The warp-per-point kernel above spends ~1100 warp instructions per point on index bookkeeping, 33-wide loops
+// on 32 lanes and shared-memory round trips, and runs at 15-20 % of the HBM rate.  Here a LANE owns a point:
+// a persistent CTA (8 warps) pulls tiles of 16 consecutive points - 16*C*C contiguous floats - through a
+// double-buffered shared tile by bulk async copies (mbarrier completion), lane (p, h) walks rows kk of point p
+// with the blended row in REGISTERS (C is a template parameter): row L1 norm, the 1xC . CxC partial product
+// (forward) or the dot with grad_out and the grad_insT row (backward, written IN PLACE into the tile, which then
+// leaves by one bulk async store).  Point stride C*C is odd, so the 16 points of a half-warp hit 16 different
+// banks and the two halves (rows 16 apart) the other 16.  The sixteen row groups' partial outputs are summed in a
+// fixed order.  HBM-bound: 4*C*C bytes per point forward, 8*C*C backward.
+// ---------------------------------------------------------------------------------------------
+constexpr int kTileP = 16;      // points per tile
+constexpr int kTileThreads = 256;
+constexpr int kTileGroups = 2 * kTileThreads / 32;  // row groups: (warp, half-warp)
+__device__ __forceinline__ void ta_mbar_init(uint64_t* bar) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void ta_mbar_wait(uint64_t* bar, unsigned parity) {
+  asm volatile(
+      "{\n.reg .pred p;\nTA_WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@!p bra TA_WAIT_%=;\n}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void ta_bulk_load(float* dst, const float* src, unsigned bytes, uint64_t* bar) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+  for (unsigned o = 0; o < bytes; o += 8192u) {
+    const unsigned n = min(8192u, bytes - o);
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(reinterpret_cast<const unsigned char*>(dst) + o)), "l"(reinterpret_cast<const unsigned char*>(src) + o),
+                   "r"(n), "r"(smem_u32(bar)) : "memory");
+  }
+}
+__device__ __forceinline__ void ta_bulk_store(float* dst, const float* src, unsigned bytes) {
+  for (unsigned o = 0; o < bytes; o += 8192u) {
+    const unsigned n = min(8192u, bytes - o);
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                 ::"l"(reinterpret_cast<unsigned char*>(dst) + o), "r"(smem_u32(reinterpret_cast<const unsigned char*>(src) + o)), "r"(n) : "memory");
+  }
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+
+template <int C>
+struct TileSmem {
+  static constexpr int C2 = C * C;
+  static constexpr int kTile = ((kTileP * C2 + 3) / 4) * 4;             // floats per tile buffer
+  static constexpr int kRowT = C * (kTileP + 1);                        // one [C][17] tile
+  static constexpr int kOffE = 2 * kTile;                               // lam * ema_t
+  static constexpr int kOffL = kOffE + ((C2 + 3) / 4) * 4;              // lt[2][C][17]
+  static constexpr int kOffG = kOffL + 2 * kRowT;                       // gt[2][C][17]
+  static constexpr int kOffO = kOffG + 2 * kRowT;                       // ot[C][17]
+  static constexpr int kOffP = kOffO + kRowT;                           // part[16][16][C]  (forward)
+  static constexpr int kFloats = kOffP + kTileGroups * kTileP * C;
+  static constexpr size_t kBytes = (size_t)kFloats * sizeof(float);
+};
+
+template <int C, bool BWD>
+__global__ void __launch_bounds__(kTileThreads, 1)
+transition_apply_tile_kernel(int B, int N, const float* __restrict__ logits, const float* __restrict__ ema_t,
+                             const float* __restrict__ insT, float lam, const float* __restrict__ grad_out,
+                             float* __restrict__ out_or_gl, float* __restrict__ grad_insT) {
+  using L = TileSmem<C>;
+  constexpr int C2 = C * C, LP = kTileP + 1;
+  extern __shared__ __align__(128) float ta_smem[];
+  __shared__ uint64_t bar[2];
+  float* E_s = ta_smem + L::kOffE;
+  float* ot = ta_smem + L::kOffO;
+  float* part = ta_smem + L::kOffP;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5, p = lane & 15, h = lane >> 4;
+  const int64_t BN = (int64_t)B * N;
+  const int64_t ntiles = (BN + kTileP - 1) / kTileP;
+  const float oml = 1.0f - lam;
+  if (t == 0) {
+    ta_mbar_init(&bar[0]);
+    ta_mbar_init(&bar[1]);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  for (int e = t; e < C2; e += kTileThreads) E_s[e] = lam * ema_t[e];
+  __syncthreads();
+  // Tile `tile` -> buffers `buf`: the matrices by bulk async copy (thread 0; full tiles only, 16*C*C*4 bytes is a
+  // multiple of 16), the logits / grad_out rows of its 16 points by 4-byte async copies (all threads; thread t
+  // always serves point t & 15, so the (b, n) split of the point index is computed once per tile).
+  auto issue = [&](int64_t tile, int buf) {
+    if (t == 0 && (tile + 1) * kTileP <= BN)
+      ta_bulk_load(ta_smem + buf * L::kTile, insT + tile * kTileP * C2, (unsigned)(kTileP * C2 * 4), &bar[buf]);
+    const int pt = t & 15;
+    const int64_t g = tile * kTileP + pt;
+    if (g < BN) {
+      const int64_t b = g / N, n = g - b * N;
+      float* lt = ta_smem + L::kOffL + buf * L::kRowT;
+      float* gt = ta_smem + L::kOffG + buf * L::kRowT;
+      for (int c = t >> 4; c < C; c += kTileThreads / 16) {
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(lt + c * LP + pt)), "l"(logits + (b * C + c) * N + n) : "memory");
+        if (BWD) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(gt + c * LP + pt)), "l"(grad_out + (b * C + c) * N + n) : "memory");
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  int64_t tile = blockIdx.x;
+  if (tile < ntiles) issue(tile, 0);
+  for (int it = 0; tile < ntiles; tile += gridDim.x, it++) {
+    const int cur = it & 1;
+    float* Tb = ta_smem + cur * L::kTile;
+    const float* lt = ta_smem + L::kOffL + cur * L::kRowT;
+    const float* gt = ta_smem + L::kOffG + cur * L::kRowT;
+    const int64_t g0 = tile * kTileP;
+    const int npts = (int)min((int64_t)kTileP, BN - g0);
+    const bool full = npts == kTileP;
+    const int64_t nxt = tile + gridDim.x;
+    if (nxt < ntiles) {
+      if (BWD && t == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // the store that still reads the other buffer
+      issue(nxt, cur ^ 1);
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+    if (!full)  // ragged last tile: its byte count need not be a multiple of 16
+      for (int e = t; e < npts * C2; e += kTileThreads) Tb[e] = __ldg(insT + g0 * C2 + e);
+    __syncthreads();
+    if (full) ta_mbar_wait(&bar[cur], (unsigned)((it >> 1) & 1));
+
+    if (p < npts) {
+      float* Tp = Tb + p * C2;
+      float acc[C];  // forward: partial out[j]; backward: grad_out[j] of this point
+#pragma unroll
+      for (int j = 0; j < C; j++) acc[j] = BWD ? gt[j * LP + p] : 0.f;
+#pragma unroll 1
+      for (int t4 = 0; t4 < 2 * ((C + 31) / 32); t4++) {
+        const int kk = (t4 >> 1) * 32 + warp + 8 * (t4 & 1) + 16 * h;
+        if (kk < C) {
+          float v[C];
+          float s = 0.f, d = 0.f;
+#pragma unroll
+          for (int j = 0; j < C; j++) {
+            v[j] = __fmaf_rn(oml, Tp[kk * C + j], E_s[kk * C + j]);
+            s += fabsf(v[j]);
+            if (BWD) d = __fmaf_rn(acc[j], v[j], d);
+          }
+          const float inv = 1.0f / fmaxf(s, 1e-12f);  // F.normalize: x / max(||x||_1, 1e-12)
+          const float l = lt[kk * LP + p];
+          if (!BWD) {
+            const float ca = l * inv;
+#pragma unroll
+            for (int j = 0; j < C; j++) acc[j] = __fmaf_rn(ca, v[j], acc[j]);
+          } else {
+            const float cb = d * inv;  // sum_m go[m] * newT[kk][m] = grad_logits[kk]
+            ot[kk * LP + p] = cb;
+            if (grad_insT != nullptr) {
+              const float ca = oml * l * inv;
+#pragma unroll
+              for (int j = 0; j < C; j++) {
+                const float sgn = v[j] > 0.f ? 1.0f : (v[j] < 0.f ? -1.0f : 0.f);
+                Tp[kk * C + j] = ca * (acc[j] - sgn * cb);  // in place: this lane is the only user of the row
+              }
+            }
+          }
+        }
+      }
+      if (!BWD) {
+#pragma unroll
+        for (int j = 0; j < C; j++) part[((warp * 2 + h) * kTileP + p) * C + j] = acc[j];
+      }
+    }
+    if (BWD && grad_insT != nullptr) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
+    if (!BWD || out_or_gl != nullptr) {
+      const int pt = t & 15;
+      if (pt < npts) {
+        const int64_t g = g0 + pt, b = g / N, n = g - b * N;
+        for (int c = t >> 4; c < C; c += kTileThreads / 16) {
+          float o;
+          if (BWD) o = ot[c * LP + pt];
+          else {
+            o = 0.f;
+#pragma unroll
+            for (int q = 0; q < kTileGroups; q++) o += part[(q * kTileP + pt) * C + c];
+          }
+          out_or_gl[(b * C + c) * N + n] = o;
+        }
+      }
+    }
+    if (BWD && grad_insT != nullptr) {
+      if (full) {
+        if (t == 0) ta_bulk_store(grad_insT + g0 * C2, Tb, (unsigned)(kTileP * C2 * 4));
+      } else {
+        for (int e = t; e < npts * C2; e += kTileThreads) grad_insT[g0 * C2 + e] = Tb[e];
+      }
+    }
+    __syncthreads();  // ot / part are rewritten by the next tile
+  }
+  if (BWD && t == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
+template <int C, bool BWD>
+static int launch_apply_tile(int B, int N, const float* logits, const float* ema_t, const float* insT, float lam,
+                             const float* grad_out, float* out_or_gl, float* grad_insT, cudaStream_t s) {
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(transition_apply_tile_kernel<C, BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TileSmem<C>::kBytes);
+    if (e != cudaSuccess) { set_error("transition_apply: cudaFuncSetAttribute(%zu): %s", TileSmem<C>::kBytes, cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
+    configured = true;
+  }
+  const int64_t tiles = ((int64_t)B * N + kTileP - 1) / kTileP;
+  const int per_sm = TileSmem<C>::kBytes > 110 * 1024 ? 1 : (TileSmem<C>::kBytes > 72 * 1024 ? 2 : 3);
+  const int grid = (int)std::min<int64_t>(tiles, (int64_t)kNumSMs * per_sm);
+  transition_apply_tile_kernel<C, BWD><<<grid, kTileThreads, TileSmem<C>::kBytes, s>>>(B, N, logits, ema_t, insT, lam, grad_out, out_or_gl, grad_insT);
+  count_launch(1);
+  return check_launch(BWD ? "transition_apply_tile_kernel<bwd>" : "transition_apply_tile_kernel<fwd>");
+}
+
 template <bool BWD>
 static int launch_apply(int B, int C, int N, const float* logits, const float* ema_t, const float* insT,
                         float lam, const float* grad_out, float* out_or_gl, float* grad_insT, cudaStream_t s) {
+  if (!apply_force_warp_kernel() && (((uintptr_t)insT) & 15) == 0 && (grad_insT == nullptr || (((uintptr_t)grad_insT) & 15) == 0)) {
+    switch (C) {  // the class counts of the reference configs (17), BASELINE config 4 (33) and the small test shape
+      case 5: return launch_apply_tile<5, BWD>(B, N, logits, ema_t, insT, lam, grad_out, out_or_gl, grad_insT, s);
+      case 17: return launch_apply_tile<17, BWD>(B, N, logits, ema_t, insT, lam, grad_out, out_or_gl, grad_insT, s);
+      case 33: return launch_apply_tile<33, BWD>(B, N, logits, ema_t, insT, lam, grad_out, out_or_gl, grad_insT, s);
+      default: break;
+    }
+  }
   int nbuf = 2;
   if (ApplySmem(C, 2).bytes() > (size_t)112 * 1024) nbuf = 1;  // keep two CTAs per SM
   const ApplySmem L(C, nbuf);

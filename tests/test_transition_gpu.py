@@ -93,7 +93,7 @@ def test_golden_class_statistics(cuda):
     assert torch.equal(cn.cpu(), t(f"{tag}_mf_cnum", "cpu"))
 
 
-@pytest.mark.parametrize("C,B,N", [(17, 2, 16000), (33, 2, 4096), (33, 3, 1000), (8, 2, 333), (64, 1, 130)])
+@pytest.mark.parametrize("C,B,N", [(17, 2, 16000), (33, 2, 4096), (33, 3, 1000), (33, 2, 1003), (17, 3, 7), (8, 2, 333), (64, 1, 130)])
 def test_oracle_sigt_apply_large(cuda, C, B, N):
     g = torch.Generator().manual_seed(C * 1000 + N)
     x = torch.softmax(torch.randn(B, C, N, generator=g) * 3, 1)
@@ -173,3 +173,37 @@ def test_oracle_class_pick_large(cuda):
     corrc, ema2c = T.class_T_step(ctc, ema.cuda(), sigma.cuda(), T.LABEL_PROJ_33, 0.999, 0.999)
     close(corrc, corr, rtol=1e-5, atol=1e-8)
     close(ema2c, ema2, rtol=1e-5, atol=1e-8)
+
+
+@pytest.mark.parametrize("C,B,N", [(33, 2, 16000), (17, 5, 1001), (5, 1, 15), (33, 1, 37)])
+def test_apply_tile_kernel_vs_warp_kernel(cuda, C, B, N):
+    """The lane-per-point tile kernel (bulk async tiles of 16 points, default for C in {5,17,33}) against the
+    warp-per-point kernel (geot_group_points_config(1) selects it): forward, grad_logits, grad_insT, including a
+    ragged last tile, negative entries (sign term of the L1-norm gradient) and only-logits / only-insT gradients."""
+    from geot_b200 import _lib
+    g = torch.Generator(device="cuda").manual_seed(C + N)
+    logits = torch.randn(B, C, N, device="cuda", generator=g)
+    ema = torch.softmax(torch.randn(C, C, device="cuda", generator=g), 1)
+    insT = torch.randn(B * N, C, C, device="cuda", generator=g)  # signed on purpose
+    go = torch.randn(B, C, N, device="cuda", generator=g)
+
+    def run(need_l, need_i):
+        l = logits.clone().requires_grad_(need_l); i = insT.clone().requires_grad_(need_i)
+        out = T.apply_transition(l, ema, i, 0.9)
+        out.backward(go)
+        return out.detach(), l.grad, i.grad
+
+    res = {}
+    for direct in (0, 1):
+        _lib.lib().geot_group_points_config(direct)
+        try:
+            res[direct] = [run(True, True), run(True, False), run(False, True)]
+        finally:
+            _lib.lib().geot_group_points_config(0)
+    for a, b in zip(res[0], res[1]):
+        for x, y in zip(a, b):
+            assert (x is None) == (y is None)
+            if x is not None:
+                assert rel(x, y) < 1e-5
+    ref = R.transition_apply(logits, ema, insT, 0.9)
+    assert rel(res[0][0][0], ref) < 1e-5
