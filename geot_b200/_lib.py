@@ -42,6 +42,8 @@ _SIGNATURES = {
     "geot_scatter_plan_bytes": [_i, _i, _i64],
     "geot_scatter_plan_build": [_i, _i, _i64, _vp, _vp, _sz, _vp],
     "geot_group_points_grad": [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp],
+    "geot_scatter_plan_pieces": [_i, _i64],
+    "geot_group_points_grad_pieces": [_i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp],
     "geot_gather_points_grad": [_i, _i, _i, _i, _vp, _vp, _vp, _vp],
     "geot_three_nn": [_i, _i, _i, _vp, _vp, _vp, _vp, _vp],
     "geot_three_interpolate": [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp],

@@ -34,7 +34,7 @@ class _PointNet2Batch:
 
     @staticmethod
     def group_points_grad_wrapper(B, C, N, M, nsample, grad_out, idx, grad_points):
-        F_.group_points_grad(grad_out, F_.ScatterPlan(idx, B, N), N, out=grad_points)
+        F_.group_points_grad(grad_out, F_.grouping_plan(idx, B, N), N, out=grad_points)
         return 1
 
     @staticmethod
@@ -177,7 +177,7 @@ class _PointNet2Ext:
     @classmethod
     def group_points_grad(cls, grad_out, idx, n):
         cls._chk(grad_out, torch.float32, "grad_out"); cls._chk(idx, torch.int32, "idx")
-        return F_.group_points_grad(grad_out, F_.ScatterPlan(idx, idx.shape[0], n), n)
+        return F_.group_points_grad(grad_out, F_.grouping_plan(idx, idx.shape[0], n), n)
 
 
 pointnet2_batch_cuda = _PointNet2Batch()

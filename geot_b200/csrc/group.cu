@@ -391,7 +391,7 @@ seg_reduce_cmajor_kernel(int C, int N, int64_t E, const float* __restrict__ g,
 // Summation order = plan order (ascending source), exactly as in the direct kernel: same bits.
 constexpr int kPrTaskCap = 5456;  // non-empty targets the compact task list can hold (6 bytes each in 32 KB)
 __global__ void __launch_bounds__(1024, 1)
-seg_reduce_planrow_kernel(int C, int N, int E, int cpc, const float* __restrict__ g, const int* __restrict__ row_ptr,
+seg_reduce_planrow_kernel(int C, int N, int E, int Q, int cpc, const float* __restrict__ g, const int* __restrict__ row_ptr,
                           const int* __restrict__ perm, float* __restrict__ dst) {
   extern __shared__ __align__(16) unsigned char pr_smem[];
   __shared__ uint64_t bar;
@@ -406,82 +406,136 @@ seg_reduce_planrow_kernel(int C, int N, int E, int cpc, const float* __restrict_
   unsigned short* t_len = rp16 + 2 * kPrTaskCap;
   const int t = threadIdx.x, lane = t & 31;
   const int b = blockIdx.y, c_first = blockIdx.x * cpc;
+  const int nc = min(cpc, C - c_first);
+  const int64_t Etot = (int64_t)E * Q;  // a gradient row has Q pieces of E values; the plan has one CSR per (cloud, piece)
   if (t == 0) {
     mbar_init(&bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    s_ne = 0;
   }
-  if (t < 64) s_bin[t] = 0;
-  __syncthreads();
-  if (t == 0) {
-    bulk_g2s_chunked(row, g + ((int64_t)b * C + c_first) * E, (unsigned)E * 4u, &bar);
-  }
-  const int* __restrict__ pm = perm + (int64_t)b * E;
-  const int* __restrict__ rp = row_ptr + (int64_t)b * (N + 1);
-  for (int i = t; i < E; i += 1024) perm16[i] = (unsigned short)__ldg(pm + i);
-  // ball_query keeps the LOWEST indices of every ball, so most points are never a neighbour (80 % of the targets
-  // are empty at the bench shape) and the rest have ~10 sources.  When the non-empty targets fit the task list
-  // they are bucketed by segment length (64 bins, longest first): a warp then works on 32 segments of (almost)
-  // equal length - no empty targets, no divergence on the segment loop.
-  for (int k = t; k < N; k += 1024) {
-    const int len = __ldg(rp + k + 1) - __ldg(rp + k);
-    if (len > 0) atomicAdd(&s_bin[63 - min(len, 63)], 1);
-  }
-  __syncthreads();
-  if (t < 32) {  // exclusive scan of the 64 bins (bin 0 = longest)
-    const int a0 = s_bin[2 * lane], a1 = s_bin[2 * lane + 1];
-    int inc = a0 + a1;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int y = __shfl_up_sync(0xffffffffu, inc, o);
-      if (lane >= o) inc += y;
-    }
-    s_bin[2 * lane] = inc - a0 - a1;
-    s_bin[2 * lane + 1] = inc - a1;
-    if (lane == 31) s_ne = inc;
-  }
-  __syncthreads();
-  const int ne = s_ne;
-  const bool compact = ne <= kPrTaskCap;
-  if (compact) {
+  unsigned loads = 0;  // bulk copies waited for so far (mbarrier phase parity)
+#pragma unroll 1
+  for (int q = 0; q < Q; q++) {
+    __syncthreads();  // previous piece: every thread is done with perm16 / the task list / s_bin
+    if (t == 0) s_ne = 0;
+    if (t < 64) s_bin[t] = 0;
+    __syncthreads();
+    if (t == 0) bulk_g2s_chunked(row, g + ((int64_t)b * C + c_first) * Etot + (int64_t)q * E, (unsigned)E * 4u, &bar);
+    const int* __restrict__ pm = perm + ((int64_t)b * Q + q) * E;
+    const int* __restrict__ rp = row_ptr + ((int64_t)b * Q + q) * (N + 1);
+    for (int i = t; i < E; i += 1024) perm16[i] = (unsigned short)__ldg(pm + i);
+    // ball_query keeps the LOWEST indices of every ball, so most points are never a neighbour (80 % of the targets
+    // are empty at the bench shape) and the rest have ~10 sources.  When the non-empty targets fit the task list
+    // they are bucketed by segment length (64 bins, longest first): a warp then works on 32 segments of (almost)
+    // equal length - no empty targets, no divergence on the segment loop.
     for (int k = t; k < N; k += 1024) {
-      const int s0 = __ldg(rp + k), len = __ldg(rp + k + 1) - s0;
-      if (len > 0) {
-        const int pos = atomicAdd(&s_bin[63 - min(len, 63)], 1);  // order inside a bin is free: sums do not depend on it
-        t_tgt[pos] = (unsigned short)k; t_start[pos] = (unsigned short)s0; t_len[pos] = (unsigned short)len;
-      }
+      const int len = __ldg(rp + k + 1) - __ldg(rp + k);
+      if (len > 0) atomicAdd(&s_bin[63 - min(len, 63)], 1);
     }
-  } else {
-    for (int i = t; i <= N; i += 1024) rp16[i] = (unsigned short)__ldg(rp + i);
-  }
-  __syncthreads();
-  const int nc = min(cpc, C - c_first);
-  for (int ci = 0; ci < nc; ci++) {
-    float* __restrict__ out = dst + ((int64_t)b * C + c_first + ci) * N;
+    __syncthreads();
+    if (t < 32) {  // exclusive scan of the 64 bins (bin 0 = longest)
+      const int a0 = s_bin[2 * lane], a1 = s_bin[2 * lane + 1];
+      int inc = a0 + a1;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int y = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += y;
+      }
+      s_bin[2 * lane] = inc - a0 - a1;
+      s_bin[2 * lane + 1] = inc - a1;
+      if (lane == 31) s_ne = inc;
+    }
+    __syncthreads();
+    const int ne = s_ne;
+    const bool compact = ne <= kPrTaskCap;
     if (compact) {
-      for (int k = t; k < N; k += 1024) out[k] = 0.f;  // empty targets; the others are overwritten below
-      mbar_wait(&bar, (unsigned)(ci & 1));
-      __syncthreads();  // zero fill ordered before the sums of this CTA
-      for (int i = t; i < ne; i += 1024) {
-        const int s0 = t_start[i], e0 = s0 + t_len[i];
-        float acc = 0.f;
-        for (int p = s0; p < e0; p++) acc = __fadd_rn(acc, row[perm16[p]]);
-        out[t_tgt[i]] = acc;
+      for (int k = t; k < N; k += 1024) {
+        const int s0 = __ldg(rp + k), len = __ldg(rp + k + 1) - s0;
+        if (len > 0) {
+          const int pos = atomicAdd(&s_bin[63 - min(len, 63)], 1);  // order inside a bin is free: sums do not depend on it
+          t_tgt[pos] = (unsigned short)k; t_start[pos] = (unsigned short)s0; t_len[pos] = (unsigned short)len;
+        }
       }
     } else {
-      mbar_wait(&bar, (unsigned)(ci & 1));
-      for (int k = t; k < N; k += 1024) {
-        const int s0 = rp16[k], e0 = rp16[k + 1];
-        float acc = 0.f;
-        for (int p = s0; p < e0; p++) acc = __fadd_rn(acc, row[perm16[p]]);
-        out[k] = acc;
+      for (int i = t; i <= N; i += 1024) rp16[i] = (unsigned short)__ldg(rp + i);
+    }
+    __syncthreads();
+    for (int ci = 0; ci < nc; ci++) {
+      float* __restrict__ out = dst + ((int64_t)b * C + c_first + ci) * N;
+      // piece 0 writes every target, later pieces add to it: the same thread order every run, so the sum
+      // ((piece 0 + piece 1) + ...) is fixed
+      if (compact) {
+        if (q == 0)
+          for (int k = t; k < N; k += 1024) out[k] = 0.f;  // empty targets; the others are overwritten below
+        mbar_wait(&bar, loads & 1u);
+        __syncthreads();  // zero fill ordered before the sums of this CTA
+        for (int i = t; i < ne; i += 1024) {
+          const int s0 = t_start[i], e0 = s0 + t_len[i];
+          float acc = 0.f;
+          for (int p = s0; p < e0; p++) acc = __fadd_rn(acc, row[perm16[p]]);
+          const int k = t_tgt[i];
+          out[k] = q == 0 ? acc : __fadd_rn(out[k], acc);
+        }
+      } else {
+        mbar_wait(&bar, loads & 1u);
+        for (int k = t; k < N; k += 1024) {
+          const int s0 = rp16[k], e0 = rp16[k + 1];
+          float acc = 0.f;
+          for (int p = s0; p < e0; p++) acc = __fadd_rn(acc, row[perm16[p]]);
+          out[k] = q == 0 ? acc : __fadd_rn(out[k], acc);
+        }
+      }
+      loads++;
+      __syncthreads();  // every thread is done with the row buffer (and, for later pieces, its writes to out are ordered)
+      if (t == 0 && ci + 1 < nc) {
+        bulk_g2s_chunked(row, g + ((int64_t)b * C + c_first + ci + 1) * Etot + (int64_t)q * E, (unsigned)E * 4u, &bar);
       }
     }
-    __syncthreads();  // every thread is done with the row buffer
-    if (t == 0 && ci + 1 < nc) {
-      bulk_g2s_chunked(row, g + ((int64_t)b * C + c_first + ci + 1) * E, (unsigned)E * 4u, &bar);
-    }
   }
+}
+
+// Pieces plan without the shared-memory path (unaligned gradient): one thread per target, pieces in order.
+__global__ void __launch_bounds__(256)
+seg_reduce_pieces_direct_kernel(int C, int N, int E, int Q, const float* __restrict__ g, const int* __restrict__ row_ptr,
+                                const int* __restrict__ perm, float* __restrict__ dst) {
+  const int b = blockIdx.z, c = blockIdx.y;
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= N) return;
+  const float* __restrict__ gr = g + ((int64_t)b * C + c) * E * Q;
+  float total = 0.f;
+  for (int q = 0; q < Q; q++) {
+    const int* __restrict__ rp = row_ptr + ((int64_t)b * Q + q) * (N + 1);
+    const int* __restrict__ pm = perm + ((int64_t)b * Q + q) * E;
+    float acc = 0.f;
+    for (int p = rp[k]; p < rp[k + 1]; p++) acc = __fadd_rn(acc, __ldg(gr + (int64_t)q * E + __ldg(pm + p)));
+    total = q == 0 ? acc : __fadd_rn(total, acc);
+  }
+  dst[((int64_t)b * C + c) * N + k] = total;
+}
+
+static size_t planrow_smem(int N, int64_t E) {
+  return (size_t)E * 4 + (size_t)((E + 7) & ~7) * 2 + std::max((size_t)(N + 1) * 2, (size_t)kPrTaskCap * 6) + 16;
+}
+static int launch_planrow(int B, int C, int N, int E, int Q, const float* g, const int* row_ptr, const int* perm, float* dst,
+                          cudaStream_t s, const char* what) {
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(seg_reduce_planrow_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+    if (e != cudaSuccess) { set_error("%s: cudaFuncSetAttribute: %s", what, cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
+    configured = true;
+  }
+  // channels per CTA: amortise the per-CTA plan setup (~0.8 of a row) without leaving the last wave half empty
+  int cpc = 4;
+  double best = 0.0;
+  for (int k = 4; k <= 8; k++) {
+    const double ctas = (double)B * ((C + k - 1) / k);
+    const double waves = std::ceil(ctas / kNumSMs);
+    const double score = ctas / (waves * kNumSMs) * k / (k + 0.8);
+    if (score > best) { best = score; cpc = k; }
+  }
+  dim3 grid((C + cpc - 1) / cpc, B);
+  seg_reduce_planrow_kernel<<<grid, 1024, planrow_smem(N, E), s>>>(C, N, E, Q, cpc, g, row_ptr, perm, dst);
+  count_launch(1);
+  return check_launch(what);
 }
 
 template <int DIV, bool WEIGHTED>
@@ -491,30 +545,9 @@ static int launch_seg_reduce(int B, int C, int N, int64_t E, const float* g, con
   GEOT_REQUIRE(g && plan && dst, "%s: NULL pointer", what);
   GEOT_REQUIRE(B <= 65535 && (C + kSegCCH - 1) / kSegCCH <= 65535, "%s: B or C exceeds grid limits", what);
   const PlanView pv = plan_view(plan, B, N);
-  if (DIV == 1 && !WEIGHTED && !g_group_force_direct && E <= 65535 && E % 4 == 0 && E >= N && (((uintptr_t)g & 15) == 0)) {
-    const size_t smem = (size_t)E * 4 + (size_t)((E + 7) & ~7) * 2 + std::max((size_t)(N + 1) * 2, (size_t)kPrTaskCap * 6) + 16;
-    if (smem <= 226 * 1024) {
-      static bool configured = false;
-      if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(seg_reduce_planrow_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
-        if (e != cudaSuccess) { set_error("%s: cudaFuncSetAttribute: %s", what, cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
-        configured = true;
-      }
-      // channels per CTA: amortise the per-CTA plan setup (~0.8 of a row) without leaving the last wave half empty
-      int cpc = 4;
-      double best = 0.0;
-      for (int k = 4; k <= 8; k++) {
-        const double ctas = (double)B * ((C + k - 1) / k);
-        const double waves = std::ceil(ctas / kNumSMs);
-        const double score = ctas / (waves * kNumSMs) * k / (k + 0.8);
-        if (score > best) { best = score; cpc = k; }
-      }
-      dim3 grid((C + cpc - 1) / cpc, B);
-      seg_reduce_planrow_kernel<<<grid, 1024, smem, s>>>(C, N, (int)E, cpc, g, pv.row_ptr, pv.perm, dst);
-      count_launch(1);
-      return check_launch(what);
-    }
-  }
+  if (DIV == 1 && !WEIGHTED && !g_group_force_direct && E <= 65535 && E % 4 == 0 && E >= N && (((uintptr_t)g & 15) == 0) &&
+      planrow_smem(N, E) <= (size_t)226 * 1024)
+    return launch_planrow(B, C, N, (int)E, 1, g, pv.row_ptr, pv.perm, dst, s, what);
   dim3 grid((N + 255) / 256, (C + kSegCCH - 1) / kSegCCH, B);
   seg_reduce_cmajor_kernel<DIV, WEIGHTED><<<grid, 256, 0, s>>>(C, N, E, g, w, pv.row_ptr, pv.perm, dst);
   count_launch(1);
@@ -762,6 +795,36 @@ GEOT_API int geot_group_points_grad(int B, int C, int N, int M, int nsample, con
   GEOT_REQUIRE(B >= 0 && C >= 0 && N >= 0 && M >= 0 && nsample >= 0, "group_points_grad: bad sizes");
   return launch_seg_reduce<1, false>(B, C, N, (int64_t)M * nsample, grad_out, nullptr, plan, grad_points,
                                      as_stream(stream), "group_points_grad");
+}
+
+GEOT_API int geot_scatter_plan_pieces(int N, int64_t E) {
+  if (N <= 0 || E <= 0) return 1;
+  for (int Q = 1; Q <= 64; Q++) {
+    if (E % Q) continue;
+    const int64_t e = E / Q;
+    if (e <= 65535 && e % 4 == 0 && e >= N / 2 && planrow_smem(N, e) <= (size_t)226 * 1024) return Q;
+  }
+  return 1;
+}
+
+GEOT_API int geot_group_points_grad_pieces(int B, int C, int N, int M, int nsample, int pieces, const float* grad_out,
+                                           const void* plan, float* grad_points, geot_stream_t stream) {
+  GEOT_REQUIRE(B >= 0 && C >= 0 && N >= 0 && M >= 0 && nsample >= 0 && pieces >= 1, "group_points_grad_pieces: bad sizes");
+  const int64_t E = (int64_t)M * nsample;
+  if (pieces == 1) return geot_group_points_grad(B, C, N, M, nsample, grad_out, plan, grad_points, stream);
+  GEOT_REQUIRE(E % pieces == 0 && E / pieces <= 65535 && (int64_t)B * pieces <= 65535, "group_points_grad_pieces: M*nsample=%lld is not divisible into %d pieces of <= 65535 edges", (long long)E, pieces);
+  if (B == 0 || C == 0 || N == 0) return GEOT_OK;
+  GEOT_REQUIRE(grad_out && plan && grad_points, "group_points_grad_pieces: NULL pointer");
+  const int Ep = (int)(E / pieces);
+  const PlanView pv = plan_view(plan, B * pieces, N);
+  cudaStream_t s = as_stream(stream);
+  if (!g_group_force_direct && Ep % 4 == 0 && (((uintptr_t)grad_out & 15) == 0) && planrow_smem(N, Ep) <= (size_t)226 * 1024)
+    return launch_planrow(B, C, N, Ep, pieces, grad_out, pv.row_ptr, pv.perm, grad_points, s, "group_points_grad_pieces");
+  GEOT_REQUIRE(C <= 65535 && B <= 65535, "group_points_grad_pieces: B or C exceeds grid limits");
+  dim3 grid((N + 255) / 256, C, B);
+  seg_reduce_pieces_direct_kernel<<<grid, 256, 0, s>>>(C, N, Ep, pieces, grad_out, pv.row_ptr, pv.perm, grad_points);
+  count_launch(1);
+  return check_launch("group_points_grad_pieces");
 }
 
 GEOT_API int geot_gather_points_grad(int B, int C, int N, int M, const float* grad_out, const void* plan,

@@ -150,10 +150,18 @@ class ScatterPlan:
     Built lazily on the first backward that needs it and cached on the idx tensor's autograd context,
     so e.g. the xyz- and feature-grouping of one QueryAndGroup share it."""
 
-    def __init__(self, idx, B, N):
+    def __init__(self, idx, B, N, pieces=1):
+        """pieces > 1 (only for group_points_grad, see grouping_plan): one CSR per (cloud, piece of the neighbour
+        list) - the same build over the same idx buffer viewed as (B*pieces, E/pieces)."""
         dev = check_cuda(idx)
+        self.pieces = int(pieces)
+        self.clouds = B
+        E = idx.numel() // max(B, 1)
+        if self.pieces > 1:
+            assert E % self.pieces == 0
+            B, E = B * self.pieces, E // self.pieces
         self.B, self.N = B, N
-        self.E = idx.numel() // max(B, 1)
+        self.E = E
         with torch.cuda.device(dev):
             nbytes = int(_lib.lib().geot_scatter_plan_bytes(B, N, self.E))
             self.ws = torch.empty((max(nbytes, 1),), dtype=torch.uint8, device=dev)
@@ -171,6 +179,13 @@ class ScatterPlan:
         return self.ws[off: off + self.B * self.E * 4].view(_i32).view(self.B, self.E)
 
 
+def grouping_plan(idx, B, N):
+    """Scatter plan for group_points_grad: split into pieces when the neighbour list of a cloud (M*ns entries) is
+    too long for the shared-memory backward kernel in one go (geot_scatter_plan_pieces)."""
+    E = idx.numel() // max(B, 1)
+    return ScatterPlan(idx, B, N, pieces=int(_lib.lib().geot_scatter_plan_pieces(N, E)))
+
+
 def group_points_grad(grad_out, plan, N, out=None):
     """grad_out (B,C,M,ns) -> grad_points (B,C,N), fixed summation order."""
     dev = check_cuda(grad_out, out)
@@ -178,7 +193,10 @@ def group_points_grad(grad_out, plan, N, out=None):
     with torch.cuda.device(dev):
         if out is None:
             out = torch.empty((B, Cc, N), dtype=_f32, device=dev)
-        call("geot_group_points_grad", B, Cc, N, M, ns, ptr(grad_out), plan.ptr, ptr(out), stream_ptr())
+        if getattr(plan, "pieces", 1) > 1:
+            call("geot_group_points_grad_pieces", B, Cc, N, M, ns, plan.pieces, ptr(grad_out), plan.ptr, ptr(out), stream_ptr())
+        else:
+            call("geot_group_points_grad", B, Cc, N, M, ns, ptr(grad_out), plan.ptr, ptr(out), stream_ptr())
     return out
 
 

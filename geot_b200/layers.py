@@ -94,7 +94,7 @@ class GroupingOperation(Function):
     def backward(ctx, grad_out: torch.Tensor):
         idx, N, cache = ctx.for_backwards
         if cache.plan is None or cache.plan.N != N:
-            cache.plan = F_.ScatterPlan(idx, idx.shape[0], N)
+            cache.plan = F_.grouping_plan(idx, idx.shape[0], N)
         return F_.group_points_grad(grad_out.contiguous(), cache.plan, N), None
 
 

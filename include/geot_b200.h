@@ -145,6 +145,13 @@ int geot_scatter_plan_build(int B, int N, int64_t E, const int* idx, void* plan,
  * plan = geot_scatter_plan_build(B,N,M*ns,idx). */
 int geot_group_points_grad(int B, int C, int N, int M, int nsample, const float* grad_out,
                            const void* plan, float* grad_points, geot_stream_t stream);
+/* Large neighbourhood tensors (M*nsample > 65535, or a row that does not fit shared memory): the gradient row is
+ * processed in `pieces` contiguous parts through the shared-memory kernel.  pieces = geot_scatter_plan_pieces(N, E)
+ * (1 = use the call above); the plan must then be built as geot_scatter_plan_build(B*pieces, N, E/pieces, idx, ...),
+ * i.e. one CSR per (cloud, piece) over the SAME idx buffer.  Result = sum over pieces in order: deterministic. */
+int geot_scatter_plan_pieces(int N, int64_t E);
+int geot_group_points_grad_pieces(int B, int C, int N, int M, int nsample, int pieces, const float* grad_out,
+                                  const void* plan, float* grad_points, geot_stream_t stream);
 /* replaces pointnet2_batch_cuda.gather_points_grad_wrapper (sampling_gpu.cu:53-70). plan over E = M. */
 int geot_gather_points_grad(int B, int C, int N, int M, const float* grad_out, const void* plan,
                             float* grad_points, geot_stream_t stream);

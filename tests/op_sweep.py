@@ -80,11 +80,11 @@ for (B, N, M, ns, Cc, r) in [(64, 16384, 1024, 32, 64, 0.1), (16, 16384, 4096, 3
            (lambda: R.ref_group_points(B, Cc, N, M, ns, p(feat), p(nbr), p(g_r))) if R else None, nb_fwd, lambda: (g == g_r).all())
     go = torch.randn(B, Cc, M, ns, device=dev)
     gp = torch.empty((B, Cc, N), device=dev); gp_r = torch.empty_like(gp)
-    plan = F.ScatterPlan(nbr, B, N)
+    plan = F.grouping_plan(nbr, B, N)
     report("grouping_operation bwd", tag + " (plan cached)", lambda: F.group_points_grad(go, plan, N, out=gp),
            (lambda: (gp_r.zero_(), R.ref_group_points_grad(B, Cc, N, M, ns, p(go), p(nbr), p(gp_r)))) if R else None, nb_fwd,
            lambda: torch.allclose(gp, gp_r, rtol=1e-4, atol=1e-4))
-    report("scatter plan build", tag, lambda: F.ScatterPlan(nbr, B, N), None, B * (4 * M * ns * 3 + 8 * N))
+    report("scatter plan build", tag, lambda: F.grouping_plan(nbr, B, N), None, B * (4 * M * ns * 3 + 8 * N))
     # three_nn / three_interpolate: upsample the M sampled points back to N
     d2 = torch.empty((B, N, 3), device=dev); i3 = torch.empty((B, N, 3), dtype=i32, device=dev)
     d2_r = torch.empty_like(d2); i3_r = torch.empty_like(i3)

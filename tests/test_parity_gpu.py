@@ -245,6 +245,39 @@ def test_scatter_plan_is_stable_csr(cuda):
         assert np.array_equal(rp[b], np.concatenate([[0], np.cumsum(np.bincount(idx[b], minlength=N))]))
 
 
+@pytest.mark.parametrize("B,C,N,M,ns", [(2, 5, 4096, 1024, 64), (2, 9, 16384, 4096, 32), (1, 4, 8192, 1536, 32), (3, 3, 2048, 2048, 48)])
+def test_group_points_grad_pieces(cuda, oracle, B, C, N, M, ns):
+    """Neighbour lists too long for one shared-memory pass (M*ns > 65535 or row + plan > 227 KB) are reduced piece
+    by piece (geot_scatter_plan_pieces / geot_group_points_grad_pieces): against the oracle, against the
+    single-plan direct kernel, and bit-for-bit against the piece-ordered direct kernel (same summation order)."""
+    xyz = clouds("tooth", B, N)
+    q = xyz[:, :M]
+    nbr = F.ball_query(cu(q), cu(xyz), 0.2, ns)
+    E = M * ns
+    Q = int(_lib.lib().geot_scatter_plan_pieces(N, E))
+    assert Q > 1, (N, E, Q)
+    g = torch.randn(B, C, M, ns, device="cuda")
+    plan_q = F.grouping_plan(nbr, B, N)
+    assert plan_q.pieces == Q
+    got = F.group_points_grad(g, plan_q, N)
+    single = F.group_points_grad(g, F.ScatterPlan(nbr, B, N), N)
+    exp = oracle.grouping_operation_grad(g.cpu().numpy(), nbr.cpu().numpy(), N)
+    np.testing.assert_allclose(got.cpu().numpy(), exp, rtol=1e-4, atol=1e-4)
+    np.testing.assert_allclose(single.cpu().numpy(), exp, rtol=1e-4, atol=1e-4)
+    _lib.lib().geot_group_points_config(1)
+    try:
+        direct = F.group_points_grad(g, plan_q, N)
+    finally:
+        _lib.lib().geot_group_points_config(0)
+    assert torch.equal(got, direct)
+    assert torch.equal(got, F.group_points_grad(g, plan_q, N))
+    # through autograd (layers.GroupingOperation picks the pieces plan itself)
+    from geot_b200 import layers
+    feat = torch.randn(B, C, N, device="cuda", requires_grad=True)
+    layers.grouping_operation(feat, nbr).backward(g)
+    assert torch.equal(feat.grad, got)
+
+
 def test_scatter_plan_large_universe_heavy_segments(cuda):
     """E > 2^20: the CTA bitmap sort of long segments walks the source universe in two chunks."""
     rng = np.random.default_rng(7)
