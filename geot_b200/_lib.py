@@ -127,6 +127,25 @@ def stream_ptr():
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+class on_device:
+    """`with on_device(dev):` = torch.cuda.device(dev) without the two set_device calls when dev is already current
+    (the common case; the guard costs microseconds that matter for the 5-microsecond kernels)."""
+    __slots__ = ("idx", "prev")
+
+    def __init__(self, dev):
+        self.idx = dev.index if (dev is not None and dev.index is not None) else torch.cuda.current_device()
+
+    def __enter__(self):
+        self.prev = torch.cuda.current_device()
+        if self.prev != self.idx:
+            torch.cuda.set_device(self.idx)
+
+    def __exit__(self, *exc):
+        if self.prev != self.idx:
+            torch.cuda.set_device(self.prev)
+        return False
+
+
 def check_cuda(*tensors):
     """Every tensor must live on one CUDA device and be contiguous; returns that device."""
     dev = None

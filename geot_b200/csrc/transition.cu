@@ -19,7 +19,7 @@ namespace geot {
 
 void count_launch(int n);
 
-constexpr int kSigtThreads = 256;
+constexpr int kSigtThreads = 384;  // 12 warps: 33 rows in 3 rounds; 8 warps left the FMA pipe idle half the time
 constexpr int kSigtWarps = kSigtThreads / 32;
 constexpr int kSigtTile = 64;  // points per CTA tile: lane l owns points l and l+32
 
@@ -114,10 +114,11 @@ sigt_kernel(int B, int N, const float* __restrict__ x, const float* __restrict__
         float* acc = h ? acc1 : acc0;
         const int64_t gbase = g0 + h * 32;  // first point of this half
         if (BWD) {  // stage-in the upstream gradient rows of these 32 points, coalesced
+          const float* __restrict__ gin = grad_in + (gbase * C + kk) * C;  // row kk of point gbase; next point C*C floats on
+          const int nvalid = (int)min((int64_t)32, BN - gbase);
           for (int f = lane; f < 32 * C; f += 32) {
             const int pt = f / C, j = f - pt * C;
-            const int64_t g = gbase + pt;
-            stage[f] = (g < BN) ? __ldg(grad_in + (g * C + kk) * C + j) : 0.f;
+            stage[f] = (pt < nvalid) ? __ldg(gin + pt * (C * C) + j) : 0.f;
           }
           __syncwarp();
         }
@@ -149,10 +150,14 @@ sigt_kernel(int B, int N, const float* __restrict__ x, const float* __restrict__
           for (int j = 0; j < C; j++) stage[lane * C + j] = acc[j] * inv;
         }
         __syncwarp();
-        for (int f = lane; f < 32 * C; f += 32) {
-          const int pt = f / C, j = f - pt * C;
-          const int64_t g = gbase + pt;
-          if (g < BN) insT_or_graw[(g * C + kk) * C + j] = stage[f];
+        {
+          float* __restrict__ orow = insT_or_graw + (gbase * C + kk) * C;
+          const int nvalid = (int)min((int64_t)32, BN - gbase);
+#pragma unroll 4
+          for (int f = lane; f < 32 * C; f += 32) {
+            const int pt = f / C, j = f - pt * C;
+            if (pt < nvalid) orow[pt * (C * C) + j] = stage[f];
+          }
         }
         __syncwarp();
       }

@@ -11,7 +11,7 @@ import ctypes as C
 import torch
 
 from . import _lib
-from ._lib import call, check_cuda, ptr, stream_ptr
+from ._lib import call, check_cuda, on_device, ptr, stream_ptr
 
 _i32 = torch.int32
 _f32 = torch.float32
@@ -32,7 +32,7 @@ def furthest_point_sampling(xyz, npoint, flags=0, temp=None, out=None):
     """xyz (B,N,3) fp32 -> idx (B,npoint) int32.  flags: _lib.GEOT_FPS_* (which reference kernel to match)."""
     dev = check_cuda(xyz, temp, out)
     B, N, _ = xyz.shape
-    with torch.cuda.device(dev):
+    with on_device(dev):
         if out is None:
             out = torch.empty((B, npoint), dtype=_i32, device=dev)
         needs_temp = N > 16384 or (flags & _lib.GEOT_FPS_FORCE_GENERIC)
@@ -46,7 +46,7 @@ def furthestsampling(xyz, offset, new_offset, weights=None, n_max=None, m_total=
     """Offset-format FPS: xyz (n,3), cumulative int32 offset/new_offset (b) -> GLOBAL idx (m_total)."""
     dev = check_cuda(xyz, offset, new_offset, weights, tmp, out)
     n, b = xyz.shape[0], offset.shape[0]
-    with torch.cuda.device(dev):
+    with on_device(dev):
         if n_max is None or m_total is None:
             # one host sync, like the reference's own Python (pointops.py:69-72 reads offset on the host)
             o = offset.cpu()
@@ -71,7 +71,7 @@ def ball_query(new_xyz, xyz, radius, nsample, out=None, workspace=None, use_grid
     dev = check_cuda(new_xyz, xyz, out)
     B, N, _ = xyz.shape
     M = new_xyz.shape[1]
-    with torch.cuda.device(dev):
+    with on_device(dev):
         if out is None:
             out = torch.empty((B, M, nsample), dtype=_i32, device=dev)
         ws_bytes = int(_lib.lib().geot_ball_query_workspace_bytes(B, N)) if use_grid else 0
@@ -85,7 +85,7 @@ def ball_query(new_xyz, xyz, radius, nsample, out=None, workspace=None, use_grid
 def ballquery_offset(radius, nsample, xyz, new_xyz, offset, new_offset, out=None):
     dev = check_cuda(xyz, new_xyz, offset, new_offset, out)
     m, b = new_xyz.shape[0], offset.shape[0]
-    with torch.cuda.device(dev):
+    with on_device(dev):
         if out is None:
             out = torch.empty((m, nsample), dtype=_i32, device=dev)
         call("geot_ballquery_offset", b, m, float(radius), nsample, ptr(xyz), ptr(new_xyz), ptr(offset), ptr(new_offset), ptr(out), stream_ptr())
@@ -99,7 +99,7 @@ def knnquery(nsample, xyz, new_xyz, offset=None, new_offset=None, n_per=0, m_per
     new_xyz (b*m_per,3)."""
     dev = check_cuda(xyz, new_xyz, offset, new_offset, idx, dist2)
     m = new_xyz.shape[0]
-    with torch.cuda.device(dev):
+    with on_device(dev):
         if offset is not None:
             b = offset.shape[0]
             if m_per is None:
@@ -125,7 +125,7 @@ def group_points(points, idx, out=None):
     dev = check_cuda(points, idx, out)
     B, Cc, N = points.shape
     _, M, ns = idx.shape
-    with torch.cuda.device(dev):
+    with on_device(dev):
         if out is None:
             out = torch.empty((B, Cc, M, ns), dtype=_f32, device=dev)
         call("geot_group_points", B, Cc, N, M, ns, ptr(points), ptr(idx), ptr(out), stream_ptr())
@@ -137,7 +137,7 @@ def gather_points(points, idx, out=None):
     dev = check_cuda(points, idx, out)
     B, Cc, N = points.shape
     M = idx.shape[1]
-    with torch.cuda.device(dev):
+    with on_device(dev):
         if out is None:
             out = torch.empty((B, Cc, M), dtype=_f32, device=dev)
         call("geot_gather_points", B, Cc, N, M, ptr(points), ptr(idx), ptr(out), stream_ptr())
@@ -162,7 +162,7 @@ class ScatterPlan:
             B, E = B * self.pieces, E // self.pieces
         self.B, self.N = B, N
         self.E = E
-        with torch.cuda.device(dev):
+        with on_device(dev):
             nbytes = int(_lib.lib().geot_scatter_plan_bytes(B, N, self.E))
             self.ws = torch.empty((max(nbytes, 1),), dtype=torch.uint8, device=dev)
             call("geot_scatter_plan_build", B, N, self.E, ptr(idx), ptr(self.ws), nbytes, stream_ptr())
@@ -190,7 +190,7 @@ def group_points_grad(grad_out, plan, N, out=None):
     """grad_out (B,C,M,ns) -> grad_points (B,C,N), fixed summation order."""
     dev = check_cuda(grad_out, out)
     B, Cc, M, ns = grad_out.shape
-    with torch.cuda.device(dev):
+    with on_device(dev):
         if out is None:
             out = torch.empty((B, Cc, N), dtype=_f32, device=dev)
         if getattr(plan, "pieces", 1) > 1:
@@ -203,7 +203,7 @@ def group_points_grad(grad_out, plan, N, out=None):
 def gather_points_grad(grad_out, plan, N, out=None):
     dev = check_cuda(grad_out, out)
     B, Cc, M = grad_out.shape
-    with torch.cuda.device(dev):
+    with on_device(dev):
         if out is None:
             out = torch.empty((B, Cc, N), dtype=_f32, device=dev)
         call("geot_gather_points_grad", B, Cc, N, M, ptr(grad_out), plan.ptr, ptr(out), stream_ptr())
@@ -218,7 +218,7 @@ def three_nn(unknown, known, dist2=None, idx=None):
     dev = check_cuda(unknown, known, dist2, idx)
     B, n, _ = unknown.shape
     m = known.shape[1]
-    with torch.cuda.device(dev):
+    with on_device(dev):
         if dist2 is None:
             dist2 = torch.empty((B, n, 3), dtype=_f32, device=dev)
         if idx is None:
@@ -232,7 +232,7 @@ def three_interpolate(points, idx, weight, out=None):
     dev = check_cuda(points, idx, weight, out)
     B, Cc, m = points.shape
     n = idx.shape[1]
-    with torch.cuda.device(dev):
+    with on_device(dev):
         if out is None:
             out = torch.empty((B, Cc, n), dtype=_f32, device=dev)
         call("geot_three_interpolate", B, Cc, m, n, ptr(points), ptr(idx), ptr(weight), ptr(out), stream_ptr())
@@ -242,7 +242,7 @@ def three_interpolate(points, idx, weight, out=None):
 def three_interpolate_grad(grad_out, weight, plan, m, out=None):
     dev = check_cuda(grad_out, weight, out)
     B, Cc, n = grad_out.shape
-    with torch.cuda.device(dev):
+    with on_device(dev):
         if out is None:
             out = torch.empty((B, Cc, m), dtype=_f32, device=dev)
         call("geot_three_interpolate_grad", B, Cc, n, m, ptr(grad_out), ptr(weight), plan.ptr, ptr(out), stream_ptr())
@@ -256,7 +256,7 @@ def grouping_forward(input, idx, out=None):
     dev = check_cuda(input, idx, out)
     m, ns = idx.shape
     c = input.shape[1]
-    with torch.cuda.device(dev):
+    with on_device(dev):
         if out is None:
             out = torch.empty((m, ns, c), dtype=_f32, device=dev)
         call("geot_grouping_forward", m, ns, c, ptr(input), ptr(idx), ptr(out), stream_ptr())
@@ -266,7 +266,7 @@ def grouping_forward(input, idx, out=None):
 def grouping_backward(grad_output, plan, n, out=None):
     dev = check_cuda(grad_output, out)
     m, ns, c = grad_output.shape
-    with torch.cuda.device(dev):
+    with on_device(dev):
         if out is None:
             out = torch.empty((n, c), dtype=_f32, device=dev)
         call("geot_grouping_backward", m, ns, c, n, ptr(grad_output), plan.ptr, ptr(out), stream_ptr())
@@ -277,7 +277,7 @@ def interpolation_forward(input, idx, weight, out=None):
     dev = check_cuda(input, idx, weight, out)
     n, k = idx.shape
     c = input.shape[1]
-    with torch.cuda.device(dev):
+    with on_device(dev):
         if out is None:
             out = torch.empty((n, c), dtype=_f32, device=dev)
         call("geot_interpolation_forward", n, c, k, ptr(input), ptr(idx), ptr(weight), ptr(out), stream_ptr())
@@ -287,7 +287,7 @@ def interpolation_forward(input, idx, weight, out=None):
 def interpolation_backward(grad_output, weight, plan, m, k, out=None):
     dev = check_cuda(grad_output, weight, out)
     n, c = grad_output.shape
-    with torch.cuda.device(dev):
+    with on_device(dev):
         if out is None:
             out = torch.empty((m, c), dtype=_f32, device=dev)
         call("geot_interpolation_backward", n, c, k, m, ptr(grad_output), ptr(weight), plan.ptr, ptr(out), stream_ptr())
@@ -298,7 +298,7 @@ def subtraction_forward(input1, input2, idx, out=None):
     dev = check_cuda(input1, input2, idx, out)
     n, ns = idx.shape
     c = input1.shape[1]
-    with torch.cuda.device(dev):
+    with on_device(dev):
         if out is None:
             out = torch.empty((n, ns, c), dtype=_f32, device=dev)
         call("geot_subtraction_forward", n, ns, c, ptr(input1), ptr(input2), ptr(idx), ptr(out), stream_ptr())
@@ -308,7 +308,7 @@ def subtraction_forward(input1, input2, idx, out=None):
 def subtraction_backward(grad_output, plan, g1=None, g2=None):
     dev = check_cuda(grad_output, g1, g2)
     n, ns, c = grad_output.shape
-    with torch.cuda.device(dev):
+    with on_device(dev):
         if g1 is None:
             g1 = torch.empty((n, c), dtype=_f32, device=dev)
         if g2 is None:
@@ -321,7 +321,7 @@ def aggregation_forward(input, position, weight, idx, out=None):
     dev = check_cuda(input, position, weight, idx, out)
     n, ns, c = position.shape
     w_c = weight.shape[2]
-    with torch.cuda.device(dev):
+    with on_device(dev):
         if out is None:
             out = torch.empty((n, c), dtype=_f32, device=dev)
         call("geot_aggregation_forward", n, ns, c, w_c, ptr(input), ptr(position), ptr(weight), ptr(idx), ptr(out), stream_ptr())
@@ -332,7 +332,7 @@ def aggregation_backward(input, position, weight, idx, grad_output, plan, gi=Non
     dev = check_cuda(input, position, weight, idx, grad_output, gi, gp, gw)
     n, ns, c = position.shape
     w_c = weight.shape[2]
-    with torch.cuda.device(dev):
+    with on_device(dev):
         if gi is None:
             gi = torch.empty((n, c), dtype=_f32, device=dev)
         if gp is None:
@@ -355,7 +355,7 @@ def sigt_forward(x, W, cm=None, out=None):
     dev = check_cuda(x, W, cm, out)
     B, Cc, N = x.shape
     stride = 2 * Cc if cm is not None else Cc
-    with torch.cuda.device(dev):
+    with on_device(dev):
         if out is None:
             out = torch.empty((B * N, Cc, Cc), dtype=_f32, device=dev)
         nb = int(_lib.lib().geot_sigt_workspace_bytes(Cc))
@@ -369,7 +369,7 @@ def sigt_backward(x, W, cm, grad_insT):
     dev = check_cuda(x, W, cm, grad_insT)
     B, Cc, N = x.shape
     stride = 2 * Cc if cm is not None else Cc
-    with torch.cuda.device(dev):
+    with on_device(dev):
         grad_W = torch.empty_like(W)
         g_raw = torch.empty((B * N, Cc * Cc), dtype=_f32, device=dev)
         nb = int(_lib.lib().geot_sigt_backward_workspace_bytes(B, Cc, N))
@@ -382,7 +382,7 @@ def transition_apply_forward(logits, ema_t, insT, lam, out=None):
     """logits (B,C,N), ema_t (C,C), insT (B*N,C,C) -> corrected logits (B,C,N)."""
     dev = check_cuda(logits, ema_t, insT, out)
     B, Cc, N = logits.shape
-    with torch.cuda.device(dev):
+    with on_device(dev):
         if out is None:
             out = torch.empty_like(logits)
         call("geot_transition_apply_forward", B, Cc, N, ptr(logits), ptr(ema_t), ptr(insT), float(lam), ptr(out), stream_ptr())
@@ -392,7 +392,7 @@ def transition_apply_forward(logits, ema_t, insT, lam, out=None):
 def transition_apply_backward(logits, ema_t, insT, lam, grad_out, need_logits=True, need_insT=True):
     dev = check_cuda(logits, ema_t, insT, grad_out)
     B, Cc, N = logits.shape
-    with torch.cuda.device(dev):
+    with on_device(dev):
         gl = torch.empty_like(logits) if need_logits else None
         gi = torch.empty_like(insT) if need_insT else None
         call("geot_transition_apply_backward", B, Cc, N, ptr(logits), ptr(ema_t), ptr(insT), float(lam), ptr(grad_out), ptr(gl), ptr(gi), stream_ptr())
@@ -407,7 +407,7 @@ def manifold_loss_forward(points, labels, insT, idx, sigma, mode):
     dev = check_cuda(points, labels, insT, idx)
     B, N, D = points.shape
     Cc, k = insT.shape[1], idx.shape[2]
-    with torch.cuda.device(dev):
+    with on_device(dev):
         coef = torch.empty((B * N, k), dtype=_f32, device=dev)
         loss = torch.empty((1,), dtype=_f32, device=dev)
         nb = int(_lib.lib().geot_manifold_workspace_bytes(B * N))
@@ -420,7 +420,7 @@ def manifold_loss_backward(insT, idx, coef, plan, grad_loss):
     dev = check_cuda(insT, idx, coef, grad_loss)
     B, N, k = idx.shape
     Cc = insT.shape[1]
-    with torch.cuda.device(dev):
+    with on_device(dev):
         g = torch.empty_like(insT)
         call("geot_manifold_loss_backward", B, N, Cc, k, ptr(insT), ptr(idx), ptr(coef), plan.ptr, ptr(grad_loss), ptr(g), stream_ptr())
     return g
@@ -430,7 +430,7 @@ def class_pick(pred_u):
     """pred_u (B,C,N) softmax -> class_T (C,C), best_val (C), best_idx (C) int64 (flat b*N+n)."""
     dev = check_cuda(pred_u)
     B, Cc, N = pred_u.shape
-    with torch.cuda.device(dev):
+    with on_device(dev):
         class_T = torch.empty((Cc, Cc), dtype=_f32, device=dev)
         best_v = torch.empty((Cc,), dtype=_f32, device=dev)
         best_i = torch.empty((Cc,), dtype=torch.int64, device=dev)
@@ -444,7 +444,7 @@ def class_t_step(class_T, ema_t, sigma, label_proj, geo_lambda, ema_decay):
     """-> (ema_t_corr, new ema_t); label_proj int32 (C) on the device."""
     dev = check_cuda(class_T, ema_t, sigma, label_proj)
     Cc = class_T.shape[0]
-    with torch.cuda.device(dev):
+    with on_device(dev):
         corr = torch.empty_like(class_T)
         ema_out = torch.empty_like(class_T)
         call("geot_class_t_step", Cc, ptr(class_T), ptr(ema_t), ptr(sigma), ptr(label_proj), float(geo_lambda), float(ema_decay), ptr(corr), ptr(ema_out), stream_ptr())
@@ -455,7 +455,7 @@ def mean_feature_update(probs, target, cm, c_num):
     """In-place running class-mean update (train.py:884-895 semantics); probs (BN,C), target (BN) int64."""
     dev = check_cuda(probs, target, cm, c_num)
     BN, Cc = probs.shape
-    with torch.cuda.device(dev):
+    with on_device(dev):
         nb = max(int(_lib.lib().geot_class_pick_workspace_bytes(Cc)), 512)
         ws = _ws(nb, dev)
         call("geot_mean_feature_update", BN, Cc, ptr(probs), ptr(target), ptr(cm), ptr(c_num), ptr(ws), nb, stream_ptr())

@@ -65,9 +65,13 @@ for (B, N, M, ns, Cc, r) in [(64, 16384, 1024, 32, 64, 0.1), (16, 16384, 4096, 3
            B * (12 * N + 4 * M), lambda: (idx == idx_r).all())
     xyz_t = xyz.transpose(1, 2).contiguous()
     cen_t = torch.empty((B, 3, M), device=dev); cen_r = torch.empty_like(cen_t)
-    report("gather_operation fwd", tag + " (C=3)", lambda: F.gather_points(xyz_t, idx, out=cen_t),
+    report("gather_operation fwd", tag + " (C=3; 5 us kernels, host call overhead decides)", lambda: F.gather_points(xyz_t, idx, out=cen_t),
            (lambda: R.ref_gather_points(B, 3, N, M, p(xyz_t), p(idx), p(cen_r))) if R else None,
            B * (4 * M + 2 * 12 * M), lambda: (cen_t == cen_r).all())
+    fg = torch.empty((B, Cc, M), device=dev); fg_r = torch.empty_like(fg)
+    report("gather_operation fwd", tag + f" (C={Cc})", lambda: F.gather_points(feat, idx, out=fg),
+           (lambda: R.ref_gather_points(B, Cc, N, M, p(feat), p(idx), p(fg_r))) if R else None,
+           B * (4 * M + 2 * 4 * Cc * M), lambda: (fg == fg_r).all())
     centres = cen_t.transpose(1, 2).contiguous()
     nbr = torch.empty((B, M, ns), dtype=i32, device=dev); nbr_r = torch.zeros_like(nbr)
     ws = torch.empty(int(_lib.lib().geot_ball_query_workspace_bytes(B, N)), dtype=torch.uint8, device=dev)

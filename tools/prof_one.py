@@ -28,6 +28,19 @@ if what == "knn":
     kb = 8
     kx = xyz[:kb].reshape(-1, 3).contiguous()
     koff = torch.arange(1, kb + 1, device="cuda", dtype=torch.int32) * N
+if what in ("sigt", "manifold"):
+    from geot_b200 import transition as T
+    Ct, Bt, Nt = 33, 2, 16000
+    logits = torch.randn(Bt, Ct, Nt, device="cuda") * 3
+    pt = logits.softmax(1)
+    cmt = torch.rand(Ct, Ct, device="cuda"); cmt = cmt / cmt.sum(1, keepdim=True)
+    modt = T.sig_t_mean(Ct).cuda()
+    got = torch.randn(Bt * Nt, Ct, Ct, device="cuda")
+    post = xyz[:Bt, :Nt].contiguous()
+    labt = logits.argmax(1)
+    insTt = modt(pt, cmt).detach().requires_grad_(True)
+    losst = T.threeD_space_loss(k=32, sigma=1.0, num_classes=Ct)
+    idxt = T._neighbours(32, post)
 torch.cuda.synchronize()
 for _ in range(3):
     if what == "fps": F.furthest_point_sampling(xyz, M)
@@ -39,4 +52,8 @@ for _ in range(3):
     elif what == "threenn": F.three_nn(xyz, centres)
     elif what == "tibwd": F.three_interpolate_grad(go3, w, plan3, M)
     elif what == "knn": F.knnquery(16, kx, kx, koff, koff, m_per=N)
+    elif what == "sigt":
+        modt.zero_grad(set_to_none=True); modt(pt, cmt).backward(got)
+    elif what == "manifold":
+        insTt.grad = None; losst(post, labt, insTt, idx=idxt).backward()
 torch.cuda.synchronize()
