@@ -26,13 +26,20 @@ manifold_fwd_kernel(int B, int N, int D, int C2, int k, const float* __restrict_
                     const int64_t* __restrict__ labels, const float* __restrict__ insT,
                     const int* __restrict__ idx, float inv_two_sigma2, int mode,
                     float* __restrict__ coef, float* __restrict__ per_point) {
+  extern __shared__ float mf_smem[];  // 8 warps x C2 floats
   const int lane = threadIdx.x & 31;
+  float* ti = mf_smem + (size_t)(threadIdx.x >> 5) * C2;
   const int64_t BN = (int64_t)B * N;
   const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   for (int64_t g = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; g < BN; g += warps) {
     const int64_t base = (g / N) * N;  // first point of this cloud
     const float* __restrict__ Ti = insT + g * C2;
     const int64_t lab_i = labels[g];
+    // T_i goes to shared memory once: re-reading it per neighbour from global doubled the L2 traffic (L1 keeps only
+    // ~25 % of it), and 35 registers per lane for it cost more occupancy than it saved
+    __syncwarp();
+    for (int f = lane; f < C2; f += 32) ti[f] = __ldg(Ti + f);
+    __syncwarp();
     float num = 0.f, den = 0.f;  // lane-partial sums over this lane's neighbours
     for (int s0 = 0; s0 < k; s0 += 32) {
       const int s = s0 + lane;
@@ -44,8 +51,9 @@ manifold_fwd_kernel(int B, int N, int D, int C2, int k, const float* __restrict_
         const int64_t o = __shfl_sync(0xffffffffu, nb, q);
         const float* __restrict__ Tj = insT + o * C2;
         float a = 0.f;
+#pragma unroll 4
         for (int f = lane; f < C2; f += 32) {
-          const float d = __ldg(Ti + f) - __ldg(Tj + f);
+          const float d = ti[f] - __ldg(Tj + f);
           a = __fmaf_rn(d, d, a);
         }
 #pragma unroll
@@ -105,9 +113,10 @@ sum_scale_kernel(int64_t n, const float* __restrict__ v, double scale, float* __
 // ---------------------------------------------------------------------------------------------
 // Manifold loss backward w.r.t. insT.  One warp per target point a:
 //   grad[a] = 2*g*scale * ( sum_{s<k} coef[a,s] (T_a - T_{nbr(a,s)})  +  sum_{(i,s): nbr(i,s)=a} coef[i,s] (T_a - T_i) )
-// NT = ceil(C*C / 32) register slots per lane.
+// PARTS warps share a point, each owning a contiguous range of 32*NT matrix entries (NT register slots per lane):
+// at C=33 one warp per point needs 184 registers (7 warps per SM, too few loads in flight to fill the L2 pipe).
 // ---------------------------------------------------------------------------------------------
-template <int NT>
+template <int NT, int PARTS>
 __global__ void __launch_bounds__(256)
 manifold_bwd_kernel(int B, int N, int C2, int k, const float* __restrict__ insT, const int* __restrict__ idx,
                     const float* __restrict__ coef, const int* __restrict__ row_ptr,
@@ -118,13 +127,15 @@ manifold_bwd_kernel(int B, int N, int C2, int k, const float* __restrict__ insT,
   const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   const float gs = 2.0f * scale * __ldg(grad_loss);
   const int64_t E = (int64_t)N * k;
-  for (int64_t g = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; g < BN; g += warps) {
+  for (int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < BN * PARTS; w += warps) {
+    const int64_t g = w / PARTS;
+    const int f0 = (int)(w - g * PARTS) * (32 * NT);  // first entry of this warp's part
     const int64_t b = g / N, a = g - b * N, base = b * N;
     const float* __restrict__ Ta = insT + g * C2;
     float ta[NT], acc[NT];
 #pragma unroll
     for (int t = 0; t < NT; t++) {
-      const int f = lane + 32 * t;
+      const int f = f0 + lane + 32 * t;
       ta[t] = f < C2 ? __ldg(Ta + f) : 0.f;
       acc[t] = 0.f;
     }
@@ -132,7 +143,7 @@ manifold_bwd_kernel(int B, int N, int C2, int k, const float* __restrict__ insT,
       const float* __restrict__ To = insT + other * C2;
 #pragma unroll
       for (int t = 0; t < NT; t++) {
-        const int f = lane + 32 * t;
+        const int f = f0 + lane + 32 * t;
         if (f < C2) acc[t] = __fmaf_rn(c, ta[t] - __ldg(To + f), acc[t]);
       }
     };
@@ -148,7 +159,7 @@ manifold_bwd_kernel(int B, int N, int C2, int k, const float* __restrict__ insT,
     float* __restrict__ out = grad_insT + g * C2;
 #pragma unroll
     for (int t = 0; t < NT; t++) {
-      const int f = lane + 32 * t;
+      const int f = f0 + lane + 32 * t;
       if (f < C2) out[f] = gs * acc[t];
     }
   }
@@ -321,7 +332,7 @@ GEOT_API int geot_manifold_loss_forward(int B, int N, int D, int C, int k, const
                                         const int64_t* labels, const float* insT, const int* idx,
                                         float sigma, int mode, float* coef, float* loss, void* workspace,
                                         size_t workspace_bytes, geot_stream_t stream) {
-  GEOT_REQUIRE(B >= 1 && N >= 1 && D >= 1 && C >= 1 && k >= 1, "manifold_loss_forward: bad sizes B=%d N=%d D=%d C=%d k=%d", B, N, D, C, k);
+  GEOT_REQUIRE(B >= 1 && N >= 1 && D >= 1 && C >= 1 && C <= 64 && k >= 1, "manifold_loss_forward: bad sizes (1 <= C <= 64) B=%d N=%d D=%d C=%d k=%d", B, N, D, C, k);
   GEOT_REQUIRE(mode == GEOT_MANIFOLD_3D || mode == GEOT_MANIFOLD_FEATURE, "manifold_loss_forward: unknown mode %d", mode);
   GEOT_REQUIRE(points && labels && insT && idx && coef && loss, "manifold_loss_forward: NULL pointer");
   GEOT_REQUIRE(sigma > 0.f, "manifold_loss_forward: sigma must be positive");
@@ -334,8 +345,17 @@ GEOT_API int geot_manifold_loss_forward(int B, int N, int D, int C, int k, const
   float* per_point = reinterpret_cast<float*>(workspace);
   const int64_t want = (BN + 7) / 8;
   const int grid = (int)(want < (int64_t)kNumSMs * 8 ? want : (int64_t)kNumSMs * 8);
-  manifold_fwd_kernel<<<grid, 256, 0, s>>>(B, N, D, C * C, k, points, labels, insT, idx,
-                                           1.0f / (2.0f * (sigma * sigma)), mode, coef, per_point);
+  const size_t smem = (size_t)8 * C * C * sizeof(float);
+  if (smem > 48 * 1024) {
+    static size_t configured = 0;
+    if (smem > configured) {
+      cudaError_t e = cudaFuncSetAttribute(manifold_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) { set_error("manifold_loss_forward: cudaFuncSetAttribute(%zu): %s", smem, cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
+      configured = smem;
+    }
+  }
+  manifold_fwd_kernel<<<grid, 256, smem, s>>>(B, N, D, C * C, k, points, labels, insT, idx,
+                                              1.0f / (2.0f * (sigma * sigma)), mode, coef, per_point);
   count_launch(1);
   int rc = check_launch("manifold_fwd_kernel");
   if (rc) return rc;
@@ -362,10 +382,14 @@ GEOT_API int geot_manifold_loss_backward(int B, int N, int C, int k, const float
   const int C2 = C * C;
   const int nt = (C2 + 31) / 32;
   const float scale = 1.0f / (float)BN;
-  if (nt <= 10) manifold_bwd_kernel<10><<<grid, 256, 0, s>>>(B, N, C2, k, insT, idx, coef, row_ptr, perm, grad_loss, scale, grad_insT);
-  else if (nt <= 35) manifold_bwd_kernel<35><<<grid, 256, 0, s>>>(B, N, C2, k, insT, idx, coef, row_ptr, perm, grad_loss, scale, grad_insT);
-  else if (nt <= 64) manifold_bwd_kernel<64><<<grid, 256, 0, s>>>(B, N, C2, k, insT, idx, coef, row_ptr, perm, grad_loss, scale, grad_insT);
-  else manifold_bwd_kernel<128><<<grid, 256, 0, s>>>(B, N, C2, k, insT, idx, coef, row_ptr, perm, grad_loss, scale, grad_insT);
+  auto grid_of = [&](int parts) {
+    const int64_t want_w = (BN * parts + 7) / 8;
+    return (int)(want_w < (int64_t)kNumSMs * 16 ? want_w : (int64_t)kNumSMs * 16);
+  };
+  if (nt <= 10) manifold_bwd_kernel<10, 1><<<grid_of(1), 256, 0, s>>>(B, N, C2, k, insT, idx, coef, row_ptr, perm, grad_loss, scale, grad_insT);
+  else if (nt <= 36) manifold_bwd_kernel<18, 2><<<grid_of(2), 256, 0, s>>>(B, N, C2, k, insT, idx, coef, row_ptr, perm, grad_loss, scale, grad_insT);
+  else if (nt <= 64) manifold_bwd_kernel<16, 4><<<grid_of(4), 256, 0, s>>>(B, N, C2, k, insT, idx, coef, row_ptr, perm, grad_loss, scale, grad_insT);
+  else manifold_bwd_kernel<16, 8><<<grid_of(8), 256, 0, s>>>(B, N, C2, k, insT, idx, coef, row_ptr, perm, grad_loss, scale, grad_insT);
   count_launch(1);
   return check_launch("manifold_bwd_kernel");
 }
