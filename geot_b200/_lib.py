@@ -39,6 +39,7 @@ _SIGNATURES = {
     "geot_group_points": [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp],
     "geot_gather_points": [_i, _i, _i, _i, _vp, _vp, _vp, _vp],
     "geot_group_points_config": [_i],
+    "geot_group_xyz_relative": [_i, _i, _i, _i, _vp, _vp, _vp, _i, _f, _vp, _vp],
     "geot_scatter_plan_bytes": [_i, _i, _i64],
     "geot_scatter_plan_build": [_i, _i, _i64, _vp, _vp, _sz, _vp],
     "geot_group_points_grad": [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp],
@@ -119,12 +120,20 @@ def launch_count() -> int:
 
 
 def ptr(t):
-    """Device pointer of a tensor (None -> NULL)."""
-    return None if t is None else C.c_void_p(t.data_ptr())
+    """Device pointer of a tensor as an int (None -> NULL); ctypes converts it through the declared argtypes."""
+    return None if t is None else t.data_ptr()
+
+
+try:  # raw stream handle without building a torch.cuda.Stream object per call (private but long-stable torch API)
+    _raw_stream = torch._C._cuda_getCurrentRawStream
+except AttributeError:  # pragma: no cover
+    _raw_stream = None
 
 
 def stream_ptr():
-    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    if _raw_stream is not None:
+        return _raw_stream(torch.cuda.current_device())
+    return torch.cuda.current_stream().cuda_stream
 
 
 class on_device:
@@ -163,8 +172,14 @@ def check_cuda(*tensors):
     return dev
 
 
+_fn_cache = {}
+
+
 def call(name, *args):
-    rc = getattr(lib(), name)(*args)
+    fn = _fn_cache.get(name)
+    if fn is None:
+        fn = _fn_cache[name] = getattr(lib(), name)
+    rc = fn(*args)
     if rc != 0:
         msg = lib().geot_last_error()
         raise GeotError(f"{name} failed ({rc}): {msg.decode() if msg else ''}")

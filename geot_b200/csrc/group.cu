@@ -718,6 +718,78 @@ GEOT_API int geot_group_points(int B, int C, int N, int M, int nsample, const fl
   return launch_group(B, C, N, (int64_t)M * nsample, points, idx, out, as_stream(stream), "group_points");
 }
 
+namespace geot {
+// ---------------------------------------------------------------------------------------------
+// Fused xyz grouping of QueryAndGroup / KNNGroup (group.py:235-250, :297-312):
+//     out[b,c,j,s] = (xyz[b, idx[b,j,s], c] - new_xyz[b,j,c]) (/ divisor)
+// straight from the point-major (B,N,3) cloud: no (B,3,N) transpose copy, no separate subtract and divide passes
+// over the (B,3,M,ns) tensor.  Same fp32 operations as the composite (one subtraction, one multiplication by the
+// reciprocal of the divisor - what torch does for tensor / scalar), so the result is bit-identical to it.  One thread per 4 consecutive neighbours of a query (int4 idx, float4 stores).
+// ---------------------------------------------------------------------------------------------
+template <int VEC>
+__global__ void __launch_bounds__(256)
+group_xyz_rel_kernel(int N, int M, int ns, const float* __restrict__ xyz, const float* __restrict__ new_xyz,
+                     const int* __restrict__ idx, int relative, float divisor, float* __restrict__ out) {
+  const int b = blockIdx.y;
+  const int64_t E = (int64_t)M * ns;
+  const int64_t e0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * VEC;
+  if (e0 >= E) return;
+  const int j = (int)(e0 / ns);  // VEC divides ns: the VEC neighbours belong to one query
+  const float* __restrict__ cloud = xyz + (int64_t)b * N * 3;
+  float cx = 0.f, cy = 0.f, cz = 0.f;
+  if (relative) {
+    const float* __restrict__ q = new_xyz + ((int64_t)b * M + j) * 3;
+    cx = __ldg(q); cy = __ldg(q + 1); cz = __ldg(q + 2);
+  }
+  // torch divides a tensor by a Python scalar as a multiplication by the fp32 reciprocal (BinaryDivTrueKernel.cu,
+  // is_cpu_scalar branch); group.py:249 `grouped_xyz /= self.radius` therefore is x * (1.0f / radius): same here
+  const float inv = divisor != 0.f ? __fdiv_rn(1.0f, divisor) : 1.0f;
+  int id[VEC];
+  if (VEC == 4) {
+    const int4 v = __ldg(reinterpret_cast<const int4*>(idx + (int64_t)b * E + e0));
+    id[0] = v.x; id[1] = v.y; id[2] = v.z; id[3] = v.w;
+  } else {
+    id[0] = __ldg(idx + (int64_t)b * E + e0);
+  }
+  float ox[VEC], oy[VEC], oz[VEC];
+#pragma unroll
+  for (int v = 0; v < VEC; v++) {
+    const float* __restrict__ p = cloud + (int64_t)id[v] * 3;
+    ox[v] = __fsub_rn(__ldg(p), cx); oy[v] = __fsub_rn(__ldg(p + 1), cy); oz[v] = __fsub_rn(__ldg(p + 2), cz);
+    if (divisor != 0.f) { ox[v] = __fmul_rn(ox[v], inv); oy[v] = __fmul_rn(oy[v], inv); oz[v] = __fmul_rn(oz[v], inv); }
+  }
+  float* __restrict__ o = out + (int64_t)b * 3 * E + e0;
+  if (VEC == 4) {
+    __stcs(reinterpret_cast<float4*>(o), make_float4(ox[0], ox[1], ox[2], ox[3]));
+    __stcs(reinterpret_cast<float4*>(o + E), make_float4(oy[0], oy[1], oy[2], oy[3]));
+    __stcs(reinterpret_cast<float4*>(o + 2 * E), make_float4(oz[0], oz[1], oz[2], oz[3]));
+  } else {
+    o[0] = ox[0]; o[E] = oy[0]; o[2 * E] = oz[0];
+  }
+}
+
+}  // namespace geot
+
+GEOT_API int geot_group_xyz_relative(int B, int N, int M, int nsample, const float* xyz, const float* new_xyz,
+                                     const int* idx, int relative, float divisor, float* out, geot_stream_t stream) {
+  GEOT_REQUIRE(B >= 0 && N >= 0 && M >= 0 && nsample >= 0, "group_xyz_relative: bad sizes");
+  const int64_t E = (int64_t)M * nsample;
+  if (B == 0 || E == 0) return GEOT_OK;
+  GEOT_REQUIRE(xyz && idx && out && (!relative || new_xyz), "group_xyz_relative: NULL pointer");
+  GEOT_REQUIRE(B <= 65535, "group_xyz_relative: B exceeds grid limits");
+  cudaStream_t s = as_stream(stream);
+  const bool vec = nsample % 4 == 0 && (((uintptr_t)idx | (uintptr_t)out) & 15) == 0;
+  if (vec) {
+    dim3 grid((unsigned)((E / 4 + 255) / 256), B);
+    group_xyz_rel_kernel<4><<<grid, 256, 0, s>>>(N, M, nsample, xyz, new_xyz, idx, relative, divisor, out);
+  } else {
+    dim3 grid((unsigned)((E + 255) / 256), B);
+    group_xyz_rel_kernel<1><<<grid, 256, 0, s>>>(N, M, nsample, xyz, new_xyz, idx, relative, divisor, out);
+  }
+  count_launch(1);
+  return check_launch("group_xyz_rel_kernel");
+}
+
 /* testing / A-B timing: direct != 0 disables the row-staged forward kernel (process-wide). */
 GEOT_API void geot_group_points_config(int direct) { g_group_force_direct = direct != 0; }
 

@@ -132,6 +132,19 @@ def group_points(points, idx, out=None):
     return out
 
 
+def group_xyz_relative(xyz, new_xyz, idx, relative=True, divisor=0.0, out=None):
+    """Fused xyz grouping of QueryAndGroup: xyz (B,N,3), new_xyz (B,M,3), idx (B,M,ns) -> (B,3,M,ns) =
+    (xyz[idx] - new_xyz) / divisor, without the (B,3,N) transpose copy or separate subtract / divide passes."""
+    dev = check_cuda(xyz, new_xyz, idx, out)
+    B, N, _ = xyz.shape
+    M, ns = idx.shape[1], idx.shape[2]
+    with on_device(dev):
+        if out is None:
+            out = torch.empty((B, 3, M, ns), dtype=_f32, device=dev)
+        call("geot_group_xyz_relative", B, N, M, ns, ptr(xyz), ptr(new_xyz), ptr(idx), int(bool(relative)), float(divisor), ptr(out), stream_ptr())
+    return out
+
+
 def gather_points(points, idx, out=None):
     """points (B,C,N), idx (B,M) -> (B,C,M)."""
     dev = check_cuda(points, idx, out)

@@ -245,6 +245,13 @@ class GroupKNN(nn.Module):
         return k_dist.values, k_dist.indices.transpose(1, 2).contiguous().int()
 
 
+def _fusable(query_xyz, support_xyz):
+    """The fused xyz grouping has no backward: used when neither position tensor takes part in autograd."""
+    return (support_xyz.is_cuda and support_xyz.dtype == torch.float32 and query_xyz.dtype == torch.float32
+            and support_xyz.is_contiguous() and query_xyz.is_contiguous()
+            and not (torch.is_grad_enabled() and (support_xyz.requires_grad or query_xyz.requires_grad)))
+
+
 class QueryAndGroup(nn.Module):
     """group.py:206-255: ball_query -> group xyz -> subtract centre (-> /radius) -> group features."""
 
@@ -265,12 +272,17 @@ class QueryAndGroup(nn.Module):
         idx = ball_query(self.radius, self.nsample, support_xyz, query_xyz)
         if self.return_only_idx:
             return idx
-        xyz_trans = support_xyz.transpose(1, 2).contiguous()
-        grouped_xyz = grouping_operation(xyz_trans, idx)  # (B,3,npoint,nsample)
-        if self.relative_xyz:
-            grouped_xyz = grouped_xyz - query_xyz.transpose(1, 2).unsqueeze(-1)
-            if self.normalize_dp:
-                grouped_xyz /= self.radius
+        if _fusable(query_xyz, support_xyz):
+            # positions carry no gradient (the usual case): one kernel straight from the (B,N,3) cloud
+            grouped_xyz = F_.group_xyz_relative(support_xyz, query_xyz, idx, relative=self.relative_xyz,
+                                                divisor=self.radius if (self.relative_xyz and self.normalize_dp) else 0.0)
+        else:
+            xyz_trans = support_xyz.transpose(1, 2).contiguous()
+            grouped_xyz = grouping_operation(xyz_trans, idx)  # (B,3,npoint,nsample)
+            if self.relative_xyz:
+                grouped_xyz = grouped_xyz - query_xyz.transpose(1, 2).unsqueeze(-1)
+                if self.normalize_dp:
+                    grouped_xyz /= self.radius
         grouped_features = grouping_operation(features, idx) if features is not None else None
         return grouped_xyz, grouped_features
 
@@ -300,10 +312,13 @@ class KNNGroup(nn.Module):
         if self.return_only_idx:
             return idx
         idx = idx.int()
-        xyz_trans = support_xyz.transpose(1, 2).contiguous()
-        grouped_xyz = grouping_operation(xyz_trans, idx)
-        if self.relative_xyz:
-            grouped_xyz -= query_xyz.transpose(1, 2).unsqueeze(-1)
+        if _fusable(query_xyz, support_xyz):
+            grouped_xyz = F_.group_xyz_relative(support_xyz, query_xyz, idx.contiguous(), relative=self.relative_xyz)
+        else:
+            xyz_trans = support_xyz.transpose(1, 2).contiguous()
+            grouped_xyz = grouping_operation(xyz_trans, idx)
+            if self.relative_xyz:
+                grouped_xyz -= query_xyz.transpose(1, 2).unsqueeze(-1)
         if self.normalize_dp:
             grouped_xyz /= torch.amax(torch.sqrt(torch.sum(grouped_xyz ** 2, dim=1)), dim=(1, 2)).view(-1, 1, 1, 1)
         if features is not None:

@@ -16,6 +16,7 @@ from torch.autograd import Function
 
 from . import _lib
 from . import functional as F_
+from . import layers as _layers
 from .layers import (GatherOperation, GroupingOperation, ThreeInterpolate, ThreeNN)
 
 _FPS_EXT = _lib.GEOT_FPS_CAP512 | _lib.GEOT_FPS_MAGSKIP
@@ -83,11 +84,15 @@ class QueryAndGroup(nn.Module):
                     sample_ind = torch.randint(0, num_unique, (self.nsample - num_unique,), dtype=torch.long)
                     all_ind = torch.cat((unique_ind, unique_ind[sample_ind]))
                     idx[i_batch, i_region, :] = all_ind
-        xyz_trans = xyz.transpose(1, 2).contiguous()
-        grouped_xyz = grouping_operation(xyz_trans, idx)
-        grouped_xyz = grouped_xyz - new_xyz.transpose(1, 2).unsqueeze(-1)
-        if self.normalize_xyz:
-            grouped_xyz = grouped_xyz / self.radius
+        if _layers._fusable(new_xyz, xyz):  # positions outside autograd: one fused kernel, same bits
+            grouped_xyz = F_.group_xyz_relative(xyz, new_xyz, idx, relative=True,
+                                                divisor=self.radius if self.normalize_xyz else 0.0)
+        else:
+            xyz_trans = xyz.transpose(1, 2).contiguous()
+            grouped_xyz = grouping_operation(xyz_trans, idx)
+            grouped_xyz = grouped_xyz - new_xyz.transpose(1, 2).unsqueeze(-1)
+            if self.normalize_xyz:
+                grouped_xyz = grouped_xyz / self.radius
         if features is not None:
             grouped_features = grouping_operation(features, idx)
             new_features = torch.cat([grouped_xyz, grouped_features], dim=1) if self.use_xyz else grouped_features

@@ -122,6 +122,13 @@ int geot_knnquery(int b, int n, int m, int nsample, const float* xyz, const floa
  * and pointnet2._ext.group_points.  points (B,C,N), idx (B,M,ns) -> out (B,C,M,ns). */
 int geot_group_points(int B, int C, int N, int M, int nsample, const float* points, const int* idx,
                       float* out, geot_stream_t stream);
+/* Fused xyz grouping of QueryAndGroup / KNNGroup (group.py:235-250, :297-312; pointnet2_utils.py:291-373):
+ * out[b,c,j,s] = (xyz[b,idx[b,j,s],c] - new_xyz[b,j,c]) / divisor, straight from the (B,N,3) cloud - replaces
+ * transpose(1,2).contiguous() + grouping_operation + subtraction (+ division).  relative = 0 skips the subtraction,
+ * divisor = 0 skips the division.  xyz (B,N,3), new_xyz (B,M,3), idx (B,M,ns) -> out (B,3,M,ns); bit-identical to
+ * the composite. */
+int geot_group_xyz_relative(int B, int N, int M, int nsample, const float* xyz, const float* new_xyz,
+                            const int* idx, int relative, float divisor, float* out, geot_stream_t stream);
 /* testing / A-B timing: direct != 0 makes group/gather forward always take the direct L2-gather kernel
  * instead of the row-staged one (process-wide switch; results are identical). */
 void geot_group_points_config(int direct);

@@ -78,6 +78,10 @@ for (B, N, M, ns, Cc, r) in [(64, 16384, 1024, 32, 64, 0.1), (16, 16384, 4096, 3
     report("ball_query", tag, lambda: F.ball_query(centres, xyz, r, ns, out=nbr, workspace=ws),
            (lambda: (nbr_r.zero_(), R.ref_ball_query(B, N, M, f32(r), ns, p(centres), p(xyz), p(nbr_r)))) if R else None,
            B * (12 * N + 12 * M + 4 * M * ns), lambda: (nbr == nbr_r).all())
+    gx = torch.empty((B, 3, M, ns), device=dev)
+    report("QueryAndGroup xyz branch (fused)", tag, lambda: F.group_xyz_relative(xyz, centres, nbr, relative=True, divisor=r, out=gx),
+           lambda: ((F.group_points(xyz.transpose(1, 2).contiguous(), nbr) - centres.transpose(1, 2).unsqueeze(-1)) / r),
+           B * (4 * M * ns + 12 * N + 12 * M + 12 * M * ns), None)
     g = torch.empty((B, Cc, M, ns), device=dev); g_r = torch.empty_like(g)
     nb_fwd = B * (4 * M * ns + 4 * Cc * N + 4 * Cc * M * ns)
     report("grouping_operation fwd", tag, lambda: F.group_points(feat, nbr, out=g),

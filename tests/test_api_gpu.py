@@ -8,6 +8,7 @@ import torch
 
 from geot_b200 import layers, pointnet2_utils, pointops, synth
 from geot_b200 import backends
+from geot_b200 import functional as F
 
 pytestmark = pytest.mark.gpu
 
@@ -59,6 +60,25 @@ def test_query_and_group_matches_torch_composition(cuda, oracle):
     # twin API (argument order xyz, new_xyz) returns the concatenated tensor
     nf = pointnet2_utils.QueryAndGroup(0.1, 32, use_xyz=True)(xyz, q, feat.detach())
     assert nf.shape == (2, 11, 256, 32) and torch.equal(nf[:, 3:], fj.detach())
+
+
+@pytest.mark.parametrize("ns,relative,normalize", [(32, True, True), (7, True, False), (16, False, False), (5, True, True)])
+def test_fused_xyz_grouping_equals_composite(cuda, ns, relative, normalize):
+    """QueryAndGroup's xyz branch as one kernel (geot_group_xyz_relative) against the unfused composite
+    (transpose copy + grouping_operation + subtract + divide), which is taken when a position tensor requires grad:
+    bit-identical, for vectorised (ns % 4 == 0) and scalar neighbour counts."""
+    xyz = cu(synth.tooth_batch(3, 3000))
+    q = xyz[:, :200].contiguous()
+    g = layers.QueryAndGroup(0.15, ns, relative_xyz=relative, normalize_dp=normalize)
+    fused, _ = g(q, xyz, None)
+    xyz_g = xyz.clone().requires_grad_(True)
+    comp, _ = g(q, xyz_g, None)
+    assert comp.grad_fn is not None and fused.grad_fn is None
+    assert torch.equal(fused, comp.detach())
+    nbr = layers.ball_query(0.15, ns, xyz, q)
+    out = torch.empty(3, 3, 200, ns, device="cuda")
+    F.group_xyz_relative(xyz, q, nbr, relative=relative, divisor=0.15 if (relative and normalize) else 0.0, out=out)
+    assert torch.equal(out, fused)
 
 
 def test_knn_group_and_knn_point(cuda):
