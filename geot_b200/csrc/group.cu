@@ -29,13 +29,13 @@ static bool g_group_force_direct = false;  // testing / A-B timing: geot_group_p
 // VEC = 4: E % 4 == 0 and 16-byte aligned idx/out.  grid (ceil(E/VEC/256), ceil(C/CCH), B).
 template <int VEC>
 __global__ void __launch_bounds__(256)
-group_points_kernel(int C, int N, int64_t E, const float* __restrict__ points,
+group_points_kernel(int C, int N, int64_t E, int cch, const float* __restrict__ points,
                     const int* __restrict__ idx, float* __restrict__ out) {
   const int b = blockIdx.z;
-  const int c0 = blockIdx.y * kGroupCCH;
+  const int c0 = blockIdx.y * cch;
   const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // entry group
   if (g * VEC >= E) return;
-  const int c1 = min(C, c0 + kGroupCCH);
+  const int c1 = min(C, c0 + cch);
   if (VEC == 4) {
     const int4 id = __ldg(reinterpret_cast<const int4*>(idx + (int64_t)b * E) + g);
     for (int c = c0; c < c1; c++) {
@@ -161,13 +161,14 @@ static int launch_group(int B, int C, int N, int64_t E, const float* points, con
     count_launch(1);
     return check_launch(what);
   }
-  if (vec) {
-    dim3 grid((unsigned)((E / 4 + 255) / 256), (C + kGroupCCH - 1) / kGroupCCH, B);
-    group_points_kernel<4><<<grid, 256, 0, s>>>(C, N, E, points, idx, out);
-  } else {
-    dim3 grid((unsigned)((E + 255) / 256), (C + kGroupCCH - 1) / kGroupCCH, B);
-    group_points_kernel<1><<<grid, 256, 0, s>>>(C, N, E, points, idx, out);
-  }
+  // channels per thread: kGroupCCH amortises the idx load, but a short index list (gather_operation: E = M) then
+  // leaves most SMs without work - halve it until the grid has a few waves
+  const int64_t xb = vec ? (E / 4 + 255) / 256 : (E + 255) / 256;
+  int cch = kGroupCCH;
+  while (cch > 1 && xb * ((C + cch - 1) / cch) * B < 4 * (int64_t)kNumSMs && (C + cch / 2 - 1) / (cch / 2) <= 65535) cch >>= 1;
+  dim3 grid((unsigned)xb, (C + cch - 1) / cch, B);
+  if (vec) group_points_kernel<4><<<grid, 256, 0, s>>>(C, N, E, cch, points, idx, out);
+  else group_points_kernel<1><<<grid, 256, 0, s>>>(C, N, E, cch, points, idx, out);
   count_launch(1);
   return check_launch(what);
 }

@@ -25,5 +25,15 @@ for r in sw["rows"]:
     ref = f"{r['ref_ms']:.4f}" if r["ref_ms"] else "-"
     sp = f"{r['speedup']:.2f}x" if r["speedup"] else "-"
     L.append(f"| {r['op']} | {r['shape']} | {r['ours_ms']:.4f} | {ref} | {sp} | {r['gbs']:.0f} | {100*r['hbm_frac']:.1f} | {r['match_ref']} |")
+tp = os.path.join(ROOT, "profiles", f"{tag}_transition_sweep.json")
+if os.path.exists(tp):
+    ts = json.load(open(tp))
+    L += ["", "## Transition-matrix path against the reference's torch expressions (oracle/transition_ref.py) on the same GPU", "",
+          "`python tests/transition_sweep.py`; forward and forward+backward per op.  `max rel err` of the weight gradient includes "
+          "clamp-edge flips: a pre-activation within one ulp of the 1e-5 clamp edge passes gradient on one side and none on the "
+          "other (torch fp32 against torch fp64 differs by the same amount).", "",
+          "| op | shape | ours ms | torch ms | speed-up | algorithmic GB/s | % HBM | max rel err |", "|---|---|---|---|---|---|---|---|"]
+    for r in ts["rows"]:
+        L.append(f"| {r['op']} | {r['shape']} | {r['ours_ms']:.4f} | {r['ref_ms']:.4f} | {r['speedup']:.2f}x | {r['gbs']:.0f} | {100*r['hbm_frac']:.1f} | {r['max_rel_err']:.1e} |")
 open(os.path.join(ROOT, "profiles", f"REPORT_{tag}.md"), "w").write("\n".join(L) + "\n")
 print("\n".join(L[:24]))

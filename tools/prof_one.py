@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Dev tool (GPU box): launch ONE op of the bench workload a few times so ncu can capture it.
-usage: python tools/prof_one.py {fps|fps_noprune|ball|group|group3|groupbwd|threenn|tibwd|knn} [B]"""
+usage: python tools/prof_one.py {fps|fps_noprune|ball|group|group3|groupbwd|threenn|tibwd|knn|sigt|apply|manifold} [B]"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
@@ -28,7 +28,7 @@ if what == "knn":
     kb = 8
     kx = xyz[:kb].reshape(-1, 3).contiguous()
     koff = torch.arange(1, kb + 1, device="cuda", dtype=torch.int32) * N
-if what in ("sigt", "manifold"):
+if what in ("sigt", "manifold", "apply"):
     from geot_b200 import transition as T
     Ct, Bt, Nt = 33, 2, 16000
     logits = torch.randn(Bt, Ct, Nt, device="cuda") * 3
@@ -41,6 +41,9 @@ if what in ("sigt", "manifold"):
     insTt = modt(pt, cmt).detach().requires_grad_(True)
     losst = T.threeD_space_loss(k=32, sigma=1.0, num_classes=Ct)
     idxt = T._neighbours(32, post)
+    emat = torch.rand(Ct, Ct, device="cuda"); emat = emat / emat.sum(1, keepdim=True)
+    lgt = logits.clone().requires_grad_(True)
+    go2t = torch.randn(Bt, Ct, Nt, device="cuda")
 torch.cuda.synchronize()
 for _ in range(3):
     if what == "fps": F.furthest_point_sampling(xyz, M)
@@ -54,6 +57,8 @@ for _ in range(3):
     elif what == "knn": F.knnquery(16, kx, kx, koff, koff, m_per=N)
     elif what == "sigt":
         modt.zero_grad(set_to_none=True); modt(pt, cmt).backward(got)
+    elif what == "apply":
+        lgt.grad = None; insTt.grad = None; T.apply_transition(lgt, emat, insTt, 0.9).backward(go2t)
     elif what == "manifold":
         insTt.grad = None; losst(post, labt, insTt, idx=idxt).backward()
 torch.cuda.synchronize()
