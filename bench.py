@@ -125,6 +125,26 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def bind_to_gpu_cpus(local):
+    """Multi-rank runs: pin this process (and so the first touch of its pinned host buffers) to the CPUs NVML reports
+    as local to its GPU, so that the per-step host->device copies of the ranks do not all cross one socket.
+    Returns the number of CPUs bound to (0 = left as is)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        allowed = os.sched_getaffinity(0)
+        cpus = [64 * i + b for i, w in enumerate(mask) for b in range(64) if (w >> b) & 1 and (64 * i + b) in allowed]
+        if cpus and len(cpus) < len(allowed):
+            os.sched_setaffinity(0, cpus)
+            return len(cpus)
+    except Exception:
+        pass
+    return 0
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -137,6 +157,7 @@ def run_ours(args):
     assert torch.cuda.is_available(), "bench.py needs a GPU (no CPU fallback exists)"
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa_cpus = bind_to_gpu_cpus(local) if world > 1 else 0  # before the pinned buffers are first touched
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         # NCCL prints its version banner to stdout on the first communicator; stdout must carry ONE JSON line
@@ -267,7 +288,8 @@ def run_ours(args):
                 "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic",
                 "config": {"workload": WORKLOAD, "clouds_per_gpu": B, "sharding": "by cloud, no data-path collective",
-                           "l2_policy": "no flush: one step touches 843 MB (inputs 281 MB + outputs 562 MB) > 126 MB L2"},
+                           "l2_policy": "no flush: one step touches 843 MB (inputs 281 MB + outputs 562 MB) > 126 MB L2",
+                           "rank_cpu_binding": numa_cpus},
                 "e2e": {"value": total_pts / (ms_e2e * 1e-3), "unit": "points/s", "ms_per_step": ms_e2e,
                         "h2d_bytes_per_step": (xyz_h.numel() + feat_h.numel()) * 4,
                         "d2h_bytes_per_step": sum(t.numel() for t in out_h) * 4},
