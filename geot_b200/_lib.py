@@ -64,6 +64,9 @@ _SIGNATURES = {
     "geot_transition_apply_forward": [_i, _i, _i, _vp, _vp, _vp, _f, _vp, _vp],
     "geot_transition_apply_backward": [_i, _i, _i, _vp, _vp, _vp, _f, _vp, _vp, _vp, _vp],
     "geot_manifold_workspace_bytes": [_i64],
+    "geot_poly1_focal_workspace_bytes": [_i64],
+    "geot_poly1_focal_forward": [_i, _i, _i, _vp, _vp, _vp, _vp, _f, _f, _f, _f, _vp, _vp, _vp, _sz, _vp],
+    "geot_poly1_focal_backward": [_i, _i, _i, _vp, _vp, _vp, _vp, _f, _f, _f, _f, _vp, _vp, _vp, _vp],
     "geot_manifold_loss_forward": [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _f, _i, _vp, _vp, _vp, _sz, _vp],
     "geot_manifold_loss_backward": [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
     "geot_class_pick_workspace_bytes": [_i],
@@ -78,6 +81,7 @@ _RESTYPES = {
     "geot_ball_query_workspace_bytes": _sz,
     "geot_group_points_config": None,
     "geot_knnquery_workspace_bytes": _sz,
+    "geot_poly1_focal_workspace_bytes": _sz,
     "geot_sigt_workspace_bytes": _sz,
     "geot_sigt_backward_workspace_bytes": _sz,
     "geot_manifold_workspace_bytes": _sz,

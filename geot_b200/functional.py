@@ -473,3 +473,30 @@ def mean_feature_update(probs, target, cm, c_num):
         ws = _ws(nb, dev)
         call("geot_mean_feature_update", BN, Cc, ptr(probs), ptr(target), ptr(cm), ptr(c_num), ptr(ws), nb, stream_ptr())
     return cm, c_num
+
+
+# --------------------------------------------------------------------------------------------------
+# unsupervised poly-1 focal loss (Poly1FocalLoss_U_corr)
+# --------------------------------------------------------------------------------------------------
+def poly1_focal_forward(logits, labels, conf, mask, thresh, epsilon, alpha, gamma):
+    """logits (B,C,N) f32, labels (B,N) int64, conf (B,N) f32 or None, mask (B,N) f32 or None -> (loss (1,), denom (1,))."""
+    dev = check_cuda(logits, labels, conf, mask)
+    B, Cc, N = logits.shape
+    with on_device(dev):
+        loss = torch.empty((1,), dtype=_f32, device=dev)
+        denom = torch.empty((1,), dtype=_f32, device=dev)
+        nb = int(_lib.lib().geot_poly1_focal_workspace_bytes(B * N))
+        ws = _ws(nb, dev)
+        call("geot_poly1_focal_forward", B, Cc, N, ptr(logits), ptr(labels), ptr(conf), ptr(mask), float(thresh), float(epsilon),
+             float(alpha), float(gamma), ptr(loss), ptr(denom), ptr(ws), nb, stream_ptr())
+    return loss, denom
+
+
+def poly1_focal_backward(logits, labels, conf, mask, thresh, epsilon, alpha, gamma, denom, grad_loss):
+    dev = check_cuda(logits, labels, conf, mask, denom, grad_loss)
+    B, Cc, N = logits.shape
+    with on_device(dev):
+        g = torch.empty_like(logits)
+        call("geot_poly1_focal_backward", B, Cc, N, ptr(logits), ptr(labels), ptr(conf), ptr(mask), float(thresh), float(epsilon),
+             float(alpha), float(gamma), ptr(denom), ptr(grad_loss), ptr(g), stream_ptr())
+    return g

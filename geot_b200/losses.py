@@ -1,0 +1,54 @@
+"""geot_b200.losses — the criterion that consumes the transition-corrected logits.
+
+`Poly1FocalLoss_U_corr` mirrors openpoints/loss/build.py:799-892 (constructor arguments, `forward(logits, labels,
+logits_pred, thresh=0.95, mask=None)`); the 8-10 elementwise (B,C,N) passes of the reference and their saved
+activations are one CUDA pass forward and one backward (geot_b200/csrc/unsup_loss.cu).  CUDA only."""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+from torch.autograd import Function
+
+from . import functional as F_
+
+
+class _Poly1(Function):
+    @staticmethod
+    def forward(ctx, logits, labels, conf, mask, thresh, epsilon, alpha, gamma):
+        logits = logits.contiguous().float()
+        labels = labels.contiguous().long()
+        conf = None if conf is None else conf.contiguous().float()
+        mask = None if mask is None else mask.contiguous().float()
+        loss, denom = F_.poly1_focal_forward(logits, labels, conf, mask, thresh, epsilon, alpha, gamma)
+        ctx.save_for_backward(logits, labels, conf, mask, denom)
+        ctx.hp = (float(thresh), float(epsilon), float(alpha), float(gamma))
+        return loss.view(())
+
+    @staticmethod
+    def backward(ctx, grad_loss):
+        logits, labels, conf, mask, denom = ctx.saved_tensors
+        thresh, epsilon, alpha, gamma = ctx.hp
+        g = F_.poly1_focal_backward(logits, labels, conf, mask, thresh, epsilon, alpha, gamma, denom,
+                                    grad_loss.contiguous().float().view(1))
+        return g, None, None, None, None, None, None, None
+
+
+class Poly1FocalLoss_U_corr(nn.Module):
+    """openpoints/loss/build.py:799-892.  logits (B,C,N) (the corrected student logits, train.py:592), labels (B,N)
+    pseudo labels, logits_pred (B,N) teacher confidence; points with confidence >= thresh (or mask != 0) are kept.
+    `weight` / `pos_weight` / `label_is_onehot` / `reduction` exist for signature parity; the shipped configs leave
+    them at their defaults and anything else raises."""
+
+    def __init__(self, epsilon: float = 1.0, alpha: float = 0.25, gamma: float = 2.0, reduction: str = "mean",
+                 weight=None, pos_weight=None, label_is_onehot: bool = False, **kwargs):
+        super().__init__()
+        if weight is not None or pos_weight is not None or label_is_onehot:
+            raise NotImplementedError("Poly1FocalLoss_U_corr: weight / pos_weight / one-hot labels are not used by the "
+                                      "reference configs and are not implemented by the CUDA path")
+        self.epsilon, self.alpha, self.gamma, self.reduction = epsilon, alpha, gamma, reduction
+
+    def forward(self, logits, labels, logits_pred, thresh=0.95, mask=None):
+        if logits.dim() != 3:
+            raise ValueError("Poly1FocalLoss_U_corr expects (B, C, N) logits")
+        return _Poly1.apply(logits, labels, None if mask is not None else logits_pred, mask, thresh,
+                            self.epsilon, self.alpha, self.gamma)

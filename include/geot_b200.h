@@ -283,6 +283,23 @@ int geot_mean_feature_update(int64_t BN, int C, const float* probs, const int64_
                              float* c_num, void* workspace, size_t workspace_bytes,
                              geot_stream_t stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Unsupervised poly-1 focal loss on the transition-corrected logits.  replaces Poly1FocalLoss_U_corr.forward
+ * (openpoints/loss/build.py:830-892; criterion_u of cfgs/tooth_semi/transformer_finetune_fixmatch_ntm.yaml:54,
+ * called at examples/segmentation/train.py:592) and its autograd, weight = pos_weight = None.
+ * logits (B,C,N), labels (B,N) int64, conf (B,N) teacher confidence compared >= thresh, or mask (B,N) float weights
+ * (non-NULL mask wins) -> loss[0] = sum(keep * poly1) / (C * sum(keep) + 0.001), denom[0] = that denominator.
+ * backward: grad_logits (B,C,N) = grad_loss[0] * keep * d poly1 / d logit / denom, every element written.
+ * workspace: geot_poly1_focal_workspace_bytes(B*N) (per-CTA partial sums; summed in a fixed order).
+ * --------------------------------------------------------------------------------------------- */
+size_t geot_poly1_focal_workspace_bytes(int64_t BN);
+int geot_poly1_focal_forward(int B, int C, int N, const float* logits, const int64_t* labels, const float* conf,
+                             const float* mask, float thresh, float epsilon, float alpha, float gamma,
+                             float* loss, float* denom, void* workspace, size_t workspace_bytes, geot_stream_t stream);
+int geot_poly1_focal_backward(int B, int C, int N, const float* logits, const int64_t* labels, const float* conf,
+                              const float* mask, float thresh, float epsilon, float alpha, float gamma,
+                              const float* denom, const float* grad_loss, float* grad_logits, geot_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -169,3 +169,23 @@ def mean_feature_update(cm, c_num, probs, target):
         cm[kk] = (cm[kk] * c_num[kk] + mean_feats * cur_num) / (c_num[kk] + cur_num)
         c_num[kk] += cur_num
     return cm, c_num
+
+
+def poly1_focal_u_corr(logits, labels, logits_pred, thresh=0.95, mask=None, epsilon=1.0, alpha=0.25, gamma=2.0):
+    """openpoints/loss/build.py:830-892 (Poly1FocalLoss_U_corr.forward; weight = pos_weight = None as in the
+    shipped configs).  logits (B,C,N) corrected student logits, labels (B,N) pseudo labels, logits_pred (B,N)
+    teacher confidence -> scalar: sigmoid-focal + poly1 term, masked mean over points with confidence >= thresh
+    (or an explicit (B,N) mask), denominator C * #kept + 0.001.
+    Pinned against the reference class by tests/golden/make_loss_golden.py."""
+    C = logits.shape[1]
+    p = torch.sigmoid(logits)
+    onehot = F.one_hot(labels.unsqueeze(1), C).transpose(1, -1).squeeze(-1).to(dtype=logits.dtype)
+    ce = F.binary_cross_entropy_with_logits(logits, onehot, reduction="none")
+    pt = onehot * p + (1 - onehot) * (1 - p)
+    FL = ce * ((1 - pt) ** gamma)
+    if alpha >= 0:
+        FL = (alpha * onehot + (1 - alpha) * (1 - onehot)) * FL
+    poly1 = FL + epsilon * torch.pow(1 - pt, gamma + 1)
+    keep = mask if mask is not None else logits_pred.ge(torch.tensor(thresh, device=logits_pred.device))
+    keep = keep.unsqueeze(1).repeat(1, C, 1)
+    return torch.sum(poly1 * keep) / (keep.sum() + 0.001)

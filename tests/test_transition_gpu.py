@@ -207,3 +207,49 @@ def test_apply_tile_kernel_vs_warp_kernel(cuda, C, B, N):
                 assert rel(x, y) < 1e-5
     ref = R.transition_apply(logits, ema, insT, 0.9)
     assert rel(res[0][0][0], ref) < 1e-5
+
+
+# ---------------------------------------------------------------------------------------------
+# Poly1FocalLoss_U_corr (the criterion consuming the corrected logits)
+# ---------------------------------------------------------------------------------------------
+from tests.test_transition_oracle_cpu import LOSS_VARIANTS, loss_case  # noqa: E402  (golden fixtures of the reference class)
+
+
+@pytest.mark.parametrize("tag", ["C17", "C33", "C5"])
+@pytest.mark.parametrize("variant,hp", LOSS_VARIANTS)
+def test_golden_poly1_focal_loss(cuda, tag, variant, hp):
+    from geot_b200 import losses
+    logits, labels, conf, mask, thresh, exp_loss, exp_grad = loss_case(tag, variant)
+    x = logits.cuda().requires_grad_(True)
+    crit = losses.Poly1FocalLoss_U_corr(**hp)
+    loss = crit(x, labels.cuda(), conf.cuda(), thresh=thresh, mask=None if mask is None else mask.cuda())
+    close(loss, exp_loss, rtol=1e-5, atol=1e-8)   # north_star tolerance: 1e-5 relative
+    loss.backward()
+    assert rel(x.grad, exp_grad) < 1e-5
+
+
+def test_poly1_focal_loss_large_vs_oracle(cuda):
+    """cfg4 size (B=2+2+2 views -> 6 x 16000 points, C=33): against the oracle's torch expression on the GPU,
+    nothing kept (denominator 0.001), everything kept, and run-to-run identical bits."""
+    from geot_b200 import losses
+    g = torch.Generator(device="cuda").manual_seed(7)
+    B, C, N = 6, 33, 16000
+    logits = (torch.randn(B, C, N, device="cuda", generator=g) * 4).requires_grad_(True)
+    labels = torch.randint(0, C, (B, N), device="cuda", generator=g)
+    conf = torch.rand(B, N, device="cuda", generator=g)
+    crit = losses.Poly1FocalLoss_U_corr()
+    for thresh in (0.95, 0.0, 2.0):
+        logits.grad = None
+        loss = crit(logits, labels, conf, thresh=thresh)
+        loss.backward()
+        g1 = logits.grad.clone(); logits.grad = None
+        ref = R.poly1_focal_u_corr(logits, labels, conf, thresh=thresh)
+        ref.backward()
+        close(loss, ref, rtol=1e-5, atol=1e-8)
+        if thresh < 2.0:
+            assert rel(g1, logits.grad) < 1e-5
+        else:
+            assert float(g1.abs().max()) == 0.0 and float(loss) == 0.0
+        logits.grad = None
+        l2 = crit(logits, labels, conf, thresh=thresh); l2.backward()
+        assert torch.equal(l2, loss) and torch.equal(logits.grad, g1)

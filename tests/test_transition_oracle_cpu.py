@@ -75,3 +75,27 @@ def test_class_statistics():
         R.mean_feature_update(cm, cn, t(f"{tag}_mf_probs"), t(f"{tag}_mf_target"))
     torch.testing.assert_close(cm, t(f"{tag}_mf_cm"), rtol=1e-6, atol=1e-8)
     assert torch.equal(cn, t(f"{tag}_mf_cnum"))
+
+
+LG = np.load(os.path.join(os.path.dirname(__file__), "golden", "loss_golden.npz"))
+LOSS_VARIANTS = [("thr", {}), ("low", {}), ("mask", {}), ("hp", dict(epsilon=0.5, alpha=-1.0, gamma=1.5))]
+
+
+def loss_case(tag, variant):
+    """Inputs and expected outputs of one golden case of tests/golden/make_loss_golden.py."""
+    logits = torch.from_numpy(LG[f"{tag}_logits"]); labels = torch.from_numpy(LG[f"{tag}_labels"]); conf = torch.from_numpy(LG[f"{tag}_conf"])
+    mask = torch.from_numpy(LG[f"{tag}_{variant}_mask"]) if f"{tag}_{variant}_mask" in LG else None
+    thresh = float(LG[f"{tag}_{variant}_thresh"]) if f"{tag}_{variant}_thresh" in LG else 0.5
+    return logits, labels, conf, mask, thresh, torch.from_numpy(LG[f"{tag}_{variant}_loss"]), torch.from_numpy(LG[f"{tag}_{variant}_grad"])
+
+
+@pytest.mark.parametrize("tag", ["C17", "C33", "C5"])
+@pytest.mark.parametrize("variant,hp", LOSS_VARIANTS)
+def test_golden_poly1_focal_u_corr(tag, variant, hp):
+    """oracle restatement of Poly1FocalLoss_U_corr against the reference class's own outputs (loss and gradient)."""
+    logits, labels, conf, mask, thresh, exp_loss, exp_grad = loss_case(tag, variant)
+    x = logits.clone().requires_grad_(True)
+    loss = R.poly1_focal_u_corr(x, labels, conf, thresh=thresh, mask=mask, **hp)
+    torch.testing.assert_close(loss, exp_loss, rtol=1e-6, atol=1e-9)
+    loss.backward()
+    torch.testing.assert_close(x.grad, exp_grad, rtol=1e-5, atol=1e-10)

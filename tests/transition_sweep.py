@@ -117,6 +117,23 @@ for (B, N, C, k) in [(2, 16000, 17, 32), (2, 16000, 33, 32), (16, 16384, 33, 32)
             report("threeD_space_loss fwd+bwd", tag, ours_loss, ref_loss, 3 * 4 * BN * C * C, rel(t1.grad, t2.grad))
         except Exception as e:  # keep the sweep going; the parity tests own correctness
             print("threeD_space_loss skipped:", repr(e)[:200])
+    # ---- (f) rank 3: the criterion on the corrected logits, forward + backward
+    from geot_b200 import losses
+    crit = losses.Poly1FocalLoss_U_corr()
+    conf = torch.rand(B, N, device="cuda", generator=g)
+    labels_u = logits.argmax(1)
+    x1 = logits.clone().requires_grad_(True); x2 = logits.clone().requires_grad_(True)
+
+    def ours_crit():
+        x1.grad = None
+        crit(x1, labels_u, conf, thresh=0.5).backward()
+
+    def ref_crit():
+        x2.grad = None
+        R.poly1_focal_u_corr(x2, labels_u, conf, thresh=0.5).backward()
+
+    ours_crit(); ref_crit()
+    report("Poly1FocalLoss_U_corr fwd+bwd", tag, ours_crit, ref_crit, 3 * 4 * BN * C + 12 * BN, rel(x1.grad, x2.grad))
     del logits, p, insT, go
     torch.cuda.empty_cache()
 
