@@ -670,13 +670,8 @@ GEOT_API int geot_knnquery(int b, int n, int m, int nsample, const float* xyz, c
         cudaFuncSetAttribute(knn_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         attr_done = true;
       }
-      static float alpha = -1.f;
-      if (alpha < 0.f) {  // tuning knob: points per occupied cell = alpha * (k+1)
-        const char* e = getenv("GEOT_KNN_ALPHA");
-        alpha = e ? (float)atof(e) : 0.f;
-      }
-      // measured optimum: ~0.8 (k+1) points per occupied cell at k = 16, less for longer lists (0.4 at 32, 0.3 at 64)
-      const float a = alpha > 0.f ? alpha : fminf(fmaxf(13.f / (float)(nsample + 1), 0.3f), 0.8f);
+      // points per occupied cell = a * (k+1).  Measured optimum: ~0.8 at k = 16, less for longer lists (0.4 at 32, 0.3 at 64)
+      const float a = fminf(fmaxf(13.f / (float)(nsample + 1), 0.3f), 0.8f);
       knn_build_kernel<<<b, 1024, smem, s>>>(nsample, a, xyz, offset, n_per, seg_grid, base + w.slots, reinterpret_cast<float4*>(base + w.sorted));
       count_launch(1);
       int rc = check_launch("knn_build_kernel");
