@@ -5,7 +5,10 @@ One step = one pass of the hot path over one batch of synthetic tooth-scan-shape
     furthest_point_sample(M=1024) -> gather centres -> ball_query(r=0.1, ns=32)
     -> grouping_operation(xyz, C=3) -> grouping_operation(features, C=64)
 on B=64 clouds x N=16384 points PER GPU (weak scaling: every rank owns 64 different clouds,
-no data-path collective).  `value` = points of all ranks / device time (inputs resident in HBM);
+no data-path collective).  `value` = points of all ranks / device time (inputs resident in HBM), with
+`--in-flight` (default 3) independent steps enqueued on as many streams, each with its own output set: one step
+alone leaves 84 of the 148 SMs idle while its FPS runs (one CTA per cloud, M-1 dependent rounds), and consecutive
+steps work on independent batches; `config.ms_per_step_one_in_flight` is the strictly serial number;
 `e2e` = the same pass with HOST buffers: pinned host -> device copy of xyz+features every step and a
 device -> host read of the sampled / neighbour indices and centres inside the timed region.
 
@@ -193,14 +196,52 @@ def run_ours(args):
     def make_ops(xyz, feat):
         return {
             "fps": lambda: F.furthest_point_sampling(xyz, M, out=fps_idx),
-            "gather_centres": lambda: (xyz_t.copy_(xyz.transpose(1, 2)), F.gather_points(xyz_t, fps_idx, out=centres_t),
-                                       centres.copy_(centres_t.transpose(1, 2))),
+            # centres = xyz[fps_idx], gathered point-major: same values as the reference's transpose -> gather_operation
+            # -> transpose chain (checked once below), without the two copies
+            "gather_centres": lambda: F.gather_rows(xyz, fps_idx, out=centres),
             "ball_query": lambda: F.ball_query(centres, xyz, RADIUS, NS, out=nbr, workspace=bq_ws),
-            "group_xyz": lambda: F.group_points(xyz_t, nbr, out=g_xyz),
+            # grouping_operation(xyz^T, idx) straight from the (B,N,3) cloud (no (B,3,N) copy): identical output
+            "group_xyz": lambda: F.group_xyz_relative(xyz, centres, nbr, relative=False, out=g_xyz),
             "group_feat": lambda: F.group_points(feat, nbr, out=g_feat),
         }
 
     ops = make_ops(xyz, feat)
+
+    # `value`: several (default 3) steps in flight.  One step keeps 64 of the 148 SMs busy for its first 0.55 ms (FPS: one CTA per
+    # cloud, M-1 dependent rounds); consecutive steps work on independent batches, so step i+1 is enqueued on a second
+    # stream with its own output set and its FPS runs beside step i's ball query / grouping (and beside step i's FPS:
+    # 2 x 64 CTAs fit).  Every step still runs all five ops on all 64 clouds inside the timed region.
+    def out_set():
+        return dict(fps_idx=torch.empty_like(fps_idx), centres=torch.empty_like(centres), nbr=torch.empty_like(nbr),
+                    g_xyz=torch.empty_like(g_xyz), g_feat=torch.empty_like(g_feat), bq_ws=torch.empty_like(bq_ws))
+
+    def make_ops_on(o):
+        return [lambda: F.furthest_point_sampling(xyz, M, out=o["fps_idx"]),
+                lambda: F.gather_rows(xyz, o["fps_idx"], out=o["centres"]),
+                lambda: F.ball_query(o["centres"], xyz, RADIUS, NS, out=o["nbr"], workspace=o["bq_ws"]),
+                lambda: F.group_xyz_relative(xyz, o["centres"], o["nbr"], relative=False, out=o["g_xyz"]),
+                lambda: F.group_points(feat, o["nbr"], out=o["g_feat"])]
+
+    NPIPE = max(1, args.in_flight)
+    pipe_outs = [dict(fps_idx=fps_idx, centres=centres, nbr=nbr, g_xyz=g_xyz, g_feat=g_feat, bq_ws=bq_ws)] + [out_set() for _ in range(NPIPE - 1)]
+    pipe_ops = [make_ops_on(o) for o in pipe_outs]
+    pipe_streams = [torch.cuda.Stream(device=dev) for _ in range(NPIPE)]
+    pipe_i = [0]
+
+    def step_pipelined():
+        k = pipe_i[0] % NPIPE
+        pipe_i[0] += 1
+        with torch.cuda.stream(pipe_streams[k]):
+            for f in pipe_ops[k]:
+                f()
+
+    # one-time check that the two fused ops equal the reference's composite chain on this batch
+    for f in ops.values():
+        f()
+    xyz_t.copy_(xyz.transpose(1, 2))
+    F.gather_points(xyz_t, fps_idx, out=centres_t)
+    assert torch.equal(centres, centres_t.transpose(1, 2)), "gather_rows != transpose/gather_operation/transpose"
+    assert torch.equal(g_xyz, F.group_points(xyz_t, nbr)), "group_xyz_relative(relative=False) != grouping_operation(xyz^T)"
 
     def step():
         for f in ops.values():
@@ -238,14 +279,23 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, steps, warmup):
+    def timed(fn, steps, warmup, side_streams=()):
+        """CUDA events on the current stream around exactly `steps` calls; work that fn enqueues on side_streams starts
+        after the first event and is waited for before the second."""
         for _ in range(warmup):
             fn()
         barrier()
+        cur = torch.cuda.current_stream()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
+        for st in side_streams:
+            st.wait_event(e0)
         for _ in range(steps):
             fn()
+        for st in side_streams:
+            done = torch.cuda.Event()
+            done.record(st)
+            cur.wait_event(done)
         e1.record()
         barrier()
         ms = torch.tensor([e0.elapsed_time(e1) / steps], device=dev)
@@ -257,8 +307,11 @@ def run_ours(args):
     if sampler:
         sampler.start()
     l0 = _lib.launch_count()
-    ms = timed(step, args.steps, args.warmup)
+    ms_serial = timed(step, args.steps, args.warmup)
     launches = (_lib.launch_count() - l0) * world // (args.steps + args.warmup) * args.steps
+    ms = timed(step_pipelined, args.steps, max(args.warmup, 4), side_streams=pipe_streams)
+    # the second output set must hold what the first holds (same inputs): the pipelined steps did the full work
+    assert all(torch.equal(o["nbr"], nbr) and torch.equal(o["g_feat"], g_feat) for o in pipe_outs[1:]), "pipelined step differs"
     ms_e2e = timed(step_e2e, args.steps, max(args.warmup, 3))
     if sampler:
         sampler.stop()
@@ -289,7 +342,8 @@ def run_ours(args):
                 "dtype": "f32", "data": "synthetic",
                 "config": {"workload": WORKLOAD, "clouds_per_gpu": B, "sharding": "by cloud, no data-path collective",
                            "l2_policy": "no flush: one step touches 843 MB (inputs 281 MB + outputs 562 MB) > 126 MB L2",
-                           "rank_cpu_binding": numa_cpus},
+                           "rank_cpu_binding": numa_cpus,
+                           "steps_in_flight": NPIPE, "ms_per_step_one_in_flight": ms_serial},
                 "e2e": {"value": total_pts / (ms_e2e * 1e-3), "unit": "points/s", "ms_per_step": ms_e2e,
                         "h2d_bytes_per_step": (xyz_h.numel() + feat_h.numel()) * 4,
                         "d2h_bytes_per_step": sum(t.numel() for t in out_h) * 4},
@@ -325,6 +379,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--in-flight", type=int, default=3, help="independent steps in flight for `value` (streams + output sets)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

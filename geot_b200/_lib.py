@@ -39,6 +39,7 @@ _SIGNATURES = {
     "geot_group_points": [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp],
     "geot_gather_points": [_i, _i, _i, _i, _vp, _vp, _vp, _vp],
     "geot_group_points_config": [_i],
+    "geot_gather_rows": [_i, _i, _i, _i, _vp, _vp, _vp, _vp],
     "geot_group_xyz_relative": [_i, _i, _i, _i, _vp, _vp, _vp, _i, _f, _vp, _vp],
     "geot_scatter_plan_bytes": [_i, _i, _i64],
     "geot_scatter_plan_build": [_i, _i, _i64, _vp, _vp, _sz, _vp],

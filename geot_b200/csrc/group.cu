@@ -791,6 +791,31 @@ GEOT_API int geot_group_xyz_relative(int B, int N, int M, int nsample, const flo
   return check_launch("group_xyz_rel_kernel");
 }
 
+namespace geot {
+// Point-major gather: out[b,j,:] = src[b, idx[b,j], :] for D floats per point (D = 3: the sampled centres
+// new_xyz = xyz[fps_idx]).  The reference reaches this through transpose(1,2).contiguous() -> gather_operation ->
+// transpose(1,2).contiguous() (e.g. pointnet2_modules / subsample.py:108-144 callers); same values, no copies.
+__global__ void __launch_bounds__(256)
+gather_rows_kernel(int N, int M, int D, const float* __restrict__ src, const int* __restrict__ idx, float* __restrict__ out) {
+  const int b = blockIdx.y;
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // (j, d) flattened
+  if (e >= (int64_t)M * D) return;
+  const int j = (int)(e / D), d = (int)(e - (int64_t)j * D);
+  out[(int64_t)b * M * D + e] = __ldg(src + ((int64_t)b * N + __ldg(idx + (int64_t)b * M + j)) * D + d);
+}
+}  // namespace geot
+
+GEOT_API int geot_gather_rows(int B, int N, int M, int D, const float* src, const int* idx, float* out, geot_stream_t stream) {
+  GEOT_REQUIRE(B >= 0 && N >= 0 && M >= 0 && D >= 1, "gather_rows: bad sizes");
+  if (B == 0 || M == 0) return GEOT_OK;
+  GEOT_REQUIRE(src && idx && out, "gather_rows: NULL pointer");
+  GEOT_REQUIRE(B <= 65535, "gather_rows: B exceeds grid limits");
+  dim3 grid((unsigned)(((int64_t)M * D + 255) / 256), B);
+  gather_rows_kernel<<<grid, 256, 0, as_stream(stream)>>>(N, M, D, src, idx, out);
+  count_launch(1);
+  return check_launch("gather_rows_kernel");
+}
+
 /* testing / A-B timing: direct != 0 disables the row-staged forward kernel (process-wide). */
 GEOT_API void geot_group_points_config(int direct) { g_group_force_direct = direct != 0; }
 

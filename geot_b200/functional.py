@@ -132,6 +132,18 @@ def group_points(points, idx, out=None):
     return out
 
 
+def gather_rows(src, idx, out=None):
+    """Point-major gather: src (B,N,D), idx (B,M) -> (B,M,D); D=3: new_xyz = xyz[fps_idx] without the two transposes."""
+    dev = check_cuda(src, idx, out)
+    B, N, D = src.shape
+    M = idx.shape[1]
+    with on_device(dev):
+        if out is None:
+            out = torch.empty((B, M, D), dtype=_f32, device=dev)
+        call("geot_gather_rows", B, N, M, D, ptr(src), ptr(idx), ptr(out), stream_ptr())
+    return out
+
+
 def group_xyz_relative(xyz, new_xyz, idx, relative=True, divisor=0.0, out=None):
     """Fused xyz grouping of QueryAndGroup: xyz (B,N,3), new_xyz (B,M,3), idx (B,M,ns) -> (B,3,M,ns) =
     (xyz[idx] - new_xyz) / divisor, without the (B,3,N) transpose copy or separate subtract / divide passes."""

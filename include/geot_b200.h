@@ -122,6 +122,10 @@ int geot_knnquery(int b, int n, int m, int nsample, const float* xyz, const floa
  * and pointnet2._ext.group_points.  points (B,C,N), idx (B,M,ns) -> out (B,C,M,ns). */
 int geot_group_points(int B, int C, int N, int M, int nsample, const float* points, const int* idx,
                       float* out, geot_stream_t stream);
+/* Point-major gather: src (B,N,D), idx (B,M) -> out (B,M,D) = src[b, idx[b,j], :].  D = 3 gives the sampled centres
+ * new_xyz = xyz[fps_idx] that the reference computes as gather_operation(xyz.transpose(1,2).contiguous(), idx)
+ * .transpose(1,2).contiguous() (sampling_gpu.cu:15-31 between two transpose copies). */
+int geot_gather_rows(int B, int N, int M, int D, const float* src, const int* idx, float* out, geot_stream_t stream);
 /* Fused xyz grouping of QueryAndGroup / KNNGroup (group.py:235-250, :297-312; pointnet2_utils.py:291-373):
  * out[b,c,j,s] = (xyz[b,idx[b,j,s],c] - new_xyz[b,j,c]) / divisor, straight from the (B,N,3) cloud - replaces
  * transpose(1,2).contiguous() + grouping_operation + subtraction (+ division).  relative = 0 skips the subtraction,

@@ -81,6 +81,17 @@ def test_fused_xyz_grouping_equals_composite(cuda, ns, relative, normalize):
     assert torch.equal(out, fused)
 
 
+@pytest.mark.parametrize("B,N,M,D", [(3, 5000, 777, 3), (2, 100, 100, 1), (1, 4096, 1, 7)])
+def test_gather_rows_equals_transpose_gather_transpose(cuda, B, N, M, D):
+    """Point-major gather (new_xyz = xyz[fps_idx]) against the reference's chain transpose -> gather_operation -> transpose."""
+    src = torch.randn(B, N, D, device="cuda")
+    idx = torch.randint(0, N, (B, M), device="cuda", dtype=torch.int32)
+    got = F.gather_rows(src, idx)
+    chain = layers.gather_operation(src.transpose(1, 2).contiguous(), idx).transpose(1, 2).contiguous()
+    assert torch.equal(got, chain)
+    assert torch.equal(got, torch.gather(src, 1, idx.long().unsqueeze(-1).expand(-1, -1, D)))
+
+
 def test_knn_group_and_knn_point(cuda):
     xyz = cu(synth.tooth_batch(2, 2048))
     q = xyz[:, :300].contiguous() + 1e-3
