@@ -22,7 +22,8 @@
 namespace geot {
 
 void count_launch(int n);
-bool direct_kernels_forced();  // geot_group_points_config (group.cu)
+bool direct_kernels_forced();  // geot_group_points_config(1) (group.cu)
+bool staged_kernels_forced();  // geot_group_points_config(2)
 int three_interpolate_grad_impl(int B, int C, int n, int m, const float* grad_out, const float* weight,
                                 const void* plan, float* grad_points, cudaStream_t s);
 
@@ -98,7 +99,7 @@ three_nn_kernel(int n, int m, const float* __restrict__ unknown, const float* __
 }
 
 // ---------------------------------------------------------------------------------------------
-// three_nn over a uniform grid (default for 64 <= m <= kNgMaxM = 7168).  The brute-force kernel above evaluates all m
+// three_nn over a uniform grid (default for 64 <= m <= kNgMaxM = 9216).  The brute-force kernel above evaluates all m
 // known points per unknown point (n*m distances per cloud).  The known cloud is small (it is the SAMPLED level
 // of a feature-propagation stage), so every CTA bins it into shared memory itself - bounding box, cell size for
 // ~1.5 points per occupied cell (measured, one re-binning if the first guess is off), counting sort of
@@ -108,9 +109,9 @@ three_nn_kernel(int n, int m, const float* __restrict__ unknown, const float* __
 // reference's strict-'<' scan in ascending index order produces (interpolate_gpu.cu:44-55), so the result does
 // not depend on the order candidates are visited in: bit-identical idx and dist2, no fallback pass.
 // ---------------------------------------------------------------------------------------------
-constexpr int kNgMaxM = 7168;
+constexpr int kNgMaxM = 9216;
 constexpr int kNgMaxDim = 64;      // cells per axis
-constexpr int kNgMaxCells = 8000;  // cells in total (two int tables of this size live in shared memory)
+constexpr int kNgMaxCells = 8000;  // cells in total (one int table of this size lives in shared memory)
 constexpr int kNgThreads = 1024;
 
 __device__ __forceinline__ bool lex_lt(float d, int k, float D, int K) { return d < D || (d == D && k < K); }
@@ -133,8 +134,7 @@ three_nn_grid_kernel(int n, int m, const float* __restrict__ unknown, const floa
   __shared__ int s_occupied;
   float4* sorted = reinterpret_cast<float4*>(ng_smem);               // m entries
   int* cells = reinterpret_cast<int*>(ng_smem + (size_t)m * 16);     // kNgMaxCells + 1: histogram -> cursor
-  int* cell_start = cells + kNgMaxCells + 1;                         // kNgMaxCells + 1
-  unsigned* runs = reinterpret_cast<unsigned*>(cell_start + kNgMaxCells + 1);  // 9 x kNgThreads: {start:16 | length:16}
+  unsigned* runs = reinterpret_cast<unsigned*>(cells + kNgMaxCells + 1);  // 9 x kNgThreads: {start:16 | length:16}
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int b = blockIdx.y;
   const float* __restrict__ kn = known + (int64_t)b * m * 3;
@@ -218,7 +218,7 @@ three_nn_grid_kernel(int n, int m, const float* __restrict__ unknown, const floa
     if (Gn == G || (capped && Gn > G)) break;
     G = Gn;
   }
-  {  // exclusive scan of the histogram -> cell_start, cells becomes the scatter cursor
+  {  // exclusive scan of the histogram: cells = scatter cursor; after the scatter cells[i] = end of cell i = start of cell i+1
     const int PER = (ncell + kNgThreads - 1) / kNgThreads;
     const int i0 = t * PER;
     int sum = 0;
@@ -241,10 +241,8 @@ three_nn_grid_kernel(int n, int m, const float* __restrict__ unknown, const floa
     for (int i = i0; i < min(i0 + PER, ncell); i++) {
       const int v = cells[i];
       cells[i] = run;
-      cell_start[i] = run;
       run += v;
     }
-    if (t == 0) cell_start[ncell] = m;
   }
   __syncthreads();
   for (int k = t; k < m; k += kNgThreads) {
@@ -287,7 +285,7 @@ three_nn_grid_kernel(int n, int m, const float* __restrict__ unknown, const floa
       xa = max(xa, 0); xb = min(xb, dx - 1);
       if (xa > xb) return;
       const int row = (z * dy + y) * dx;
-      p = cell_start[row + xa]; e = cell_start[row + xb + 1];
+      p = (row + xa) ? cells[row + xa - 1] : 0; e = cells[row + xb];
     };
     {  // ring 1: the non-empty x-runs of the 3x3 rows go to a per-thread list in shared memory (converged code),
        // then they are walked as ONE flat candidate sequence: a warp's cost is its longest list, not the sum
@@ -433,11 +431,13 @@ GEOT_API int geot_three_nn(int B, int n, int m, const float* unknown, const floa
   if (B == 0 || n == 0) return GEOT_OK;
   GEOT_REQUIRE(unknown && dist2 && idx && (m == 0 || known), "three_nn: NULL pointer");
   GEOT_REQUIRE(B <= 65535, "three_nn: B exceeds grid limits");
-  if (m >= 64 && m <= kNgMaxM && !direct_kernels_forced()) {
-    const size_t smem = (size_t)m * 16 + (size_t)(kNgMaxCells + 1) * 8 + (size_t)9 * kNgThreads * 4;
+  // the grid costs a fixed ~50 us (every CTA bins the known cloud first); below ~5e7 distance evaluations the
+  // brute-force kernel finishes sooner (measured: B=6, n=8192, m=512 brute 45 us vs grid 80 us; B=16, n=4096, m=1024 grid 43 vs 78)
+  if (m >= 64 && m <= kNgMaxM && ((double)B * n * m >= 5e7 || staged_kernels_forced()) && !direct_kernels_forced()) {
+    const size_t smem = (size_t)m * 16 + (size_t)(kNgMaxCells + 1) * 4 + (size_t)9 * kNgThreads * 4;
     static bool configured = false;
     if (!configured) {
-      cudaError_t e = cudaFuncSetAttribute(three_nn_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kNgMaxM * 16 + (kNgMaxCells + 1) * 8 + 9 * kNgThreads * 4);
+      cudaError_t e = cudaFuncSetAttribute(three_nn_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kNgMaxM * 16 + (kNgMaxCells + 1) * 4 + 9 * kNgThreads * 4);
       if (e != cudaSuccess) { set_error("three_nn: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
       configured = true;
     }

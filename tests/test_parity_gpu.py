@@ -335,12 +335,15 @@ def test_three_nn_grid_vs_scan(cuda, kind, B, n, m):
         unknown = np.ascontiguousarray(big[:, :n])
     unknown[:, 3::97] += np.float32(7.0)
     unknown[:, 5::131] *= np.float32(-3.0)
-    gd, gi = F.three_nn(cu(unknown), cu(known))
-    _lib.lib().geot_group_points_config(1)
+    _lib.lib().geot_group_points_config(2)  # grid even where the work-size heuristic would pick the brute-force kernel
     try:
+        gd, gi = F.three_nn(cu(unknown), cu(known))
+        _lib.lib().geot_group_points_config(1)
         sd, si = F.three_nn(cu(unknown), cu(known))
     finally:
         _lib.lib().geot_group_points_config(0)
+    dd, di = F.three_nn(cu(unknown), cu(known))  # default dispatch
+    assert torch.equal(di, si) and torch.equal(dd, sd)
     assert torch.equal(gi, si)
     assert torch.equal(gd, sd)
 
