@@ -31,12 +31,39 @@ def knn(x, src, k, transpose=False):
     return (idx.view(b, n, k) - base).long(), torch.sqrt(d2).view(b, n, k)
 
 
+class _FpsPrefixCache:
+    """FPS is greedy from index 0, so the first k samples of a longer run ARE the k-sample run (round j only depends on
+    the j-1 earlier picks).  GeoT samples the same cloud three times per forward with decreasing targets
+    (transformer.py:1037-1039, downsample_targets [8192, 4096, 2048]): the second and third calls are prefixes of the
+    first.  One entry: the last tensor sampled (held alive, so its storage cannot be recycled under the cache) with its
+    version counter; any in-place write or a different tensor misses."""
+
+    def __init__(self):
+        self.x = None
+        self.version = -1
+        self.idx = None  # (b, k_max) global indices
+
+    def get(self, x, k):
+        if self.x is x and self.version == x._version and self.idx is not None and self.idx.shape[1] >= k:
+            return self.idx[:, :k]
+        return None
+
+    def put(self, x, idx):
+        self.x, self.version, self.idx = x, x._version, idx
+
+
+_fps_cache = _FpsPrefixCache()
+
+
 def fps(x, k):
     """pointops.py:24-32: x (b,n,3) -> sampled xyz (b,k,3)."""
     b, n, _ = x.shape
-    x = x.contiguous().view(-1, 3)
-    idx = F_.furthestsampling(x, _cum_offsets(b, n, x.device), _cum_offsets(b, k, x.device), n_max=n, m_total=b * k).long()
-    return x[idx].view(b, k, 3)
+    idx = _fps_cache.get(x, k)
+    flat = x.contiguous().view(-1, 3)
+    if idx is None:
+        idx = F_.furthestsampling(flat, _cum_offsets(b, n, x.device), _cum_offsets(b, k, x.device), n_max=n, m_total=b * k).long().view(b, k)
+        _fps_cache.put(x, idx)
+    return flat[idx.reshape(-1)].view(b, k, 3)
 
 
 def fps_weight(x, k, weight=None):

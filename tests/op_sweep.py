@@ -140,5 +140,31 @@ for (b, n_per, k, c) in [(8, 16384, 16, 32), (8, 4096, 16, 64)]:
     del x, o, o_r, go, gi, gi_r, plan
     torch.cuda.empty_cache()
 
+# ---------------------------------------------------------------- cfg4: B_tot = 6 clouds x N = 16000 (GeoT's own step)
+b, n_per = 6, 16000
+n = b * n_per
+xyz6 = torch.from_numpy(synth.tooth_batch(b, n_per)).to(dev)
+flat = xyz6.reshape(n, 3).contiguous()
+off = torch.arange(1, b + 1, device=dev, dtype=i32) * n_per
+for m_per in (8192, 4096, 2048):  # transformer.py:1037-1039: three pointops.furthestsampling calls per forward
+    noff = torch.arange(1, b + 1, device=dev, dtype=i32) * m_per
+    out = torch.empty((b * m_per,), dtype=i32, device=dev); out_r = torch.zeros_like(out)
+    tmp = torch.empty((n,), device=dev)
+    report("pointops.furthestsampling", f"b={b} n={n_per} m={m_per}",
+           lambda: F.furthestsampling(flat, off, noff, n_max=n_per, m_total=b * m_per, out=out),
+           (lambda: (tmp.fill_(1e10), RP.ref_furthestsampling(b, n_per, p(flat), p(off), p(noff), p(tmp), p(out_r)))) if RP else None,
+           b * (12 * n_per + 4 * m_per), lambda: (out == out_r).all())
+idx512 = torch.empty((b, 512), dtype=i32, device=dev)
+report("furthest_point_sample (_ext rule)", f"B={b} N={n_per} M=512 (transformer.py:271)",
+       lambda: F.furthest_point_sampling(xyz6, 512, out=idx512, flags=_lib.GEOT_FPS_CAP512 | _lib.GEOT_FPS_MAGSKIP), None,
+       b * (12 * n_per + 4 * 512))
+for (nq, mk) in [(16000, 8192), (8192, 512), (4096, 512)]:  # the feature-propagation levels
+    unknown = xyz6[:, :nq].contiguous(); known = xyz6[:, torch.randperm(n_per, device=dev)[:mk]].contiguous()
+    d2 = torch.empty((b, nq, 3), device=dev); i3 = torch.empty((b, nq, 3), dtype=i32, device=dev)
+    d2_r = torch.empty_like(d2); i3_r = torch.empty_like(i3)
+    report("three_nn", f"B={b} n={nq} m={mk}", lambda: F.three_nn(unknown, known, dist2=d2, idx=i3),
+           (lambda: R.ref_three_nn(b, nq, mk, p(unknown), p(known), p(d2_r), p(i3_r))) if R else None,
+           b * (12 * nq + 12 * mk + 24 * nq), lambda: (i3 == i3_r).all())
+
 if args.out:
     json.dump({"hbm_peak_gbs": PEAK, "rows": rows}, open(args.out, "w"), indent=1)

@@ -92,6 +92,22 @@ def test_gather_rows_equals_transpose_gather_transpose(cuda, B, N, M, D):
     assert torch.equal(got, torch.gather(src, 1, idx.long().unsqueeze(-1).expand(-1, -1, D)))
 
 
+def test_pointops_fps_prefix_cache(cuda):
+    """pointops.fps on the same tensor with decreasing targets (transformer.py:1037-1039) is served from the longest run:
+    identical to fresh runs; an in-place write or another tensor invalidates the entry."""
+    x = cu(synth.tooth_batch(2, 6000))
+    a8 = pointops.fps(x, 2000)
+    a4 = pointops.fps(x, 1000)
+    a2 = pointops.fps(x, 500)
+    assert torch.equal(a4, a8[:, :1000]) and torch.equal(a2, a8[:, :500])
+    y = x.clone()
+    assert torch.equal(pointops.fps(y, 1000), a4) and torch.equal(pointops.fps(x.clone(), 500), a2)  # fresh runs
+    x.mul_(1.5)  # in-place edit: version counter moves, the cache must miss
+    b4 = pointops.fps(x, 1000)
+    assert torch.equal(b4, pointops.fps(x.clone(), 1000))
+    assert torch.allclose(b4, a4 * 1.5)
+
+
 def test_knn_group_and_knn_point(cuda):
     xyz = cu(synth.tooth_batch(2, 2048))
     q = xyz[:, :300].contiguous() + 1e-3
