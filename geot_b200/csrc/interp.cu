@@ -468,7 +468,9 @@ GEOT_API int geot_three_interpolate(int B, int C, int m, int n, const float* poi
   if (B == 0 || C == 0 || n == 0) return GEOT_OK;
   GEOT_REQUIRE(points && idx && weight && out, "three_interpolate: NULL pointer");
   GEOT_REQUIRE(B <= 65535 && (C + kTiCCH - 1) / kTiCCH <= 65535, "three_interpolate: B or C exceeds grid limits");
-  if (m > 0 && m % 4 == 0 && (((uintptr_t)points & 15) == 0) && (size_t)m * 4 <= 96 * 1024 && n >= 2 * m) {
+  // rows staged in shared memory whenever a row (m floats) is not much longer than what it produces (n outputs): the
+  // direct kernel pays a 32-byte L2 sector per 4-byte gather (measured 3.6x slower at cfg4's m=8192 -> n=16000)
+  if (m > 0 && m % 4 == 0 && (((uintptr_t)points & 15) == 0) && (size_t)m * 4 <= 96 * 1024 && (8 * (int64_t)n >= m || staged_kernels_forced()) && !direct_kernels_forced()) {
     int G = (int)std::min<size_t>(16, (64 * 1024) / ((size_t)m * 4));
     if (G < 1) G = 1;
     if (G > C) G = C;
