@@ -574,7 +574,10 @@ plan_wsort_kernel(int64_t E, const float* __restrict__ w, const int* __restrict_
   wsorted[base + e] = __ldg(w + base + __ldg(perm + base + e));
 }
 
-template <int R>
+// LPT = lanes per target: 8 for long segments (~48 edges when n/m = 16), 2 when a target has only a handful of
+// edges (n/m = 2: six on average) - then 512 targets are in flight per CTA instead of 128 and the per-target
+// round trip to L2, not the edge count, is what is being hidden.
+template <int R, int LPT>
 __global__ void __launch_bounds__(1024, 1)
 seg_reduce_wrows_kernel(int C, int n, int m, const float* __restrict__ g, const int* __restrict__ row_ptr,
                         const int* __restrict__ perm, const float* __restrict__ wsorted, float* __restrict__ dst) {
@@ -599,27 +602,27 @@ seg_reduce_wrows_kernel(int C, int n, int m, const float* __restrict__ g, const 
   mbar_wait(&bar, 0);
   const int* __restrict__ pm = perm + (int64_t)b * E;
   const float* __restrict__ ws = wsorted + (int64_t)b * E;
-  const int sub = t & 7;
-  for (int k = t >> 3; k < m; k += 128) {
+  const int sub = t % LPT;
+  for (int k = t / LPT; k < m; k += 1024 / LPT) {
     const int s0 = rp_s[k], e0 = rp_s[k + 1];
     float acc[R];
 #pragma unroll
     for (int r = 0; r < R; r++) acc[r] = 0.f;
     // up to 64 edges of the segment per round: all 8 {perm, w} pairs of a lane are requested before the first
     // is used, so a typical segment (~48 edges) costs one L2 round trip instead of one per pair
-    for (int p0 = s0 + sub; p0 < e0; p0 += 64) {
+    for (int p0 = s0 + sub; p0 < e0; p0 += 8 * LPT) {
       int sr[8];
       float wt[8];
 #pragma unroll
       for (int j = 0; j < 8; j++) {
-        const int p = p0 + 8 * j;
+        const int p = p0 + LPT * j;
         const bool ok = p < e0;
         sr[j] = ok ? __ldg(pm + p) : 0;
         wt[j] = ok ? __ldg(ws + p) : 0.f;
       }
 #pragma unroll
       for (int j = 0; j < 8; j++) {
-        if (p0 + 8 * j < e0) {
+        if (p0 + LPT * j < e0) {
           const int src = sr[j] / 3;
 #pragma unroll
           for (int r = 0; r < R; r++) acc[r] = __fadd_rn(acc[r], __fmul_rn(rows[(size_t)r * n + src], wt[j]));
@@ -628,9 +631,8 @@ seg_reduce_wrows_kernel(int C, int n, int m, const float* __restrict__ g, const 
     }
 #pragma unroll
     for (int r = 0; r < R; r++) {
-      acc[r] = __fadd_rn(acc[r], __shfl_xor_sync(0xffffffffu, acc[r], 4));
-      acc[r] = __fadd_rn(acc[r], __shfl_xor_sync(0xffffffffu, acc[r], 2));
-      acc[r] = __fadd_rn(acc[r], __shfl_xor_sync(0xffffffffu, acc[r], 1));
+#pragma unroll
+      for (int o = LPT / 2; o > 0; o >>= 1) acc[r] = __fadd_rn(acc[r], __shfl_xor_sync(0xffffffffu, acc[r], o));
     }
     if (sub == 0) {
 #pragma unroll
@@ -642,19 +644,26 @@ seg_reduce_wrows_kernel(int C, int n, int m, const float* __restrict__ g, const 
   for (int i = t; i < nc * m; i += 1024) out[i] = outs[i];
 }
 
-template <int R>
-static int launch_wrows(int B, int C, int n, int m, size_t smem, const float* g, const PlanView& pv, const float* wsorted,
-                        float* dst, cudaStream_t s) {
+template <int R, int LPT>
+static int launch_wrows_t(int B, int C, int n, int m, size_t smem, const float* g, const PlanView& pv, const float* wsorted,
+                          float* dst, cudaStream_t s) {
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(seg_reduce_wrows_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(seg_reduce_wrows_kernel<R, LPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
     if (e != cudaSuccess) { set_error("three_interpolate_grad: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
     configured = true;
   }
   dim3 grid((C + R - 1) / R, B);
-  seg_reduce_wrows_kernel<R><<<grid, 1024, smem, s>>>(C, n, m, g, pv.row_ptr, pv.perm, wsorted, dst);
+  seg_reduce_wrows_kernel<R, LPT><<<grid, 1024, smem, s>>>(C, n, m, g, pv.row_ptr, pv.perm, wsorted, dst);
   count_launch(1);
   return check_launch("seg_reduce_wrows_kernel");
+}
+template <int R>
+static int launch_wrows(int B, int C, int n, int m, size_t smem, const float* g, const PlanView& pv, const float* wsorted,
+                        float* dst, cudaStream_t s) {
+  // average segment = 3n / m edges
+  if ((int64_t)3 * n < (int64_t)24 * m) return launch_wrows_t<R, 2>(B, C, n, m, smem, g, pv, wsorted, dst, s);
+  return launch_wrows_t<R, 8>(B, C, n, m, smem, g, pv, wsorted, dst, s);
 }
 
 static int three_interpolate_grad_rows(int B, int C, int n, int m, const float* g, const float* w, const void* plan,
