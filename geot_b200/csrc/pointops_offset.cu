@@ -219,6 +219,94 @@ aggregation_bwd_in_kernel(int n, int ns, int c, int w_c, const float* __restrict
   gin[t] = acc;
 }
 
+// ---- float4 variants (c % 4 == 0, w_c % 4 == 0, 16-byte aligned): the scalar kernels above mirror the reference's
+// thread-per-(point, channel) mapping and run at its speed; here a thread owns 4 consecutive channels, whose weights
+// w[.., ci % w_c] are 4 consecutive floats as well, so every access is a 16-byte vector.
+__global__ void __launch_bounds__(256)
+aggregation_fwd_vec_kernel(int n, int ns, int c, int w_c, const float* __restrict__ input,
+                           const float* __restrict__ position, const float* __restrict__ weight,
+                           const int* __restrict__ idx, float* __restrict__ output) {
+  const int c4 = c >> 2;
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (int64_t)n * c4) return;
+  const int p = (int)(t / c4), ci = (int)(t - (int64_t)p * c4) * 4;
+  const int wi = ci % w_c;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+  for (int s = 0; s < ns; s++) {
+    const int64_t r = (int64_t)p * ns + s;
+    const float4 a = ld4(input + (int64_t)__ldg(idx + r) * c + ci);
+    const float4 q = ld4(position + r * c + ci);
+    const float4 w = ld4(weight + r * w_c + wi);
+    acc.x = __fmaf_rn(__fadd_rn(a.x, q.x), w.x, acc.x);
+    acc.y = __fmaf_rn(__fadd_rn(a.y, q.y), w.y, acc.y);
+    acc.z = __fmaf_rn(__fadd_rn(a.z, q.z), w.z, acc.z);
+    acc.w = __fmaf_rn(__fadd_rn(a.w, q.w), w.w, acc.w);
+  }
+  *reinterpret_cast<float4*>(output + (int64_t)p * c + ci) = acc;
+}
+
+// grad_position and grad_weight in one pass over (p, s): the T = c/4 threads of a row are T consecutive lanes;
+// lanes whose channel groups share a weight slot (q % G equal, G = w_c/4) are summed with a fixed xor tree.
+__global__ void __launch_bounds__(256)
+aggregation_bwd_pw_vec_kernel(int n, int ns, int c, int w_c, const float* __restrict__ input,
+                              const float* __restrict__ position, const float* __restrict__ weight,
+                              const int* __restrict__ idx, const float* __restrict__ g,
+                              float* __restrict__ gpos, float* __restrict__ gw) {
+  const int T = c >> 2, G = w_c >> 2;
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t rows = (int64_t)n * ns;
+  const bool live = t < rows * T;
+  const int64_t r = live ? t / T : 0;
+  const int q = live ? (int)(t - r * T) : 0;
+  const int ci = q * 4, wi = ci % w_c;
+  const int p = (int)(r / ns);
+  float4 part = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (live) {
+    const float4 go = ld4(g + (int64_t)p * c + ci);
+    const float4 w = ld4(weight + r * w_c + wi);
+    __stcs(reinterpret_cast<float4*>(gpos + r * c + ci), make_float4(__fmul_rn(go.x, w.x), __fmul_rn(go.y, w.y), __fmul_rn(go.z, w.z), __fmul_rn(go.w, w.w)));
+    const float4 a = ld4(input + (int64_t)__ldg(idx + r) * c + ci);
+    const float4 ps = ld4(position + r * c + ci);
+    part = make_float4(__fmul_rn(go.x, __fadd_rn(a.x, ps.x)), __fmul_rn(go.y, __fadd_rn(a.y, ps.y)),
+                       __fmul_rn(go.z, __fadd_rn(a.z, ps.z)), __fmul_rn(go.w, __fadd_rn(a.w, ps.w)));
+  }
+  for (int o = T >> 1; o >= G; o >>= 1) {  // T and G are powers of two, T <= 32: rows never straddle a warp
+    part.x = __fadd_rn(part.x, __shfl_xor_sync(0xffffffffu, part.x, o));
+    part.y = __fadd_rn(part.y, __shfl_xor_sync(0xffffffffu, part.y, o));
+    part.z = __fadd_rn(part.z, __shfl_xor_sync(0xffffffffu, part.z, o));
+    part.w = __fadd_rn(part.w, __shfl_xor_sync(0xffffffffu, part.w, o));
+  }
+  if (live && q < G) *reinterpret_cast<float4*>(gw + r * w_c + q * 4) = part;
+}
+
+__global__ void __launch_bounds__(256)
+aggregation_bwd_in_vec_kernel(int n, int ns, int c, int w_c, const float* __restrict__ weight,
+                              const float* __restrict__ g, const int* __restrict__ row_ptr,
+                              const int* __restrict__ perm, float* __restrict__ gin) {
+  const int c4 = c >> 2;
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (int64_t)n * c4) return;
+  const int tgt = (int)(t / c4), ci = (int)(t - (int64_t)tgt * c4) * 4;
+  const int wi = ci % w_c;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  const int p0 = row_ptr[tgt], p1 = row_ptr[tgt + 1];
+#pragma unroll 4
+  for (int p = p0; p < p1; p++) {
+    const int src = __ldg(perm + p);
+    const float4 go = ld4(g + (int64_t)(src / ns) * c + ci);
+    const float4 w = ld4(weight + (int64_t)src * w_c + wi);
+    acc.x = __fadd_rn(acc.x, __fmul_rn(go.x, w.x)); acc.y = __fadd_rn(acc.y, __fmul_rn(go.y, w.y));
+    acc.z = __fadd_rn(acc.z, __fmul_rn(go.z, w.z)); acc.w = __fadd_rn(acc.w, __fmul_rn(go.w, w.w));
+  }
+  *reinterpret_cast<float4*>(gin + (int64_t)tgt * c + ci) = acc;
+}
+
+static inline bool pow2(int v) { return v > 0 && (v & (v - 1)) == 0; }
+static inline bool aligned16(const void* a, const void* b, const void* c2, const void* d) {
+  return ((((uintptr_t)a) | ((uintptr_t)b) | ((uintptr_t)c2) | ((uintptr_t)d)) & 15) == 0;
+}
+
 static inline unsigned blocks_for(int64_t tot) { return (unsigned)((tot + 255) / 256); }
 
 }  // namespace geot
@@ -292,7 +380,10 @@ GEOT_API int geot_aggregation_forward(int n, int nsample, int c, int w_c, const 
   GEOT_REQUIRE(n >= 0 && nsample >= 0 && c >= 0 && w_c >= 1, "aggregation_forward: bad sizes");
   if (n == 0 || c == 0) return GEOT_OK;
   GEOT_REQUIRE(output && (nsample == 0 || (input && position && weight && idx)), "aggregation_forward: NULL pointer");
-  aggregation_fwd_kernel<<<blocks_for((int64_t)n * c), 256, 0, as_stream(stream)>>>(n, nsample, c, w_c, input, position, weight, idx, output);
+  if (c % 4 == 0 && w_c % 4 == 0 && aligned16(input, position, weight, output))
+    aggregation_fwd_vec_kernel<<<blocks_for((int64_t)n * (c / 4)), 256, 0, as_stream(stream)>>>(n, nsample, c, w_c, input, position, weight, idx, output);
+  else
+    aggregation_fwd_kernel<<<blocks_for((int64_t)n * c), 256, 0, as_stream(stream)>>>(n, nsample, c, w_c, input, position, weight, idx, output);
   count_launch(1);
   return check_launch("aggregation_fwd_kernel");
 }
@@ -306,9 +397,15 @@ GEOT_API int geot_aggregation_backward(int n, int nsample, int c, int w_c, const
   GEOT_REQUIRE(input && position && weight && idx && grad_output && plan && grad_input && grad_position && grad_weight, "aggregation_backward: NULL pointer");
   cudaStream_t s = as_stream(stream);
   const PlanPtrs pp = plan_ptrs(plan, n);
-  aggregation_bwd_in_kernel<<<blocks_for((int64_t)n * c), 256, 0, s>>>(n, nsample, c, w_c, weight, grad_output, pp.row_ptr, pp.perm, grad_input);
-  aggregation_bwd_pos_kernel<<<blocks_for((int64_t)n * nsample * c), 256, 0, s>>>(n, nsample, c, w_c, weight, grad_output, grad_position);
-  aggregation_bwd_w_kernel<<<blocks_for((int64_t)n * nsample * w_c), 256, 0, s>>>(n, nsample, c, w_c, input, position, idx, grad_output, grad_weight);
+  const bool vec = c % 4 == 0 && w_c % 4 == 0 && aligned16(input, position, weight, grad_output) && aligned16(grad_input, grad_position, grad_weight, nullptr);
+  if (vec) aggregation_bwd_in_vec_kernel<<<blocks_for((int64_t)n * (c / 4)), 256, 0, s>>>(n, nsample, c, w_c, weight, grad_output, pp.row_ptr, pp.perm, grad_input);
+  else aggregation_bwd_in_kernel<<<blocks_for((int64_t)n * c), 256, 0, s>>>(n, nsample, c, w_c, weight, grad_output, pp.row_ptr, pp.perm, grad_input);
+  if (vec && pow2(c / 4) && pow2(w_c / 4) && c / 4 <= 32 && c % w_c == 0) {
+    aggregation_bwd_pw_vec_kernel<<<blocks_for((int64_t)n * nsample * (c / 4)), 256, 0, s>>>(n, nsample, c, w_c, input, position, weight, idx, grad_output, grad_position, grad_weight);
+  } else {
+    aggregation_bwd_pos_kernel<<<blocks_for((int64_t)n * nsample * c), 256, 0, s>>>(n, nsample, c, w_c, weight, grad_output, grad_position);
+    aggregation_bwd_w_kernel<<<blocks_for((int64_t)n * nsample * w_c), 256, 0, s>>>(n, nsample, c, w_c, input, position, idx, grad_output, grad_weight);
+  }
   count_launch(3);
   return check_launch("aggregation_backward");
 }

@@ -137,6 +137,46 @@ for (b, n_per, k, c) in [(8, 16384, 16, 32), (8, 4096, 16, 64)]:
     report("pointops.grouping bwd", tag + " (plan cached)", lambda: F.grouping_backward(go, plan, n, out=gi),
            (lambda: (gi_r.zero_(), RF.ref_grouping_backward(n, k, c, p(go), p(idx), p(gi_r)))) if RF else None, nb,
            lambda: torch.allclose(gi, gi_r, rtol=1e-4, atol=1e-3))
+    # ---- the rest of a Point-Transformer block on the same neighbourhoods (offset API, channel-last)
+    x2 = torch.randn(n, c, device=dev)
+    sub = torch.empty((n, k, c), device=dev); sub_r = torch.empty_like(sub)
+    nb_s = 4 * n * k + 8 * n * c + 4 * n * k * c
+    report("pointops.subtraction fwd", tag, lambda: F.subtraction_forward(x, x2, idx, out=sub),
+           (lambda: RF.ref_subtraction_forward(n, k, c, p(x), p(x2), p(idx), p(sub_r))) if RF else None, nb_s, lambda: (sub == sub_r).all())
+    g1 = torch.empty((n, c), device=dev); g2 = torch.empty((n, c), device=dev); g1_r = torch.empty_like(g1); g2_r = torch.empty_like(g2)
+    report("pointops.subtraction bwd", tag + " (plan cached)", lambda: F.subtraction_backward(go, plan, g1=g1, g2=g2),
+           (lambda: (g1_r.zero_(), g2_r.zero_(), RF.ref_subtraction_backward(n, k, c, p(idx), p(go), p(g1_r), p(g2_r)))) if RF else None, nb_s,
+           lambda: torch.allclose(g2, g2_r, rtol=1e-4, atol=1e-3) and torch.allclose(g1, g1_r, rtol=1e-4, atol=1e-3))
+    w_c = c // 8
+    wgt = torch.randn(n, k, w_c, device=dev)
+    agg = torch.empty((n, c), device=dev); agg_r = torch.empty_like(agg)
+    nb_a = 4 * n * k + 4 * n * c + 4 * n * k * c + 4 * n * k * w_c + 4 * n * c
+    report("pointops.aggregation fwd", tag + f" w_c={w_c}", lambda: F.aggregation_forward(x, o, wgt, idx, out=agg),
+           (lambda: (agg_r.zero_(), RF.ref_aggregation_forward(n, k, c, w_c, p(x), p(o), p(wgt), p(idx), p(agg_r)))) if RF else None, nb_a,
+           lambda: torch.allclose(agg, agg_r, rtol=1e-4, atol=1e-4))
+    ga = torch.randn(n, c, device=dev)
+    gi2 = torch.empty((n, c), device=dev); gp2 = torch.empty((n, k, c), device=dev); gw2 = torch.empty((n, k, w_c), device=dev)
+    gi2_r = torch.empty_like(gi2); gp2_r = torch.empty_like(gp2); gw2_r = torch.empty_like(gw2)
+    report("pointops.aggregation bwd", tag + f" w_c={w_c} (plan cached)",
+           lambda: F.aggregation_backward(x, o, wgt, idx, ga, plan, gi=gi2, gp=gp2, gw=gw2),
+           (lambda: (gi2_r.zero_(), gp2_r.zero_(), gw2_r.zero_(),
+                     RF.ref_aggregation_backward(n, k, c, w_c, p(x), p(o), p(wgt), p(idx), p(ga), p(gi2_r), p(gp2_r), p(gw2_r)))) if RF else None,
+           2 * nb_a, lambda: torch.allclose(gi2, gi2_r, rtol=1e-3, atol=1e-2) and torch.allclose(gp2, gp2_r, rtol=1e-4, atol=1e-4))
+    # interpolation (k = 3 nearest of a 4x coarser level, as in the decoder)
+    m3 = n // 4
+    i3 = torch.randint(0, m3, (n, 3), device=dev, dtype=i32)
+    w3 = torch.rand(n, 3, device=dev); w3 = w3 / w3.sum(-1, keepdim=True)
+    xc = torch.randn(m3, c, device=dev)
+    io = torch.empty((n, c), device=dev); io_r = torch.empty_like(io)
+    nb_i = 24 * n + 4 * m3 * c + 4 * n * c
+    report("pointops.interpolation fwd", f"n={n} m={m3} c={c}", lambda: F.interpolation_forward(xc, i3, w3, out=io),
+           (lambda: (io_r.zero_(), RF.ref_interpolation_forward(n, c, 3, p(xc), p(i3), p(w3), p(io_r)))) if RF else None, nb_i,
+           lambda: torch.allclose(io, io_r, rtol=1e-5, atol=1e-5))
+    plan_i = F.ScatterPlan(i3.view(1, n, 3), 1, m3)
+    gio = torch.randn(n, c, device=dev); gim = torch.empty((m3, c), device=dev); gim_r = torch.empty_like(gim)
+    report("pointops.interpolation bwd", f"n={n} m={m3} c={c} (plan cached)", lambda: F.interpolation_backward(gio, w3, plan_i, m3, 3, out=gim),
+           (lambda: (gim_r.zero_(), RF.ref_interpolation_backward(n, c, 3, p(gio), p(i3), p(w3), p(gim_r)))) if RF else None, nb_i,
+           lambda: torch.allclose(gim, gim_r, rtol=1e-4, atol=1e-3))
     del x, o, o_r, go, gi, gi_r, plan
     torch.cuda.empty_cache()
 

@@ -427,3 +427,27 @@ def test_offset_channel_last_ops(cuda, oracle, c):
         np.testing.assert_allclose(gi.cpu().numpy(), ei, rtol=1e-4, atol=1e-5)
         assert np.array_equal(gp.cpu().numpy(), ep)
         np.testing.assert_allclose(gw.cpu().numpy(), ew, rtol=1e-4, atol=1e-5)
+
+
+@pytest.mark.parametrize("c,wc", [(64, 8), (32, 4), (48, 12), (6, 3), (128, 16), (256, 32)])
+def test_aggregation_vector_and_scalar_paths(cuda, oracle, c, wc):
+    """aggregation fwd/bwd (openpoints/cpp/pointops/src/aggregation) for channel counts that take the float4 kernels
+    (c, w_c multiples of 4; the fused grad_position + grad_weight kernel needs c/4 and w_c/4 to be powers of two, c/4 <= 32)
+    and for those that fall back to the scalar ones."""
+    rng = np.random.default_rng(c)
+    n, ns = 2500, 16
+    inp = rng.standard_normal((n, c)).astype(np.float32)
+    idn = rng.integers(0, n, (n, ns)).astype(np.int32)
+    pos = rng.standard_normal((n, ns, c)).astype(np.float32)
+    wt = rng.standard_normal((n, ns, wc)).astype(np.float32)
+    np.testing.assert_allclose(F.aggregation_forward(cu(inp), cu(pos), cu(wt), cu(idn)).cpu().numpy(),
+                               oracle.aggregation_forward(inp, pos, wt, idn), rtol=1e-4, atol=1e-5)
+    ga = rng.standard_normal((n, c)).astype(np.float32)
+    plan = F.ScatterPlan(cu(idn), 1, n)
+    gi, gp, gw = F.aggregation_backward(cu(inp), cu(pos), cu(wt), cu(idn), cu(ga), plan)
+    ei, ep, ew = oracle.aggregation_backward(inp, pos, wt, idn, ga)
+    np.testing.assert_allclose(gi.cpu().numpy(), ei, rtol=1e-4, atol=1e-5)
+    assert np.array_equal(gp.cpu().numpy(), ep)
+    np.testing.assert_allclose(gw.cpu().numpy(), ew, rtol=1e-4, atol=2e-5)
+    gi2, gp2, gw2 = F.aggregation_backward(cu(inp), cu(pos), cu(wt), cu(idn), cu(ga), plan)
+    assert torch.equal(gi, gi2) and torch.equal(gw, gw2)
