@@ -158,6 +158,21 @@ subtraction_bwd1_kernel(int n, int ns, int c, const float* __restrict__ g, float
   gi1[t] = acc;
 }
 
+__global__ void __launch_bounds__(256)
+subtraction_bwd1_vec_kernel(int n, int ns, int c, const float* __restrict__ g, float* __restrict__ gi1) {
+  const int c4 = c >> 2;
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (int64_t)n * c4) return;
+  const int p = (int)(t / c4), ci = (int)(t - (int64_t)p * c4) * 4;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 8
+  for (int s = 0; s < ns; s++) {
+    const float4 v = ld4(g + ((int64_t)p * ns + s) * c + ci);
+    acc.x = __fadd_rn(acc.x, v.x); acc.y = __fadd_rn(acc.y, v.y); acc.z = __fadd_rn(acc.z, v.z); acc.w = __fadd_rn(acc.w, v.w);
+  }
+  *reinterpret_cast<float4*>(gi1 + (int64_t)p * c + ci) = acc;
+}
+
 // ---- aggregation fwd: out[p,ci] = sum_s (in[idx[p,s],ci] + pos[p,s,ci]) * w[p,s,ci % w_c] ----------
 __global__ void __launch_bounds__(256)
 aggregation_fwd_kernel(int n, int ns, int c, int w_c, const float* __restrict__ input,
@@ -367,7 +382,10 @@ GEOT_API int geot_subtraction_backward(int n, int nsample, int c, const float* g
   GEOT_REQUIRE(n >= 0 && nsample >= 1 && c >= 0, "subtraction_backward: bad sizes");
   if (n == 0 || c == 0) return GEOT_OK;
   GEOT_REQUIRE(grad_output && grad_input1 && grad_input2, "subtraction_backward: NULL pointer");
-  subtraction_bwd1_kernel<<<blocks_for((int64_t)n * c), 256, 0, as_stream(stream)>>>(n, nsample, c, grad_output, grad_input1);
+  if (c % 4 == 0 && ((((uintptr_t)grad_output) | ((uintptr_t)grad_input1)) & 15) == 0)
+    subtraction_bwd1_vec_kernel<<<blocks_for((int64_t)n * (c / 4)), 256, 0, as_stream(stream)>>>(n, nsample, c, grad_output, grad_input1);
+  else
+    subtraction_bwd1_kernel<<<blocks_for((int64_t)n * c), 256, 0, as_stream(stream)>>>(n, nsample, c, grad_output, grad_input1);
   count_launch(1);
   int rc = check_launch("subtraction_bwd1_kernel");
   if (rc) return rc;
