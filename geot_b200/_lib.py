@@ -68,12 +68,17 @@ _SIGNATURES = {
     "geot_poly1_focal_workspace_bytes": [_i64],
     "geot_poly1_focal_forward": [_i, _i, _i, _vp, _vp, _vp, _vp, _f, _f, _f, _f, _vp, _vp, _vp, _sz, _vp],
     "geot_poly1_focal_backward": [_i, _i, _i, _vp, _vp, _vp, _vp, _f, _f, _f, _f, _vp, _vp, _vp, _vp],
+    "geot_poly1_focal_t_forward": [_i, _i, _i, _vp, _vp, _vp, _vp, _vp, _f, _f, _f, _f, _vp, _vp, _vp, _sz, _vp],
+    "geot_poly1_focal_t_backward": [_i, _i, _i, _vp, _vp, _vp, _vp, _vp, _f, _f, _f, _f, _vp, _vp, _vp, _vp, _vp],
     "geot_manifold_loss_forward": [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _f, _i, _vp, _vp, _vp, _sz, _vp],
     "geot_manifold_loss_backward": [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
     "geot_class_pick_workspace_bytes": [_i],
     "geot_class_pick": [_i, _i, _i, _vp, _vp, _vp, _vp, _vp, _sz, _vp],
     "geot_class_t_step": [_i, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp],
     "geot_mean_feature_update": [_i64, _i, _vp, _vp, _vp, _vp, _vp, _sz, _vp],
+    "geot_interp_weights": [_i64, _vp, _vp, _vp, _vp],
+    "geot_interp_argmax": [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp],
+    "geot_seg_counts": [_i64, _i, _vp, _vp, _vp, _vp],
 }
 _RESTYPES = {
     "geot_last_error": C.c_char_p,

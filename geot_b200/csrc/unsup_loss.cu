@@ -53,12 +53,17 @@ __device__ __forceinline__ float keep_of(const float* conf, const float* mask, f
   return mask != nullptr ? mask[g] : (conf[g] >= thresh ? 1.0f : 0.f);
 }
 
+// Poly1FocalLoss_U_T (build.py:661-670): beta = logits_pred / pred_u_t[b, label, n]
+__device__ __forceinline__ float beta_of(const float* conf, const float* pred_t, int64_t b, int C, int N, int lab, int64_t n) {
+  return conf[b * N + n] / __ldg(pred_t + (b * C + lab) * N + n);
+}
+
 constexpr int kLossThreads = 256;
 // grid-stride over points; partial[blockIdx] = {sum of kept poly1 terms, sum of keep}
 __global__ void __launch_bounds__(kLossThreads)
 poly1_fwd_kernel(int B, int C, int N, const float* __restrict__ logits, const int64_t* __restrict__ labels,
                  const float* __restrict__ conf, const float* __restrict__ mask, float thresh, float eps, float alpha,
-                 float gamma, double* __restrict__ partial) {
+                 float gamma, const float* __restrict__ pred_t, double* __restrict__ partial) {
   __shared__ double s_a[kLossThreads / 32], s_b[kLossThreads / 32];
   const int64_t BN = (int64_t)B * N;
   double acc = 0.0, cnt = 0.0;
@@ -71,6 +76,7 @@ poly1_fwd_kernel(int B, int C, int N, const float* __restrict__ logits, const in
       const float* __restrict__ x = logits + b * C * N + n;
       float s = 0.f;
       for (int c = 0; c < C; c++) s += poly1_element(__ldg(x + (int64_t)c * N), c == lab, eps, alpha, gamma, false).value;
+      if (pred_t != nullptr) s *= beta_of(conf, pred_t, b, C, N, lab, n);  // Poly1FocalLoss_U_T: poly1 * beta
       acc += (double)(s * k);
     }
   }
@@ -102,7 +108,7 @@ __global__ void __launch_bounds__(kLossThreads)
 poly1_bwd_kernel(int B, int C, int N, const float* __restrict__ logits, const int64_t* __restrict__ labels,
                  const float* __restrict__ conf, const float* __restrict__ mask, float thresh, float eps, float alpha,
                  float gamma, const float* __restrict__ denom, const float* __restrict__ grad_loss,
-                 float* __restrict__ grad_logits) {
+                 float* __restrict__ grad_logits, const float* __restrict__ pred_t, float* __restrict__ grad_pred_t) {
   const int64_t BN = (int64_t)B * N;
   const float scale = grad_loss[0] / denom[0];
   for (int64_t g = (int64_t)blockIdx.x * kLossThreads + threadIdx.x; g < BN; g += (int64_t)gridDim.x * kLossThreads) {
@@ -111,8 +117,26 @@ poly1_bwd_kernel(int B, int C, int N, const float* __restrict__ logits, const in
     const int lab = (int)labels[g];
     const float* __restrict__ x = logits + b * C * N + n;
     float* __restrict__ o = grad_logits + b * C * N + n;
-    for (int c = 0; c < C; c++)
-      o[(int64_t)c * N] = k != 0.f ? k * poly1_element(__ldg(x + (int64_t)c * N), c == lab, eps, alpha, gamma, true).dvalue : 0.f;
+    if (pred_t == nullptr) {
+      for (int c = 0; c < C; c++)
+        o[(int64_t)c * N] = k != 0.f ? k * poly1_element(__ldg(x + (int64_t)c * N), c == lab, eps, alpha, gamma, true).dvalue : 0.f;
+    } else {  // loss element = beta * sum_c poly1, beta = conf / after: d/d logit = beta * dpoly1, d/d after = -beta / after * sum
+      float* __restrict__ ot = grad_pred_t + b * C * N + n;
+      const float after = __ldg(pred_t + (b * C + lab) * N + n);
+      const float beta = conf[g] / after;
+      float sum = 0.f;
+      for (int c = 0; c < C; c++) {
+        float d = 0.f;
+        if (k != 0.f) {
+          const Poly1 e = poly1_element(__ldg(x + (int64_t)c * N), c == lab, eps, alpha, gamma, true);
+          d = k * beta * e.dvalue;
+          sum += e.value;
+        }
+        o[(int64_t)c * N] = d;
+        ot[(int64_t)c * N] = 0.f;
+      }
+      if (k != 0.f) ot[(int64_t)lab * N] = -k * sum * (beta / after);
+    }
   }
 }
 
@@ -127,21 +151,22 @@ using namespace geot;
 
 GEOT_API size_t geot_poly1_focal_workspace_bytes(int64_t BN) { return BN > 0 ? (size_t)loss_grid(BN) * 2 * sizeof(double) + 256 : 0; }
 
-GEOT_API int geot_poly1_focal_forward(int B, int C, int N, const float* logits, const int64_t* labels, const float* conf,
-                                      const float* mask, float thresh, float epsilon, float alpha, float gamma,
-                                      float* loss, float* denom, void* workspace, size_t workspace_bytes,
-                                      geot_stream_t stream) {
-  GEOT_REQUIRE(B >= 1 && C >= 1 && N >= 1, "poly1_focal_forward: bad sizes B=%d C=%d N=%d", B, C, N);
-  GEOT_REQUIRE(logits && labels && (conf || mask) && loss && denom, "poly1_focal_forward: NULL pointer");
+static int poly1_forward_impl(const char* who, int B, int C, int N, const float* logits, const int64_t* labels, const float* conf,
+                              const float* mask, const float* pred_t, float thresh, float epsilon, float alpha, float gamma,
+                              float* loss, float* denom, void* workspace, size_t workspace_bytes, geot_stream_t stream) {
+  GEOT_REQUIRE(B >= 1 && C >= 1 && N >= 1, "%s: bad sizes B=%d C=%d N=%d", who, B, C, N);
+  GEOT_REQUIRE(logits && labels && (conf || mask) && loss && denom, "%s: NULL pointer", who);
+  GEOT_REQUIRE(pred_t == nullptr || conf != nullptr, "%s: the beta factor needs logits_pred (conf)", who);
   const int64_t BN = (int64_t)B * N;
   if (workspace == nullptr || workspace_bytes < geot_poly1_focal_workspace_bytes(BN)) {
-    set_error("poly1_focal_forward: workspace %zu < %zu bytes", workspace_bytes, geot_poly1_focal_workspace_bytes(BN));
+    set_error("%s: workspace %zu < %zu bytes", who, workspace_bytes, geot_poly1_focal_workspace_bytes(BN));
     return GEOT_ERR_WORKSPACE;
   }
   cudaStream_t s = as_stream(stream);
   const int grid = loss_grid(BN);
   double* partial = reinterpret_cast<double*>(workspace);
-  poly1_fwd_kernel<<<grid, kLossThreads, 0, s>>>(B, C, N, logits, labels, conf, mask, thresh, epsilon, alpha, gamma, partial);
+  // with a mask the keep weights come from the mask; conf is then only the numerator of beta
+  poly1_fwd_kernel<<<grid, kLossThreads, 0, s>>>(B, C, N, logits, labels, conf, mask, thresh, epsilon, alpha, gamma, pred_t, partial);
   count_launch(1);
   int rc = check_launch("poly1_fwd_kernel");
   if (rc) return rc;
@@ -150,14 +175,49 @@ GEOT_API int geot_poly1_focal_forward(int B, int C, int N, const float* logits, 
   return check_launch("poly1_final_kernel");
 }
 
+static int poly1_backward_impl(const char* who, int B, int C, int N, const float* logits, const int64_t* labels, const float* conf,
+                               const float* mask, const float* pred_t, float thresh, float epsilon, float alpha, float gamma,
+                               const float* denom, const float* grad_loss, float* grad_logits, float* grad_pred_t,
+                               geot_stream_t stream) {
+  GEOT_REQUIRE(B >= 1 && C >= 1 && N >= 1, "%s: bad sizes B=%d C=%d N=%d", who, B, C, N);
+  GEOT_REQUIRE(logits && labels && (conf || mask) && denom && grad_loss && grad_logits, "%s: NULL pointer", who);
+  GEOT_REQUIRE(pred_t == nullptr || (conf != nullptr && grad_pred_t != nullptr), "%s: NULL pointer (beta path)", who);
+  poly1_bwd_kernel<<<loss_grid((int64_t)B * N), kLossThreads, 0, as_stream(stream)>>>(
+      B, C, N, logits, labels, conf, mask, thresh, epsilon, alpha, gamma, denom, grad_loss, grad_logits, pred_t, grad_pred_t);
+  count_launch(1);
+  return check_launch("poly1_bwd_kernel");
+}
+
+GEOT_API int geot_poly1_focal_forward(int B, int C, int N, const float* logits, const int64_t* labels, const float* conf,
+                                      const float* mask, float thresh, float epsilon, float alpha, float gamma,
+                                      float* loss, float* denom, void* workspace, size_t workspace_bytes,
+                                      geot_stream_t stream) {
+  return poly1_forward_impl("poly1_focal_forward", B, C, N, logits, labels, conf, mask, nullptr, thresh, epsilon, alpha, gamma, loss,
+                            denom, workspace, workspace_bytes, stream);
+}
+
 GEOT_API int geot_poly1_focal_backward(int B, int C, int N, const float* logits, const int64_t* labels, const float* conf,
                                        const float* mask, float thresh, float epsilon, float alpha, float gamma,
                                        const float* denom, const float* grad_loss, float* grad_logits,
                                        geot_stream_t stream) {
-  GEOT_REQUIRE(B >= 1 && C >= 1 && N >= 1, "poly1_focal_backward: bad sizes B=%d C=%d N=%d", B, C, N);
-  GEOT_REQUIRE(logits && labels && (conf || mask) && denom && grad_loss && grad_logits, "poly1_focal_backward: NULL pointer");
-  poly1_bwd_kernel<<<loss_grid((int64_t)B * N), kLossThreads, 0, as_stream(stream)>>>(B, C, N, logits, labels, conf, mask, thresh,
-                                                                                     epsilon, alpha, gamma, denom, grad_loss, grad_logits);
-  count_launch(1);
-  return check_launch("poly1_bwd_kernel");
+  return poly1_backward_impl("poly1_focal_backward", B, C, N, logits, labels, conf, mask, nullptr, thresh, epsilon, alpha, gamma,
+                             denom, grad_loss, grad_logits, nullptr, stream);
+}
+
+GEOT_API int geot_poly1_focal_t_forward(int B, int C, int N, const float* logits, const int64_t* labels, const float* conf,
+                                        const float* mask, const float* pred_t, float thresh, float epsilon, float alpha,
+                                        float gamma, float* loss, float* denom, void* workspace, size_t workspace_bytes,
+                                        geot_stream_t stream) {
+  GEOT_REQUIRE(pred_t != nullptr && conf != nullptr, "poly1_focal_t_forward: NULL pointer");
+  return poly1_forward_impl("poly1_focal_t_forward", B, C, N, logits, labels, conf, mask, pred_t, thresh, epsilon, alpha, gamma, loss,
+                            denom, workspace, workspace_bytes, stream);
+}
+
+GEOT_API int geot_poly1_focal_t_backward(int B, int C, int N, const float* logits, const int64_t* labels, const float* conf,
+                                         const float* mask, const float* pred_t, float thresh, float epsilon, float alpha,
+                                         float gamma, const float* denom, const float* grad_loss, float* grad_logits,
+                                         float* grad_pred_t, geot_stream_t stream) {
+  GEOT_REQUIRE(pred_t != nullptr && conf != nullptr, "poly1_focal_t_backward: NULL pointer");
+  return poly1_backward_impl("poly1_focal_t_backward", B, C, N, logits, labels, conf, mask, pred_t, thresh, epsilon, alpha, gamma,
+                             denom, grad_loss, grad_logits, grad_pred_t, stream);
 }

@@ -274,6 +274,37 @@ def three_interpolate_grad(grad_out, weight, plan, m, out=None):
     return out
 
 
+def interp_weights(dist2, want_dist=False):
+    """dist2 (..., 3) SQUARED three_nn distances -> inverse-distance weights (same shape) [, sqrt distances]."""
+    dev = check_cuda(dist2)
+    with on_device(dev):
+        weight = torch.empty_like(dist2)
+        dist = torch.empty_like(dist2) if want_dist else None
+        call("geot_interp_weights", dist2.numel() // 3, ptr(dist2), ptr(dist), ptr(weight), stream_ptr())
+    return (weight, dist) if want_dist else weight
+
+
+def interp_argmax(points, idx, weight, want_score=False):
+    """points (B,C,m), idx/weight (B,n,3) -> pred (B,n) int64 = argmax_c of the 3-neighbour blend [, score (B,n)]."""
+    dev = check_cuda(points, idx, weight)
+    B, Cc, m = points.shape
+    n = idx.shape[1]
+    with on_device(dev):
+        pred = torch.empty((B, n), dtype=torch.int64, device=dev)
+        score = torch.empty((B, n), dtype=_f32, device=dev) if want_score else None
+        call("geot_interp_argmax", B, Cc, m, n, ptr(points), ptr(idx), ptr(weight), ptr(pred), ptr(score), stream_ptr())
+    return (pred, score) if want_score else pred
+
+
+def seg_counts(pred, label, num_classes):
+    """pred, label (n) int64 -> counts (3C+2) int64: inter[C] | pred_cnt[C] | label_cnt[C] | correct | out-of-range."""
+    dev = check_cuda(pred, label)
+    with on_device(dev):
+        counts = torch.empty((3 * num_classes + 2,), dtype=torch.int64, device=dev)
+        call("geot_seg_counts", pred.numel(), num_classes, ptr(pred), ptr(label), ptr(counts), stream_ptr())
+    return counts
+
+
 # --------------------------------------------------------------------------------------------------
 # offset-format (channel-last) ops
 # --------------------------------------------------------------------------------------------------
@@ -512,3 +543,28 @@ def poly1_focal_backward(logits, labels, conf, mask, thresh, epsilon, alpha, gam
         call("geot_poly1_focal_backward", B, Cc, N, ptr(logits), ptr(labels), ptr(conf), ptr(mask), float(thresh), float(epsilon),
              float(alpha), float(gamma), ptr(denom), ptr(grad_loss), ptr(g), stream_ptr())
     return g
+
+
+def poly1_focal_t_forward(logits, labels, conf, mask, pred_t, thresh, epsilon, alpha, gamma):
+    """Poly1FocalLoss_U_T: as poly1_focal_forward with every point scaled by conf / pred_t[b, label, n]."""
+    dev = check_cuda(logits, labels, conf, mask, pred_t)
+    B, Cc, N = logits.shape
+    with on_device(dev):
+        loss = torch.empty((1,), dtype=_f32, device=dev)
+        denom = torch.empty((1,), dtype=_f32, device=dev)
+        nb = int(_lib.lib().geot_poly1_focal_workspace_bytes(B * N))
+        ws = _ws(nb, dev)
+        call("geot_poly1_focal_t_forward", B, Cc, N, ptr(logits), ptr(labels), ptr(conf), ptr(mask), ptr(pred_t), float(thresh),
+             float(epsilon), float(alpha), float(gamma), ptr(loss), ptr(denom), ptr(ws), nb, stream_ptr())
+    return loss, denom
+
+
+def poly1_focal_t_backward(logits, labels, conf, mask, pred_t, thresh, epsilon, alpha, gamma, denom, grad_loss):
+    dev = check_cuda(logits, labels, conf, mask, pred_t, denom, grad_loss)
+    B, Cc, N = logits.shape
+    with on_device(dev):
+        g = torch.empty_like(logits)
+        gt = torch.empty_like(pred_t)
+        call("geot_poly1_focal_t_backward", B, Cc, N, ptr(logits), ptr(labels), ptr(conf), ptr(mask), ptr(pred_t), float(thresh),
+             float(epsilon), float(alpha), float(gamma), ptr(denom), ptr(grad_loss), ptr(g), ptr(gt), stream_ptr())
+    return g, gt

@@ -170,10 +170,11 @@ three_interpolate = ThreeInterpolate.apply
 
 def three_interpolation(unknown_xyz, known_xyz, know_feat):
     """upsampling.py:92-102: three_nn -> inverse-distance weights -> three_interpolate."""
-    dist, idx = three_nn(unknown_xyz, known_xyz)
-    dist_recip = 1.0 / (dist + 1e-8)
-    norm = torch.sum(dist_recip, dim=2, keepdim=True)
-    weight = dist_recip / norm
+    assert unknown_xyz.is_contiguous()
+    assert known_xyz.is_contiguous()
+    with torch.no_grad():  # dist / idx are non-differentiable in the reference too (upsampling.py:38)
+        dist2, idx = F_.three_nn(unknown_xyz, known_xyz)
+        weight = F_.interp_weights(dist2)  # sqrt, 1/(d + 1e-8), sum, divide: one kernel instead of five
     return three_interpolate(know_feat, idx, weight)
 
 

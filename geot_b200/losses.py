@@ -1,4 +1,4 @@
-"""geot_b200.losses — the criterion that consumes the transition-corrected logits.
+"""geot_b200.losses — the criteria that consume the transition-corrected logits.
 
 `Poly1FocalLoss_U_corr` mirrors openpoints/loss/build.py:799-892 (constructor arguments, `forward(logits, labels,
 logits_pred, thresh=0.95, mask=None)`); the 8-10 elementwise (B,C,N) passes of the reference and their saved
@@ -52,3 +52,46 @@ class Poly1FocalLoss_U_corr(nn.Module):
             raise ValueError("Poly1FocalLoss_U_corr expects (B, C, N) logits")
         return _Poly1.apply(logits, labels, None if mask is not None else logits_pred, mask, thresh,
                             self.epsilon, self.alpha, self.gamma)
+
+
+class _Poly1T(Function):
+    @staticmethod
+    def forward(ctx, logits, labels, conf, mask, pred_t, thresh, epsilon, alpha, gamma):
+        logits = logits.contiguous().float()
+        labels = labels.contiguous().long()
+        conf = conf.contiguous().float()
+        mask = None if mask is None else mask.contiguous().float()
+        pred_t = pred_t.contiguous().float()
+        loss, denom = F_.poly1_focal_t_forward(logits, labels, conf, mask, pred_t, thresh, epsilon, alpha, gamma)
+        ctx.save_for_backward(logits, labels, conf, mask, pred_t, denom)
+        ctx.hp = (float(thresh), float(epsilon), float(alpha), float(gamma))
+        return loss.view(())
+
+    @staticmethod
+    def backward(ctx, grad_loss):
+        logits, labels, conf, mask, pred_t, denom = ctx.saved_tensors
+        thresh, epsilon, alpha, gamma = ctx.hp
+        g, gt = F_.poly1_focal_t_backward(logits, labels, conf, mask, pred_t, thresh, epsilon, alpha, gamma, denom,
+                                          grad_loss.contiguous().float().view(1))
+        return g, None, None, None, gt, None, None, None, None
+
+
+class Poly1FocalLoss_U_T(nn.Module):
+    """openpoints/loss/build.py:564-688 (selected at train.py:594-596).  logits (B,C,N) = the UNcorrected student
+    logits, labels (B,N), logits_pred (B,N) teacher confidence, T (C,C) class-level matrix (accepted and unused, as in the
+    reference's forward), pred_u_t (B,C,N) = the transition-corrected prediction: every point's poly-1 focal terms are
+    scaled by beta = logits_pred / pred_u_t[b, label, n].  Gradients reach `logits` and `pred_u_t` (the reference keeps
+    beta in the graph; logits_pred arrives detached, train.py:595, and gets no gradient here)."""
+
+    def __init__(self, epsilon: float = 1.0, alpha: float = 0.25, gamma: float = 2.0, reduction: str = "mean",
+                 weight=None, pos_weight=None, label_is_onehot: bool = False, **kwargs):
+        super().__init__()
+        if weight is not None or pos_weight is not None or label_is_onehot:
+            raise NotImplementedError("Poly1FocalLoss_U_T: weight / pos_weight / one-hot labels are not used by the "
+                                      "reference configs and are not implemented by the CUDA path")
+        self.epsilon, self.alpha, self.gamma, self.reduction = epsilon, alpha, gamma, reduction
+
+    def forward(self, logits, labels, logits_pred, T, pred_u_t, thresh=0.95, mask=None):
+        if logits.dim() != 3 or pred_u_t.shape != logits.shape:
+            raise ValueError("Poly1FocalLoss_U_T expects (B, C, N) logits and pred_u_t of the same shape")
+        return _Poly1T.apply(logits, labels, logits_pred, mask, pred_u_t, thresh, self.epsilon, self.alpha, self.gamma)

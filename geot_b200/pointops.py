@@ -278,9 +278,12 @@ class Interpolation(Function):
         """xyz (m,3), new_xyz (n,3), input (m,c) -> (n,c): kNN(k) + inverse-distance weights + weighted gather."""
         assert xyz.is_contiguous() and new_xyz.is_contiguous() and input.is_contiguous()
         idx, d2 = F_.knnquery(k, xyz, new_xyz, offset.int(), new_offset.int())
-        dist_recip = 1.0 / (torch.sqrt(d2) + 1e-8)
-        norm = torch.sum(dist_recip, dim=1, keepdim=True)
-        weight = (dist_recip / norm).contiguous()
+        if k == 3:
+            weight = F_.interp_weights(d2)
+        else:
+            dist_recip = 1.0 / (torch.sqrt(d2) + 1e-8)
+            norm = torch.sum(dist_recip, dim=1, keepdim=True)
+            weight = (dist_recip / norm).contiguous()
         ctx.m, ctx.k = input.shape[0], k
         ctx.save_for_backward(idx, weight)
         return F_.interpolation_forward(input, idx, weight)

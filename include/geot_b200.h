@@ -305,6 +305,38 @@ int geot_poly1_focal_backward(int B, int C, int N, const float* logits, const in
                               const float* mask, float thresh, float epsilon, float alpha, float gamma,
                               const float* denom, const float* grad_loss, float* grad_logits, geot_stream_t stream);
 
+/* Poly1FocalLoss_U_T.forward (openpoints/loss/build.py:595-688, selected at examples/segmentation/train.py:594-596) and its
+ * autograd: the same poly-1 focal terms on the UNcorrected student logits, every point scaled by
+ * beta = conf / pred_t[b, label, n] (pred_t (B,C,N) = the transition-corrected prediction, build.py:661-670; conf =
+ * logits_pred (B,N), required even when mask is given - the mask then only replaces the keep weights).
+ * backward writes every element of grad_logits and grad_pred_t (B,C,N; non-zero only in the label row). */
+int geot_poly1_focal_t_forward(int B, int C, int N, const float* logits, const int64_t* labels, const float* conf,
+                               const float* mask, const float* pred_t, float thresh, float epsilon, float alpha,
+                               float gamma, float* loss, float* denom, void* workspace, size_t workspace_bytes,
+                               geot_stream_t stream);
+int geot_poly1_focal_t_backward(int B, int C, int N, const float* logits, const int64_t* labels, const float* conf,
+                                const float* mask, const float* pred_t, float thresh, float epsilon, float alpha,
+                                float gamma, const float* denom, const float* grad_loss, float* grad_logits,
+                                float* grad_pred_t, geot_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Validation upsampling + metrics.
+ * geot_interp_weights: replaces `dist_recip = 1.0 / (dist + 1e-8); norm = sum(dist_recip, 2); weight = dist_recip / norm`
+ * (examples/segmentation/train.py:794-796, openpoints/models/layers/upsampling.py:98-100,
+ * pointnet2/pointnet2_modules.py:619-623) fed with the SQUARED distances geot_three_nn returns: total = B*n targets,
+ * dist2 (total,3) -> weight (total,3) and, when dist != NULL, dist = sqrt(dist2) (what the reference's three_nn returns).
+ * geot_interp_argmax: replaces `three_interpolate(logit, idx, weight).argmax(dim=1)` (train.py:797-798): points (B,C,m),
+ * idx/weight (B,n,3) -> pred (B,n) int64 = first arg-max over the C blended rows; score (B,n) = that maximum, may be NULL.
+ * geot_seg_counts: replaces the per-class logical_and/logical_or sums and the accuracy count of get_seg_metrics
+ * (train.py:817-826): pred, label (n) int64 -> counts (3C+2) int64 = inter[C] | pred_cnt[C] | label_cnt[C] | correct |
+ * vertices with pred or label outside [0,C); union = pred_cnt + label_cnt - inter.  counts is zeroed by the call.
+ * --------------------------------------------------------------------------------------------- */
+int geot_interp_weights(int64_t total, const float* dist2, float* dist, float* weight, geot_stream_t stream);
+int geot_interp_argmax(int B, int C, int m, int n, const float* points, const int* idx, const float* weight,
+                       int64_t* pred, float* score, geot_stream_t stream);
+int geot_seg_counts(int64_t n, int C, const int64_t* pred, const int64_t* label, int64_t* counts,
+                    geot_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -189,3 +189,24 @@ def poly1_focal_u_corr(logits, labels, logits_pred, thresh=0.95, mask=None, epsi
     keep = mask if mask is not None else logits_pred.ge(torch.tensor(thresh, device=logits_pred.device))
     keep = keep.unsqueeze(1).repeat(1, C, 1)
     return torch.sum(poly1 * keep) / (keep.sum() + 0.001)
+
+
+def poly1_focal_u_t(logits, labels, logits_pred, pred_u_t, thresh=0.95, mask=None, epsilon=1.0, alpha=0.25, gamma=2.0):
+    """openpoints/loss/build.py:595-688 (Poly1FocalLoss_U_T.forward; weight = pos_weight = None; T is accepted and unused
+    there).  As poly1_focal_u_corr on the UNcorrected logits with every point scaled by
+    beta = logits_pred / pred_u_t[b, label, n] (:661-670); beta stays in the autograd graph.
+    Pinned against the reference class by tests/golden/make_loss_golden.py (loss_t_golden.npz)."""
+    C = logits.shape[1]
+    p = torch.sigmoid(logits)
+    onehot = F.one_hot(labels.unsqueeze(1), C).transpose(1, -1).squeeze(-1).to(dtype=logits.dtype)
+    ce = F.binary_cross_entropy_with_logits(logits, onehot, reduction="none")
+    pt = onehot * p + (1 - onehot) * (1 - p)
+    FL = ce * ((1 - pt) ** gamma)
+    if alpha >= 0:
+        FL = (alpha * onehot + (1 - alpha) * (1 - onehot)) * FL
+    poly1 = FL + epsilon * torch.pow(1 - pt, gamma + 1)
+    after = torch.gather(pred_u_t, 1, labels.unsqueeze(1)).squeeze(1)  # pred_u_t[b, label[b, n], n]
+    poly1 = poly1 * (logits_pred / after).unsqueeze(1)
+    keep = mask if mask is not None else logits_pred.ge(torch.tensor(thresh, device=logits_pred.device))
+    keep = keep.unsqueeze(1).repeat(1, C, 1)
+    return torch.sum(poly1 * keep) / (keep.sum() + 0.001)

@@ -1,7 +1,8 @@
 #!/usr/bin/env python
 """Generates tests/golden/loss_golden.npz by running the REFERENCE'S OWN `Poly1FocalLoss_U_corr`
 (openpoints/loss/build.py:799-892; the class source is cut from the file and exec'd as is, only the registry
-decorator is dropped) on CPU, in the authoring container (needs /root/reference; never run in tests or on the GPU box).
+decorator is dropped) and tests/golden/loss_t_golden.npz from `Poly1FocalLoss_U_T` (build.py:564-688; `.cuda()` patched
+to the identity) on CPU, in the authoring container (needs /root/reference; never run in tests or on the GPU box).
 
     python tests/golden/make_loss_golden.py
 """
@@ -60,3 +61,36 @@ for tag, (B, C, N) in {"C17": (2, 17, 257), "C33": (3, 33, 130), "C5": (1, 5, 64
     out[f"{tag}_conf"] = conf.numpy()
 np.savez_compressed(os.path.join(HERE, "loss_golden.npz"), **out)
 print("wrote", os.path.join(HERE, "loss_golden.npz"), len(out), "arrays")
+
+# ---------------------------------------------------------------- Poly1FocalLoss_U_T (build.py:564-688)
+torch.Tensor.cuda = lambda self, *a, **k: self
+exec(compile(class_source(os.path.join(REF, "openpoints/loss/build.py"), "Poly1FocalLoss_U_T"), "<reference build.py>", "exec"), ns)
+LossT = ns["Poly1FocalLoss_U_T"]
+out = {}
+g = torch.Generator().manual_seed(2025)
+for tag, (B, C, N) in {"C17": (2, 17, 257), "C33": (3, 33, 130), "C5": (1, 5, 64)}.items():
+    logits = (torch.randn(B, C, N, generator=g) * 3).requires_grad_(True)
+    labels = torch.randint(0, C, (B, N), generator=g)
+    conf = torch.rand(B, N, generator=g)
+    conf[0, :5] = 0.95
+    pred_t = torch.softmax(torch.randn(B, C, N, generator=g) * 2, dim=1).requires_grad_(True)  # corrected prediction
+    T = torch.eye(C)
+    for variant, hp, kw in [("thr", {}, dict(thresh=0.95)), ("low", {}, dict(thresh=0.3)),
+                            ("mask", {}, dict(thresh=0.95, mask=(torch.rand(B, N, generator=g) > 0.5))),
+                            ("hp", dict(epsilon=0.5, alpha=-1.0, gamma=1.5), dict(thresh=0.5))]:
+        crit = LossT(**hp)
+        logits.grad = None; pred_t.grad = None
+        loss = crit(logits, labels, conf, T, pred_t, **kw)
+        loss.backward()
+        out[f"{tag}_{variant}_loss"] = loss.detach().numpy()
+        out[f"{tag}_{variant}_grad"] = logits.grad.detach().numpy().copy()
+        out[f"{tag}_{variant}_grad_t"] = pred_t.grad.detach().numpy().copy()
+        if "mask" in kw:
+            out[f"{tag}_{variant}_mask"] = kw["mask"].numpy()
+        out[f"{tag}_{variant}_thresh"] = np.float32(kw["thresh"])
+    out[f"{tag}_logits"] = logits.detach().numpy()
+    out[f"{tag}_labels"] = labels.numpy()
+    out[f"{tag}_conf"] = conf.numpy()
+    out[f"{tag}_pred_t"] = pred_t.detach().numpy()
+np.savez_compressed(os.path.join(HERE, "loss_t_golden.npz"), **out)
+print("wrote", os.path.join(HERE, "loss_t_golden.npz"), len(out), "arrays")

@@ -206,5 +206,44 @@ for (nq, mk) in [(16000, 8192), (8192, 512), (4096, 512)]:  # the feature-propag
            (lambda: R.ref_three_nn(b, nq, mk, p(unknown), p(known), p(d2_r), p(i3_r))) if R else None,
            b * (12 * nq + 12 * mk + 24 * nq), lambda: (i3 == i3_r).all())
 
+# ---------------------------------------------------------------- validation: 16000-point scores -> full mesh labels -> metrics
+from geot_b200 import validation as VAL
+for (Ccls, n_whole) in [(17, 100000), (33, 120000)]:  # train.py:781-832; a Teeth3DS jaw mesh has ~1e5 vertices
+    pts = xyz6[:1].contiguous()                                   # (1, 16000, 3) sampled cloud
+    mesh = (pts[:, torch.randint(0, n_per, (n_whole,), device=dev)] + 0.002 * torch.randn(1, n_whole, 3, device=dev)).contiguous()
+    prob = torch.softmax(torch.randn(1, Ccls, n_per, device=dev) * 3, dim=1)
+    d2_r = torch.empty((1, n_whole, 3), device=dev); i3_r = torch.empty((1, n_whole, 3), dtype=i32, device=dev)
+    up_r = torch.empty((1, Ccls, n_whole), device=dev)
+    res = {}
+
+    def ours_up():
+        res["o"] = VAL.upsample_labels(prob, pts, mesh)
+
+    def ref_up():  # the reference's kernels + its torch glue (train.py:793-798)
+        R.ref_three_nn(1, n_whole, n_per, p(mesh), p(pts), p(d2_r), p(i3_r))
+        dist = torch.sqrt(d2_r)
+        dist_recip = 1.0 / (dist + 1e-8)
+        weight = (dist_recip / torch.sum(dist_recip, dim=2, keepdim=True)).contiguous()
+        R.ref_three_interpolate(1, Ccls, n_per, n_whole, p(prob), p(i3_r), p(weight), p(up_r))
+        res["r"] = up_r.argmax(dim=1)
+
+    report("get_pred_whole (one cloud)", f"C={Ccls} m={n_per} n={n_whole}", ours_up, ref_up if R else None,
+           12 * n_per + 12 * n_whole + 4 * Ccls * n_per + 8 * n_whole, lambda: float((res["o"] == res["r"]).float().mean()) > 0.9999)
+    lab = torch.where(torch.rand(n_whole, device=dev) < 0.8, res["o"].view(-1), torch.randint(0, Ccls, (n_whole,), device=dev))
+
+    def ref_metrics():  # train.py:808-826 verbatim in structure: CPU tensors, Python loop over the classes
+        pw, lw = res["o"].squeeze().cpu(), lab.cpu()
+        iou = []
+        for j in torch.unique(lw).cpu().numpy():
+            if j == 0: continue
+            iou.append((torch.logical_and(pw == j, lw == j).sum() / torch.logical_or(pw == j, lw == j).sum()).float())
+        res["rm"] = (float((pw == lw).sum() / lw.view(-1).shape[0]), np.array(iou).mean())
+
+    def ours_metrics():
+        res["om"] = VAL.seg_metrics_one(res["o"], lab, Ccls)
+
+    report("get_seg_metrics (one cloud)", f"C={Ccls} n={n_whole} (incl. the device->host copy)", ours_metrics, ref_metrics, 16 * n_whole,
+           lambda: float(res["om"][0]) == res["rm"][0] and np.float32(res["om"][1]) == np.float32(res["rm"][1]))
+
 if args.out:
     json.dump({"hbm_peak_gbs": PEAK, "rows": rows}, open(args.out, "w"), indent=1)

@@ -253,3 +253,60 @@ def test_poly1_focal_loss_large_vs_oracle(cuda):
         logits.grad = None
         l2 = crit(logits, labels, conf, thresh=thresh); l2.backward()
         assert torch.equal(l2, loss) and torch.equal(logits.grad, g1)
+
+
+# ---------------------------------------------------------------------------------------------
+# Poly1FocalLoss_U_T (the beta-scaled variant, train.py:594-596)
+# ---------------------------------------------------------------------------------------------
+from tests.test_transition_oracle_cpu import loss_t_case  # noqa: E402
+
+
+@pytest.mark.parametrize("tag", ["C17", "C33", "C5"])
+@pytest.mark.parametrize("variant,hp", LOSS_VARIANTS)
+def test_golden_poly1_focal_u_t(cuda, tag, variant, hp):
+    from geot_b200 import losses
+    logits, labels, conf, pred_t, mask, thresh, exp_loss, exp_grad, exp_grad_t = loss_t_case(tag, variant)
+    x = logits.cuda().requires_grad_(True)
+    pt = pred_t.cuda().requires_grad_(True)
+    crit = losses.Poly1FocalLoss_U_T(**hp)
+    loss = crit(x, labels.cuda(), conf.cuda(), torch.eye(x.shape[1], device="cuda"), pt, thresh=thresh,
+                mask=None if mask is None else mask.cuda())
+    close(loss, exp_loss, rtol=1e-5, atol=1e-8)   # north_star tolerance: 1e-5 relative
+    loss.backward()
+    assert rel(x.grad, exp_grad) < 1e-5
+    assert rel(pt.grad, exp_grad_t) < 1e-5
+    assert x.grad.shape == x.shape and pt.grad.shape == pt.shape
+
+
+def test_poly1_focal_u_t_large_vs_oracle(cuda):
+    """cfg4 size (6 x 16000 points, C=33) against the oracle's torch expression on the GPU; with pred_u_t = conf in the
+    label row beta is exactly 1 and the loss equals Poly1FocalLoss_U_corr's on the same logits (a size-independent property)."""
+    from geot_b200 import losses
+    g = torch.Generator(device="cuda").manual_seed(9)
+    B, C, N = 6, 33, 16000
+    logits = (torch.randn(B, C, N, device="cuda", generator=g) * 4).requires_grad_(True)
+    labels = torch.randint(0, C, (B, N), device="cuda", generator=g)
+    conf = torch.rand(B, N, device="cuda", generator=g) * 0.9 + 0.1
+    pred_t = torch.softmax(torch.randn(B, C, N, device="cuda", generator=g) * 2, dim=1).requires_grad_(True)
+    crit = losses.Poly1FocalLoss_U_T()
+    T = torch.eye(C, device="cuda")
+    for thresh in (0.95, 0.0, 2.0):
+        logits.grad = None; pred_t.grad = None
+        loss = crit(logits, labels, conf, T, pred_t, thresh=thresh)
+        loss.backward()
+        g1, g1t = logits.grad.clone(), pred_t.grad.clone()
+        logits.grad = None; pred_t.grad = None
+        ref = R.poly1_focal_u_t(logits, labels, conf, pred_t, thresh=thresh)
+        ref.backward()
+        close(loss, ref, rtol=1e-5, atol=1e-8)
+        if thresh < 2.0:
+            assert rel(g1, logits.grad) < 1e-5 and rel(g1t, pred_t.grad) < 1e-5
+        else:
+            assert float(g1.abs().max()) == 0.0 and float(g1t.abs().max()) == 0.0 and float(loss) == 0.0
+        logits.grad = None; pred_t.grad = None
+        l2 = crit(logits, labels, conf, T, pred_t, thresh=thresh); l2.backward()
+        assert torch.equal(l2, loss) and torch.equal(logits.grad, g1) and torch.equal(pred_t.grad, g1t)
+    ones = torch.zeros(B, C, N, device="cuda").scatter_(1, labels.unsqueeze(1), conf.unsqueeze(1)).contiguous()
+    l_beta1 = crit(logits.detach(), labels, conf, T, ones + (ones == 0).float(), thresh=0.5)
+    l_corr = losses.Poly1FocalLoss_U_corr()(logits.detach(), labels, conf, thresh=0.5)
+    assert torch.equal(l_beta1, l_corr)

@@ -99,3 +99,28 @@ def test_golden_poly1_focal_u_corr(tag, variant, hp):
     torch.testing.assert_close(loss, exp_loss, rtol=1e-6, atol=1e-9)
     loss.backward()
     torch.testing.assert_close(x.grad, exp_grad, rtol=1e-5, atol=1e-10)
+
+
+LTG = np.load(os.path.join(os.path.dirname(__file__), "golden", "loss_t_golden.npz"))
+
+
+def loss_t_case(tag, variant):
+    """One golden case of Poly1FocalLoss_U_T (tests/golden/make_loss_golden.py, second half)."""
+    f = lambda k: torch.from_numpy(LTG[k])
+    mask = f(f"{tag}_{variant}_mask") if f"{tag}_{variant}_mask" in LTG else None
+    return (f(f"{tag}_logits"), f(f"{tag}_labels"), f(f"{tag}_conf"), f(f"{tag}_pred_t"), mask, float(LTG[f"{tag}_{variant}_thresh"]),
+            f(f"{tag}_{variant}_loss"), f(f"{tag}_{variant}_grad"), f(f"{tag}_{variant}_grad_t"))
+
+
+@pytest.mark.parametrize("tag", ["C17", "C33", "C5"])
+@pytest.mark.parametrize("variant,hp", LOSS_VARIANTS)
+def test_golden_poly1_focal_u_t(tag, variant, hp):
+    """oracle restatement of Poly1FocalLoss_U_T against the reference class's own outputs (loss and both gradients)."""
+    logits, labels, conf, pred_t, mask, thresh, exp_loss, exp_grad, exp_grad_t = loss_t_case(tag, variant)
+    x = logits.clone().requires_grad_(True)
+    pt = pred_t.clone().requires_grad_(True)
+    loss = R.poly1_focal_u_t(x, labels, conf, pt, thresh=thresh, mask=mask, **hp)
+    torch.testing.assert_close(loss, exp_loss, rtol=1e-6, atol=1e-9)
+    loss.backward()
+    torch.testing.assert_close(x.grad, exp_grad, rtol=1e-5, atol=1e-10)
+    torch.testing.assert_close(pt.grad, exp_grad_t, rtol=1e-5, atol=1e-10)
