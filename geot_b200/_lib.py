@@ -76,6 +76,8 @@ _SIGNATURES = {
     "geot_class_pick": [_i, _i, _i, _vp, _vp, _vp, _vp, _vp, _sz, _vp],
     "geot_class_t_step": [_i, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp],
     "geot_mean_feature_update": [_i64, _i, _vp, _vp, _vp, _vp, _vp, _sz, _vp],
+    "geot_graph_feature": [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp],
+    "geot_graph_feature_grad_q": [_i, _i, _i, _i, _vp, _vp, _vp],
     "geot_interp_weights": [_i64, _vp, _vp, _vp, _vp],
     "geot_interp_argmax": [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp],
     "geot_seg_counts": [_i64, _i, _vp, _vp, _vp, _vp],

@@ -568,3 +568,24 @@ def poly1_focal_t_backward(logits, labels, conf, mask, pred_t, thresh, epsilon, 
         call("geot_poly1_focal_t_backward", B, Cc, N, ptr(logits), ptr(labels), ptr(conf), ptr(mask), ptr(pred_t), float(thresh),
              float(epsilon), float(alpha), float(gamma), ptr(denom), ptr(grad_loss), ptr(g), ptr(gt), stream_ptr())
     return g, gt
+
+
+def graph_feature(x_k, x_q, idx):
+    """x_k (B,C,Nk), x_q (B,C,Nq), idx (B,Nq,k) int32 -> (B,2C,Nq,k) = cat(x_k[.., idx] - x_q, x_q)."""
+    dev = check_cuda(x_k, x_q, idx)
+    B, Cc, Nk = x_k.shape
+    Nq, k = idx.shape[1], idx.shape[2]
+    with on_device(dev):
+        out = torch.empty((B, 2 * Cc, Nq, k), dtype=_f32, device=dev)
+        call("geot_graph_feature", B, Cc, Nk, Nq, k, ptr(x_k), ptr(x_q), ptr(idx), ptr(out), stream_ptr())
+    return out
+
+
+def graph_feature_grad_q(grad_out, Cc):
+    """grad_out (B,2C,Nq,k) -> grad_x_q (B,C,Nq)."""
+    dev = check_cuda(grad_out)
+    B, _, Nq, k = grad_out.shape
+    with on_device(dev):
+        g = torch.empty((B, Cc, Nq), dtype=_f32, device=dev)
+        call("geot_graph_feature_grad_q", B, Cc, Nq, k, ptr(grad_out), ptr(g), stream_ptr())
+    return g

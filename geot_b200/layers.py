@@ -327,6 +327,54 @@ class KNNGroup(nn.Module):
         return grouped_xyz, None
 
 
+# --------------------------------------------------------------------------------------------------
+# DGCNN edge features (transformer.py:343-364)
+# --------------------------------------------------------------------------------------------------
+class GraphFeature(Function):
+    @staticmethod
+    @torch.amp.custom_fwd(device_type="cuda", cast_inputs=torch.float32)
+    def forward(ctx, x_k: torch.Tensor, x_q: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+        """x_k (B,C,Nk), x_q (B,C,Nq), idx (B,Nq,k) int32 -> (B,2C,Nq,k) = cat(x_k[.., idx] - x_q, x_q)."""
+        x_k, x_q = x_k.contiguous(), x_q.contiguous()
+        assert idx.is_contiguous() and idx.dtype == torch.int32
+        ctx.for_backwards = (idx, x_k.shape[1], x_k.shape[2])
+        return F_.graph_feature(x_k, x_q, idx)
+
+    @staticmethod
+    def backward(ctx, grad_out: torch.Tensor):
+        idx, C, Nk = ctx.for_backwards
+        grad_out = grad_out.contiguous()
+        g_k = g_q = None
+        if ctx.needs_input_grad[0]:  # deterministic scatter over the same plan machinery as grouping_operation
+            plan = F_.grouping_plan(idx, idx.shape[0], Nk)
+            g_k = F_.group_points_grad(grad_out[:, :C].contiguous(), plan, Nk)
+        if ctx.needs_input_grad[1]:
+            g_q = F_.graph_feature_grad_q(grad_out, C)
+        return g_k, g_q, None
+
+
+def knn_neighbours(k, coor_q, coor_k):
+    """coor_q (B,3,Nq), coor_k (B,3,Nk) -> idx (B,Nq,k) int32, cloud-local, ascending distance (the neighbours
+    knn_cuda.KNN(k, transpose_mode=False)(coor_k, coor_q) returns, in the layout the kNN kernel writes)."""
+    with torch.no_grad():
+        ref = coor_k.transpose(1, 2).contiguous().float()
+        query = coor_q.transpose(1, 2).contiguous().float()
+        B, Nk, _ = ref.shape
+        Nq = query.shape[1]
+        idx, _ = F_.knnquery(k, ref.view(-1, 3), query.view(-1, 3), None, None, n_per=Nk, m_per=Nq)
+        base = (torch.arange(B, device=idx.device, dtype=torch.int32) * Nk).view(B, 1, 1)
+        return (idx.view(B, Nq, k) - base).contiguous()
+
+
+def get_graph_feature(coor_q, x_q, coor_k, x_k, k=4, idx=None):
+    """DGCNN_Propagation.get_graph_feature (transformer.py:343-364) as a function: coor (B,3,N), x (B,C,N) ->
+    (B,2C,Nq,k).  kNN, gather, `feature - x_q` and the concat are two kernels; no (B,Nk,C) transpose, no
+    (B,C,Nq,k) intermediates.  `idx` (B,Nq,k) int32 may be passed when several calls share the neighbours."""
+    if idx is None:
+        idx = knn_neighbours(k, coor_q, coor_k)
+    return GraphFeature.apply(x_k, x_q, idx)
+
+
 def create_grouper(group_args):
     """group.py:338-352."""
     group_args_copy = copy.deepcopy(group_args)

@@ -305,6 +305,19 @@ int geot_poly1_focal_backward(int B, int C, int N, const float* logits, const in
                               const float* mask, float thresh, float epsilon, float alpha, float gamma,
                               const float* denom, const float* grad_loss, float* grad_logits, geot_stream_t stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * DGCNN edge features.  replaces the tensor algebra of DGCNN_Propagation.get_graph_feature after
+ * its kNN (openpoints/models/backbone/transformer.py:355-363: transpose, row gather, permute, expand, subtract, cat).
+ * x_k (B,C,Nk) key features, x_q (B,C,Nq) query features, idx (B,Nq,k) int32 neighbour indices into the Nk axis (cloud-
+ * local; the layout the kNN kernel writes) -> out (B,2C,Nq,k): out[:, :C] = x_k[.., idx] - x_q, out[:, C:] = x_q.
+ * geot_graph_feature_grad_q: grad_out (B,2C,Nq,k) -> grad_x_q (B,C,Nq) = sum_j (grad_out[:, C:] - grad_out[:, :C]);
+ * grad_x_k is geot_group_points_grad of grad_out[:, :C] over the same idx (deterministic scatter plan).
+ * --------------------------------------------------------------------------------------------- */
+int geot_graph_feature(int B, int C, int Nk, int Nq, int k, const float* x_k, const float* x_q, const int* idx,
+                       float* out, geot_stream_t stream);
+int geot_graph_feature_grad_q(int B, int C, int Nq, int k, const float* grad_out, float* grad_x_q,
+                              geot_stream_t stream);
+
 /* Poly1FocalLoss_U_T.forward (openpoints/loss/build.py:595-688, selected at examples/segmentation/train.py:594-596) and its
  * autograd: the same poly-1 focal terms on the UNcorrected student logits, every point scaled by
  * beta = conf / pred_t[b, label, n] (pred_t (B,C,N) = the transition-corrected prediction, build.py:661-670; conf =
