@@ -206,6 +206,22 @@ for (nq, mk) in [(16000, 8192), (8192, 512), (4096, 512)]:  # the feature-propag
            (lambda: R.ref_three_nn(b, nq, mk, p(unknown), p(known), p(d2_r), p(i3_r))) if R else None,
            b * (12 * nq + 12 * mk + 24 * nq), lambda: (i3 == i3_r).all())
 
+# ---------------------------------------------------------------- DGCNN edge features of the decoder (transformer.py:343-364)
+from geot_b200 import layers as L
+from oracle import graph_ref as GR
+for (Cg, Nk, Nq) in [(384, 512, 4096), (384, 4096, 8192)]:
+    x_k = torch.randn(b, Cg, Nk, device=dev); x_q = torch.randn(b, Cg, Nq, device=dev)
+    ck = xyz6[:, :Nk].transpose(1, 2).contiguous(); cq = xyz6[:, :Nq].transpose(1, 2).contiguous()
+    idx_g = L.knn_neighbours(4, cq, ck)
+    idx_ref = idx_g.long().transpose(1, 2).contiguous()
+    res = {}
+    def ours_gf(): res["o"] = F.graph_feature(x_k, x_q, idx_g)
+    def ref_gf(): res["r"] = GR.get_graph_feature(x_q, x_k, idx_ref)   # the reference's torch expression, same GPU
+    report("get_graph_feature fwd", f"B={b} C={Cg} Nk={Nk} Nq={Nq} k=4 (idx given)", ours_gf, ref_gf,
+           b * (4 * Cg * Nk + 4 * Cg * Nq + 32 * Cg * Nq + 16 * Nq), lambda: torch.equal(res["o"], res["r"]))
+    del res, x_k, x_q
+    torch.cuda.empty_cache()
+
 # ---------------------------------------------------------------- validation: 16000-point scores -> full mesh labels -> metrics
 from geot_b200 import validation as VAL
 for (Ccls, n_whole) in [(17, 100000), (33, 120000)]:  # train.py:781-832; a Teeth3DS jaw mesh has ~1e5 vertices
