@@ -603,8 +603,13 @@ seg_reduce_wrows_kernel(int C, int n, int m, const float* __restrict__ g, const 
   const int* __restrict__ pm = perm + (int64_t)b * E;
   const float* __restrict__ ws = wsorted + (int64_t)b * E;
   const int sub = t % LPT;
-  for (int k = t / LPT; k < m; k += 1024 / LPT) {
-    const int s0 = rp_s[k], e0 = rp_s[k + 1];
+  // the loop bound is WARP-uniform (kb = first target of the warp): the xor tree below is a full-mask shuffle, so a
+  // warp whose last targets fall beyond m (m not a multiple of 32 / LPT) must still run it with all 32 lanes -
+  // lanes that left the loop early would wait at the __syncthreads below and the shuffle would never complete
+  for (int kb = (t >> 5) * (32 / LPT); kb < m; kb += 1024 / LPT) {
+    const int k = kb + (t & 31) / LPT;
+    const bool valid = k < m;
+    const int s0 = valid ? rp_s[k] : 0, e0 = valid ? rp_s[k + 1] : 0;
     float acc[R];
 #pragma unroll
     for (int r = 0; r < R; r++) acc[r] = 0.f;
@@ -634,7 +639,7 @@ seg_reduce_wrows_kernel(int C, int n, int m, const float* __restrict__ g, const 
 #pragma unroll
       for (int o = LPT / 2; o > 0; o >>= 1) acc[r] = __fadd_rn(acc[r], __shfl_xor_sync(0xffffffffu, acc[r], o));
     }
-    if (sub == 0) {
+    if (sub == 0 && valid) {
 #pragma unroll
       for (int r = 0; r < R; r++) outs[(size_t)r * m + k] = acc[r];
     }
