@@ -41,15 +41,10 @@ def get_pred_whole(logits, points, points_whole, center, scale):
     return preds_whole
 
 
-@torch.no_grad()
-def seg_metrics_one(pred, label, num_classes=None):
-    """One cloud: pred, label (n) integer tensors on the GPU -> (acc, miou, mdsc) exactly as train.py:808-826 computes
-    them (classes = labels present in `label` except 0; IoU and DSC in fp32; numpy fp32 means; nan when no class)."""
-    pred = pred.reshape(-1).long().contiguous()
-    label = label.reshape(-1).long().contiguous()
-    if num_classes is None:
-        num_classes = int(torch.maximum(pred.max(), label.max()).item()) + 1 if pred.numel() else 1
-    cnt = F_.seg_counts(pred, label, num_classes).cpu()
+def metrics_from_counts(cnt, num_classes, n):
+    """Host half of get_seg_metrics: cnt = the (3C+2) int64 CPU tensor geot_seg_counts fills, n = number of vertices ->
+    (acc, miou, mdsc) exactly as train.py:808-826 computes them (classes = labels present in the ground truth except 0;
+    IoU and DSC in fp32; numpy fp32 means; nan when no class qualifies)."""
     C = num_classes
     if int(cnt[3 * C + 1]) != 0:
         raise ValueError(f"get_seg_metrics: {int(cnt[3 * C + 1])} vertices carry a class id outside [0, {C})")
@@ -62,11 +57,23 @@ def seg_metrics_one(pred, label, num_classes=None):
         jcls_or = pcnt[jcls] + lcnt[jcls] - inter[jcls]
         iou.append((jcls_and / jcls_or).float())
         dsc.append((2 * iou[-1] / (1 + iou[-1])))
-    acc = correct / label.numel()
+    acc = correct / n
     with np.errstate(all="ignore"):
         miou = np.array(iou, dtype=np.float32).mean() if iou else np.float32("nan")
         mdsc = np.array(dsc, dtype=np.float32).mean() if dsc else np.float32("nan")
     return acc, miou, mdsc
+
+
+@torch.no_grad()
+def seg_metrics_one(pred, label, num_classes=None):
+    """One cloud: pred, label (n) integer tensors on the GPU -> (acc, miou, mdsc); one histogram kernel, one copy of
+    3C+2 integers to the host, then metrics_from_counts."""
+    pred = pred.reshape(-1).long().contiguous()
+    label = label.reshape(-1).long().contiguous()
+    if num_classes is None:
+        num_classes = int(torch.maximum(pred.max(), label.max()).item()) + 1 if pred.numel() else 1
+    cnt = F_.seg_counts(pred, label, num_classes).cpu()
+    return metrics_from_counts(cnt, num_classes, label.numel())
 
 
 @torch.no_grad()

@@ -41,3 +41,27 @@ def test_metrics_edge_cases():
     # a class the prediction never produces counts with IoU 0
     acc, miou, mdsc = V.seg_metrics_one(torch.tensor([1, 1, 0, 0]), torch.tensor([1, 1, 2, 2]))
     assert float(miou) == pytest.approx(0.5) and float(mdsc) == pytest.approx(0.5)
+
+
+def _counts(pred, label, C):
+    """what geot_seg_counts returns, computed with numpy (host logic test: no GPU here)."""
+    p, l = pred.numpy().reshape(-1), label.numpy().reshape(-1)
+    inter = np.bincount(p[p == l], minlength=C)
+    return torch.from_numpy(np.concatenate([inter, np.bincount(p, minlength=C), np.bincount(l, minlength=C),
+                                            [int((p == l).sum()), 0]]).astype(np.int64))
+
+
+@pytest.mark.parametrize("tag", list(CASES))
+def test_product_host_metrics_from_counts(tag):
+    """geot_b200.validation.metrics_from_counts (the host half of the product's get_seg_metrics) on the fixture."""
+    from geot_b200 import validation as VAL
+    C = G[f"{tag}_logits"].shape[1]
+    for b in range(CASES[tag]):
+        pred, label = t(f"{tag}_pred{b}"), t(f"{tag}_label{b}")
+        acc, miou, mdsc = VAL.metrics_from_counts(_counts(pred, label, C), C, label.numel())
+        assert np.float32(float(acc)) == G[f"{tag}_acc"][b]
+        assert np.float32(miou) == G[f"{tag}_miou"][b] and np.float32(mdsc) == G[f"{tag}_mdsc"][b]
+    bad = _counts(t(f"{tag}_pred0"), t(f"{tag}_label0"), C)
+    bad[3 * C + 1] = 4
+    with pytest.raises(ValueError):
+        VAL.metrics_from_counts(bad, C, 10)
