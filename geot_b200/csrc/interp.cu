@@ -126,8 +126,12 @@ __device__ __forceinline__ void top3_push_lex(Top3& t, float d, int k) {
 __device__ __forceinline__ int ng_cell(float p, float lo, float inv) { return __float2int_rd((p - lo) * inv); }
 
 __global__ void __launch_bounds__(kNgThreads, 1)
-three_nn_grid_kernel(int n, int m, const float* __restrict__ unknown, const float* __restrict__ known,
-                     float* __restrict__ dist2, int* __restrict__ idx) {
+three_nn_grid_kernel(int n, int m, int m_total, int base, int accumulate, const float* __restrict__ unknown,
+                     const float* __restrict__ known, float* __restrict__ dist2, int* __restrict__ idx) {
+  // m = points of THIS part of the known cloud (known[b, base : base + m]); m_total = the cloud's stride.  Known clouds
+  // longer than kNgMaxM are searched part by part: a later part starts from the top-3 the earlier parts left in
+  // dist2 / idx (accumulate != 0).  Selection is lexicographic in (distance, GLOBAL index), so the top-3 of the union
+  // does not depend on how the cloud was cut, and the ring termination bound stays valid with a pre-filled top-3.
   extern __shared__ __align__(16) unsigned char ng_smem[];
   __shared__ float s_red[6][32];
   __shared__ int s_scan[32];
@@ -137,7 +141,7 @@ three_nn_grid_kernel(int n, int m, const float* __restrict__ unknown, const floa
   unsigned* runs = reinterpret_cast<unsigned*>(cells + kNgMaxCells + 1);  // 9 x kNgThreads: {start:16 | length:16}
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int b = blockIdx.y;
-  const float* __restrict__ kn = known + (int64_t)b * m * 3;
+  const float* __restrict__ kn = known + ((int64_t)b * m_total + base) * 3;
   const float kInf = __int_as_float(0x7f800000);
 
   // ---- bin the known cloud ----
@@ -247,14 +251,20 @@ three_nn_grid_kernel(int n, int m, const float* __restrict__ unknown, const floa
   __syncthreads();
   for (int k = t; k < m; k += kNgThreads) {
     const float x = __ldg(kn + (int64_t)k * 3), y = __ldg(kn + (int64_t)k * 3 + 1), z = __ldg(kn + (int64_t)k * 3 + 2);
-    sorted[atomicAdd(&cells[flat ? 0 : code_of(x, y, z)], 1)] = make_float4(x, y, z, __int_as_float(k));
+    sorted[atomicAdd(&cells[flat ? 0 : code_of(x, y, z)], 1)] = make_float4(x, y, z, __int_as_float(k + base));
   }
   __syncthreads();
   // ---- one unknown point per thread ----
   for (int i = blockIdx.x * kNgThreads + t; i < n; i += gridDim.x * kNgThreads) {
   const float* up = unknown + ((int64_t)b * n + i) * 3;
   const float qx = up[0], qy = up[1], qz = up[2];
-  Top3 best = Top3{kInf, kInf, kInf, 0, 0, 0};
+  Top3 first = Top3{kInf, kInf, kInf, 0, 0, 0};
+  if (accumulate) {
+    const float* pd = dist2 + ((int64_t)b * n + i) * 3;
+    const int* pi = idx + ((int64_t)b * n + i) * 3;
+    first = Top3{pd[0], pd[1], pd[2], pi[0], pi[1], pi[2]};
+  }
+  Top3 best = first;
   auto visit = [&](int p) {
     const float4 v = sorted[p];
     top3_push_lex(best, dist2_ref(qx, qy, qz, v.x, v.y, v.z), __float_as_int(v.w));
@@ -325,7 +335,7 @@ three_nn_grid_kernel(int n, int m, const float* __restrict__ unknown, const floa
     }
   }
   if (!done) {  // far from the known cloud / degenerate grid: every known point
-    best = Top3{kInf, kInf, kInf, 0, 0, 0};
+    best = first;
     for (int p = 0; p < m; p++) visit(p);
   }
   float* od = dist2 + ((int64_t)b * n + i) * 3;
@@ -433,8 +443,11 @@ GEOT_API int geot_three_nn(int B, int n, int m, const float* unknown, const floa
   GEOT_REQUIRE(B <= 65535, "three_nn: B exceeds grid limits");
   // the grid costs a fixed ~50 us (every CTA bins the known cloud first); below ~5e7 distance evaluations the
   // brute-force kernel finishes sooner (measured: B=6, n=8192, m=512 brute 45 us vs grid 80 us; B=16, n=4096, m=1024 grid 43 vs 78)
-  if (m >= 64 && m <= kNgMaxM && ((double)B * n * m >= 5e7 || staged_kernels_forced()) && !direct_kernels_forced()) {
-    const size_t smem = (size_t)m * 16 + (size_t)(kNgMaxCells + 1) * 4 + (size_t)9 * kNgThreads * 4;
+  // known clouds longer than the kernel's shared-memory capacity (validation: 16000 sampled points against ~1e5
+  // mesh vertices, train.py:793) are cut into P equal parts by index and searched part by part
+  const int P = (m + kNgMaxM - 1) / kNgMaxM;
+  if (m >= 64 && P <= 8 && ((double)B * n * m >= 5e7 || staged_kernels_forced()) && !direct_kernels_forced()) {
+    const int part = (m + P - 1) / P;
     static bool configured = false;
     if (!configured) {
       cudaError_t e = cudaFuncSetAttribute(three_nn_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kNgMaxM * 16 + (kNgMaxCells + 1) * 4 + 9 * kNgThreads * 4);
@@ -452,9 +465,16 @@ GEOT_API int geot_three_nn(int B, int n, int m, const float* unknown, const floa
       if (cost < best_cost) { best_cost = cost; cb = k; }
     }
     dim3 gg(cb, B);
-    three_nn_grid_kernel<<<gg, kNgThreads, smem, as_stream(stream)>>>(n, m, unknown, known, dist2, idx);
-    count_launch(1);
-    return check_launch("three_nn_grid_kernel");
+    for (int p = 0; p < P; p++) {
+      const int base = p * part, mp = std::min(part, m - base);
+      if (mp <= 0) break;
+      const size_t smem = (size_t)mp * 16 + (size_t)(kNgMaxCells + 1) * 4 + (size_t)9 * kNgThreads * 4;
+      three_nn_grid_kernel<<<gg, kNgThreads, smem, as_stream(stream)>>>(n, mp, m, base, p > 0, unknown, known, dist2, idx);
+      count_launch(1);
+      const int rc = check_launch("three_nn_grid_kernel");
+      if (rc) return rc;
+    }
+    return GEOT_OK;
   }
   dim3 grid((n + kNnThreads * kNnPerThread - 1) / (kNnThreads * kNnPerThread), B);
   three_nn_kernel<<<grid, kNnThreads, 0, as_stream(stream)>>>(n, m, unknown, known, dist2, idx);

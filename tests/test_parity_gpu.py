@@ -303,7 +303,8 @@ def test_gather_points_fwd_bwd(cuda, oracle, B, C, N, M):
 
 
 @pytest.mark.parametrize("kind,B,n,m", [("tooth", 2, 4096, 512), ("tooth", 2, 16000, 8192), ("quant", 2, 3000, 700),
-                                         ("dup", 1, 1000, 300), ("tooth", 2, 100, 2), ("tooth", 1, 513, 1)])
+                                         ("dup", 1, 1000, 300), ("tooth", 2, 100, 2), ("tooth", 1, 513, 1),
+                                         ("tooth", 1, 30000, 16000), ("quant", 1, 21000, 20000)])  # known cloud searched in 2 / 3 parts
 def test_three_nn(cuda, oracle, kind, B, n, m):
     unknown = clouds(kind, B, n)
     known = unknown[:, np.random.default_rng(8).choice(n, m, replace=False)].copy() if m <= n else clouds(kind, B, m, 3)
@@ -314,7 +315,8 @@ def test_three_nn(cuda, oracle, kind, B, n, m):
 
 
 @pytest.mark.parametrize("kind", ["tooth", "uniform", "dup", "quant", "plane", "same"])
-@pytest.mark.parametrize("B,n,m", [(3, 16384, 1024), (2, 5000, 64), (2, 3001, 8192), (1, 2048, 4097), (2, 700, 333)])
+@pytest.mark.parametrize("B,n,m", [(3, 16384, 1024), (2, 5000, 64), (2, 3001, 8192), (1, 2048, 4097), (2, 700, 333),
+                                   (2, 4000, 16000), (1, 2500, 27649)])  # 2 and 4 parts: ties across parts resolved by GLOBAL index
 def test_three_nn_grid_vs_scan(cuda, kind, B, n, m):
     """Grid search (64 <= m <= 8192) against the brute-force kernel of the same library (exact on its own, see
     test_three_nn): duplicates and quantised coordinates (ties resolved by index), unknown points far outside the
