@@ -26,6 +26,7 @@ void count_launch(int n);
 constexpr int kGroupCCH = 16;  // channels per thread in the forward gather
 static bool g_group_force_direct = false;  // testing / A-B timing: geot_group_points_config(1)
 static bool g_force_staged = false;        // geot_group_points_config(2): ignore the work-size heuristics
+static bool g_rows4_off = false;           // geot_group_points_config(3): three_interpolate without the channel-interleaved kernel (A/B)
 
 // VEC = 4: E % 4 == 0 and 16-byte aligned idx/out.  grid (ceil(E/VEC/256), ceil(C/CCH), B).
 template <int VEC>
@@ -714,6 +715,7 @@ static int three_interpolate_grad_rows(int B, int C, int n, int m, const float* 
 // used by interp.cu
 bool direct_kernels_forced() { return g_group_force_direct; }
 bool staged_kernels_forced() { return g_force_staged; }
+bool rows4_disabled() { return g_rows4_off; }
 int three_interpolate_grad_impl(int B, int C, int n, int m, const float* grad_out, const float* weight,
                                 const void* plan, float* grad_points, cudaStream_t s) {
   if (B > 0 && C > 0 && m > 0 && n > 0 && grad_out && plan && grad_points && weight) {
@@ -833,7 +835,7 @@ GEOT_API int geot_gather_rows(int B, int N, int M, int D, const float* src, cons
 }
 
 /* testing / A-B timing: direct != 0 disables the row-staged forward kernel (process-wide). */
-GEOT_API void geot_group_points_config(int mode) { g_group_force_direct = mode == 1; g_force_staged = mode == 2; }
+GEOT_API void geot_group_points_config(int mode) { g_group_force_direct = mode == 1; g_force_staged = mode == 2; g_rows4_off = mode == 3; }
 
 GEOT_API int geot_gather_points(int B, int C, int N, int M, const float* points, const int* idx,
                                 float* out, geot_stream_t stream) {

@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Dev tool (GPU box): launch ONE op of the bench workload a few times so ncu can capture it.
-usage: python tools/prof_one.py {fps|fps_noprune|ball|group|group3|groupbwd|threenn|tibwd|knn|sigt|apply|manifold} [B]"""
+usage: python tools/prof_one.py {fps|fps_noprune|ball|group|group3|groupbwd|threenn|tibwd|ti|ti_old|knn|sigt|apply|manifold} [B]"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
@@ -19,7 +19,7 @@ nbr = F.ball_query(centres, xyz, 0.1, NS)
 if what == "groupbwd":
     go = torch.randn(B, C, M, NS, device="cuda")
     plan = F.ScatterPlan(nbr, B, N)
-if what in ("threenn", "tibwd"):
+if what in ("threenn", "tibwd", "ti", "ti_old"):
     d2, i3 = F.three_nn(xyz, centres)
     w = 1.0 / (d2 + 1e-8); w = (w / w.sum(-1, keepdim=True)).contiguous()
     go3 = torch.randn(B, C, N, device="cuda")
@@ -54,6 +54,9 @@ for _ in range(3):
     elif what == "groupbwd": F.group_points_grad(go, plan, N)
     elif what == "threenn": F.three_nn(xyz, centres)
     elif what == "tibwd": F.three_interpolate_grad(go3, w, plan3, M)
+    elif what in ("ti", "ti_old"):  # (B, C, M) -> (B, C, N); ti_old = without the channel-interleaved kernel
+        _lib.lib().geot_group_points_config(3 if what == "ti_old" else 0)
+        F.three_interpolate(feat[:, :, :M].contiguous(), i3, w)
     elif what == "knn": F.knnquery(16, kx, kx, koff, koff, m_per=N)
     elif what == "sigt":
         modt.zero_grad(set_to_none=True); modt(pt, cmt).backward(got)
