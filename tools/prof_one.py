@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Dev tool (GPU box): launch ONE op of the bench workload a few times so ncu can capture it.
-usage: python tools/prof_one.py {fps|fps_noprune|ball|group|group3|groupbwd|threenn|tibwd|ti|ti_old|knn|sigt|apply|manifold} [B]"""
+usage: python tools/prof_one.py {fps|fps_noprune|ball|group|group3|groupbwd|threenn|tibwd|ti|ti_old|gf|upsample|knn|sigt|apply|manifold} [B]"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
@@ -44,6 +44,14 @@ if what in ("sigt", "manifold", "apply"):
     emat = torch.rand(Ct, Ct, device="cuda"); emat = emat / emat.sum(1, keepdim=True)
     lgt = logits.clone().requires_grad_(True)
     go2t = torch.randn(Bt, Ct, Nt, device="cuda")
+if what == "gf":  # DGCNN edge features at cfg4's last propagation level
+    gx_k = torch.randn(6, 384, 4096, device="cuda"); gx_q = torch.randn(6, 384, 8192, device="cuda")
+    gidx = torch.randint(0, 4096, (6, 8192, 4), device="cuda", dtype=torch.int32)
+if what == "upsample":  # validation: 16000 sampled points -> 100000 mesh vertices, 33 classes
+    from geot_b200 import validation as VAL
+    upts = xyz[:1, :16000].contiguous()
+    umesh = (upts[:, torch.randint(0, 16000, (100000,), device="cuda")] + 0.002 * torch.randn(1, 100000, 3, device="cuda")).contiguous()
+    uprob = torch.softmax(torch.randn(1, 33, 16000, device="cuda") * 3, dim=1)
 torch.cuda.synchronize()
 for _ in range(3):
     if what == "fps": F.furthest_point_sampling(xyz, M)
@@ -54,6 +62,8 @@ for _ in range(3):
     elif what == "groupbwd": F.group_points_grad(go, plan, N)
     elif what == "threenn": F.three_nn(xyz, centres)
     elif what == "tibwd": F.three_interpolate_grad(go3, w, plan3, M)
+    elif what == "gf": F.graph_feature(gx_k, gx_q, gidx)
+    elif what == "upsample": VAL.upsample_labels(uprob, upts, umesh)
     elif what in ("ti", "ti_old"):  # (B, C, M) -> (B, C, N); ti_old = without the channel-interleaved kernel
         _lib.lib().geot_group_points_config(3 if what == "ti_old" else 0)
         F.three_interpolate(feat[:, :, :M].contiguous(), i3, w)

@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """GPU box: three_interpolate forward, default dispatch (channel-interleaved rows) vs direct (mode 1) vs row-staged without the
-interleaved kernel (mode 3).  GEOT_TI4_SMEM_KB=16..64 sets the interleaved kernel's per-CTA row budget."""
+interleaved kernel (mode 3)."""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
