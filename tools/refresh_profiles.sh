@@ -12,7 +12,7 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-fil
 for k in "fps fps_mgr" "ball bq_build" "ball bq_grid" "group group_rows" "groupbwd seg_reduce_planrow" \
          "threenn three_nn_grid" "tibwd seg_reduce_wrows" "knn knn_grid" "knn knn_build" \
          "sigt sigt_kernel" "apply transition_apply_tile" "manifold manifold_fwd" "manifold manifold_bwd" \
-         "ti three_interpolate_rows4" "gf graph_feature_kernel" "upsample interp_argmax" "upsample three_nn_grid"; do
+         "ti three_interpolate_rows4" "gf graph_feature_kernel" "upsample interp_argmax"; do
   set -- $k
   ncu --set full --clock-control none --import-source on -k regex:$2 -c 1 -f -o gpurun_out/${tag}_full_$2 \
       python tools/prof_one.py $1 > gpurun_out/${tag}_full_$2.log 2>&1
