@@ -375,6 +375,34 @@ def get_graph_feature(coor_q, x_q, coor_k, x_k, k=4, idx=None):
     return GraphFeature.apply(x_k, x_q, idx)
 
 
+class Group(nn.Module):
+    """transformer.py:274-303 (`Group`: FPS + kNN patches of the Point-Transformer front end; same constructor and
+    `forward(xyz) -> (neighborhood (B,G,M,3), center (B,G,3), idx (B*G*M) int64 into the flattened batch)`).
+    The reference runs FPS, two transposes around gather_operation, knn_cuda, an index-base add, a fancy-index row gather
+    and a subtraction; here: FPS (the 512-thread / |p|^2 skip variant of pointnet2/_ext_src, transformer.py:271), two
+    point-major row gathers (`geot_gather_rows`: centres and patches straight from the (B,N,3) cloud, no transposes) and
+    the kNN kernel, whose indices already are the flattened-batch indices the reference builds with `idx + idx_base`."""
+
+    def __init__(self, num_group, group_size):
+        super().__init__()
+        self.num_group = num_group
+        self.group_size = group_size
+
+    @torch.no_grad()  # xyz is input data: no gradient flows through the patch coordinates in GeoT either
+    def forward(self, xyz):
+        from . import _lib
+        batch_size, num_points, _ = xyz.shape
+        xyz = xyz.contiguous().float()
+        fps_idx = F_.furthest_point_sampling(xyz, self.num_group, flags=_lib.GEOT_FPS_CAP512 | _lib.GEOT_FPS_MAGSKIP)
+        center = F_.gather_rows(xyz, fps_idx)  # B G 3
+        idx, _ = F_.knnquery(self.group_size, xyz.view(-1, 3), center.view(-1, 3), None, None, n_per=num_points, m_per=self.num_group)
+        assert idx.shape == (batch_size * self.num_group, self.group_size)
+        flat = xyz.view(1, batch_size * num_points, 3)
+        neighborhood = F_.gather_rows(flat, idx.view(1, -1)).view(batch_size, self.num_group, self.group_size, 3)
+        neighborhood = neighborhood - center.unsqueeze(2)
+        return neighborhood, center, idx.view(-1).long()
+
+
 def create_grouper(group_args):
     """group.py:338-352."""
     group_args_copy = copy.deepcopy(group_args)

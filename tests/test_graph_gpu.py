@@ -64,3 +64,21 @@ def test_knn_neighbours_match_compat_knn(cuda):
     assert torch.equal(idx.long(), ref.transpose(1, 2))
     oracle = GR.knn_idx(4, coor_k.cpu(), coor_q.cpu())
     assert torch.equal(ref.cpu(), oracle)
+
+
+@pytest.mark.parametrize("B,N,G,M", [(6, 16000, 512, 32), (2, 1000, 37, 5)])
+def test_group_fps_knn_patches(cuda, B, N, G, M):
+    """layers.Group (transformer.py:274-303) against the reference's expressions built from the same library's FPS and
+    KNN front ends: centres = xyz[fps_idx], patches = xyz.view(B*N, 3)[idx + idx_base] - centre; one subtraction per
+    element: bit-exact."""
+    from geot_b200 import compat, pointnet2_utils as pu, synth
+    xyz = torch.from_numpy(synth.tooth_batch(B, N)).cuda()
+    nb, center, idx = layers.Group(G, M)(xyz)
+    fps_idx = pu.furthest_point_sample(xyz, G)
+    center_ref = pu.gather_operation(xyz.transpose(1, 2).contiguous(), fps_idx).transpose(1, 2).contiguous()
+    _, kidx = compat.KNN(k=M, transpose_mode=True)(xyz, center_ref)  # B G M
+    flat = (kidx + torch.arange(0, B, device="cuda").view(-1, 1, 1) * N).view(-1)
+    nb_ref = xyz.view(B * N, -1)[flat, :].view(B, G, M, 3).contiguous() - center_ref.unsqueeze(2)
+    assert torch.equal(center, center_ref)
+    assert idx.dtype == torch.int64 and torch.equal(idx, flat)
+    assert nb.shape == (B, G, M, 3) and torch.equal(nb, nb_ref)
