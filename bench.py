@@ -372,6 +372,59 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def run_config(args):
+    """--config cfg2|cfg3|cfg4: BASELINE.json configs 2-4 = the reference's OWN models / op wrappers (unchanged,
+    tests/model_cases.py) timed on two backends on this GPU: geot_b200 through the pybind-shaped facades (scatter-plan
+    builds included - the facades rebuild the plan per backward call) and the reference's own kernels
+    (oracle/_ref/*.so).  Prints one JSON line: forward and forward+backward ms per backend (CUDA events, median) and
+    the per-entry-point device time inside the facades.  Not the headline metric; a profiles/ artefact."""
+    import torch
+    from tests import model_cases as mc
+    from tests import refenv
+    torch.cuda.set_device(0)
+    refenv.install("geot")
+    name = args.config
+    if name == "cfg3":
+        model, data = mc.cfg3_model(), mc.cfg3_inputs(16, 16384)
+        run = lambda be, bwd: mc.run_cfg3(be, model, data, None, backward=bwd)
+        what = "PointNet++ MSG segmentation (SURVEY Appendix B), B=16 x 16384, fwd / fwd+bwd"
+    elif name == "cfg4":
+        cfg, model, _ = mc.cfg4_models(17)
+        data, data_u = mc.cfg4_inputs(16000)
+        run = lambda be, bwd: mc.run_cfg4_model(be, model, data, data_u, None, backward=bwd)
+        what = "GeoT student WholePartSeg(PointTransformer_seg_T), 2 labeled + 2 strong + 2 weak clouds x 16000, fwd / fwd+bwd"
+    else:
+        inp, weights = mc.cfg2_inputs(8, 16384), mc.cfg2_weights()
+        run = lambda be, bwd: mc.run_cfg2(be, inp, weights, backward=bwd)
+        what = "Point-Transformer op pyramid (SURVEY Appendix C), offset format, B=8 x 16384, k=16, fwd / fwd+bwd"
+
+    def timed(be, bwd, reps):
+        ts = []
+        for i in range(reps + 2):
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            run(be, bwd)
+            e1.record()
+            torch.cuda.synchronize()
+            if i >= 2:
+                ts.append(e0.elapsed_time(e1))
+        return float(np.median(ts))
+
+    out = {"config": name, "workload": what, "reps": args.steps, "backends": {}}
+    for be in ("geot", "ref"):
+        r = {"fwd_ms": timed(be, False, args.steps), "fwd_bwd_ms": timed(be, True, args.steps)}
+        with refenv.timing() as tm:
+            run(be, True)
+        r["facade_ms"] = {k: {"calls": len(v), "ms": round(sum(v), 4)} for k, v in sorted(tm.items(), key=lambda kv: -sum(kv[1]))}
+        r["facade_total_ms"] = round(sum(sum(v) for v in tm.values()), 4)
+        out["backends"][be] = r
+    g, r = out["backends"]["geot"], out["backends"]["ref"]
+    out["speedup"] = {"fwd": r["fwd_ms"] / g["fwd_ms"], "fwd_bwd": r["fwd_bwd_ms"] / g["fwd_bwd_ms"],
+                      "ops_only": r["facade_total_ms"] / g["facade_total_ms"]}
+    print(json.dumps(out), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -380,8 +433,13 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--in-flight", type=int, default=3, help="independent steps in flight for `value` (streams + output sets)")
+    ap.add_argument("--config", default=None, choices=["cfg2", "cfg3", "cfg4"],
+                    help="time BASELINE config 2/3/4 (reference models, both backends) instead of the headline metric")
     args = ap.parse_args()
-    if args.impl == "reference":
+    if args.config:
+        args.steps = min(args.steps, 20)
+        run_config(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_ours(args)

@@ -16,39 +16,9 @@
 // thread minimises bit-reversed tid.  Hence  rank(k) = bitrev(k mod BS) * ceil(n/BS) + k div BS  and
 // the reference picks the max distance, then the min rank.  We reproduce exactly that order without
 // reproducing its thread layout.
-#include "common.cuh"
+#include "fps_common.cuh"
 
 namespace geot {
-
-void count_launch(int n);
-
-struct TieRule {
-  int log2bs;  // BS = 1 << log2bs, the reference's block size for this n
-};
-
-__device__ __forceinline__ unsigned tie_rank(int k, int log2bs, int q_count) {
-  const unsigned tid = (unsigned)k & ((1u << log2bs) - 1u);
-  const unsigned q = (unsigned)k >> log2bs;
-  const unsigned br = log2bs ? (__brev(tid) >> (32 - log2bs)) : 0u;
-  return br * (unsigned)q_count + q;
-}
-__device__ __forceinline__ int tie_unrank(unsigned rank, int log2bs, int q_count) {
-  const unsigned br = rank / (unsigned)q_count, q = rank % (unsigned)q_count;
-  const unsigned tid = log2bs ? (__brev(br) >> (32 - log2bs)) : 0u;
-  return (int)((q << log2bs) | tid);
-}
-
-// Segment of block b.  Batched: offset == nullptr, indices local.  Offset format: global indices.
-__device__ __forceinline__ void fps_segment(const int* __restrict__ offset, const int* __restrict__ new_offset,
-                                            int N, int M, int b, int64_t& start_n, int& n,
-                                            int64_t& start_m, int& m, int& idx_base) {
-  if (offset == nullptr) {
-    start_n = (int64_t)b * N; n = N; start_m = (int64_t)b * M; m = M; idx_base = 0;
-  } else {
-    const int s_n = b ? offset[b - 1] : 0, s_m = b ? new_offset[b - 1] : 0;
-    start_n = s_n; n = offset[b] - s_n; start_m = s_m; m = new_offset[b] - s_m; idx_base = s_n;
-  }
-}
 
 // ---------------------------------------------------------------------------------------------
 // Fast path: n <= CH*4096 points, 1024 threads, CH*4 points per thread.
@@ -171,20 +141,16 @@ fps_smem_kernel(const float* __restrict__ xyz, const int* __restrict__ offset,
 //     then bar.arrive(B); an idle worker issues ~10 instructions per round;
 //   * the manager waits on B.  Two named barriers in producer/consumer form, nobody waits twice.
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ unsigned morton4(unsigned v) {  // 4 bits -> every third bit
-  return (v & 1u) | ((v & 2u) << 2) | ((v & 4u) << 4) | ((v & 8u) << 6);
-}
-
-__device__ __forceinline__ void bar_sync_named(int id) { asm volatile("bar.sync %0, 1024;" ::"r"(id) : "memory"); }
-__device__ __forceinline__ void bar_arrive_named(int id) { asm volatile("bar.arrive %0, 1024;" ::"r"(id) : "memory"); }
-__device__ __forceinline__ unsigned lds_u8(unsigned a) {
-  unsigned v;
-  asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a));
-  return v;
-}
-__device__ __forceinline__ void sts_u8(unsigned a, unsigned v) { asm volatile("st.shared.u8 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
-__device__ __forceinline__ void sts_u16(unsigned a, unsigned v) { asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "h"((unsigned short)v) : "memory"); }
-__device__ __forceinline__ void sts32(unsigned a, unsigned v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+#ifdef GEOT_FPS_PROF
+// Debug build only (tools/fps_prof.py): per-round SM-clock stamps of block 0 -> a caller buffer.
+// layout: stamp[(round * 32 + warp) * 8 + k]
+__device__ long long* g_fps_prof = nullptr;
+#define FPS_PROF_INIT long long* const prof_buf = (blockIdx.x == 0 && (threadIdx.x & 31) == 0) ? g_fps_prof : nullptr
+#define FPS_STAMP(round, k) do { if (prof_buf) prof_buf[((round) * 32 + warp) * 8 + (k)] = clock64(); } while (0)
+#else
+#define FPS_PROF_INIT do {} while (0)
+#define FPS_STAMP(round, k) do {} while (0)
+#endif
 
 template <int NBK>
 struct MgrCfg {
@@ -214,6 +180,10 @@ fps_mgr_kernel(const float* __restrict__ xyz, const int* __restrict__ offset,
   __shared__ float s_red[6][32];
   __shared__ int s_scan[32];
 
+  #ifdef GEOT_FPS_PROF
+  const int abl = mag_skip >> 8;  // timing ablations (results are wrong): 1 = no bucket updates, 2 = updates without REDUX / key store
+  mag_skip &= 0xff;
+#endif
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   int64_t start_n, start_m;
   int n, m, idx_base;
@@ -402,6 +372,7 @@ fps_mgr_kernel(const float* __restrict__ xyz, const int* __restrict__ offset,
   if (t < 64) sts32(a_act + 4u * t, 0u);  // flag bytes of buckets that do not exist stay 0
   __syncthreads();
   if (rounds <= 0) return;
+  FPS_PROF_INIT;
 
   if (warp == 0) {
     // =========================== manager ===========================
@@ -448,18 +419,22 @@ fps_mgr_kernel(const float* __restrict__ xyz, const int* __restrict__ offset,
     publish(make_float4(0.f, x0, y0, z0), key);
     for (int j = 1; j <= rounds; j++) {
       bar_sync_named(2);  // workers have applied sample j-1
+      FPS_STAMP(j, 0);
 #pragma unroll
       for (int i = 0; i < BPL; i++) key[i] = lds64(a_key + 8u * (unsigned)(BPL * lane + i));
       int ghi;
       unsigned glo;
       pick(key, ghi, glo);
+      FPS_STAMP(j, 1);
       // no candidate at all (every point skipped): the reference keeps index 0
       float4 smp = make_float4(0.f, x0, y0, z0);
       if (ghi >= 0) {
         const unsigned a_w = a_base + 4u * (glo & 0x3fffu);  // the winner's coordinates, by sorted position
         smp.y = lds32f(a_w); smp.z = lds32f(a_w + Cfg::PLANE_BYTES); smp.w = lds32f(a_w + 2 * Cfg::PLANE_BYTES);
       }
+      FPS_STAMP(j, 2);
       if (j < rounds) publish(smp, key);
+      FPS_STAMP(j, 3);
       // off the critical path: un-rank the winner (rank 0 <-> index 0)
       if (lane == 0) out[j] = idx_base + (ghi >= 0 ? tie_unrank(0x7fffu - (glo >> 14), log2bs, q_count) : 0);
     }
@@ -468,8 +443,13 @@ fps_mgr_kernel(const float* __restrict__ xyz, const int* __restrict__ offset,
     const unsigned a_my = a_act + 8u * (unsigned)wk;
     for (int j = 0; j < rounds; j++) {
       bar_sync_named(1);  // manager has published the sample and the active flags of round j
-      const uint2 fl = lds64(a_my);  // one flag byte per owned bucket
+      FPS_STAMP(j, 0);
+      uint2 fl = lds64(a_my);  // one flag byte per owned bucket
+#ifdef GEOT_FPS_PROF
+      if (abl == 1) fl = make_uint2(0u, 0u);
+#endif
       if (fl.x | fl.y) {
+        FPS_STAMP(j, 1);
         const float4 smp = lds128(a_ctrl);
 #pragma unroll
         for (int c = 0; c < CHW; c++) {
@@ -491,18 +471,26 @@ fps_mgr_kernel(const float* __restrict__ xyz, const int* __restrict__ offset,
               mind[c * 4 + e] = v;
               cm = fmaxf(cm, v);
             }
+            if (cm > -5.f) FPS_STAMP(j, 4);
+#ifdef GEOT_FPS_PROF
+            if (abl == 2) continue;
+#endif
             // candidates are >= 0 or exactly -1, so the int view of the float bits is order preserving
             const int wm = __reduce_max_sync(0xffffffffu, __float_as_int(cm));
             unsigned r = 0xffffffffu;
 #pragma unroll
             for (int e = 0; e < 4; e++) r = min(r, (__float_as_int(mind[c * 4 + e]) == wm) ? rk[e] : 0xffffffffu);
+            if (r != 7u) FPS_STAMP(j, 5);
             const unsigned wr = __reduce_min_sync(0xffffffffu, r);
             // exactly one lane publishes: ranks are unique (an active bucket has a live point, so wm >= 0)
             if (r == wr) sts64(a_key + 8u * b, ((0x7fffu - (wr >> 2)) << 14) | (unsigned)(b * 128 + 4 * lane) | (wr & 3u), (unsigned)wm);
+            if (wr != 9u) FPS_STAMP(j, 6);
           }
         }
+        FPS_STAMP(j, 2);
       }
       bar_arrive_named(2);
+      FPS_STAMP(j, 3);
     }
   }
 }
@@ -611,7 +599,10 @@ static int fps_dispatch(int blocks, int n_max, const float* xyz, const int* offs
                         cudaStream_t s) {
   const int cap = (flags & GEOT_FPS_CAP512) ? 512 : 1024;
   const int log2bs = ilog2(ref_opt_n_threads(n_max, cap));
-  const int mag_skip = (flags & GEOT_FPS_MAGSKIP) ? 1 : 0;
+  int mag_skip = (flags & GEOT_FPS_MAGSKIP) ? 1 : 0;
+#ifdef GEOT_FPS_PROF
+  mag_skip |= flags & ~0xff;  // ablation selector of the profiling build
+#endif
   const bool generic = (flags & GEOT_FPS_FORCE_GENERIC) || weights != nullptr || n_max > 4 * 4096;
   if (!generic && !(flags & GEOT_FPS_NO_PRUNE)) {
     const int ch = (n_max + 4095) / 4096;
@@ -643,6 +634,12 @@ static int fps_dispatch(int blocks, int n_max, const float* xyz, const int* offs
 }  // namespace geot
 
 using namespace geot;
+
+#ifdef GEOT_FPS_PROF
+GEOT_API int geot_debug_fps_prof(long long* buf) {
+  return (int)cudaMemcpyToSymbol(g_fps_prof, &buf, sizeof(buf));
+}
+#endif
 
 GEOT_API int geot_furthest_point_sampling(int B, int N, int M, const float* xyz, float* temp, int* idx,
                                           int flags, geot_stream_t stream) {

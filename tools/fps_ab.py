@@ -1,6 +1,8 @@
 #!/usr/bin/env python
-"""Dev tool (GPU box): A/B timing of the FPS kernels on the bench workload, checked against each other."""
-import os, sys
+"""Dev tool (GPU box): A/B timing of the FPS kernels, checked against each other.
+  mgr = default: bucket-pruned manager/worker kernel (fps.cu)     brute = un-pruned one-CTA kernel
+  ref = the reference kernel (oracle/_ref), when present"""
+import json, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
 from geot_b200 import _lib, synth
@@ -15,12 +17,28 @@ def t(fn, it=20):
     e1.record(); torch.cuda.synchronize()
     return e0.elapsed_time(e1) / it
 
-for (B, N, M) in [(64, 16384, 1024), (16, 16384, 4096), (6, 16000, 8192), (64, 4096, 1024), (64, 1024, 256), (256, 16384, 1024)]:
+try:
+    from tests import refgpu
+    have_ref = refgpu.available("pn2batch")
+except Exception:
+    have_ref = False
+rows = []
+shapes = [(64, 16384, 1024), (8, 16384, 1024), (16, 16384, 4096), (6, 16000, 8192), (16, 4096, 1024), (64, 4096, 1024), (64, 1024, 256), (256, 16384, 1024)]
+if len(sys.argv) > 1 and sys.argv[1] == "quick":
+    shapes = shapes[:4]
+for (B, N, M) in shapes:
     xyz = torch.from_numpy(synth.tooth_batch(B, N)).cuda()
-    a = F.furthest_point_sampling(xyz, M)
-    b = F.furthest_point_sampling(xyz, M, flags=_lib.GEOT_FPS_NO_PRUNE)
-    ok = bool((a == b).all())
-    ta = t(lambda: F.furthest_point_sampling(xyz, M))
-    tb = t(lambda: F.furthest_point_sampling(xyz, M, flags=_lib.GEOT_FPS_NO_PRUNE))
-    t2 = t(lambda: F.furthest_point_sampling(xyz, 2))
-    print(f"FPS B={B} N={N} M={M}: mgr {ta:.3f} ms  unpruned {tb:.3f} ms  speedup {tb/ta:.2f}x  equal={ok}  ({(ta-t2)*1e3/(M-2):.3f} us/round, setup(M=2) {t2*1e3:.1f} us)", flush=True)
+    variants = {"mgr": 0, "brute": _lib.GEOT_FPS_NO_PRUNE}
+    base = F.furthest_point_sampling(xyz, M, flags=_lib.GEOT_FPS_NO_PRUNE)
+    row = {"B": B, "N": N, "M": M}
+    for name, fl in variants.items():
+        out = F.furthest_point_sampling(xyz, M, flags=fl)
+        row[name + "_equal"] = bool((out == base).all())
+        row[name + "_ms"] = t(lambda: F.furthest_point_sampling(xyz, M, flags=fl))
+    row["mgr_setup_us"] = t(lambda: F.furthest_point_sampling(xyz, 2)) * 1e3
+    row["mgr_us_per_round"] = (row["mgr_ms"] * 1e3 - row["mgr_setup_us"]) / (M - 2)
+    if have_ref and B * M <= 70000:
+        row["ref_equal"] = bool((refgpu.fps(xyz, M) == base).all())
+        row["ref_ms"] = t(lambda: refgpu.fps(xyz, M), it=3)
+    rows.append(row)
+    print(json.dumps({k: (round(v, 4) if isinstance(v, float) else v) for k, v in row.items()}), flush=True)
