@@ -81,6 +81,9 @@ _SIGNATURES = {
     "geot_interp_weights": [_i64, _vp, _vp, _vp, _vp],
     "geot_interp_argmax": [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp],
     "geot_seg_counts": [_i64, _i, _vp, _vp, _vp, _vp],
+    "geot_stats_record_floats": [_i, _i64],
+    "geot_stats_pack": [_i, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
+    "geot_stats_combine": [_i, _i, _i64, _vp, _f, _vp, _vp, _vp, _vp, _vp],
 }
 _RESTYPES = {
     "geot_last_error": C.c_char_p,
@@ -94,6 +97,7 @@ _RESTYPES = {
     "geot_sigt_backward_workspace_bytes": _sz,
     "geot_manifold_workspace_bytes": _sz,
     "geot_class_pick_workspace_bytes": _sz,
+    "geot_stats_record_floats": _i64,
 }
 
 

@@ -436,13 +436,9 @@ GEOT_API int geot_ball_query(int B, int N, int M, float radius, int nsample, con
       return GEOT_ERR_WORKSPACE;
     }
     ws = reinterpret_cast<const unsigned char*>(workspace);
-    static bool configured = false;
-    if (!configured) {
-      cudaError_t e = cudaFuncSetAttribute(bq_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBqMaxCells * 4);
-      if (e == cudaSuccess) e = cudaFuncSetAttribute(bq_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * (kBqMaxN / 8));
-      if (e != cudaSuccess) { set_error("ball_query: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
-      configured = true;
-    }
+    static DynSmem ds_build, ds_grid;
+    if (int rc = ds_build.need(bq_build_kernel, kBqMaxCells * 4, "ball_query")) return rc;
+    if (int rc = ds_grid.need(bq_grid_kernel, 8 * (kBqMaxN / 8), "ball_query")) return rc;
     bq_build_kernel<<<B, 1024, kBqMaxCells * 4, s>>>(N, radius, nsample, xyz, reinterpret_cast<unsigned char*>(workspace), stride,
                                                       (flags & GEOT_BQ_FORCE_GRID) ? 1 : 0);
     count_launch(1);

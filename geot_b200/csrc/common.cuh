@@ -87,4 +87,25 @@ __device__ __forceinline__ void sts128(unsigned a, float4 v) {
 
 constexpr int kNumSMs = 148;  // B200
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize belongs to the function IN ONE DEVICE'S CONTEXT, not to the process: a
+// launcher keeps one static DynSmem per kernel and calls need() before every launch; the attribute is (re)set when the
+// CURRENT device has not been configured for that many bytes yet (one cudaGetDevice, thread-local, per launch).
+struct DynSmem {
+  size_t configured[64] = {};
+  template <typename K>
+  int need(K kernel, size_t bytes, const char* what, bool prefer_smem_carveout = false) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e == cudaSuccess && dev >= 0 && dev < 64 && bytes <= configured[dev]) return GEOT_OK;
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (e == cudaSuccess && prefer_smem_carveout) e = cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    if (e != cudaSuccess) {
+      set_error("%s: cudaFuncSetAttribute(%zu bytes of dynamic shared memory): %s", what, bytes, cudaGetErrorString(e));
+      return GEOT_ERR_CUDA;
+    }
+    if (dev >= 0 && dev < 64) configured[dev] = bytes;  // racing threads write the same value
+    return GEOT_OK;
+  }
+};
+
 }  // namespace geot

@@ -568,12 +568,8 @@ template <int CH>
 static int launch_smem(int blocks, const float* xyz, const int* offset, const int* new_offset, int N,
                        int M, int* idx, int log2bs, int mag_skip, cudaStream_t s) {
   const size_t smem = (size_t)3 * CH * 4096 * sizeof(float);
-  static bool configured = false;  // per instantiation
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(fps_smem_kernel<CH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) { set_error("fps: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
-    configured = true;
-  }
+  static DynSmem ds;  // per instantiation
+  if (int rc = ds.need(fps_smem_kernel<CH>, smem, "fps")) return rc;
   fps_smem_kernel<CH><<<blocks, 1024, smem, s>>>(xyz, offset, new_offset, N, M, idx, log2bs, mag_skip);
   count_launch(1);
   return check_launch("fps_smem_kernel");
@@ -583,12 +579,8 @@ template <int NBK>
 static int launch_mgr(int blocks, const float* xyz, const int* offset, const int* new_offset, int N,
                       int M, int* idx, int log2bs, int mag_skip, cudaStream_t s) {
   constexpr int smem = MgrCfg<NBK>::SMEM_BYTES;
-  static bool configured = false;  // per instantiation
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(fps_mgr_kernel<NBK>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) { set_error("fps: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
-    configured = true;
-  }
+  static DynSmem ds;  // per instantiation
+  if (int rc = ds.need(fps_mgr_kernel<NBK>, smem, "fps")) return rc;
   fps_mgr_kernel<NBK><<<blocks, 1024, smem, s>>>(xyz, offset, new_offset, N, M, idx, log2bs, mag_skip);
   count_launch(1);
   return check_launch("fps_mgr_kernel");

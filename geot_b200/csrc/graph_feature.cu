@@ -100,13 +100,9 @@ GEOT_API int geot_graph_feature(int B, int C, int Nk, int Nq, int k, const float
   }
   dim3 grid((Nq + q_tile - 1) / q_tile, C, B);
   const size_t smem = staged ? (size_t)Nk * 4 : 0;
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(graph_feature_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(graph_feature_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
-    if (e != cudaSuccess) { set_error("graph_feature: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
-    configured = true;
-  }
+  static DynSmem ds4, ds0;
+  if (int rc = ds4.need(graph_feature_kernel<4, true>, 96 * 1024, "graph_feature")) return rc;
+  if (int rc = ds0.need(graph_feature_kernel<0, true>, 96 * 1024, "graph_feature")) return rc;
   if (k4 && staged) graph_feature_kernel<4, true><<<grid, kGfThreads, smem, s>>>(C, Nk, Nq, k, q_tile, x_k, x_q, idx, out);
   else if (k4) graph_feature_kernel<4, false><<<grid, kGfThreads, 0, s>>>(C, Nk, Nq, k, q_tile, x_k, x_q, idx, out);
   else if (staged) graph_feature_kernel<0, true><<<grid, kGfThreads, smem, s>>>(C, Nk, Nq, k, q_tile, x_k, x_q, idx, out);

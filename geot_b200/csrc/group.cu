@@ -24,9 +24,11 @@ namespace geot {
 void count_launch(int n);
 
 constexpr int kGroupCCH = 16;  // channels per thread in the forward gather
-static bool g_group_force_direct = false;  // testing / A-B timing: geot_group_points_config(1)
-static bool g_force_staged = false;        // geot_group_points_config(2): ignore the work-size heuristics
-static bool g_rows4_off = false;           // geot_group_points_config(3): three_interpolate without the channel-interleaved kernel (A/B)
+// Kernel-selection override for tests / A-B timing, set by geot_group_points_config().  THREAD-LOCAL, like the error
+// slot: it only affects calls made by the thread that set it, so the library stays re-entrant (no process-wide state).
+static thread_local bool g_group_force_direct = false;  // mode 1
+static thread_local bool g_force_staged = false;        // mode 2: ignore the work-size heuristics
+static thread_local bool g_rows4_off = false;           // mode 3: three_interpolate without the channel-interleaved kernel (A/B)
 
 // VEC = 4: E % 4 == 0 and 16-byte aligned idx/out.  grid (ceil(E/VEC/256), ceil(C/CCH), B).
 template <int VEC>
@@ -152,12 +154,8 @@ static int launch_group(int B, int C, int N, int64_t E, const float* points, con
   const size_t row_bytes = (size_t)N * 4;
   if (vec && !g_group_force_direct && E >= 2 * (int64_t)N && N % 4 == 0 && (((uintptr_t)points & 15) == 0) &&
       row_bytes <= 200 * 1024 && C <= 65535 * 1 && N > 0) {
-    static size_t configured = 0;
-    if (row_bytes > configured) {
-      cudaError_t e = cudaFuncSetAttribute(group_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-      if (e != cudaSuccess) { set_error("%s: cudaFuncSetAttribute: %s", what, cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
-      configured = 200 * 1024;
-    }
+    static DynSmem ds;
+    if (int rc = ds.need(group_rows_kernel, 200 * 1024, what)) return rc;
     dim3 grid(C, B);
     group_rows_kernel<<<grid, kRowThreads, row_bytes, s>>>(C, N, E, points, idx, out);
     count_launch(1);
@@ -520,12 +518,8 @@ static size_t planrow_smem(int N, int64_t E) {
 }
 static int launch_planrow(int B, int C, int N, int E, int Q, const float* g, const int* row_ptr, const int* perm, float* dst,
                           cudaStream_t s, const char* what) {
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(seg_reduce_planrow_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
-    if (e != cudaSuccess) { set_error("%s: cudaFuncSetAttribute: %s", what, cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
-    configured = true;
-  }
+  static DynSmem ds;
+  if (int rc = ds.need(seg_reduce_planrow_kernel, 226 * 1024, what)) return rc;
   // channels per CTA: amortise the per-CTA plan setup (~0.8 of a row) without leaving the last wave half empty
   int cpc = 4;
   double best = 0.0;
@@ -653,12 +647,8 @@ seg_reduce_wrows_kernel(int C, int n, int m, const float* __restrict__ g, const 
 template <int R, int LPT>
 static int launch_wrows_t(int B, int C, int n, int m, size_t smem, const float* g, const PlanView& pv, const float* wsorted,
                           float* dst, cudaStream_t s) {
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(seg_reduce_wrows_kernel<R, LPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
-    if (e != cudaSuccess) { set_error("three_interpolate_grad: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
-    configured = true;
-  }
+  static DynSmem ds;  // per instantiation
+  if (int rc = ds.need(seg_reduce_wrows_kernel<R, LPT>, 226 * 1024, "three_interpolate_grad")) return rc;
   dim3 grid((C + R - 1) / R, B);
   seg_reduce_wrows_kernel<R, LPT><<<grid, 1024, smem, s>>>(C, n, m, g, pv.row_ptr, pv.perm, wsorted, dst);
   count_launch(1);
@@ -892,12 +882,8 @@ GEOT_API int geot_scatter_plan_build(int B, int N, int64_t E, const int* idx, vo
     plan_fill_kernel<<<gf, 256, 0, s>>>(N, E, idx, cursor, tmp);
     dim3 gs((N + 255) / 256, B);
     plan_sort_small_kernel<<<gs, 256, 0, s>>>(N, E, row_ptr, tmp, perm, heavy_count, heavy_list, heavy_cap);
-    static bool configured = false;
-    if (!configured) {
-      cudaError_t e2 = cudaFuncSetAttribute(plan_sort_heavy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPlanHeavyBits / 8);
-      if (e2 != cudaSuccess) { set_error("scatter_plan_build: cudaFuncSetAttribute: %s", cudaGetErrorString(e2)); return GEOT_ERR_CUDA; }
-      configured = true;
-    }
+    static DynSmem ds_heavy;
+    if (int rc = ds_heavy.need(plan_sort_heavy_kernel, kPlanHeavyBits / 8, "scatter_plan_build")) return rc;
     const size_t bm_bytes = (size_t)std::min<int64_t>(kPlanHeavyBits, ((E + 32767) / 32768) * 32768) / 8;
     plan_sort_heavy_kernel<<<2 * kNumSMs, 1024, bm_bytes, s>>>(N, E, row_ptr, tmp, perm, heavy_count, heavy_list, heavy_cap);
     count_launch(3);

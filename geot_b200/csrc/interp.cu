@@ -516,12 +516,8 @@ GEOT_API int geot_three_nn(int B, int n, int m, const float* unknown, const floa
   const int P = (m + kNgMaxM - 1) / kNgMaxM;
   if (m >= 64 && P <= 8 && ((double)B * n * m >= 5e7 || staged_kernels_forced()) && !direct_kernels_forced()) {
     const int part = (m + P - 1) / P;
-    static bool configured = false;
-    if (!configured) {
-      cudaError_t e = cudaFuncSetAttribute(three_nn_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kNgMaxM * 16 + (kNgMaxCells + 1) * 4 + 9 * kNgThreads * 4);
-      if (e != cudaSuccess) { set_error("three_nn: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
-      configured = true;
-    }
+    static DynSmem ds;
+    if (int rc = ds.need(three_nn_grid_kernel, kNgMaxM * 16 + (kNgMaxCells + 1) * 4 + 9 * kNgThreads * 4, "three_nn")) return rc;
     // CTAs per cloud: every CTA re-bins the known cloud (~4x the cost of one 1024-query sweep), so prefer few
     // CTAs with several sweeps each, in whole waves of the 148 SMs
     const int max_cb = (n + kNgThreads - 1) / kNgThreads;
@@ -568,13 +564,8 @@ GEOT_API int geot_three_interpolate(int B, int C, int m, int n, const float* poi
     int n_tile = 16384;  // measured: long tiles amortise the register-staged rows (0.120 ms at 4096, 0.093 at 16384; bench shape)
     if (n_tile > n) n_tile = n;
     const size_t smem = (size_t)(G / 4) * m * 16;
-    static bool configured4 = false;
-    if (!configured4) {
-      cudaError_t e = cudaFuncSetAttribute(three_interpolate_rows4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-      if (e == cudaSuccess) e = cudaFuncSetAttribute(three_interpolate_rows4_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-      if (e != cudaSuccess) { set_error("three_interpolate: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
-      configured4 = true;
-    }
+    static DynSmem ds4;
+    if (int rc = ds4.need(three_interpolate_rows4_kernel, 64 * 1024, "three_interpolate", true)) return rc;
     GEOT_REQUIRE((C + G - 1) / G <= 65535, "three_interpolate: C exceeds grid limits");
     dim3 grid((n + n_tile - 1) / n_tile, (C + G - 1) / G, B);
     three_interpolate_rows4_kernel<<<grid, kTi4Threads, smem, as_stream(stream)>>>(C, m, n, G, n_tile, points, idx, weight, out);
@@ -588,12 +579,8 @@ GEOT_API int geot_three_interpolate(int B, int C, int m, int n, const float* poi
     int n_tile = std::max(4 * m, 2048);
     if (n_tile > n) n_tile = n;
     const size_t smem = (size_t)G * m * 4;
-    static bool configured = false;
-    if (!configured) {
-      cudaError_t e = cudaFuncSetAttribute(three_interpolate_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
-      if (e != cudaSuccess) { set_error("three_interpolate: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
-      configured = true;
-    }
+    static DynSmem ds;
+    if (int rc = ds.need(three_interpolate_rows_kernel, 96 * 1024, "three_interpolate")) return rc;
     GEOT_REQUIRE((C + G - 1) / G <= 65535, "three_interpolate: C exceeds grid limits");
     dim3 grid((n + n_tile - 1) / n_tile, (C + G - 1) / G, B);
     three_interpolate_rows_kernel<<<grid, kTiThreads, smem, as_stream(stream)>>>(C, m, n, G, n_tile, points, idx, weight, out);

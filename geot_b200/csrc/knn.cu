@@ -664,12 +664,9 @@ GEOT_API int geot_knnquery(int b, int n, int m, int nsample, const float* xyz, c
     unsigned char* seg_grid = grid ? base + w.seg_grid : nullptr;
     const int S = (nsample + 1 + 31) / 32;
     if (grid) {
-      static bool attr_done = false;
+      static DynSmem ds_build;
       const int smem = kKnnMaxCells * (int)sizeof(int);
-      if (!attr_done) {
-        cudaFuncSetAttribute(knn_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        attr_done = true;
-      }
+      if (int rc = ds_build.need(knn_build_kernel, smem, "knnquery")) return rc;
       // points per occupied cell = a * (k+1).  Measured optimum: ~0.8 at k = 16, less for longer lists (0.4 at 32, 0.3 at 64)
       const float a = fminf(fmaxf(13.f / (float)(nsample + 1), 0.3f), 0.8f);
       knn_build_kernel<<<b, 1024, smem, s>>>(nsample, a, xyz, offset, n_per, seg_grid, base + w.slots, reinterpret_cast<float4*>(base + w.sorted));

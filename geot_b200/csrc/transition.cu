@@ -324,12 +324,8 @@ static int sigt_grid(int64_t BN) {
 template <int C, bool BWD>
 static int launch_sigt(int B, int N, const float* x, const float* W, int stride, const float* bias,
                        const float* grad_in, float* out, cudaStream_t s) {
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(sigt_kernel<C, BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SigtSmem<C>::bytes);
-    if (e != cudaSuccess) { set_error("sigt: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
-    configured = true;
-  }
+  static DynSmem ds;  // per instantiation
+  if (int rc = ds.need(sigt_kernel<C, BWD>, SigtSmem<C>::bytes, "sigt")) return rc;
   sigt_kernel<C, BWD><<<sigt_grid((int64_t)B * N), kSigtThreads, SigtSmem<C>::bytes, s>>>(B, N, x, W, stride, bias, grad_in, out);
   count_launch(1);
   return check_launch(BWD ? "sigt_kernel<bwd>" : "sigt_kernel<fwd>");

@@ -361,12 +361,8 @@ transition_apply_tile_kernel(int B, int N, const float* __restrict__ logits, con
 template <int C, bool BWD>
 static int launch_apply_tile(int B, int N, const float* logits, const float* ema_t, const float* insT, float lam,
                              const float* grad_out, float* out_or_gl, float* grad_insT, cudaStream_t s) {
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(transition_apply_tile_kernel<C, BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TileSmem<C>::kBytes);
-    if (e != cudaSuccess) { set_error("transition_apply: cudaFuncSetAttribute(%zu): %s", TileSmem<C>::kBytes, cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
-    configured = true;
-  }
+  static DynSmem ds;  // per instantiation
+  if (int rc = ds.need(transition_apply_tile_kernel<C, BWD>, TileSmem<C>::kBytes, "transition_apply")) return rc;
   const int64_t tiles = ((int64_t)B * N + kTileP - 1) / kTileP;
   const int per_sm = TileSmem<C>::kBytes > 110 * 1024 ? 1 : (TileSmem<C>::kBytes > 72 * 1024 ? 2 : 3);
   const int grid = (int)std::min<int64_t>(tiles, (int64_t)kNumSMs * per_sm);
@@ -390,12 +386,8 @@ static int launch_apply(int B, int C, int N, const float* logits, const float* e
   if (ApplySmem(C, 2).bytes() > (size_t)112 * 1024) nbuf = 1;  // keep two CTAs per SM
   const ApplySmem L(C, nbuf);
   const size_t smem = L.bytes();
-  static size_t configured = 0;
-  if (smem > configured) {
-    cudaError_t e = cudaFuncSetAttribute(transition_apply_kernel<BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) { set_error("transition_apply: cudaFuncSetAttribute(%zu): %s", smem, cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
-    configured = smem;
-  }
+  static DynSmem ds;  // per instantiation
+  if (int rc = ds.need(transition_apply_kernel<BWD>, smem, "transition_apply")) return rc;
   const int64_t tiles = ((int64_t)B * N + kApplyTile - 1) / kApplyTile;
   const int per_sm = smem > 110 * 1024 ? 1 : (smem > 72 * 1024 ? 2 : (smem > 54 * 1024 ? 3 : 4));
   const int64_t cap = (int64_t)kNumSMs * per_sm;

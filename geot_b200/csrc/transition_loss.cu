@@ -347,12 +347,8 @@ GEOT_API int geot_manifold_loss_forward(int B, int N, int D, int C, int k, const
   const int grid = (int)(want < (int64_t)kNumSMs * 8 ? want : (int64_t)kNumSMs * 8);
   const size_t smem = (size_t)8 * C * C * sizeof(float);
   if (smem > 48 * 1024) {
-    static size_t configured = 0;
-    if (smem > configured) {
-      cudaError_t e = cudaFuncSetAttribute(manifold_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      if (e != cudaSuccess) { set_error("manifold_loss_forward: cudaFuncSetAttribute(%zu): %s", smem, cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
-      configured = smem;
-    }
+    static DynSmem ds;
+    if (int rc = ds.need(manifold_fwd_kernel, smem, "manifold_loss_forward")) return rc;
   }
   manifold_fwd_kernel<<<grid, 256, smem, s>>>(B, N, D, C * C, k, points, labels, insT, idx,
                                               1.0f / (2.0f * (sigma * sigma)), mode, coef, per_point);

@@ -12,6 +12,11 @@ torch.distributed (NCCL over NVLink on the GPU box, gloo in the CPU tests):
   allreduce_grads      one packed fp32 all_reduce(SUM) for a list of parameters' .grad (T predictor: C*C*2C floats),
                        optionally on a side stream so it overlaps the rest of the backward
 
+  StatsExchange        the three above fused around ONE collective per step: a packed record per rank
+                       (csrc/stats_exchange.cu: geot_stats_pack), one all_gather_into_tensor on a side stream, one
+                       combine kernel (geot_stats_combine: arg-max pick + fixed-rank-order sums) - what a training
+                       step uses; the three separate functions stay as the readable definition and for the gloo tests
+
 The reference reduces none of this (single process, train.py:7); these semantics are this project's definition.
 """
 from __future__ import annotations
@@ -124,3 +129,81 @@ class GradAllReduce:
                 p.grad.copy_(g)
             off += n
         self._buf = None
+
+
+class StatsExchange:
+    """All per-step statistics of the transition-matrix path in ONE collective (CUDA tensors; NCCL).
+
+        ex = StatsExchange(C, params=t_predictor.parameters())
+        ...
+        ex.launch(class_T_local, best_val_local, cm, c_num)     # after backward: packs (incl. the params' .grad),
+                                                                 # all-gathers on a side stream
+        ...                                                      # anything that does not need the results
+        class_T, cm, c_num = ex.wait()                           # combined values; params' .grad now hold the mean
+
+    Equivalent to combine_class_T + allreduce_class_means + GradAllReduce (tests/test_multidevice_gpu.py), with
+    6 launches and one collective per step instead of ~50 tensor ops and three.  World size 1: a pass-through."""
+
+    def __init__(self, num_classes, params=None, group=None, average=True):
+        self.C = int(num_classes)
+        self.params = [p for p in (params or []) if p.requires_grad]
+        self.P = sum(p.numel() for p in self.params)
+        self.group, self.average = group, average
+        self._stream = None
+        self._rec = self._all = self._out = None
+        self._pending = None
+
+    def _buffers(self, dev):
+        from . import _lib
+        if self._rec is None or self._rec.device != dev:
+            W = _world(self.group)
+            L = int(_lib.lib().geot_stats_record_floats(self.C, self.P))
+            self._rec = torch.empty((L,), dtype=torch.float32, device=dev)
+            self._all = torch.empty((W, L), dtype=torch.float32, device=dev)
+            self._grads = torch.empty((max(self.P, 1),), dtype=torch.float32, device=dev)
+            self._stream = torch.cuda.Stream(device=dev)
+        return self._rec, self._all
+
+    def launch(self, class_T, best_val, cm, c_num):
+        from . import _lib
+        W = _world(self.group)
+        if W == 1:
+            self._pending = (class_T, cm, c_num, None)
+            return self
+        dev = _lib.check_cuda(class_T, best_val, cm, c_num)
+        rec, gathered = self._buffers(dev)
+        cur = torch.cuda.current_stream(dev)
+        self._stream.wait_stream(cur)
+        with _lib.on_device(dev), torch.cuda.stream(self._stream):
+            if self.P:
+                views = [(p.grad if p.grad is not None else torch.zeros_like(p)).reshape(-1) for p in self.params]
+                torch.cat(views, out=self._grads)
+            _lib.call("geot_stats_pack", self.C, self.P, _lib.ptr(class_T), _lib.ptr(best_val), _lib.ptr(cm), _lib.ptr(c_num),
+                      _lib.ptr(self._grads) if self.P else None, _lib.ptr(rec), _lib.stream_ptr())
+            dist.all_gather_into_tensor(gathered.view(-1), rec, group=self.group)
+            out_T, out_cm, out_cn = torch.empty_like(class_T), cm.clone(), torch.empty_like(c_num)
+            _lib.call("geot_stats_combine", W, self.C, self.P, _lib.ptr(gathered), 1.0 / W if self.average else 1.0,
+                      _lib.ptr(out_T), _lib.ptr(out_cm), _lib.ptr(out_cn), _lib.ptr(self._grads) if self.P else None,
+                      _lib.stream_ptr())
+        for t in (class_T, best_val, cm, c_num):
+            t.record_stream(self._stream)
+        self._pending = (out_T, out_cm, out_cn, dev)
+        return self
+
+    def wait(self):
+        assert self._pending is not None, "StatsExchange.wait() without launch()"
+        out_T, out_cm, out_cn, dev = self._pending
+        self._pending = None
+        if dev is None:
+            return out_T, out_cm, out_cn
+        torch.cuda.current_stream(dev).wait_stream(self._stream)
+        if self.P:
+            off, views = 0, []
+            for p in self.params:
+                views.append(self._grads[off:off + p.numel()].view_as(p))
+                off += p.numel()
+            missing = [p for p in self.params if p.grad is None]
+            for p in missing:
+                p.grad = torch.empty_like(p)
+            torch._foreach_copy_([p.grad for p in self.params], views)
+        return out_T, out_cm, out_cn

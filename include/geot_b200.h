@@ -133,7 +133,8 @@ int geot_gather_rows(int B, int N, int M, int D, const float* src, const int* id
  * the composite. */
 int geot_group_xyz_relative(int B, int N, int M, int nsample, const float* xyz, const float* new_xyz,
                             const int* idx, int relative, float divisor, float* out, geot_stream_t stream);
-/* testing / A-B timing (process-wide switch; results are identical): mode 1 = always the direct kernels (L2 gathers,
+/* testing / A-B timing (a THREAD-LOCAL override, like the error slot: it affects only later calls of the calling thread;
+ * results are identical): mode 1 = always the direct kernels (L2 gathers,
  * brute-force three_nn, warp-per-point transition_apply, ...), mode 2 = the staged / grid kernels wherever their hard
  * limits allow, ignoring the work-size heuristics, mode 3 = three_interpolate forward without its channel-interleaved
  * kernel (the plain row-staged one instead), mode 0 = default dispatch. */
@@ -350,6 +351,22 @@ int geot_interp_argmax(int B, int C, int m, int n, const float* points, const in
                        int64_t* pred, float* score, geot_stream_t stream);
 int geot_seg_counts(int64_t n, int C, const int64_t* pred, const int64_t* label, int64_t* counts,
                     geot_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Multi-GPU statistics exchange (no reference counterpart: the reference is single-process,
+ * examples/segmentation/train.py:7, and reduces nothing).  One packed record per rank around ONE all-gather:
+ *   record = [ best_val (C) | class_T (C*C) | cm * c_num (C*C) | c_num (C) | grads (P) ],  geot_stats_record_floats(C,P)
+ * geot_stats_pack writes this rank's record; geot_stats_combine reads the W gathered records (W, L) and writes the
+ * global class-anchor rows (arg-max of best_val over ranks, lowest rank on ties = the single-process first-max of
+ * train.py:509-526 over the concatenated batch), the count-weighted class means / summed counts of
+ * cal_mean_feature (train.py:884-895) and grads = grad_scale * sum over ranks, all in fixed rank order (every rank
+ * computes identical bits).  grads may be NULL in both calls (P floats are then zero-filled / ignored).
+ * --------------------------------------------------------------------------------------------- */
+int64_t geot_stats_record_floats(int C, int64_t P);
+int geot_stats_pack(int C, int64_t P, const float* class_T, const float* best_val, const float* cm, const float* c_num,
+                    const float* grads, float* record, geot_stream_t stream);
+int geot_stats_combine(int W, int C, int64_t P, const float* gathered, float grad_scale, float* class_T, float* cm,
+                       float* c_num, float* grads, geot_stream_t stream);
 
 #ifdef __cplusplus
 }
