@@ -171,20 +171,27 @@ class on_device:
         return False
 
 
-def check_cuda(*tensors):
-    """Every tensor must live on one CUDA device and be contiguous; returns that device."""
+def check_cuda(*f32, i32=(), i64=()):
+    """Every tensor must live on one CUDA device, be contiguous and have the dtype the kernels read it as:
+    positional tensors float32, `i32=` int32 (indices, offsets), `i64=` int64 (labels).  Returns the device.
+    The C ABI takes raw pointers, so a float64 cloud, half features or int64 indices would otherwise be silently
+    reinterpreted; the reference's extensions raise on these too (CHECK_IS_FLOAT / .data<float>(), utils.h:8-28)."""
     dev = None
-    for t in tensors:
-        if t is None:
-            continue
-        if not t.is_cuda:
-            raise GeotError("geot_b200 ops are CUDA-only (sm_100a); got a CPU tensor — there is no CPU fallback")
-        if not t.is_contiguous():
-            raise GeotError("geot_b200 ops need contiguous tensors (the reference asserts the same, group.py:88-89)")
-        if dev is None:
-            dev = t.device
-        elif t.device != dev:
-            raise GeotError(f"tensors on different devices: {dev} vs {t.device}")
+    for group, want in ((f32, torch.float32), (i32, torch.int32), (i64, torch.int64)):
+        for t in group:
+            if t is None:
+                continue
+            if not t.is_cuda:
+                raise GeotError("geot_b200 ops are CUDA-only (sm_100a); got a CPU tensor — there is no CPU fallback")
+            if t.dtype is not want:
+                raise GeotError(f"geot_b200: expected a {want} tensor, got {t.dtype} (shape {tuple(t.shape)}); "
+                                "coordinates / features / weights are float32, indices and offsets int32, labels int64")
+            if not t.is_contiguous():
+                raise GeotError("geot_b200 ops need contiguous tensors (the reference asserts the same, group.py:88-89)")
+            if dev is None:
+                dev = t.device
+            elif t.device != dev:
+                raise GeotError(f"tensors on different devices: {dev} vs {t.device}")
     return dev
 
 

@@ -17,6 +17,15 @@ _i32 = torch.int32
 _f32 = torch.float32
 
 
+def _wrote(*tensors):
+    """The kernels write through raw pointers, which does not touch torch's version counter.  Caches keyed on a
+    tensor's version (the scatter plan of an idx tensor, the FPS prefix cache) would not notice a caller-provided
+    `out=` buffer being refilled, so those paths bump the counter explicitly."""
+    for t in tensors:
+        if t is not None:
+            torch.autograd.graph.increment_version(t)
+
+
 def _as_f32(t):
     return t if t.dtype == _f32 else t.float()
 
@@ -30,8 +39,9 @@ def _as_i32(t):
 # --------------------------------------------------------------------------------------------------
 def furthest_point_sampling(xyz, npoint, flags=0, temp=None, out=None):
     """xyz (B,N,3) fp32 -> idx (B,npoint) int32.  flags: _lib.GEOT_FPS_* (which reference kernel to match)."""
-    dev = check_cuda(xyz, temp, out)
+    dev = check_cuda(xyz, temp, i32=(out,))
     B, N, _ = xyz.shape
+    _wrote(out)
     with on_device(dev):
         if out is None:
             out = torch.empty((B, npoint), dtype=_i32, device=dev)
@@ -44,8 +54,9 @@ def furthest_point_sampling(xyz, npoint, flags=0, temp=None, out=None):
 
 def furthestsampling(xyz, offset, new_offset, weights=None, n_max=None, m_total=None, tmp=None, out=None, flags=0):
     """Offset-format FPS: xyz (n,3), cumulative int32 offset/new_offset (b) -> GLOBAL idx (m_total)."""
-    dev = check_cuda(xyz, offset, new_offset, weights, tmp, out)
+    dev = check_cuda(xyz, weights, tmp, i32=(offset, new_offset, out))
     n, b = xyz.shape[0], offset.shape[0]
+    _wrote(out)
     with on_device(dev):
         if n_max is None or m_total is None:
             # one host sync, like the reference's own Python (pointops.py:69-72 reads offset on the host)
@@ -68,9 +79,10 @@ def ball_query(new_xyz, xyz, radius, nsample, out=None, workspace=None, use_grid
     """new_xyz (B,M,3), xyz (B,N,3) -> idx (B,M,nsample) int32.  `workspace`: a uint8 tensor of at least
     geot_ball_query_workspace_bytes(B,N) bytes (allocated here when None); use_grid=False forces the
     index-order scan for every cloud (same result; testing / A-B timing)."""
-    dev = check_cuda(new_xyz, xyz, out)
+    dev = check_cuda(new_xyz, xyz, i32=(out,))
     B, N, _ = xyz.shape
     M = new_xyz.shape[1]
+    _wrote(out)
     with on_device(dev):
         if out is None:
             out = torch.empty((B, M, nsample), dtype=_i32, device=dev)
@@ -83,8 +95,9 @@ def ball_query(new_xyz, xyz, radius, nsample, out=None, workspace=None, use_grid
 
 
 def ballquery_offset(radius, nsample, xyz, new_xyz, offset, new_offset, out=None):
-    dev = check_cuda(xyz, new_xyz, offset, new_offset, out)
+    dev = check_cuda(xyz, new_xyz, i32=(offset, new_offset, out))
     m, b = new_xyz.shape[0], offset.shape[0]
+    _wrote(out)
     with on_device(dev):
         if out is None:
             out = torch.empty((m, nsample), dtype=_i32, device=dev)
@@ -97,8 +110,9 @@ def knnquery(nsample, xyz, new_xyz, offset=None, new_offset=None, n_per=0, m_per
 
     offset/new_offset given: offset format (ragged).  Otherwise batched: xyz is (b*n_per,3) and
     new_xyz (b*m_per,3)."""
-    dev = check_cuda(xyz, new_xyz, offset, new_offset, idx, dist2)
+    dev = check_cuda(xyz, new_xyz, dist2, i32=(offset, new_offset, idx))
     m = new_xyz.shape[0]
+    _wrote(idx, dist2)
     with on_device(dev):
         if offset is not None:
             b = offset.shape[0]
@@ -122,7 +136,7 @@ def knnquery(nsample, xyz, new_xyz, offset=None, new_offset=None, n_per=0, m_per
 # --------------------------------------------------------------------------------------------------
 def group_points(points, idx, out=None):
     """points (B,C,N), idx (B,M,ns) -> (B,C,M,ns)."""
-    dev = check_cuda(points, idx, out)
+    dev = check_cuda(points, out, i32=(idx,))
     B, Cc, N = points.shape
     _, M, ns = idx.shape
     with on_device(dev):
@@ -134,7 +148,8 @@ def group_points(points, idx, out=None):
 
 def gather_rows(src, idx, out=None):
     """Point-major gather: src (B,N,D), idx (B,M) -> (B,M,D); D=3: new_xyz = xyz[fps_idx] without the two transposes."""
-    dev = check_cuda(src, idx, out)
+    dev = check_cuda(src, out, i32=(idx,))
+    _wrote(out)
     B, N, D = src.shape
     M = idx.shape[1]
     with on_device(dev):
@@ -147,7 +162,7 @@ def gather_rows(src, idx, out=None):
 def group_xyz_relative(xyz, new_xyz, idx, relative=True, divisor=0.0, out=None):
     """Fused xyz grouping of QueryAndGroup: xyz (B,N,3), new_xyz (B,M,3), idx (B,M,ns) -> (B,3,M,ns) =
     (xyz[idx] - new_xyz) / divisor, without the (B,3,N) transpose copy or separate subtract / divide passes."""
-    dev = check_cuda(xyz, new_xyz, idx, out)
+    dev = check_cuda(xyz, new_xyz, out, i32=(idx,))
     B, N, _ = xyz.shape
     M, ns = idx.shape[1], idx.shape[2]
     with on_device(dev):
@@ -159,9 +174,10 @@ def group_xyz_relative(xyz, new_xyz, idx, relative=True, divisor=0.0, out=None):
 
 def gather_points(points, idx, out=None):
     """points (B,C,N), idx (B,M) -> (B,C,M)."""
-    dev = check_cuda(points, idx, out)
+    dev = check_cuda(points, out, i32=(idx,))
     B, Cc, N = points.shape
     M = idx.shape[1]
+    _wrote(out)
     with on_device(dev):
         if out is None:
             out = torch.empty((B, Cc, M), dtype=_f32, device=dev)
@@ -178,7 +194,7 @@ class ScatterPlan:
     def __init__(self, idx, B, N, pieces=1):
         """pieces > 1 (only for group_points_grad, see grouping_plan): one CSR per (cloud, piece of the neighbour
         list) - the same build over the same idx buffer viewed as (B*pieces, E/pieces)."""
-        dev = check_cuda(idx)
+        dev = check_cuda(i32=(idx,))
         self.pieces = int(pieces)
         self.clouds = B
         E = idx.numel() // max(B, 1)
@@ -240,7 +256,8 @@ def gather_points_grad(grad_out, plan, N, out=None):
 # --------------------------------------------------------------------------------------------------
 def three_nn(unknown, known, dist2=None, idx=None):
     """unknown (B,n,3), known (B,m,3) -> SQUARED dist2 (B,n,3), idx (B,n,3) int32."""
-    dev = check_cuda(unknown, known, dist2, idx)
+    dev = check_cuda(unknown, known, dist2, i32=(idx,))
+    _wrote(dist2, idx)
     B, n, _ = unknown.shape
     m = known.shape[1]
     with on_device(dev):
@@ -254,7 +271,7 @@ def three_nn(unknown, known, dist2=None, idx=None):
 
 def three_interpolate(points, idx, weight, out=None):
     """points (B,C,m), idx/weight (B,n,3) -> (B,C,n)."""
-    dev = check_cuda(points, idx, weight, out)
+    dev = check_cuda(points, weight, out, i32=(idx,))
     B, Cc, m = points.shape
     n = idx.shape[1]
     with on_device(dev):
@@ -286,7 +303,7 @@ def interp_weights(dist2, want_dist=False):
 
 def interp_argmax(points, idx, weight, want_score=False):
     """points (B,C,m), idx/weight (B,n,3) -> pred (B,n) int64 = argmax_c of the 3-neighbour blend [, score (B,n)]."""
-    dev = check_cuda(points, idx, weight)
+    dev = check_cuda(points, weight, i32=(idx,))
     B, Cc, m = points.shape
     n = idx.shape[1]
     with on_device(dev):
@@ -298,7 +315,7 @@ def interp_argmax(points, idx, weight, want_score=False):
 
 def seg_counts(pred, label, num_classes):
     """pred, label (n) int64 -> counts (3C+2) int64: inter[C] | pred_cnt[C] | label_cnt[C] | correct | out-of-range."""
-    dev = check_cuda(pred, label)
+    dev = check_cuda(i64=(pred, label))
     with on_device(dev):
         counts = torch.empty((3 * num_classes + 2,), dtype=torch.int64, device=dev)
         call("geot_seg_counts", pred.numel(), num_classes, ptr(pred), ptr(label), ptr(counts), stream_ptr())
@@ -309,7 +326,7 @@ def seg_counts(pred, label, num_classes):
 # offset-format (channel-last) ops
 # --------------------------------------------------------------------------------------------------
 def grouping_forward(input, idx, out=None):
-    dev = check_cuda(input, idx, out)
+    dev = check_cuda(input, out, i32=(idx,))
     m, ns = idx.shape
     c = input.shape[1]
     with on_device(dev):
@@ -330,7 +347,7 @@ def grouping_backward(grad_output, plan, n, out=None):
 
 
 def interpolation_forward(input, idx, weight, out=None):
-    dev = check_cuda(input, idx, weight, out)
+    dev = check_cuda(input, weight, out, i32=(idx,))
     n, k = idx.shape
     c = input.shape[1]
     with on_device(dev):
@@ -351,7 +368,7 @@ def interpolation_backward(grad_output, weight, plan, m, k, out=None):
 
 
 def subtraction_forward(input1, input2, idx, out=None):
-    dev = check_cuda(input1, input2, idx, out)
+    dev = check_cuda(input1, input2, out, i32=(idx,))
     n, ns = idx.shape
     c = input1.shape[1]
     with on_device(dev):
@@ -374,7 +391,7 @@ def subtraction_backward(grad_output, plan, g1=None, g2=None):
 
 
 def aggregation_forward(input, position, weight, idx, out=None):
-    dev = check_cuda(input, position, weight, idx, out)
+    dev = check_cuda(input, position, weight, out, i32=(idx,))
     n, ns, c = position.shape
     w_c = weight.shape[2]
     with on_device(dev):
@@ -385,7 +402,7 @@ def aggregation_forward(input, position, weight, idx, out=None):
 
 
 def aggregation_backward(input, position, weight, idx, grad_output, plan, gi=None, gp=None, gw=None):
-    dev = check_cuda(input, position, weight, idx, grad_output, gi, gp, gw)
+    dev = check_cuda(input, position, weight, grad_output, gi, gp, gw, i32=(idx,))
     n, ns, c = position.shape
     w_c = weight.shape[2]
     with on_device(dev):
@@ -460,7 +477,7 @@ MANIFOLD_3D, MANIFOLD_FEATURE = 0, 1
 
 def manifold_loss_forward(points, labels, insT, idx, sigma, mode):
     """points (B,N,D), labels (B,N) int64, insT (B*N,C,C), idx (B,N,k) int32 local -> (loss (1,), coef (B*N,k))."""
-    dev = check_cuda(points, labels, insT, idx)
+    dev = check_cuda(points, insT, i32=(idx,), i64=(labels,))
     B, N, D = points.shape
     Cc, k = insT.shape[1], idx.shape[2]
     with on_device(dev):
@@ -473,7 +490,7 @@ def manifold_loss_forward(points, labels, insT, idx, sigma, mode):
 
 
 def manifold_loss_backward(insT, idx, coef, plan, grad_loss):
-    dev = check_cuda(insT, idx, coef, grad_loss)
+    dev = check_cuda(insT, coef, grad_loss, i32=(idx,))
     B, N, k = idx.shape
     Cc = insT.shape[1]
     with on_device(dev):
@@ -498,7 +515,7 @@ def class_pick(pred_u):
 
 def class_t_step(class_T, ema_t, sigma, label_proj, geo_lambda, ema_decay):
     """-> (ema_t_corr, new ema_t); label_proj int32 (C) on the device."""
-    dev = check_cuda(class_T, ema_t, sigma, label_proj)
+    dev = check_cuda(class_T, ema_t, sigma, i32=(label_proj,))
     Cc = class_T.shape[0]
     with on_device(dev):
         corr = torch.empty_like(class_T)
@@ -509,7 +526,7 @@ def class_t_step(class_T, ema_t, sigma, label_proj, geo_lambda, ema_decay):
 
 def mean_feature_update(probs, target, cm, c_num):
     """In-place running class-mean update (train.py:884-895 semantics); probs (BN,C), target (BN) int64."""
-    dev = check_cuda(probs, target, cm, c_num)
+    dev = check_cuda(probs, cm, c_num, i64=(target,))
     BN, Cc = probs.shape
     with on_device(dev):
         nb = max(int(_lib.lib().geot_class_pick_workspace_bytes(Cc)), 512)
@@ -523,7 +540,7 @@ def mean_feature_update(probs, target, cm, c_num):
 # --------------------------------------------------------------------------------------------------
 def poly1_focal_forward(logits, labels, conf, mask, thresh, epsilon, alpha, gamma):
     """logits (B,C,N) f32, labels (B,N) int64, conf (B,N) f32 or None, mask (B,N) f32 or None -> (loss (1,), denom (1,))."""
-    dev = check_cuda(logits, labels, conf, mask)
+    dev = check_cuda(logits, conf, mask, i64=(labels,))
     B, Cc, N = logits.shape
     with on_device(dev):
         loss = torch.empty((1,), dtype=_f32, device=dev)
@@ -536,7 +553,7 @@ def poly1_focal_forward(logits, labels, conf, mask, thresh, epsilon, alpha, gamm
 
 
 def poly1_focal_backward(logits, labels, conf, mask, thresh, epsilon, alpha, gamma, denom, grad_loss):
-    dev = check_cuda(logits, labels, conf, mask, denom, grad_loss)
+    dev = check_cuda(logits, conf, mask, denom, grad_loss, i64=(labels,))
     B, Cc, N = logits.shape
     with on_device(dev):
         g = torch.empty_like(logits)
@@ -547,7 +564,7 @@ def poly1_focal_backward(logits, labels, conf, mask, thresh, epsilon, alpha, gam
 
 def poly1_focal_t_forward(logits, labels, conf, mask, pred_t, thresh, epsilon, alpha, gamma):
     """Poly1FocalLoss_U_T: as poly1_focal_forward with every point scaled by conf / pred_t[b, label, n]."""
-    dev = check_cuda(logits, labels, conf, mask, pred_t)
+    dev = check_cuda(logits, conf, mask, pred_t, i64=(labels,))
     B, Cc, N = logits.shape
     with on_device(dev):
         loss = torch.empty((1,), dtype=_f32, device=dev)
@@ -560,7 +577,7 @@ def poly1_focal_t_forward(logits, labels, conf, mask, pred_t, thresh, epsilon, a
 
 
 def poly1_focal_t_backward(logits, labels, conf, mask, pred_t, thresh, epsilon, alpha, gamma, denom, grad_loss):
-    dev = check_cuda(logits, labels, conf, mask, pred_t, denom, grad_loss)
+    dev = check_cuda(logits, conf, mask, pred_t, denom, grad_loss, i64=(labels,))
     B, Cc, N = logits.shape
     with on_device(dev):
         g = torch.empty_like(logits)
@@ -572,7 +589,7 @@ def poly1_focal_t_backward(logits, labels, conf, mask, pred_t, thresh, epsilon, 
 
 def graph_feature(x_k, x_q, idx):
     """x_k (B,C,Nk), x_q (B,C,Nq), idx (B,Nq,k) int32 -> (B,2C,Nq,k) = cat(x_k[.., idx] - x_q, x_q)."""
-    dev = check_cuda(x_k, x_q, idx)
+    dev = check_cuda(x_k, x_q, i32=(idx,))
     B, Cc, Nk = x_k.shape
     Nq, k = idx.shape[1], idx.shape[2]
     with on_device(dev):

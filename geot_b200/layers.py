@@ -66,10 +66,22 @@ def fps(data, number):
 
 
 class _PlanCache:
-    """One scatter plan per idx tensor, shared by every grouping_operation that used it."""
+    """One scatter plan per idx tensor, shared by every grouping_operation that used it.  The plan is only valid for
+    the CONTENT it was built from: it remembers the tensor's version counter (every in-place write - torch ops and the
+    library's own `out=` paths, which bump it explicitly - changes it) and storage address, and is rebuilt otherwise."""
 
     def __init__(self):
         self.plan = None
+        self.version = -1
+        self.data_ptr = 0
+
+    def get(self, idx, N, version_at_forward):
+        if idx._version != version_at_forward:
+            raise RuntimeError("grouping_operation: idx was modified in place between forward and backward")
+        if self.plan is None or self.plan.N != N or self.version != idx._version or self.data_ptr != idx.data_ptr():
+            self.plan = F_.grouping_plan(idx, idx.shape[0], N)
+            self.version, self.data_ptr = idx._version, idx.data_ptr()
+        return self.plan
 
 
 class GroupingOperation(Function):
@@ -87,15 +99,13 @@ class GroupingOperation(Function):
                 idx._geot_plan_cache = cache
             except Exception:  # tensor subclasses that refuse attributes: no sharing, still correct
                 pass
-        ctx.for_backwards = (idx, N, cache)
+        ctx.for_backwards = (idx, N, cache, idx._version)
         return F_.group_points(features, idx)
 
     @staticmethod
     def backward(ctx, grad_out: torch.Tensor):
-        idx, N, cache = ctx.for_backwards
-        if cache.plan is None or cache.plan.N != N:
-            cache.plan = F_.grouping_plan(idx, idx.shape[0], N)
-        return F_.group_points_grad(grad_out.contiguous(), cache.plan, N), None
+        idx, N, cache, version = ctx.for_backwards
+        return F_.group_points_grad(grad_out.contiguous(), cache.get(idx, N, version), N), None
 
 
 grouping_operation = GroupingOperation.apply

@@ -7,6 +7,7 @@ import torch
 
 from geot_b200 import _lib, synth
 from geot_b200 import functional as F
+from tests.tolerance import assert_sum_close
 
 pytestmark = pytest.mark.gpu
 RTOL, ATOL = 1e-5, 1e-6
@@ -99,7 +100,7 @@ def test_group_points_grad_plan_resident_vs_direct(cuda, oracle):
         finally:
             _lib.lib().geot_group_points_config(0)
         assert torch.equal(res[0], res[1])
-        np.testing.assert_allclose(res[0].cpu().numpy(), exp, rtol=RTOL, atol=1e-4)
+        assert_sum_close(res[0], exp, oracle.grouping_operation_grad(np.abs(g), idx, N), what="group_points_grad")
 
 
 BALL_CASES = [("tooth", 2, 16384, 1024, 0.1, 32), ("tooth", 2, 4099, 257, 0.2, 64), ("tooth", 3, 1000, 64, 0.05, 16),
@@ -262,8 +263,9 @@ def test_group_points_grad_pieces(cuda, oracle, B, C, N, M, ns):
     got = F.group_points_grad(g, plan_q, N)
     single = F.group_points_grad(g, F.ScatterPlan(nbr, B, N), N)
     exp = oracle.grouping_operation_grad(g.cpu().numpy(), nbr.cpu().numpy(), N)
-    np.testing.assert_allclose(got.cpu().numpy(), exp, rtol=1e-4, atol=1e-4)
-    np.testing.assert_allclose(single.cpu().numpy(), exp, rtol=1e-4, atol=1e-4)
+    terms = oracle.grouping_operation_grad(np.abs(g.cpu().numpy()), nbr.cpu().numpy(), N)
+    assert_sum_close(got, exp, terms, what="group_points_grad in pieces")
+    assert_sum_close(single, exp, terms, what="group_points_grad single plan")
     _lib.lib().geot_group_points_config(1)
     try:
         direct = F.group_points_grad(g, plan_q, N)
@@ -411,9 +413,26 @@ def test_three_interpolate_grad_rows_vs_direct(cuda, oracle, B, C, m, n):
     finally:
         _lib.lib().geot_group_points_config(0)
     exp = oracle.three_interpolate_grad(g.cpu().numpy(), idx.cpu().numpy(), w.cpu().numpy(), m)
-    np.testing.assert_allclose(direct.cpu().numpy(), exp, rtol=1e-4, atol=1e-4)
-    np.testing.assert_allclose(got.cpu().numpy(), exp, rtol=1e-4, atol=1e-4)
+    terms = oracle.three_interpolate_grad(np.abs(g.cpu().numpy()), idx.cpu().numpy(), w.cpu().numpy(), m)
+    assert_sum_close(direct, exp, terms, what="three_interpolate_grad direct")
+    assert_sum_close(got, exp, terms, what="three_interpolate_grad row-resident")
     assert torch.equal(got, F.three_interpolate_grad(g, w, plan, m)), "run-to-run identical"
+
+
+def _check_aggregation(oracle, inp, pos, wt, idn, ga, plan):
+    """aggregation fwd / bwd against the oracle's double sums, each within 1e-5 of the sum of the magnitudes of its
+    terms (the oracle evaluated on |inputs|): out = sum_s (inp[idx]+pos)*w, grad_input = scatter of ga*w,
+    grad_position = ga*w (one product: exact), grad_weight = sum_c ga*(inp[idx]+pos)."""
+    a = np.abs
+    assert_sum_close(F.aggregation_forward(cu(inp), cu(pos), cu(wt), cu(idn)), oracle.aggregation_forward(inp, pos, wt, idn),
+                     oracle.aggregation_forward(a(inp), a(pos), a(wt), idn), what="aggregation_forward")
+    gi, gp, gw = F.aggregation_backward(cu(inp), cu(pos), cu(wt), cu(idn), cu(ga), plan)
+    ei, ep, ew = oracle.aggregation_backward(inp, pos, wt, idn, ga)
+    ti, _, tw = oracle.aggregation_backward(a(inp), a(pos), a(wt), idn, a(ga))
+    assert_sum_close(gi, ei, ti, what="aggregation grad_input")
+    assert np.array_equal(gp.cpu().numpy(), ep)
+    assert_sum_close(gw, ew, tw, what="aggregation grad_weight")
+    return gi, gp, gw
 
 
 @pytest.mark.parametrize("c", [32, 7])
@@ -447,14 +466,7 @@ def test_offset_channel_last_ops(cuda, oracle, c):
         wc = c // 4
         pos = rng.standard_normal((n, ns, c)).astype(np.float32)
         wt = rng.standard_normal((n, ns, wc)).astype(np.float32)
-        np.testing.assert_allclose(F.aggregation_forward(cu(inp), cu(pos), cu(wt), cu(idn)).cpu().numpy(),
-                                   oracle.aggregation_forward(inp, pos, wt, idn), rtol=1e-4, atol=1e-5)
-        ga = rng.standard_normal((n, c)).astype(np.float32)
-        gi, gp, gw = F.aggregation_backward(cu(inp), cu(pos), cu(wt), cu(idn), cu(ga), plan)
-        ei, ep, ew = oracle.aggregation_backward(inp, pos, wt, idn, ga)
-        np.testing.assert_allclose(gi.cpu().numpy(), ei, rtol=1e-4, atol=1e-5)
-        assert np.array_equal(gp.cpu().numpy(), ep)
-        np.testing.assert_allclose(gw.cpu().numpy(), ew, rtol=1e-4, atol=1e-5)
+        _check_aggregation(oracle, inp, pos, wt, idn, rng.standard_normal((n, c)).astype(np.float32), plan)
 
 
 @pytest.mark.parametrize("c,wc", [(64, 8), (32, 4), (48, 12), (6, 3), (128, 16), (256, 32)])
@@ -468,14 +480,8 @@ def test_aggregation_vector_and_scalar_paths(cuda, oracle, c, wc):
     idn = rng.integers(0, n, (n, ns)).astype(np.int32)
     pos = rng.standard_normal((n, ns, c)).astype(np.float32)
     wt = rng.standard_normal((n, ns, wc)).astype(np.float32)
-    np.testing.assert_allclose(F.aggregation_forward(cu(inp), cu(pos), cu(wt), cu(idn)).cpu().numpy(),
-                               oracle.aggregation_forward(inp, pos, wt, idn), rtol=1e-4, atol=1e-5)
     ga = rng.standard_normal((n, c)).astype(np.float32)
     plan = F.ScatterPlan(cu(idn), 1, n)
-    gi, gp, gw = F.aggregation_backward(cu(inp), cu(pos), cu(wt), cu(idn), cu(ga), plan)
-    ei, ep, ew = oracle.aggregation_backward(inp, pos, wt, idn, ga)
-    np.testing.assert_allclose(gi.cpu().numpy(), ei, rtol=1e-4, atol=1e-5)
-    assert np.array_equal(gp.cpu().numpy(), ep)
-    np.testing.assert_allclose(gw.cpu().numpy(), ew, rtol=1e-4, atol=2e-5)
+    gi, gp, gw = _check_aggregation(oracle, inp, pos, wt, idn, ga, plan)
     gi2, gp2, gw2 = F.aggregation_backward(cu(inp), cu(pos), cu(wt), cu(idn), cu(ga), plan)
     assert torch.equal(gi, gi2) and torch.equal(gw, gw2)
