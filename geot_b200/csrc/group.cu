@@ -326,6 +326,280 @@ plan_sort_heavy_kernel(int N, int64_t E, const int* __restrict__ row_ptr, const 
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Fused plan build: the whole CSR of one cloud by ONE CTA in shared memory (counts -> scan -> fill -> per-segment
+// sort), one launch instead of two memsets and five kernels.  In training every idx tensor is new each step and the
+// reference API has no plan argument (the facades rebuild the plan per backward call), so the build is on the
+// critical path of every backward: 0.20-0.28 ms with the multi-kernel path at the bench shape, launch- and
+// global-atomic-bound.  Here the counters are shared-memory atomics (N+1 ints), the scatter goes straight into `perm`
+// and every segment is then sorted in place: short ones by a thread (insertion, <= kPlanSmall entries), long ones
+// (first-hit padding of ball_query, empty balls) by the whole CTA through a bitmap over the source universe [0,E).
+// Same output as the multi-kernel path, bit for bit (ascending sources per target).  Limits: N <= kFusedMaxN targets
+// per cloud, E <= kFusedMaxE sources per cloud; larger problems (the offset-format ops with one 10^5-point segment)
+// keep the multi-kernel path, where the work amortises the launches.
+// ---------------------------------------------------------------------------------------------
+constexpr int kFusedMaxN = 40960;          // (N+1) counters: 160 KB
+constexpr int kFusedMaxE = 1 << 19;        // bitmap: 64 KB
+constexpr int kFusedThread = 2;            // a pair is ordered by its own thread; anything longer goes to the warp sorter
+                                           // (an insertion sort in local memory costs ~60 cycles per step and the whole
+                                           // warp waits for its longest segment: measured 70 us of the 85 us build)
+constexpr int kFusedWarp = 512;            // up to this length: rank sort by one warp (registers + shuffles); longer: CTA bitmap
+
+// Warp-cooperative sort of one segment of L <= kFusedWarp DISTINCT values, in place: every lane holds up to 16 of
+// them, rank(x) = #{y < x} by broadcasting every value to every lane; cost ~ (L/32)^2 * 32 shuffles.
+#ifdef GEOT_FPS_PROF
+__device__ long long g_plan_prof[16];
+#define PLAN_STAMP(k) do { if (blockIdx.x == 0 && threadIdx.x == 0) g_plan_prof[k] = clock64(); } while (0)
+#else
+#define PLAN_STAMP(k) do {} while (0)
+#endif
+
+// Warp-cooperative sort of one segment of L <= kFusedWarp DISTINCT values, in place: every lane holds NV of them,
+// rank(x) = #{y < x} by broadcasting every value to every lane; NV * 32 shuffles, NV * NV * 32 compares.
+template <int NV, typename T>
+__device__ __forceinline__ void plan_warp_sort_t(T* __restrict__ seg, int L, int lane) {
+  int v[NV], r[NV];
+#pragma unroll
+  for (int i = 0; i < NV; i++) {
+    v[i] = (lane + 32 * i < L) ? (int)seg[lane + 32 * i] : 0x7fffffff;
+    r[i] = 0;
+  }
+#pragma unroll
+  for (int j = 0; j < NV; j++) {
+    const int live = min(32, L - 32 * j);  // lanes that hold a value of row j (uniform): short segments cost 2 L instructions
+#pragma unroll 4
+    for (int src = 0; src < live; src++) {
+      const int y = __shfl_sync(0xffffffffu, v[j], src);
+#pragma unroll
+      for (int i = 0; i < NV; i++) r[i] += (y < v[i]) ? 1 : 0;
+    }
+  }
+  __syncwarp();
+#pragma unroll
+  for (int i = 0; i < NV; i++)
+    if (lane + 32 * i < L) seg[r[i]] = (T)v[i];
+}
+template <typename T>
+__device__ __noinline__ void plan_warp_sort(T* __restrict__ seg, int L, int lane) {
+  const int nv = (L + 31) >> 5;  // values per lane, uniform across the warp
+  if (nv <= 1) plan_warp_sort_t<1>(seg, L, lane);
+  else if (nv <= 2) plan_warp_sort_t<2>(seg, L, lane);
+  else if (nv <= 3) plan_warp_sort_t<3>(seg, L, lane);
+  else if (nv <= 4) plan_warp_sort_t<4>(seg, L, lane);
+  else if (nv <= 6) plan_warp_sort_t<6>(seg, L, lane);
+  else if (nv <= 8) plan_warp_sort_t<8>(seg, L, lane);
+  else if (nv <= 12) plan_warp_sort_t<12>(seg, L, lane);
+  else plan_warp_sort_t<16>(seg, L, lane);
+}
+
+// One thread sorts one segment of 3..16 values in registers: Batcher's odd-even merge network (63 compare-exchanges, no
+// local memory, no divergence inside a warp - every lane runs the same 126 min/max instructions on its own segment).
+template <typename T>
+__device__ __forceinline__ void plan_thread_sort16(T* __restrict__ seg, int L) {
+  int v[16];
+#pragma unroll
+  for (int i = 0; i < 16; i++) v[i] = i < L ? (int)seg[i] : 0x7fffffff;
+#define PLAN_CE(a, b) { const int lo_ = min(v[a], v[b]), hi_ = max(v[a], v[b]); v[a] = lo_; v[b] = hi_; }
+  PLAN_CE(0,1); PLAN_CE(2,3); PLAN_CE(0,2); PLAN_CE(1,3); PLAN_CE(1,2); PLAN_CE(4,5);
+  PLAN_CE(6,7); PLAN_CE(4,6); PLAN_CE(5,7); PLAN_CE(5,6); PLAN_CE(0,4); PLAN_CE(2,6);
+  PLAN_CE(2,4); PLAN_CE(1,5); PLAN_CE(3,7); PLAN_CE(3,5); PLAN_CE(1,2); PLAN_CE(3,4);
+  PLAN_CE(5,6); PLAN_CE(8,9); PLAN_CE(10,11); PLAN_CE(8,10); PLAN_CE(9,11); PLAN_CE(9,10);
+  PLAN_CE(12,13); PLAN_CE(14,15); PLAN_CE(12,14); PLAN_CE(13,15); PLAN_CE(13,14); PLAN_CE(8,12);
+  PLAN_CE(10,14); PLAN_CE(10,12); PLAN_CE(9,13); PLAN_CE(11,15); PLAN_CE(11,13); PLAN_CE(9,10);
+  PLAN_CE(11,12); PLAN_CE(13,14); PLAN_CE(0,8); PLAN_CE(4,12); PLAN_CE(4,8); PLAN_CE(2,10);
+  PLAN_CE(6,14); PLAN_CE(6,10); PLAN_CE(2,4); PLAN_CE(6,8); PLAN_CE(10,12); PLAN_CE(1,9);
+  PLAN_CE(5,13); PLAN_CE(5,9); PLAN_CE(3,11); PLAN_CE(7,15); PLAN_CE(7,11); PLAN_CE(3,5);
+  PLAN_CE(7,9); PLAN_CE(11,13); PLAN_CE(1,2); PLAN_CE(3,4); PLAN_CE(5,6); PLAN_CE(7,8);
+  PLAN_CE(9,10); PLAN_CE(11,12); PLAN_CE(13,14);
+#undef PLAN_CE
+#pragma unroll
+  for (int i = 0; i < 16; i++)
+    if (i < L) seg[i] = (T)v[i];
+}
+
+// T = unsigned short: the cloud's whole source list lives in shared memory while it is filled and sorted (E <= 65535)
+// and leaves by one coalesced pass; T = int: it is filled and sorted in place in global memory (longer lists).
+template <typename T>
+__global__ void __launch_bounds__(1024, 1)
+plan_build_fused_kernel(int N, int E, int list_cap, const int* __restrict__ idx_all, int* __restrict__ row_ptr_all, int* __restrict__ perm_all) {
+  constexpr bool kSmemList = sizeof(T) == 2;
+  extern __shared__ int plan_sm[];
+  int* cnt = plan_sm;                                   // N+1 counters, later cursors
+  unsigned* bm = reinterpret_cast<unsigned*>(plan_sm + N + 1);   // E bits (very long segments only)
+  const int bm_words = ((((E + 31) >> 5) + 1023) >> 10) << 10;
+  __shared__ int s_warp[32];
+  __shared__ int s_carry, s_heavy_n;
+  __shared__ int s_heavy[256];
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5, b = blockIdx.x;
+  const int* __restrict__ idx = idx_all + (int64_t)b * E;
+  int* __restrict__ row_ptr = row_ptr_all + (int64_t)b * (N + 1);
+  int* __restrict__ perm_out = perm_all + (int64_t)b * E;
+  T* __restrict__ perm = kSmemList ? reinterpret_cast<T*>(bm + bm_words) : reinterpret_cast<T*>(perm_out);
+  // work lists of the sort phase (target ids): segments of 3..16 entries / of 17..kFusedWarp entries
+  int* list16 = reinterpret_cast<int*>(bm + bm_words) + (kSmemList ? ((E + 1) >> 1) : 0);
+  int* listw = list16 + list_cap;
+  __shared__ int s_n16, s_nw;
+  PLAN_STAMP(0);
+  for (int i = t; i <= N; i += 1024) cnt[i] = 0;
+  if (t == 0) { s_carry = 0; s_heavy_n = 0; s_n16 = 0; s_nw = 0; }
+  __syncthreads();
+  PLAN_STAMP(1);
+  constexpr int U = 8;  // loads in flight per thread: the edge loops are L2-latency bound otherwise
+  for (int e0 = t; e0 < E; e0 += 1024 * U) {
+    int k[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) k[u] = (e0 + u * 1024 < E) ? __ldg(idx + e0 + u * 1024) : -1;
+#pragma unroll
+    for (int u = 0; u < U; u++)
+      if ((unsigned)k[u] < (unsigned)N) atomicAdd(&cnt[k[u] + 1], 1);   // integer: order-free
+  }
+  __syncthreads();
+  PLAN_STAMP(2);
+  // inclusive scan of cnt[0..N] (counts stored shifted by one => exclusive start offsets): every thread owns P
+  // consecutive counters (P odd: conflict-free strides), one block-wide scan of the thread totals
+  {
+    const int P = (((N + 1) + 1023) >> 10) | 1;
+    const int lo = min(t * P, N + 1), hi = min(lo + P, N + 1);
+    int tot = 0;
+    for (int i = lo; i < hi; i++) tot += cnt[i];
+    int inc = tot;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int u = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += u;
+    }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    int w = s_warp[lane], winc = w;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int u = __shfl_up_sync(0xffffffffu, winc, o);
+      if (lane >= o) winc += u;
+    }
+    int run = __shfl_sync(0xffffffffu, winc - w, warp) + inc - tot;
+    for (int i = lo; i < hi; i++) { run += cnt[i]; cnt[i] = run; }
+    __syncthreads();
+    for (int i = t; i <= N; i += 1024) row_ptr[i] = cnt[i];
+    __syncthreads();  // the fill below turns the counters into cursors: nobody may still be copying them out
+  }
+  PLAN_STAMP(3);
+  // fill: cnt[k] is the cursor of target k; afterwards cnt[k] = start of segment k+1
+  for (int e0 = t; e0 < E; e0 += 1024 * U) {
+    int k[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) k[u] = (e0 + u * 1024 < E) ? __ldg(idx + e0 + u * 1024) : -1;
+#pragma unroll
+    for (int u = 0; u < U; u++)
+      if ((unsigned)k[u] < (unsigned)N) perm[atomicAdd(&cnt[k[u]], 1)] = (T)(e0 + u * 1024);
+  }
+  __syncthreads();  // the CTA's own global writes are visible to it after the barrier
+  PLAN_STAMP(4);
+  // every segment into ascending source order.  Only ~20 % of the targets of a ball query are non-empty, so the
+  // segments are first classified into dense work lists: 3..16 entries -> one THREAD each (sorting network in
+  // registers), 17..kFusedWarp -> one WARP each (rank sort), longer -> the whole CTA through a bitmap.
+  for (int base = warp * 32; base < N; base += 1024) {
+    const int k = base + lane;
+    int s = 0, L = 0;
+    if (k < N) { s = k ? cnt[k - 1] : 0; L = cnt[k] - s; }
+    if (L == 2) {
+      T* __restrict__ seg = perm + s;
+      const T x0 = seg[0], x1 = seg[1];
+      if (x0 > x1) { seg[0] = x1; seg[1] = x0; }
+    }
+    if (L > kFusedWarp) {
+      const int slot = atomicAdd(&s_heavy_n, 1);
+      if (slot < 256) s_heavy[slot] = k;
+    }
+    const bool is16 = L >= 3 && L <= 16, isw = L > 16 && L <= kFusedWarp;
+    const unsigned m16 = __ballot_sync(0xffffffffu, is16), mw = __ballot_sync(0xffffffffu, isw);
+    int p16 = 0, pw = 0;
+    if (lane == 0) {
+      if (m16) p16 = atomicAdd(&s_n16, __popc(m16));
+      if (mw) pw = atomicAdd(&s_nw, __popc(mw));
+    }
+    p16 = __shfl_sync(0xffffffffu, p16, 0) + __popc(m16 & lanemask_lt());
+    pw = __shfl_sync(0xffffffffu, pw, 0) + __popc(mw & lanemask_lt());
+    bool overflow = false;
+    if (is16) { if (p16 < list_cap) list16[p16] = k; else overflow = true; }
+    if (isw) { if (pw < list_cap) listw[pw] = k; else overflow = true; }
+    unsigned now = __ballot_sync(0xffffffffu, overflow);  // lists full (tiny shared-memory budget): sort these right here
+    while (now) {
+      const int src = __ffs(now) - 1;
+      now &= now - 1;
+      plan_warp_sort(perm + __shfl_sync(0xffffffffu, s, src), __shfl_sync(0xffffffffu, L, src), lane);
+    }
+  }
+  __syncthreads();
+  {
+    const int n16 = min(s_n16, list_cap), nw = min(s_nw, list_cap);
+    for (int i = t; i < n16; i += 1024) {
+      const int k = list16[i], s = k ? cnt[k - 1] : 0;
+      plan_thread_sort16(perm + s, cnt[k] - s);
+    }
+    for (int i = warp; i < nw; i += 32) {
+      const int k = listw[i], s = k ? cnt[k - 1] : 0;
+      plan_warp_sort(perm + s, cnt[k] - s, lane);
+    }
+  }
+  __syncthreads();
+  PLAN_STAMP(5);
+  const int heavy_n = s_heavy_n;
+#ifdef GEOT_FPS_PROF
+  if (blockIdx.x == 0 && threadIdx.x == 0) g_plan_prof[7] = heavy_n;
+#endif
+  if (heavy_n == 0) {
+    if (kSmemList) for (int i = t; i < E; i += 1024) perm_out[i] = (int)perm[i];
+    return;
+  }
+  const int nwords = (E + 31) >> 5;
+  const int wpt = (nwords + 1023) >> 10;  // words per thread, consecutive: thread order = source order
+  // more than 256 very long segments cannot be listed: rescan the targets instead (same work, no list)
+  const int items = heavy_n <= 256 ? heavy_n : N;
+  for (int item = 0; item < items; item++) {
+    const int k = heavy_n <= 256 ? s_heavy[item] : item;
+    const int s = k ? cnt[k - 1] : 0, L = cnt[k] - s;
+    if (L <= kFusedWarp) continue;  // (only reachable in rescan mode; uniform across the CTA)
+    T* __restrict__ seg = perm + s;
+    for (int i = t; i < wpt * 1024; i += 1024) bm[i] = 0u;
+    __syncthreads();
+    for (int i = t; i < L; i += 1024) { const int v = (int)seg[i]; atomicOr(&bm[v >> 5], 1u << (v & 31)); }
+    __syncthreads();
+    int c = 0;
+    for (int i = 0; i < wpt; i++) c += __popc(bm[t * wpt + i]);
+    int inc = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += y;
+    }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    int w = s_warp[lane], winc = w;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, winc, o);
+      if (lane >= o) winc += y;
+    }
+    int o = __shfl_sync(0xffffffffu, winc - w, warp) + inc - c;
+    for (int i = 0; i < wpt; i++) {
+      unsigned word = bm[t * wpt + i];
+      while (word) {
+        seg[o++] = (T)((((t * wpt + i)) << 5) + __ffs(word) - 1);
+        word &= word - 1;
+      }
+    }
+    __syncthreads();
+  }
+  if (kSmemList) for (int i = t; i < E; i += 1024) perm_out[i] = (int)perm[i];
+  PLAN_STAMP(6);
+}
+
+#ifdef GEOT_FPS_PROF
+}  // namespace geot
+GEOT_API int geot_debug_plan_prof(long long* host16) { return (int)cudaMemcpyFromSymbol(host16, geot::g_plan_prof, 16 * sizeof(long long)); }
+namespace geot {
+#endif
+
 static inline size_t plan_align(size_t b) { return (b + 255) & ~(size_t)255; }
 struct PlanView {
   const int* row_ptr;
@@ -855,6 +1129,30 @@ GEOT_API int geot_scatter_plan_build(int B, int N, int64_t E, const int* idx, vo
   cudaStream_t s = as_stream(stream);
   int* row_ptr = reinterpret_cast<int*>(plan);
   int* perm = reinterpret_cast<int*>(reinterpret_cast<char*>(plan) + plan_rowptr_bytes(B, N));
+  // enough clouds to fill the GPU with one CTA each, or so little work that the launch count decides
+  if (N >= 1 && N <= kFusedMaxN && E >= 1 && E <= kFusedMaxE && (B >= 4 || E <= (1 << 17)) && !g_force_staged) {
+    // one CTA per cloud builds the whole CSR in shared memory (see plan_build_fused_kernel)
+    const size_t kBudget = (size_t)220 * 1024;  // + 1.2 KB of static shared memory in the kernel
+    const size_t smem = (size_t)(N + 1) * 4 + (size_t)((((E + 31) >> 5) + 1023) / 1024) * 1024 * 4;
+    const size_t smem16 = smem + (size_t)((E + 1) / 2) * 4;  // + the source list as 16-bit entries
+    static DynSmem ds_fused16, ds_fused32;
+    // the two work lists of the sort phase take what is left, at most one entry per target each
+    auto lists = [&](size_t base) { return (int)std::min<size_t>((size_t)N, (kBudget - base) / 8); };
+    if (E <= 65535 && smem16 + 8 * 256 <= kBudget) {
+      const int cap = lists(smem16);
+      if (int rc = ds_fused16.need(plan_build_fused_kernel<unsigned short>, kBudget, "scatter_plan_build")) return rc;
+      plan_build_fused_kernel<unsigned short><<<B, 1024, smem16 + (size_t)cap * 8, s>>>(N, (int)E, cap, idx, row_ptr, perm);
+      count_launch(1);
+      return check_launch("plan_build_fused_kernel<u16>");
+    }
+    if (smem + 8 * 256 <= kBudget) {
+      const int cap = lists(smem);
+      if (int rc = ds_fused32.need(plan_build_fused_kernel<int>, kBudget, "scatter_plan_build")) return rc;
+      plan_build_fused_kernel<int><<<B, 1024, smem + (size_t)cap * 8, s>>>(N, (int)E, cap, idx, row_ptr, perm);
+      count_launch(1);
+      return check_launch("plan_build_fused_kernel<int>");
+    }
+  }
   cudaError_t err = cudaMemsetAsync(row_ptr, 0, (size_t)B * (N + 1) * sizeof(int), s);
   if (err != cudaSuccess) { set_error("scatter_plan_build: memset: %s", cudaGetErrorString(err)); return GEOT_ERR_CUDA; }
   if (E > 0) {

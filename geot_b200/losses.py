@@ -95,3 +95,31 @@ class Poly1FocalLoss_U_T(nn.Module):
         if logits.dim() != 3 or pred_u_t.shape != logits.shape:
             raise ValueError("Poly1FocalLoss_U_T expects (B, C, N) logits and pred_u_t of the same shape")
         return _Poly1T.apply(logits, labels, logits_pred, mask, pred_u_t, thresh, self.epsilon, self.alpha, self.gamma)
+
+
+class Poly1FocalLoss_U_T_v1(nn.Module):
+    """openpoints/loss/build.py:690-795: the class-level variant.  Instead of receiving the corrected prediction it forms
+    it itself, `pred_u_t = (T + delta_T)^T . pred_u` (the matmul of build.py:766-770), takes beta = logits_pred /
+    pred_u_t[b, label, n] and returns `(loss, delta_T)`.  The (C x C) . (C x BN) product is a dense contraction - a plain
+    library GEMM, in the reference's own statement order so that pred_u_t has the same bits; everything after it (the
+    8-10 elementwise (B,C,N) passes and the masked mean) is the fused kernel pair of Poly1FocalLoss_U_T.  Gradients reach
+    `logits`, `pred_u` and - through the GEMM - `delta_T` (the learnable class-level revision) and `T`."""
+
+    def __init__(self, epsilon: float = 1.0, alpha: float = 0.25, gamma: float = 2.0, reduction: str = "mean",
+                 weight=None, pos_weight=None, label_is_onehot: bool = False, **kwargs):
+        super().__init__()
+        if weight is not None or pos_weight is not None or label_is_onehot:
+            raise NotImplementedError("Poly1FocalLoss_U_T_v1: weight / pos_weight / one-hot labels are not used by the "
+                                      "reference configs and are not implemented by the CUDA path")
+        self.epsilon, self.alpha, self.gamma, self.reduction = epsilon, alpha, gamma, reduction
+
+    def forward(self, logits, labels, logits_pred, T, pred_u, delta_T, thresh=0.95, mask=None):
+        if logits.dim() != 3 or pred_u.shape != logits.shape:
+            raise ValueError("Poly1FocalLoss_U_T_v1 expects (B, C, N) logits and pred_u of the same shape")
+        batch_size, num_point = labels.shape
+        ema_t_corr = T + delta_T                                                           # build.py:766
+        pred_u_t = pred_u.transpose(1, 0).contiguous().view(-1, batch_size * num_point)    # :767
+        pred_u_t = torch.matmul(ema_t_corr.t(), pred_u_t)                                  # :768
+        pred_u_t = pred_u_t.view(-1, batch_size, num_point).transpose(1, 0).contiguous()   # :769  (B, C, N)
+        loss = _Poly1T.apply(logits, labels, logits_pred, mask, pred_u_t, thresh, self.epsilon, self.alpha, self.gamma)
+        return loss, delta_T

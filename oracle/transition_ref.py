@@ -210,3 +210,11 @@ def poly1_focal_u_t(logits, labels, logits_pred, pred_u_t, thresh=0.95, mask=Non
     keep = mask if mask is not None else logits_pred.ge(torch.tensor(thresh, device=logits_pred.device))
     keep = keep.unsqueeze(1).repeat(1, C, 1)
     return torch.sum(poly1 * keep) / (keep.sum() + 0.001)
+
+
+def poly1_focal_u_t_v1(logits, labels, logits_pred, T, pred_u, delta_T, thresh=0.95, mask=None, epsilon=1.0, alpha=0.25, gamma=2.0):
+    """openpoints/loss/build.py:690-795 (Poly1FocalLoss_U_T_v1.forward): the corrected prediction is formed inside the
+    loss from the class-level matrix, pred_u_t[b,:,n] = (T + delta_T)^T . pred_u[b,:,n] (build.py:766-770), then
+    beta = logits_pred / pred_u_t[b, label, n] scales the poly-1 focal terms as in Poly1FocalLoss_U_T."""
+    pred_u_t = torch.einsum("ij,bin->bjn", T + delta_T, pred_u)
+    return poly1_focal_u_t(logits, labels, logits_pred, pred_u_t, thresh=thresh, mask=mask, epsilon=epsilon, alpha=alpha, gamma=gamma)

@@ -12,9 +12,10 @@ import argparse, ctypes as C, json, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
 import numpy as np, torch
-from geot_b200 import _lib, synth
+from geot_b200 import _lib, backends, synth
 from geot_b200 import functional as F
 import refgpu
+import ref_backends
 
 ap = argparse.ArgumentParser(); ap.add_argument("--out", default=None); args = ap.parse_args()
 try:
@@ -93,6 +94,13 @@ for (B, N, M, ns, Cc, r) in [(64, 16384, 1024, 32, 64, 0.1), (16, 16384, 4096, 3
            (lambda: (gp_r.zero_(), R.ref_group_points_grad(B, Cc, N, M, ns, p(go), p(nbr), p(gp_r)))) if R else None, nb_fwd,
            lambda: torch.allclose(gp, gp_r, rtol=1e-4, atol=1e-4))
     report("scatter plan build", tag, lambda: F.grouping_plan(nbr, B, N), None, B * (4 * M * ns * 3 + 8 * N))
+    # what a training step pays: idx is new every step, so the plan is built once per backward ...
+    report("grouping_operation bwd", tag + " (INCL. plan build)", lambda: F.group_points_grad(go, F.grouping_plan(nbr, B, N), N, out=gp),
+           (lambda: (gp_r.zero_(), R.ref_group_points_grad(B, Cc, N, M, ns, p(go), p(nbr), p(gp_r)))) if R else None, nb_fwd, None)
+    # ... and what unmodified reference code pays through the pybind-shaped facade (caller-zeroed buffer, plan per call)
+    report("grouping_operation bwd", tag + " (through facade)",
+           lambda: (gp.zero_(), backends.pointnet2_batch_cuda.group_points_grad_wrapper(B, Cc, N, M, ns, go, nbr, gp)),
+           lambda: (gp_r.zero_(), ref_backends.pointnet2_batch_cuda.group_points_grad_wrapper(B, Cc, N, M, ns, go, nbr, gp_r)), nb_fwd, None)
     # three_nn / three_interpolate: upsample the M sampled points back to N
     d2 = torch.empty((B, N, 3), device=dev); i3 = torch.empty((B, N, 3), dtype=i32, device=dev)
     d2_r = torch.empty_like(d2); i3_r = torch.empty_like(i3)
@@ -112,6 +120,11 @@ for (B, N, M, ns, Cc, r) in [(64, 16384, 1024, 32, 64, 0.1), (16, 16384, 4096, 3
     report("three_interpolate bwd", tag + " (plan cached)", lambda: F.three_interpolate_grad(go3, w, plan3, M, out=gm),
            (lambda: (gm_r.zero_(), R.ref_three_interpolate_grad(B, Cc, N, M, p(go3), p(i3), p(w), p(gm_r)))) if R else None, nb_ti,
            lambda: torch.allclose(gm, gm_r, rtol=1e-4, atol=1e-3))
+    report("three_interpolate bwd", tag + " (INCL. plan build)", lambda: F.three_interpolate_grad(go3, w, F.ScatterPlan(i3, B, M), M, out=gm),
+           (lambda: (gm_r.zero_(), R.ref_three_interpolate_grad(B, Cc, N, M, p(go3), p(i3), p(w), p(gm_r)))) if R else None, nb_ti, None)
+    report("three_interpolate bwd", tag + " (through facade)",
+           lambda: (gm.zero_(), backends.pointnet2_batch_cuda.three_interpolate_grad_wrapper(B, Cc, N, M, go3, i3, w, gm)),
+           lambda: (gm_r.zero_(), ref_backends.pointnet2_batch_cuda.three_interpolate_grad_wrapper(B, Cc, N, M, go3, i3, w, gm_r)), nb_ti, None)
     del xyz, feat, g, g_r, go, gp, gp_r, o, o_r, go3, plan, plan3
     torch.cuda.empty_cache()
 
@@ -137,6 +150,11 @@ for (b, n_per, k, c) in [(8, 16384, 16, 32), (8, 4096, 16, 64)]:
     report("pointops.grouping bwd", tag + " (plan cached)", lambda: F.grouping_backward(go, plan, n, out=gi),
            (lambda: (gi_r.zero_(), RF.ref_grouping_backward(n, k, c, p(go), p(idx), p(gi_r)))) if RF else None, nb,
            lambda: torch.allclose(gi, gi_r, rtol=1e-4, atol=1e-3))
+    report("pointops.grouping bwd", tag + " (INCL. plan build)", lambda: F.grouping_backward(go, F.ScatterPlan(idx.view(1, n, k), 1, n), n, out=gi),
+           (lambda: (gi_r.zero_(), RF.ref_grouping_backward(n, k, c, p(go), p(idx), p(gi_r)))) if RF else None, nb, None)
+    report("pointops.grouping bwd", tag + " (through facade)",
+           lambda: (gi.zero_(), backends.pointops_cuda.grouping_backward_cuda(n, k, c, go, idx, gi)),
+           lambda: (gi_r.zero_(), ref_backends.pointops_cuda.grouping_backward_cuda(n, k, c, go, idx, gi_r)), nb, None)
     # ---- the rest of a Point-Transformer block on the same neighbourhoods (offset API, channel-last)
     x2 = torch.randn(n, c, device=dev)
     sub = torch.empty((n, k, c), device=dev); sub_r = torch.empty_like(sub)

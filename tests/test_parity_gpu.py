@@ -485,3 +485,36 @@ def test_aggregation_vector_and_scalar_paths(cuda, oracle, c, wc):
     gi, gp, gw = _check_aggregation(oracle, inp, pos, wt, idn, ga, plan)
     gi2, gp2, gw2 = F.aggregation_backward(cu(inp), cu(pos), cu(wt), cu(idn), cu(ga), plan)
     assert torch.equal(gi, gi2) and torch.equal(gw, gw2)
+
+
+@pytest.mark.parametrize("B,N,E_shape", [(4, 16384, (1024, 32)), (2, 4096, (1024, 64)), (3, 1000, (250, 16)), (2, 8192, (16000, 3)),
+                                         (1, 37, (5, 8)), (2, 40000, (4096, 32)), (1, 2048, (16384, 16))])
+def test_scatter_plan_fused_builder_equals_multi_kernel_builder(cuda, B, N, E_shape):
+    """The one-CTA-per-cloud fused builder (shared-memory counters, in-place segment sort) against the multi-kernel
+    builder (mode 2 of the thread-local override forces it): identical row_ptr and perm - ascending sources per target -
+    including long segments (first-hit padding, all-zero rows) and out-of-range indices, which both skip."""
+    rng = np.random.default_rng(N + B)
+    M, ns = E_shape
+    idx = rng.integers(0, N, (B, M, ns)).astype(np.int32)
+    idx[:, : max(M // 8, 1)] = idx[:, : max(M // 8, 1), :1]      # padded rows -> a few long segments
+    idx[:, -max(M // 16, 1):] = 0                                  # empty balls -> one very long segment at target 0
+    idx[0, 0, 0] = -1
+    idx[-1, -1, -1] = N + 5
+    t = cu(idx)
+    fused = F.ScatterPlan(t, B, N)
+    _lib.lib().geot_group_points_config(2)
+    try:
+        multi = F.ScatterPlan(t, B, N)
+    finally:
+        _lib.lib().geot_group_points_config(0)
+    assert torch.equal(fused.row_ptr(), multi.row_ptr())
+    total = fused.row_ptr()[:, -1]
+    for b in range(B):
+        n_b = int(total[b])
+        assert torch.equal(fused.perm()[b, :n_b], multi.perm()[b, :n_b])
+    rp, pm = fused.row_ptr().cpu().numpy(), fused.perm().cpu().numpy()
+    flat = idx.reshape(B, -1)
+    for b in range(B):
+        for k in (0, int(flat[b, 5]) if 0 <= flat[b, 5] < N else 1, N - 1):
+            seg = pm[b, rp[b, k]:rp[b, k + 1]]
+            assert np.array_equal(seg, np.nonzero(flat[b] == k)[0])

@@ -375,3 +375,45 @@ def test_sigt_clamp_edge_flips_are_counted_and_bounded(cuda):
     err = (gW.double() - gW64).abs()
     bound = 1e-5 * gW64.abs().max() + flipped_terms + 1e-9
     assert bool((err <= bound).all()), float((err / bound).max())
+
+
+# ---------------------------------------------------------------------------------------------
+# Poly1FocalLoss_U_T_v1 (class-level T^T . p inside the loss, build.py:690-795)
+# ---------------------------------------------------------------------------------------------
+from tests.test_transition_oracle_cpu import loss_tv1_case  # noqa: E402
+
+
+@pytest.mark.parametrize("tag", ["C17", "C33", "C5"])
+@pytest.mark.parametrize("variant,hp", LOSS_VARIANTS)
+def test_golden_poly1_focal_u_t_v1(cuda, tag, variant, hp):
+    from geot_b200 import losses
+    c = loss_tv1_case(tag, variant)
+    x = c["logits"].cuda().requires_grad_(True)
+    pu = c["pred_u"].cuda().requires_grad_(True)
+    dT = c["delta_T"].cuda().requires_grad_(True)
+    loss, ret = losses.Poly1FocalLoss_U_T_v1(**hp)(x, c["labels"].cuda(), c["conf"].cuda(), c["T"].cuda(), pu, dT, thresh=c["thresh"],
+                                                  mask=None if c["mask"] is None else c["mask"].cuda())
+    assert ret is dT                                            # the reference returns (loss, delta_T)
+    close(loss, c["loss"], rtol=1e-5, atol=1e-8)
+    loss.backward()
+    assert rel(x.grad, c["grad"]) < 1e-5 and rel(pu.grad, c["grad_u"]) < 1e-5 and rel(dT.grad, c["grad_dT"]) < 1e-5
+
+
+def test_poly1_focal_u_t_v1_cfg4_size_vs_oracle(cuda):
+    """6 x 16000 points, C=33 against the oracle's torch expression in float64 on the GPU."""
+    from geot_b200 import losses
+    g = torch.Generator(device="cuda").manual_seed(10)
+    B, C, N = 6, 33, 16000
+    logits = (torch.randn(B, C, N, device="cuda", generator=g) * 4).requires_grad_(True)
+    labels = torch.randint(0, C, (B, N), device="cuda", generator=g)
+    conf = torch.rand(B, N, device="cuda", generator=g) * 0.9 + 0.1
+    pred_u = torch.softmax(torch.randn(B, C, N, device="cuda", generator=g) * 2, dim=1).requires_grad_(True)
+    T = torch.nn.functional.normalize(torch.rand(C, C, device="cuda", generator=g) + torch.eye(C, device="cuda") * 4, p=1, dim=1)
+    dT = (torch.randn(C, C, device="cuda", generator=g) * 0.01).requires_grad_(True)
+    loss, _ = losses.Poly1FocalLoss_U_T_v1()(logits, labels, conf, T, pred_u, dT, thresh=0.5)
+    loss.backward()
+    x64, pu64, dT64 = (t.detach().double().requires_grad_(True) for t in (logits, pred_u, dT))
+    ref = R.poly1_focal_u_t_v1(x64, labels, conf.double(), T.double(), pu64, dT64, thresh=0.5)
+    ref.backward()
+    assert rel(loss, ref) < 1e-5
+    assert rel(logits.grad, x64.grad) < 1e-5 and rel(pred_u.grad, pu64.grad) < 1e-5 and rel(dT.grad, dT64.grad) < 1e-5

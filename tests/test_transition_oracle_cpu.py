@@ -124,3 +124,31 @@ def test_golden_poly1_focal_u_t(tag, variant, hp):
     loss.backward()
     torch.testing.assert_close(x.grad, exp_grad, rtol=1e-5, atol=1e-10)
     torch.testing.assert_close(pt.grad, exp_grad_t, rtol=1e-5, atol=1e-10)
+
+
+LV1 = np.load(os.path.join(os.path.dirname(__file__), "golden", "loss_tv1_golden.npz"))
+
+
+def loss_tv1_case(tag, variant):
+    """One golden case of Poly1FocalLoss_U_T_v1 (tests/golden/make_loss_golden.py, third part)."""
+    f = lambda k: torch.from_numpy(LV1[k])
+    mask = f(f"{tag}_{variant}_mask") if f"{tag}_{variant}_mask" in LV1 else None
+    return dict(logits=f(f"{tag}_logits"), labels=f(f"{tag}_labels"), conf=f(f"{tag}_conf"), pred_u=f(f"{tag}_pred_u"), T=f(f"{tag}_T"),
+                delta_T=f(f"{tag}_delta_T"), mask=mask, thresh=float(LV1[f"{tag}_{variant}_thresh"]), loss=f(f"{tag}_{variant}_loss"),
+                grad=f(f"{tag}_{variant}_grad"), grad_u=f(f"{tag}_{variant}_grad_u"), grad_dT=f(f"{tag}_{variant}_grad_dT"))
+
+
+@pytest.mark.parametrize("tag", ["C17", "C33", "C5"])
+@pytest.mark.parametrize("variant,hp", LOSS_VARIANTS)
+def test_golden_poly1_focal_u_t_v1(tag, variant, hp):
+    """oracle restatement of Poly1FocalLoss_U_T_v1 against the reference class's own outputs (loss and three gradients)."""
+    c = loss_tv1_case(tag, variant)
+    x = c["logits"].clone().requires_grad_(True)
+    pu = c["pred_u"].clone().requires_grad_(True)
+    dT = c["delta_T"].clone().requires_grad_(True)
+    loss = R.poly1_focal_u_t_v1(x, c["labels"], c["conf"], c["T"], pu, dT, thresh=c["thresh"], mask=c["mask"], **hp)
+    torch.testing.assert_close(loss, c["loss"], rtol=1e-6, atol=1e-9)
+    loss.backward()
+    torch.testing.assert_close(x.grad, c["grad"], rtol=1e-5, atol=1e-10)
+    torch.testing.assert_close(pu.grad, c["grad_u"], rtol=1e-5, atol=1e-9)
+    torch.testing.assert_close(dT.grad, c["grad_dT"], rtol=2e-5, atol=1e-8)
