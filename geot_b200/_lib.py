@@ -148,8 +148,14 @@ except AttributeError:  # pragma: no cover
 
 def stream_ptr():
     if _raw_stream is not None:
-        return _raw_stream(torch.cuda.current_device())
+        return _raw_stream(_cur_dev())
     return torch.cuda.current_stream().cuda_stream
+
+
+try:  # current device without the lazy-init / Python wrapper cost of torch.cuda.current_device() (0.25 -> 0.05 us)
+    _cur_dev = torch._C._cuda_getDevice
+except AttributeError:  # pragma: no cover
+    _cur_dev = torch.cuda.current_device
 
 
 class on_device:
@@ -158,10 +164,10 @@ class on_device:
     __slots__ = ("idx", "prev")
 
     def __init__(self, dev):
-        self.idx = dev.index if (dev is not None and dev.index is not None) else torch.cuda.current_device()
+        self.idx = dev.index if (dev is not None and dev.index is not None) else _cur_dev()
 
     def __enter__(self):
-        self.prev = torch.cuda.current_device()
+        self.prev = _cur_dev()
         if self.prev != self.idx:
             torch.cuda.set_device(self.idx)
 

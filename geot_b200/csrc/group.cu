@@ -166,6 +166,10 @@ static int launch_group(int B, int C, int N, int64_t E, const float* points, con
   const int64_t xb = vec ? (E / 4 + 255) / 256 : (E + 255) / 256;
   int cch = kGroupCCH;
   while (cch > 1 && xb * ((C + cch - 1) / cch) * B < 4 * (int64_t)kNumSMs && (C + cch / 2 - 1) / (cch / 2) <= 65535) cch >>= 1;
+  // a sparse gather (gather_operation: 1 of 16 points of every row) is bound by DRAM sector fetches, not by the idx
+  // loads: one channel per thread keeps the most independent 4-byte gathers in flight (the reference kernel's mapping,
+  // sampling_gpu.cu:15-31, plus the int4 idx load and the 16-byte store)
+  if (2 * E <= (int64_t)N && C <= 65535) cch = 1;
   dim3 grid((unsigned)xb, (C + cch - 1) / cch, B);
   if (vec) group_points_kernel<4><<<grid, 256, 0, s>>>(C, N, E, cch, points, idx, out);
   else group_points_kernel<1><<<grid, 256, 0, s>>>(C, N, E, cch, points, idx, out);
