@@ -19,6 +19,7 @@ GEOT_FPS_CAP512 = 1
 GEOT_FPS_MAGSKIP = 2
 GEOT_FPS_FORCE_GENERIC = 4
 GEOT_FPS_NO_PRUNE = 8
+GEOT_FPS_SPEC = 16
 GEOT_BQ_FORCE_GRID = 1
 GEOT_KNN_NO_GRID = 1
 

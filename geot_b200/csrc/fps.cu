@@ -163,11 +163,11 @@ struct MgrCfg {
   static constexpr int KEY_OFF = HIST_OFF + 4096 * 4;
   static constexpr int BOX_OFF = KEY_OFF + NBK * 8;
   static constexpr int ACT_OFF = BOX_OFF + NBK * 24;
-  static constexpr int CTRL_OFF = ACT_OFF + 256;  // 8 flag bytes per worker
-  static constexpr int SMEM_BYTES = CTRL_OFF + 16;
+  static constexpr int CTRL_OFF = ACT_OFF + 512;  // 2 buffers of 8 flag bytes per worker
+  static constexpr int SMEM_BYTES = CTRL_OFF + 64;  // 2 x {sample (16 B), speculative winner key (8 B), pad}
 };
 
-template <int NBK>
+template <int NBK, bool SPEC>
 __global__ void __launch_bounds__(1024, 1)
 fps_mgr_kernel(const float* __restrict__ xyz, const int* __restrict__ offset,
                const int* __restrict__ new_offset, int N, int M, int* __restrict__ idx, int log2bs,
@@ -369,10 +369,168 @@ fps_mgr_kernel(const float* __restrict__ xyz, const int* __restrict__ offset,
       }
     }
   }
-  if (t < 64) sts32(a_act + 4u * t, 0u);  // flag bytes of buckets that do not exist stay 0
+  if (t < 128) sts32(a_act + 4u * t, 0u);  // flag bytes of buckets that do not exist stay 0 (both buffers)
   __syncthreads();
   if (rounds <= 0) return;
   FPS_PROF_INIT;
+
+  if constexpr (SPEC) {
+    // ================= speculative variant: the manager runs ONE ROUND AHEAD of the workers =================
+    // While the workers apply sample r, the manager already guesses sample r+1 = the best candidate among the buckets
+    // the current sample does NOT touch (their keys cannot change in this round), fetches its coordinates and runs the
+    // box tests for it.  The guess is the true winner iff no bucket updated in round r ends up with a larger key -
+    // each worker checks that for its own buckets after the round (one 64-bit compare), one __syncthreads_or
+    // collects the verdict.  Valid in 92-95 % of the rounds on tooth clouds (profiles/r02_fps_study.md); then the
+    // manager's whole chain (pick, coordinates, box tests: ~300-450 cycles) is off the critical path.  Otherwise the
+    // manager picks the true winner from the final keys as before (one extra barrier).  Box tests of a guessed round
+    // use the bucket maxima from BEFORE the running round (larger or equal): a superset of the exact active set, and
+    // updating a bucket that cannot change is a no-op, so the result is bit-identical in both cases.
+    int* out = idx + start_m;
+    if (warp == 0) {
+      float box[BPL][6];
+      unsigned o_flag[BPL];  // byte offset of a bucket's flag inside a flag buffer
+      uint2 key[BPL];
+#pragma unroll
+      for (int i = 0; i < BPL; i++) {
+        const int b = BPL * lane + i;
+#pragma unroll
+        for (int a = 0; a < 6; a++) box[i][a] = lds32f(a_box + 4u * (unsigned)(b * 6 + a));
+        o_flag[i] = 8u * (unsigned)(b % NWK) + (unsigned)(b / NWK);
+        key[i] = lds64(a_key + 8u * (unsigned)b);
+      }
+      auto box_flags = [&](float sx, float sy, float sz) -> unsigned {
+        unsigned f = 0;
+#pragma unroll
+        for (int i = 0; i < BPL; i++) {
+          const float gx = fmaxf(fmaxf(__fsub_rn(box[i][0], sx), __fsub_rn(sx, box[i][3])), 0.f);
+          const float gy = fmaxf(fmaxf(__fsub_rn(box[i][1], sy), __fsub_rn(sy, box[i][4])), 0.f);
+          const float gz = fmaxf(fmaxf(__fsub_rn(box[i][2], sz), __fsub_rn(sz, box[i][5])), 0.f);
+          const float lb = __fmaf_rn(gz, gz, __fmaf_rn(gx, gx, __fmul_rn(gy, gy)));
+          f |= (lb < __uint_as_float(key[i].y) ? 1u : 0u) << i;
+        }
+        return f;
+      };
+      auto publish = [&](int buf, unsigned f, float sx, float sy, float sz, unsigned klo, int khi) {
+#pragma unroll
+        for (int i = 0; i < BPL; i++) sts_u8(a_act + 256u * buf + o_flag[i], (f >> i) & 1u);
+        if (lane == 0) {
+          sts128(a_ctrl + 32u * buf, make_float4(0.f, sx, sy, sz));
+          sts64(a_ctrl + 32u * buf + 16u, klo, (unsigned)khi);
+        }
+      };
+      // arg-max of the 64-bit keys over the buckets whose bit in `skip` is clear
+      auto pick = [&](unsigned skip, int& ghi, unsigned& glo) {
+        unsigned long long best = 0ull;  // below every real key (value bits ^ sign >= 0x3f800000 for -1.0f ... )
+#pragma unroll
+        for (int i = 0; i < BPL; i++) {
+          const unsigned long long k64 = ((unsigned long long)(key[i].y ^ 0x80000000u) << 32) | key[i].x;
+          if (!((skip >> i) & 1u)) best = k64 > best ? k64 : best;
+        }
+        const unsigned bh = (unsigned)(best >> 32);
+        const unsigned gh = __reduce_max_sync(0xffffffffu, bh);
+        glo = __reduce_max_sync(0xffffffffu, bh == gh ? (unsigned)best : 0u);
+        ghi = gh == 0u ? (int)0x80000000 : (int)(gh ^ 0x80000000u);  // nothing eligible -> below every value
+      };
+      unsigned fprev = 0u, fcur = box_flags(x0, y0, z0);
+      publish(0, fcur, x0, y0, z0, 0u, 0);
+      __syncthreads();
+      for (int r = 0; r < rounds; r++) {
+        const int nb = (r + 1) & 1;
+        // keys of the buckets of round r-1 are final: refresh them, then guess the winner outside the running round
+#pragma unroll
+        for (int i = 0; i < BPL; i++)
+          if ((fprev >> i) & 1u) key[i] = lds64(a_key + 8u * (unsigned)(BPL * lane + i));
+        int ghi;
+        unsigned glo;
+        pick(fcur, ghi, glo);
+        const bool spec_ok = ghi >= 0;
+        float sx = x0, sy = y0, sz = z0;
+        if (spec_ok) {
+          const unsigned a_w = a_base + 4u * (glo & 0x3fffu);
+          sx = lds32f(a_w); sy = lds32f(a_w + Cfg::PLANE_BYTES); sz = lds32f(a_w + 2 * Cfg::PLANE_BYTES);
+        }
+        unsigned fnext = box_flags(sx, sy, sz);
+        publish(nb, fnext, sx, sy, sz, glo, ghi);
+        __syncthreads();                                   // A: round r applied everywhere, the guess is published
+        const int bad = __syncthreads_or(spec_ok ? 0 : 1);  // B: did any updated bucket beat the guess?
+        if (bad) {
+          // the true winner, from the final keys of round r (nobody writes keys between B and C)
+#pragma unroll
+          for (int i = 0; i < BPL; i++)
+            if ((fcur >> i) & 1u) key[i] = lds64(a_key + 8u * (unsigned)(BPL * lane + i));
+          pick(0u, ghi, glo);
+          sx = x0; sy = y0; sz = z0;  // no candidate at all (every point skipped): the reference keeps index 0
+          if (ghi >= 0) {
+            const unsigned a_w = a_base + 4u * (glo & 0x3fffu);
+            sx = lds32f(a_w); sy = lds32f(a_w + Cfg::PLANE_BYTES); sz = lds32f(a_w + 2 * Cfg::PLANE_BYTES);
+          }
+          fnext = box_flags(sx, sy, sz);
+          publish(nb, fnext, sx, sy, sz, glo, ghi);
+          __syncthreads();                                 // C
+        }
+        // the winner's (~rank) for now: un-ranking (an integer division) leaves the manager's serial chain and is done
+        // by all threads after the last round
+        if (lane == 0) out[r + 1] = ghi >= 0 ? (int)(glo >> 14) : -1;
+        fprev = bad ? 0u : fcur;
+        fcur = fnext;
+      }
+    } else {
+      const unsigned a_my = a_act + 8u * (unsigned)wk;
+      __syncthreads();
+      for (int r = 0; r < rounds; r++) {
+        const unsigned buf = (unsigned)(r & 1);
+        uint2 fl = lds64(a_my + 256u * buf);  // one flag byte per owned bucket
+#ifdef GEOT_FPS_PROF
+        if (abl == 1) fl = make_uint2(0u, 0u);
+#endif
+        const float4 smp = lds128(a_ctrl + 32u * buf);
+        int my_hi = (int)0x80000000;                 // the largest key this warp produced in this round
+        unsigned my_lo = 0u;
+        if (fl.x | fl.y) {
+#pragma unroll
+          for (int c = 0; c < CHW; c++) {
+            const unsigned f = c < 4 ? (fl.x >> (8 * c)) & 0xffu : (fl.y >> (8 * (c - 4))) & 0xffu;
+            const int b = c * NWK + wk;
+            if (f && b < NBK) {
+              const unsigned a_pt = a_base + 16u * (unsigned)(b * 32 + lane);
+              const float4 X = lds128(a_pt), Y = lds128(a_pt + Cfg::PLANE_BYTES), Z = lds128(a_pt + 2 * Cfg::PLANE_BYTES);
+              const float xs[4] = {X.x, X.y, X.z, X.w}, ys[4] = {Y.x, Y.y, Y.z, Y.w}, zs[4] = {Z.x, Z.y, Z.z, Z.w};
+              unsigned k01 = kreg[2 * c], k23 = kreg[2 * c + 1];
+              asm volatile("" : "+r"(k01), "+r"(k23));
+              const unsigned rk[4] = {((k01 & 0xffffu) << 2) | 0u, ((k01 >> 16) << 2) | 1u,
+                                      ((k23 & 0xffffu) << 2) | 2u, ((k23 >> 16) << 2) | 3u};
+              float cm = -1.0f;
+#pragma unroll
+              for (int e = 0; e < 4; e++) {
+                const float d = dist2_ref(xs[e], ys[e], zs[e], smp.y, smp.z, smp.w);
+                const float v = fminf(d, mind[c * 4 + e]);
+                mind[c * 4 + e] = v;
+                cm = fmaxf(cm, v);
+              }
+              const int wm = __reduce_max_sync(0xffffffffu, __float_as_int(cm));
+              unsigned rr = 0xffffffffu;
+#pragma unroll
+              for (int e = 0; e < 4; e++) rr = min(rr, (__float_as_int(mind[c * 4 + e]) == wm) ? rk[e] : 0xffffffffu);
+              const unsigned wr = __reduce_min_sync(0xffffffffu, rr);
+              const unsigned hi_bits = (0x7fffu - (wr >> 2)) << 14;  // (~rank): decides between equal values; ranks are unique
+              if (rr == wr) sts64(a_key + 8u * b, hi_bits | (unsigned)(b * 128 + 4 * lane) | (wr & 3u), (unsigned)wm);
+              if (wm > my_hi || (wm == my_hi && hi_bits > my_lo)) { my_hi = wm; my_lo = hi_bits; }
+            }
+          }
+        }
+        __syncthreads();                                   // A
+        const uint2 g = lds64(a_ctrl + 32u * (buf ^ 1u) + 16u);  // the guessed winner's key {lo, hi}
+        const int bad_here = (my_hi > (int)g.y) || (my_hi == (int)g.y && my_lo > (g.x & ~0x3fffu));
+        if (__syncthreads_or(bad_here)) __syncthreads();   // B (, C)
+      }
+    }
+    __syncthreads();  // out[1..rounds] hold (~rank) or -1: rank 0 <-> index 0
+    for (int j = 1 + t; j <= rounds; j += NT) {
+      const int v = out[j];
+      out[j] = idx_base + (v >= 0 ? tie_unrank(0x7fffu - (unsigned)v, log2bs, q_count) : 0);
+    }
+    return;
+  }
 
   if (warp == 0) {
     // =========================== manager ===========================
@@ -577,11 +735,16 @@ static int launch_smem(int blocks, const float* xyz, const int* offset, const in
 
 template <int NBK>
 static int launch_mgr(int blocks, const float* xyz, const int* offset, const int* new_offset, int N,
-                      int M, int* idx, int log2bs, int mag_skip, cudaStream_t s) {
+                      int M, int* idx, int log2bs, int mag_skip, bool spec, cudaStream_t s) {
   constexpr int smem = MgrCfg<NBK>::SMEM_BYTES;
-  static DynSmem ds;  // per instantiation
-  if (int rc = ds.need(fps_mgr_kernel<NBK>, smem, "fps")) return rc;
-  fps_mgr_kernel<NBK><<<blocks, 1024, smem, s>>>(xyz, offset, new_offset, N, M, idx, log2bs, mag_skip);
+  static DynSmem ds, ds_spec;  // per instantiation
+  if (spec) {
+    if (int rc = ds_spec.need(fps_mgr_kernel<NBK, true>, smem, "fps")) return rc;
+    fps_mgr_kernel<NBK, true><<<blocks, 1024, smem, s>>>(xyz, offset, new_offset, N, M, idx, log2bs, mag_skip);
+  } else {
+    if (int rc = ds.need(fps_mgr_kernel<NBK, false>, smem, "fps")) return rc;
+    fps_mgr_kernel<NBK, false><<<blocks, 1024, smem, s>>>(xyz, offset, new_offset, N, M, idx, log2bs, mag_skip);
+  }
   count_launch(1);
   return check_launch("fps_mgr_kernel");
 }
@@ -598,11 +761,12 @@ static int fps_dispatch(int blocks, int n_max, const float* xyz, const int* offs
   const bool generic = (flags & GEOT_FPS_FORCE_GENERIC) || weights != nullptr || n_max > 4 * 4096;
   if (!generic && !(flags & GEOT_FPS_NO_PRUNE)) {
     const int ch = (n_max + 4095) / 4096;
+    const bool spec = (flags & GEOT_FPS_SPEC) != 0;
     switch (ch) {
-      case 1: return launch_mgr<32>(blocks, xyz, offset, new_offset, N, M, idx, log2bs, mag_skip, s);
-      case 2: return launch_mgr<64>(blocks, xyz, offset, new_offset, N, M, idx, log2bs, mag_skip, s);
-      case 3: return launch_mgr<96>(blocks, xyz, offset, new_offset, N, M, idx, log2bs, mag_skip, s);
-      default: return launch_mgr<128>(blocks, xyz, offset, new_offset, N, M, idx, log2bs, mag_skip, s);
+      case 1: return launch_mgr<32>(blocks, xyz, offset, new_offset, N, M, idx, log2bs, mag_skip, spec, s);
+      case 2: return launch_mgr<64>(blocks, xyz, offset, new_offset, N, M, idx, log2bs, mag_skip, spec, s);
+      case 3: return launch_mgr<96>(blocks, xyz, offset, new_offset, N, M, idx, log2bs, mag_skip, spec, s);
+      default: return launch_mgr<128>(blocks, xyz, offset, new_offset, N, M, idx, log2bs, mag_skip, spec, s);
     }
   }
   if (!generic) {

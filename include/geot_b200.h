@@ -59,6 +59,7 @@ uint64_t geot_launch_count(void);
 #define GEOT_FPS_MAGSKIP 2
 #define GEOT_FPS_FORCE_GENERIC 4 /* testing: take the large-N fallback regardless of N */
 #define GEOT_FPS_NO_PRUNE 8      /* testing / A-B timing: the un-pruned one-CTA-per-cloud kernel (every round visits every point) */
+#define GEOT_FPS_SPEC 16         /* A-B: the pruned kernel with the manager guessing one round ahead (same indices) */
 
 /* replaces pointnet2_batch_cuda.furthest_point_sampling_wrapper(B,N,M,xyz,temp,idx) and
  * pointnet2._ext.furthest_point_sampling(points, nsamples).  xyz (B,N,3) -> idx (B,M) int32. */

@@ -40,6 +40,10 @@ def test_fps_batched(cuda, oracle, kind, B, N, M, variant):
     assert np.array_equal(got, exp), "generic fallback kernel"
     got = F.furthest_point_sampling(cu(xyz), M, flags=flags | _lib.GEOT_FPS_NO_PRUNE).cpu().numpy()
     assert np.array_equal(got, exp), "un-pruned one-CTA kernel"
+    got = F.furthest_point_sampling(cu(xyz), M, flags=flags | _lib.GEOT_FPS_SPEC).cpu().numpy()
+    assert np.array_equal(got, exp), "pruned kernel, manager guessing one round ahead"
+    got = F.furthest_point_sampling(cu(xyz), M, flags=flags & ~_lib.GEOT_FPS_SPEC).cpu().numpy()
+    assert np.array_equal(got, exp), "pruned kernel, manager in lock-step"
 
 
 def test_fps_large_n_uses_fallback(cuda, oracle):

@@ -28,7 +28,7 @@ if len(sys.argv) > 1 and sys.argv[1] == "quick":
     shapes = shapes[:4]
 for (B, N, M) in shapes:
     xyz = torch.from_numpy(synth.tooth_batch(B, N)).cuda()
-    variants = {"mgr": 0, "brute": _lib.GEOT_FPS_NO_PRUNE}
+    variants = {"mgr": 0, "spec": _lib.GEOT_FPS_SPEC, "brute": _lib.GEOT_FPS_NO_PRUNE}
     base = F.furthest_point_sampling(xyz, M, flags=_lib.GEOT_FPS_NO_PRUNE)
     row = {"B": B, "N": N, "M": M}
     for name, fl in variants.items():

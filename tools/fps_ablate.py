@@ -19,10 +19,10 @@ def t(fn, it=10):
 
 for (B, N, M) in [(8, 16384, 1024), (8, 4096, 1024)]:
     xyz = torch.from_numpy(synth.tooth_batch(B, N)).cuda()
-    for name, base in (("mgr", 0),):
+    for name, base in (("mgr", 0), ("spec", _lib.GEOT_FPS_SPEC)):
         setup = t(lambda: F.furthest_point_sampling(xyz, 2, flags=base)) * 1e3
         row = []
-        for abl in (0, 1, 2):
+        for abl in (0, 1):
             ms = t(lambda: F.furthest_point_sampling(xyz, M, flags=base | (abl << 8)))
             row.append((ms * 1e3 - setup) / (M - 2) * 1.965e3)
-        print(f"N={N} {name:5s} cycles/round: full {row[0]:7.0f}   no updates {row[1]:7.0f}   updates w/o REDUX+key {row[2]:7.0f}   (setup {setup:.0f} us)", flush=True)
+        print(f"N={N} {name:5s} cycles/round: full {row[0]:7.0f}   no updates {row[1]:7.0f}   (setup {setup:.0f} us)", flush=True)
