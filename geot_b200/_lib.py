@@ -71,8 +71,9 @@ _SIGNATURES = {
     "geot_poly1_focal_backward": [_i, _i, _i, _vp, _vp, _vp, _vp, _f, _f, _f, _f, _vp, _vp, _vp, _vp],
     "geot_poly1_focal_t_forward": [_i, _i, _i, _vp, _vp, _vp, _vp, _vp, _f, _f, _f, _f, _vp, _vp, _vp, _sz, _vp],
     "geot_poly1_focal_t_backward": [_i, _i, _i, _vp, _vp, _vp, _vp, _vp, _f, _f, _f, _f, _vp, _vp, _vp, _vp, _vp],
-    "geot_manifold_loss_forward": [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _f, _i, _vp, _vp, _vp, _sz, _vp],
-    "geot_manifold_loss_backward": [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
+    "geot_spatial_order": [_i, _i, _i, _vp, _vp, _vp],
+    "geot_manifold_loss_forward": [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _f, _i, _vp, _vp, _vp, _sz, _vp],
+    "geot_manifold_loss_backward": [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
     "geot_class_pick_workspace_bytes": [_i],
     "geot_class_pick": [_i, _i, _i, _vp, _vp, _vp, _vp, _vp, _sz, _vp],
     "geot_class_t_step": [_i, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp],

@@ -475,9 +475,22 @@ def transition_apply_backward(logits, ema_t, insT, lam, grad_out, need_logits=Tr
 MANIFOLD_3D, MANIFOLD_FEATURE = 0, 1
 
 
-def manifold_loss_forward(points, labels, insT, idx, sigma, mode):
-    """points (B,N,D), labels (B,N) int64, insT (B*N,C,C), idx (B,N,k) int32 local -> (loss (1,), coef (B*N,k))."""
-    dev = check_cuda(points, insT, i32=(idx,), i64=(labels,))
+def spatial_order(points):
+    """points (B,N,D) -> order (B,N) int32: the points of every cloud listed cell by cell of a 16^3 Morton grid over
+    their first three coordinates (a processing order for the manifold kernels; not a deterministic permutation
+    inside a cell, and no result depends on it)."""
+    dev = check_cuda(points)
+    B, N, D = points.shape
+    with on_device(dev):
+        order = torch.empty((B, N), dtype=_i32, device=dev)
+        call("geot_spatial_order", B, N, D, ptr(points), ptr(order), stream_ptr())
+    return order
+
+
+def manifold_loss_forward(points, labels, insT, idx, sigma, mode, order=None):
+    """points (B,N,D), labels (B,N) int64, insT (B*N,C,C), idx (B,N,k) int32 local -> (loss (1,), coef (B*N,k)).
+    order: optional (B,N) int32 processing order (spatial_order)."""
+    dev = check_cuda(points, insT, i32=(idx, order), i64=(labels,))
     B, N, D = points.shape
     Cc, k = insT.shape[1], idx.shape[2]
     with on_device(dev):
@@ -485,17 +498,17 @@ def manifold_loss_forward(points, labels, insT, idx, sigma, mode):
         loss = torch.empty((1,), dtype=_f32, device=dev)
         nb = int(_lib.lib().geot_manifold_workspace_bytes(B * N))
         ws = _ws(nb, dev)
-        call("geot_manifold_loss_forward", B, N, D, Cc, k, ptr(points), ptr(labels), ptr(insT), ptr(idx), float(sigma), mode, ptr(coef), ptr(loss), ptr(ws), nb, stream_ptr())
+        call("geot_manifold_loss_forward", B, N, D, Cc, k, ptr(points), ptr(labels), ptr(insT), ptr(idx), ptr(order), float(sigma), mode, ptr(coef), ptr(loss), ptr(ws), nb, stream_ptr())
     return loss, coef
 
 
-def manifold_loss_backward(insT, idx, coef, plan, grad_loss):
-    dev = check_cuda(insT, coef, grad_loss, i32=(idx,))
+def manifold_loss_backward(insT, idx, coef, plan, grad_loss, order=None):
+    dev = check_cuda(insT, coef, grad_loss, i32=(idx, order))
     B, N, k = idx.shape
     Cc = insT.shape[1]
     with on_device(dev):
         g = torch.empty_like(insT)
-        call("geot_manifold_loss_backward", B, N, Cc, k, ptr(insT), ptr(idx), ptr(coef), plan.ptr, ptr(grad_loss), ptr(g), stream_ptr())
+        call("geot_manifold_loss_backward", B, N, Cc, k, ptr(insT), ptr(idx), ptr(coef), plan.ptr, ptr(order), ptr(grad_loss), ptr(g), stream_ptr())
     return g
 
 

@@ -120,16 +120,19 @@ class _Manifold(Function):
     @staticmethod
     def forward(ctx, insT, points, labels, idx, sigma, mode):
         insT = insT.contiguous()
-        loss, coef = F_.manifold_loss_forward(points, labels, insT, idx, sigma, mode)
-        ctx.save_for_backward(insT, idx, coef)
+        # points are visited cell by cell of a Morton grid: a neighbourhood's (C,C) matrices stay in L2 (the (BN,C,C)
+        # tensor does not fit it); a scheduling order only, results are independent of it
+        order = F_.spatial_order(points)
+        loss, coef = F_.manifold_loss_forward(points, labels, insT, idx, sigma, mode, order=order)
+        ctx.save_for_backward(insT, idx, coef, order)
         return loss.view(())
 
     @staticmethod
     def backward(ctx, grad_loss):
-        insT, idx, coef = ctx.saved_tensors
+        insT, idx, coef, order = ctx.saved_tensors
         B, N, k = idx.shape
         plan = F_.ScatterPlan(idx, B, N)
-        g = F_.manifold_loss_backward(insT, idx, coef, plan, grad_loss.contiguous().float().view(1))
+        g = F_.manifold_loss_backward(insT, idx, coef, plan, grad_loss.contiguous().float().view(1), order=order)
         return g, None, None, None, None, None
 
 

@@ -256,19 +256,23 @@ int geot_transition_apply_backward(int B, int C, int N, const float* logits, con
  *   idx (B,N,k) int32 LOCAL neighbour indices (self excluded); mode GEOT_MANIFOLD_3D: w in {0,1}*exp, per point
  *   sum(w*Td)/(sum(w)+1e-3), mean over points; GEOT_MANIFOLD_FEATURE: w in {-1,+1}*exp, mean over points*k.
  * Outputs: coef (B*N,k) = d loss_point / d Tdist (kept for the backward), loss (1 float, device).
- * workspace: geot_manifold_workspace_bytes(B*N). */
+ * workspace: geot_manifold_workspace_bytes(B*N).
+ * order (B,N) int32 or NULL: the order in which the points of each cloud are PROCESSED (geot_spatial_order: Morton
+ * cells of the first three coordinates).  It keeps a neighbourhood's matrices L2-resident - the (BN,C,C) tensor does
+ * not fit the L2 - and changes no result bit: every point writes its own outputs, the final sum runs in index order. */
 #define GEOT_MANIFOLD_3D 0
 #define GEOT_MANIFOLD_FEATURE 1
 size_t geot_manifold_workspace_bytes(int64_t BN);
+int geot_spatial_order(int B, int N, int D, const float* points, int* order, geot_stream_t stream);
 int geot_manifold_loss_forward(int B, int N, int D, int C, int k, const float* points,
-                               const int64_t* labels, const float* insT, const int* idx, float sigma,
-                               int mode, float* coef, float* loss, void* workspace,
+                               const int64_t* labels, const float* insT, const int* idx, const int* order,
+                               float sigma, int mode, float* coef, float* loss, void* workspace,
                                size_t workspace_bytes, geot_stream_t stream);
 /* backward w.r.t. insT (weights are detached in the reference, insT_loss.py:106-108): grad_insT (B*N,C*C),
  * every element written, fixed summation order.  plan = geot_scatter_plan_build(B, N, N*k, idx);
  * grad_loss: 1 float on the device (upstream gradient of the scalar loss). */
 int geot_manifold_loss_backward(int B, int N, int C, int k, const float* insT, const int* idx,
-                                const float* coef, const void* plan, const float* grad_loss,
+                                const float* coef, const void* plan, const int* order, const float* grad_loss,
                                 float* grad_insT, geot_stream_t stream);
 
 /* replaces the per-class loop train.py:509-526 (filter_outlier off): for every class cc the FIRST point in

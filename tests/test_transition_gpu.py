@@ -417,3 +417,25 @@ def test_poly1_focal_u_t_v1_cfg4_size_vs_oracle(cuda):
     ref.backward()
     assert rel(loss, ref) < 1e-5
     assert rel(logits.grad, x64.grad) < 1e-5 and rel(pred_u.grad, pu64.grad) < 1e-5 and rel(dT.grad, dT64.grad) < 1e-5
+
+
+def test_manifold_processing_order_changes_no_bit(cuda):
+    """The Morton-cell processing order of the manifold kernels (L2 locality) must not change a single bit of the loss,
+    the coefficients or the gradient - with the order, without it, and with a reversed one."""
+    g = torch.Generator(device="cuda").manual_seed(3)
+    B, N, C, k = 2, 6000, 17, 16
+    pos = torch.from_numpy(synth.tooth_batch(B, N, first_cloud=11)).cuda()
+    labels = torch.randint(0, 4, (B, N), device="cuda", generator=g)
+    insT = torch.softmax(torch.randn((B * N, C, C), device="cuda", generator=g), 2).contiguous()
+    idx = T._neighbours(k, pos)
+    order = F_.spatial_order(pos)
+    assert torch.equal(torch.sort(order.long(), 1).values, torch.arange(N, device="cuda").expand(B, N))   # a permutation
+    plan = F_.ScatterPlan(idx, B, N)
+    gl = torch.ones((1,), device="cuda")
+    res = []
+    for o in (None, order, order.flip(1).contiguous()):
+        loss, coef = F_.manifold_loss_forward(pos, labels, insT, idx, 1.0, F_.MANIFOLD_3D, order=o)
+        grad = F_.manifold_loss_backward(insT, idx, coef, plan, gl, order=o)
+        res.append((loss, coef, grad))
+    for r in res[1:]:
+        assert all(torch.equal(a, b) for a, b in zip(res[0], r))
