@@ -669,6 +669,29 @@ seg_reduce_cmajor_kernel(int C, int N, int64_t E, const float* __restrict__ g,
 // hits shared memory: no 32-byte L2 sector per 4-byte element, no global latency inside the segment loops.
 // Summation order = plan order (ascending source), exactly as in the direct kernel: same bits.
 constexpr int kPrTaskCap = 5456;  // non-empty targets the compact task list can hold (6 bytes each in 32 KB)
+// one segment of the 16-bit plan, summed in ascending plan order (the order of the direct kernel: same bits).  The plan
+// entries are read two per 32-bit word: the gather loop sits on the shared-memory instruction queue (MIO throttle,
+// two LDS per source), this makes it three per two sources.  GEOT_SEG_SUM16=0 keeps the one-entry-per-load loop (A/B).
+#ifndef GEOT_SEG_SUM16
+#define GEOT_SEG_SUM16 1
+#endif
+__device__ __forceinline__ float seg_sum16(const float* __restrict__ row, const unsigned short* __restrict__ perm16, int s0, int e0) {
+  float acc = 0.f;
+#if GEOT_SEG_SUM16
+  int p = s0;
+  if ((p & 1) && p < e0) { acc = __fadd_rn(acc, row[perm16[p]]); p++; }
+  const unsigned* pp = reinterpret_cast<const unsigned*>(perm16 + p);  // perm16 is 16-byte aligned, p even
+  for (; p + 1 < e0; p += 2) {
+    const unsigned u = *pp++;
+    acc = __fadd_rn(acc, row[u & 0xffffu]);
+    acc = __fadd_rn(acc, row[u >> 16]);
+  }
+  if (p < e0) acc = __fadd_rn(acc, row[perm16[p]]);
+#else
+  for (int p = s0; p < e0; p++) acc = __fadd_rn(acc, row[perm16[p]]);
+#endif
+  return acc;
+}
 __global__ void __launch_bounds__(1024, 1)
 seg_reduce_planrow_kernel(int C, int N, int E, int Q, int cpc, const float* __restrict__ g, const int* __restrict__ row_ptr,
                           const int* __restrict__ perm, float* __restrict__ dst) {
@@ -749,8 +772,7 @@ seg_reduce_planrow_kernel(int C, int N, int E, int Q, int cpc, const float* __re
         __syncthreads();  // zero fill ordered before the sums of this CTA
         for (int i = t; i < ne; i += 1024) {
           const int s0 = t_start[i], e0 = s0 + t_len[i];
-          float acc = 0.f;
-          for (int p = s0; p < e0; p++) acc = __fadd_rn(acc, row[perm16[p]]);
+          float acc = seg_sum16(row, perm16, s0, e0);
           const int k = t_tgt[i];
           out[k] = q == 0 ? acc : __fadd_rn(out[k], acc);
         }
@@ -758,8 +780,7 @@ seg_reduce_planrow_kernel(int C, int N, int E, int Q, int cpc, const float* __re
         mbar_wait(&bar, loads & 1u);
         for (int k = t; k < N; k += 1024) {
           const int s0 = rp16[k], e0 = rp16[k + 1];
-          float acc = 0.f;
-          for (int p = s0; p < e0; p++) acc = __fadd_rn(acc, row[perm16[p]]);
+          float acc = seg_sum16(row, perm16, s0, e0);
           out[k] = q == 0 ? acc : __fadd_rn(out[k], acc);
         }
       }

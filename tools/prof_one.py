@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Dev tool (GPU box): launch ONE op of the bench workload a few times so ncu can capture it.
-usage: python tools/prof_one.py {fps|fps_noprune|ball|group|group3|groupbwd|threenn|tibwd|ti|ti_old|gf|upsample|knn|sigt|apply|manifold} [B]"""
+usage: python tools/prof_one.py {fps|fps_noprune|ball|group|group3|groupbwd|plan|threenn|tibwd|ti|ti_old|gf|upsample|knn|sigt|apply|manifold} [B]"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
@@ -60,6 +60,7 @@ for _ in range(3):
     elif what == "group": F.group_points(feat, nbr)
     elif what == "group3": F.group_points(xyz_t, nbr)
     elif what == "groupbwd": F.group_points_grad(go, plan, N)
+    elif what == "plan": F.ScatterPlan(nbr, B, N)
     elif what == "threenn": F.three_nn(xyz, centres)
     elif what == "tibwd": F.three_interpolate_grad(go3, w, plan3, M)
     elif what == "gf": F.graph_feature(gx_k, gx_q, gidx)
