@@ -1155,7 +1155,7 @@ GEOT_API int geot_scatter_plan_build(int B, int N, int64_t E, const int* idx, vo
   int* row_ptr = reinterpret_cast<int*>(plan);
   int* perm = reinterpret_cast<int*>(reinterpret_cast<char*>(plan) + plan_rowptr_bytes(B, N));
   // enough clouds to fill the GPU with one CTA each, or so little work that the launch count decides
-  if (N >= 1 && N <= kFusedMaxN && E >= 1 && E <= kFusedMaxE && (B >= 4 || E <= (1 << 17)) && !g_force_staged) {
+  if (N >= 1 && N <= kFusedMaxN && E >= 1 && E <= kFusedMaxE && (B >= 4 || E <= (1 << 15)) && !g_force_staged) {
     // one CTA per cloud builds the whole CSR in shared memory (see plan_build_fused_kernel)
     const size_t kBudget = (size_t)220 * 1024;  // + 1.2 KB of static shared memory in the kernel
     const size_t smem = (size_t)(N + 1) * 4 + (size_t)((((E + 31) >> 5) + 1023) / 1024) * 1024 * 4;
