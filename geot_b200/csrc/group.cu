@@ -860,12 +860,16 @@ static int launch_seg_reduce(int B, int C, int N, int64_t E, const float* g, con
 // shared memory.  Per-target sums: lane-strided partial sums then a fixed xor tree, i.e. a fixed order
 // (run-to-run identical); results leave through a shared staging row as coalesced stores.
 // ---------------------------------------------------------------------------------------------
+// One packed record per edge in plan order: {source point = perm / 3, weight bits}.  The reduce kernel then needs ONE
+// 8-byte load per edge instead of two 4-byte loads and a division by 3 (it is instruction-bound: ~16 instructions per
+// edge and R <= 3 channels before, round-1 ncu: 150 M warp instructions for 201 M edge-channels).
 __global__ void __launch_bounds__(256)
-plan_wsort_kernel(int64_t E, const float* __restrict__ w, const int* __restrict__ perm, float* __restrict__ wsorted) {
+plan_wsort_kernel(int64_t E, const float* __restrict__ w, const int* __restrict__ perm, int2* __restrict__ edges) {
   const int64_t e = (int64_t)blockIdx.x * 256 + threadIdx.x;
   if (e >= E) return;
   const int64_t base = (int64_t)blockIdx.y * E;
-  wsorted[base + e] = __ldg(w + base + __ldg(perm + base + e));
+  const int p = __ldg(perm + base + e);
+  edges[base + e] = make_int2(p / 3, __float_as_int(__ldg(w + base + p)));
 }
 
 // LPT = lanes per target: 8 for long segments (~48 edges when n/m = 16), 2 when a target has only a handful of
@@ -874,7 +878,7 @@ plan_wsort_kernel(int64_t E, const float* __restrict__ w, const int* __restrict_
 template <int R, int LPT>
 __global__ void __launch_bounds__(1024, 1)
 seg_reduce_wrows_kernel(int C, int n, int m, const float* __restrict__ g, const int* __restrict__ row_ptr,
-                        const int* __restrict__ perm, const float* __restrict__ wsorted, float* __restrict__ dst) {
+                        const int2* __restrict__ edges, float* __restrict__ dst) {
   extern __shared__ __align__(16) unsigned char wr_smem[];
   __shared__ uint64_t bar;
   float* rows = reinterpret_cast<float*>(wr_smem);          // R x n
@@ -894,8 +898,7 @@ seg_reduce_wrows_kernel(int C, int n, int m, const float* __restrict__ g, const 
   for (int i = t; i <= m; i += 1024) rp_s[i] = __ldg(rp + i);
   __syncthreads();
   mbar_wait(&bar, 0);
-  const int* __restrict__ pm = perm + (int64_t)b * E;
-  const float* __restrict__ ws = wsorted + (int64_t)b * E;
+  const int2* __restrict__ ed = edges + (int64_t)b * E;
   const int sub = t % LPT;
   // the loop bound is WARP-uniform (kb = first target of the warp): the xor tree below is a full-mask shuffle, so a
   // warp whose last targets fall beyond m (m not a multiple of 32 / LPT) must still run it with all 32 lanes -
@@ -910,21 +913,18 @@ seg_reduce_wrows_kernel(int C, int n, int m, const float* __restrict__ g, const 
     // up to 64 edges of the segment per round: all 8 {perm, w} pairs of a lane are requested before the first
     // is used, so a typical segment (~48 edges) costs one L2 round trip instead of one per pair
     for (int p0 = s0 + sub; p0 < e0; p0 += 8 * LPT) {
-      int sr[8];
-      float wt[8];
+      int2 e8[8];
 #pragma unroll
       for (int j = 0; j < 8; j++) {
         const int p = p0 + LPT * j;
-        const bool ok = p < e0;
-        sr[j] = ok ? __ldg(pm + p) : 0;
-        wt[j] = ok ? __ldg(ws + p) : 0.f;
+        e8[j] = p < e0 ? __ldg(ed + p) : make_int2(0, 0);
       }
 #pragma unroll
       for (int j = 0; j < 8; j++) {
         if (p0 + LPT * j < e0) {
-          const int src = sr[j] / 3;
+          const float wt = __int_as_float(e8[j].y);
 #pragma unroll
-          for (int r = 0; r < R; r++) acc[r] = __fadd_rn(acc[r], __fmul_rn(rows[(size_t)r * n + src], wt[j]));
+          for (int r = 0; r < R; r++) acc[r] = __fadd_rn(acc[r], __fmul_rn(rows[(size_t)r * n + e8[j].x], wt));
         }
       }
     }
@@ -944,17 +944,17 @@ seg_reduce_wrows_kernel(int C, int n, int m, const float* __restrict__ g, const 
 }
 
 template <int R, int LPT>
-static int launch_wrows_t(int B, int C, int n, int m, size_t smem, const float* g, const PlanView& pv, const float* wsorted,
+static int launch_wrows_t(int B, int C, int n, int m, size_t smem, const float* g, const PlanView& pv, const int2* wsorted,
                           float* dst, cudaStream_t s) {
   static DynSmem ds;  // per instantiation
   if (int rc = ds.need(seg_reduce_wrows_kernel<R, LPT>, 226 * 1024, "three_interpolate_grad")) return rc;
   dim3 grid((C + R - 1) / R, B);
-  seg_reduce_wrows_kernel<R, LPT><<<grid, 1024, smem, s>>>(C, n, m, g, pv.row_ptr, pv.perm, wsorted, dst);
+  seg_reduce_wrows_kernel<R, LPT><<<grid, 1024, smem, s>>>(C, n, m, g, pv.row_ptr, wsorted, dst);
   count_launch(1);
   return check_launch("seg_reduce_wrows_kernel");
 }
 template <int R>
-static int launch_wrows(int B, int C, int n, int m, size_t smem, const float* g, const PlanView& pv, const float* wsorted,
+static int launch_wrows(int B, int C, int n, int m, size_t smem, const float* g, const PlanView& pv, const int2* wsorted,
                         float* dst, cudaStream_t s) {
   // average segment = 3n / m edges
   if ((int64_t)3 * n < (int64_t)24 * m) return launch_wrows_t<R, 2>(B, C, n, m, smem, g, pv, wsorted, dst, s);
@@ -980,10 +980,11 @@ static int three_interpolate_grad_rows(int B, int C, int n, int m, const float* 
     if (score > best) { best = score; R = r; }
   }
   if (R == 0) return GEOT_OK;
-  // plan workspace: [row_ptr | perm | cursor | tmp(B*E ints) | ...]; tmp is scratch of the plan build, reused here
+  // plan workspace: [row_ptr | perm | cursor | tmp(B*E ints) | heavy list | spare(B*E ints)]; everything from tmp on is
+  // scratch of the plan build (at least 2 x B*E ints, geot_scatter_plan_bytes) and holds the packed edges here
   const PlanView pv = plan_view(plan, B, m);
   const size_t perm_b = plan_align((size_t)B * (size_t)E * sizeof(int));
-  float* wsorted = reinterpret_cast<float*>(const_cast<char*>(reinterpret_cast<const char*>(plan)) + plan_rowptr_bytes(B, m) + perm_b + plan_rowptr_bytes(B, m));
+  int2* wsorted = reinterpret_cast<int2*>(const_cast<char*>(reinterpret_cast<const char*>(plan)) + plan_rowptr_bytes(B, m) + perm_b + plan_rowptr_bytes(B, m));
   dim3 gw((unsigned)((E + 255) / 256), B);
   plan_wsort_kernel<<<gw, 256, 0, s>>>(E, w, pv.perm, wsorted);
   count_launch(1);
@@ -1137,8 +1138,10 @@ static inline int plan_heavy_cap(int B, int64_t E) { return (int)std::min<int64_
 GEOT_API size_t geot_scatter_plan_bytes(int B, int N, int64_t E) {
   if (B < 0 || N < 0 || E < 0) return 0;
   const size_t perm_b = plan_align((size_t)B * (size_t)E * sizeof(int));
+  // [row_ptr | perm] = the plan; [cursor | tmp | heavy count | heavy list | spare] = scratch of the build, reused by
+  // three_interpolate_grad for its packed {source, weight} edges (8 bytes per edge: tmp + spare)
   return plan_rowptr_bytes(B, N) + perm_b + plan_rowptr_bytes(B, N) + perm_b + 256 +
-         plan_align((size_t)plan_heavy_cap(B, E) * sizeof(int));
+         plan_align((size_t)plan_heavy_cap(B, E) * sizeof(int)) + perm_b;
 }
 
 GEOT_API int geot_scatter_plan_build(int B, int N, int64_t E, const int* idx, void* plan,
