@@ -425,20 +425,26 @@ __device__ __forceinline__ void plan_thread_sort16(T* __restrict__ seg, int L) {
 // and leaves by one coalesced pass; T = int: it is filled and sorted in place in global memory (longer lists).
 template <typename T>
 __global__ void __launch_bounds__(1024, 1)
-plan_build_fused_kernel(int N, int E, int list_cap, const int* __restrict__ idx_all, int* __restrict__ row_ptr_all, int* __restrict__ perm_all) {
+plan_build_fused_kernel(int Nall, int E, int list_cap, int nmax, const int* __restrict__ idx_all, int* __restrict__ row_ptr_all, int* __restrict__ perm_all) {
   constexpr bool kSmemList = sizeof(T) == 2;
+  // grid (B, S): with few clouds the targets of a cloud are split into S ranges, one CTA each.  Every CTA scans ALL
+  // sources of the cloud (L2-resident) but keeps only those whose target falls into [t_lo, t_hi); the number of sources
+  // with a smaller target - its offset into the cloud's list - is counted in the same scan, so the CTAs of a cloud
+  // never talk to each other.  N below is the LOCAL target count, targets are re-based by t_lo.
+  const int t_lo = (int)((int64_t)blockIdx.y * Nall / gridDim.y), t_hi = (int)((int64_t)(blockIdx.y + 1) * Nall / gridDim.y);
+  const int N = t_hi - t_lo;
   extern __shared__ int plan_sm[];
   int* cnt = plan_sm;                                   // N+1 counters, later cursors
-  unsigned* bm = reinterpret_cast<unsigned*>(plan_sm + N + 1);   // E bits (very long segments only)
+  unsigned* bm = reinterpret_cast<unsigned*>(plan_sm + nmax + 1);   // E bits (very long segments only)
   const int bm_words = ((((E + 31) >> 5) + 1023) >> 10) << 10;
   __shared__ int s_warp[32];
   __shared__ int s_carry, s_heavy_n;
   __shared__ int s_heavy[256];
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5, b = blockIdx.x;
   const int* __restrict__ idx = idx_all + (int64_t)b * E;
-  int* __restrict__ row_ptr = row_ptr_all + (int64_t)b * (N + 1);
-  int* __restrict__ perm_out = perm_all + (int64_t)b * E;
-  T* __restrict__ perm = kSmemList ? reinterpret_cast<T*>(bm + bm_words) : reinterpret_cast<T*>(perm_out);
+  int* __restrict__ row_ptr = row_ptr_all + (int64_t)b * (Nall + 1) + t_lo;
+  int* __restrict__ perm_out = perm_all + (int64_t)b * E;   // + the range's offset, known after the count pass
+  __shared__ int s_below[32];
   // work lists of the sort phase (target ids): segments of 3..16 entries / of 17..kFusedWarp entries
   int* list16 = reinterpret_cast<int*>(bm + bm_words) + (kSmemList ? ((E + 1) >> 1) : 0);
   int* listw = list16 + list_cap;
@@ -449,15 +455,23 @@ plan_build_fused_kernel(int N, int E, int list_cap, const int* __restrict__ idx_
   __syncthreads();
   PLAN_STAMP(1);
   constexpr int U = 8;  // loads in flight per thread: the edge loops are L2-latency bound otherwise
+  int below = 0;        // sources of this cloud whose (valid) target lies before this CTA's range
   for (int e0 = t; e0 < E; e0 += 1024 * U) {
     int k[U];
 #pragma unroll
     for (int u = 0; u < U; u++) k[u] = (e0 + u * 1024 < E) ? __ldg(idx + e0 + u * 1024) : -1;
 #pragma unroll
-    for (int u = 0; u < U; u++)
-      if ((unsigned)k[u] < (unsigned)N) atomicAdd(&cnt[k[u] + 1], 1);   // integer: order-free
+    for (int u = 0; u < U; u++) {
+      if ((unsigned)(k[u] - t_lo) < (unsigned)N) atomicAdd(&cnt[k[u] - t_lo + 1], 1);   // integer: order-free
+      else if ((unsigned)k[u] < (unsigned)t_lo) below++;
+    }
   }
+  below = __reduce_add_sync(0xffffffffu, below);
+  if (lane == 0) s_below[warp] = below;
   __syncthreads();
+  const int list_base = __reduce_add_sync(0xffffffffu, s_below[lane]);   // identical in every thread
+  perm_out += list_base;
+  T* __restrict__ perm = kSmemList ? reinterpret_cast<T*>(bm + bm_words) : reinterpret_cast<T*>(perm_out);
   PLAN_STAMP(2);
   // inclusive scan of cnt[0..N] (counts stored shifted by one => exclusive start offsets): every thread owns P
   // consecutive counters (P odd: conflict-free strides), one block-wide scan of the thread totals
@@ -483,7 +497,8 @@ plan_build_fused_kernel(int N, int E, int list_cap, const int* __restrict__ idx_
     int run = __shfl_sync(0xffffffffu, winc - w, warp) + inc - tot;
     for (int i = lo; i < hi; i++) { run += cnt[i]; cnt[i] = run; }
     __syncthreads();
-    for (int i = t; i <= N; i += 1024) row_ptr[i] = cnt[i];
+    // row_ptr[t_lo + i]; the entry at t_hi belongs to the next range (its own offset + 0), the last range also writes row_ptr[Nall]
+    for (int i = t; i < N + (t_hi == Nall ? 1 : 0); i += 1024) row_ptr[i] = list_base + cnt[i];
     __syncthreads();  // the fill below turns the counters into cursors: nobody may still be copying them out
   }
   PLAN_STAMP(3);
@@ -494,7 +509,7 @@ plan_build_fused_kernel(int N, int E, int list_cap, const int* __restrict__ idx_
     for (int u = 0; u < U; u++) k[u] = (e0 + u * 1024 < E) ? __ldg(idx + e0 + u * 1024) : -1;
 #pragma unroll
     for (int u = 0; u < U; u++)
-      if ((unsigned)k[u] < (unsigned)N) perm[atomicAdd(&cnt[k[u]], 1)] = (T)(e0 + u * 1024);
+      if ((unsigned)(k[u] - t_lo) < (unsigned)N) perm[atomicAdd(&cnt[k[u] - t_lo], 1)] = (T)(e0 + u * 1024);
   }
   __syncthreads();  // the CTA's own global writes are visible to it after the barrier
   PLAN_STAMP(4);
@@ -551,8 +566,9 @@ plan_build_fused_kernel(int N, int E, int list_cap, const int* __restrict__ idx_
 #ifdef GEOT_FPS_PROF
   if (blockIdx.x == 0 && threadIdx.x == 0) g_plan_prof[7] = heavy_n;
 #endif
+  const int n_local = N > 0 ? cnt[N - 1] : 0;  // sources whose target lies in this range
   if (heavy_n == 0) {
-    if (kSmemList) for (int i = t; i < E; i += 1024) perm_out[i] = (int)perm[i];
+    if (kSmemList) for (int i = t; i < n_local; i += 1024) perm_out[i] = (int)perm[i];
     return;
   }
   const int nwords = (E + 31) >> 5;
@@ -594,7 +610,7 @@ plan_build_fused_kernel(int N, int E, int list_cap, const int* __restrict__ idx_
     }
     __syncthreads();
   }
-  if (kSmemList) for (int i = t; i < E; i += 1024) perm_out[i] = (int)perm[i];
+  if (kSmemList) for (int i = t; i < n_local; i += 1024) perm_out[i] = (int)perm[i];
   PLAN_STAMP(6);
 }
 
@@ -1157,26 +1173,32 @@ GEOT_API int geot_scatter_plan_build(int B, int N, int64_t E, const int* idx, vo
   cudaStream_t s = as_stream(stream);
   int* row_ptr = reinterpret_cast<int*>(plan);
   int* perm = reinterpret_cast<int*>(reinterpret_cast<char*>(plan) + plan_rowptr_bytes(B, N));
-  // enough clouds to fill the GPU with one CTA each, or so little work that the launch count decides
-  if (N >= 1 && N <= kFusedMaxN && E >= 1 && E <= kFusedMaxE && (B >= 4 || E <= (1 << 15)) && !g_force_staged) {
-    // one CTA per cloud builds the whole CSR in shared memory (see plan_build_fused_kernel)
-    const size_t kBudget = (size_t)220 * 1024;  // + 1.2 KB of static shared memory in the kernel
-    const size_t smem = (size_t)(N + 1) * 4 + (size_t)((((E + 31) >> 5) + 1023) / 1024) * 1024 * 4;
+  // with few clouds, S CTAs per cloud (one target range each): the sort phase - most of the build - divides by S,
+  // the two scans of the cloud's sources do not
+  int S = 1;
+  while (S < 8 && (int64_t)B * S * 2 <= kNumSMs && N / (S * 2) >= 256) S *= 2;
+  const int nmax = (N + S - 1) / S + 1;  // targets per CTA (upper bound)
+  // every CTA scans all E sources of its cloud twice: that has to stay small next to the multi-kernel path's launches
+  // (measured: B=1, E=524288 on 8 CTAs 0.235 ms against 0.116 ms for the multi-kernel path)
+  if (N >= 1 && nmax <= kFusedMaxN && E >= 1 && E <= kFusedMaxE && (E <= (1 << 17) || (int64_t)B * S >= 16) && B <= 65535 && !g_force_staged) {
+    // the whole CSR of a cloud (or of one target range of it) in shared memory (see plan_build_fused_kernel)
+    const size_t kBudget = (size_t)220 * 1024;  // + 1.3 KB of static shared memory in the kernel
+    const size_t smem = (size_t)(nmax + 1) * 4 + (size_t)((((E + 31) >> 5) + 1023) / 1024) * 1024 * 4;
     const size_t smem16 = smem + (size_t)((E + 1) / 2) * 4;  // + the source list as 16-bit entries
     static DynSmem ds_fused16, ds_fused32;
     // the two work lists of the sort phase take what is left, at most one entry per target each
-    auto lists = [&](size_t base) { return (int)std::min<size_t>((size_t)N, (kBudget - base) / 8); };
+    auto lists = [&](size_t base) { return (int)std::min<size_t>((size_t)nmax, (kBudget - base) / 8); };
     if (E <= 65535 && smem16 + 8 * 256 <= kBudget) {
       const int cap = lists(smem16);
       if (int rc = ds_fused16.need(plan_build_fused_kernel<unsigned short>, kBudget, "scatter_plan_build")) return rc;
-      plan_build_fused_kernel<unsigned short><<<B, 1024, smem16 + (size_t)cap * 8, s>>>(N, (int)E, cap, idx, row_ptr, perm);
+      plan_build_fused_kernel<unsigned short><<<dim3(B, S), 1024, smem16 + (size_t)cap * 8, s>>>(N, (int)E, cap, nmax, idx, row_ptr, perm);
       count_launch(1);
       return check_launch("plan_build_fused_kernel<u16>");
     }
     if (smem + 8 * 256 <= kBudget) {
       const int cap = lists(smem);
       if (int rc = ds_fused32.need(plan_build_fused_kernel<int>, kBudget, "scatter_plan_build")) return rc;
-      plan_build_fused_kernel<int><<<B, 1024, smem + (size_t)cap * 8, s>>>(N, (int)E, cap, idx, row_ptr, perm);
+      plan_build_fused_kernel<int><<<dim3(B, S), 1024, smem + (size_t)cap * 8, s>>>(N, (int)E, cap, nmax, idx, row_ptr, perm);
       count_launch(1);
       return check_launch("plan_build_fused_kernel<int>");
     }
