@@ -263,78 +263,94 @@ def _fusable(query_xyz, support_xyz):
             and not (torch.is_grad_enabled() and (support_xyz.requires_grad or query_xyz.requires_grad)))
 
 
-class QueryAndGroup(nn.Module):
-    """group.py:206-255: ball_query -> group xyz -> subtract centre (-> /radius) -> group features."""
+class _Grouper(nn.Module):
+    """Shared body of the two neighbourhood groupers: neighbour search (subclass) -> positions of the neighbours,
+    relative to their centre when `relative_xyz` -> optional scale -> grouped features.  With positions outside
+    autograd (the usual case) the position part is ONE kernel reading the (B,N,3) cloud directly; otherwise it is
+    grouping_operation on the transposed cloud, which has the deterministic backward."""
+
+    relative_xyz = True
+    return_only_idx = False
+
+    def _neighbours(self, query_xyz, support_xyz):
+        raise NotImplementedError
+
+    def _fused_divisor(self):
+        return 0.0
+
+    def _rescale(self, grouped_xyz, fused):
+        return grouped_xyz
+
+    def forward(self, query_xyz, support_xyz, features=None):
+        idx = self._neighbours(query_xyz, support_xyz)
+        if self.return_only_idx:
+            return idx
+        idx = idx.int().contiguous()
+        fused = _fusable(query_xyz, support_xyz)
+        if fused:
+            grouped_xyz = F_.group_xyz_relative(support_xyz, query_xyz, idx, relative=self.relative_xyz,
+                                                divisor=self._fused_divisor())
+        else:
+            grouped_xyz = grouping_operation(support_xyz.transpose(1, 2).contiguous(), idx)   # (B,3,npoint,nsample)
+            if self.relative_xyz:
+                grouped_xyz = grouped_xyz - query_xyz.transpose(1, 2).unsqueeze(-1)
+        grouped_xyz = self._rescale(grouped_xyz, fused)
+        return grouped_xyz, (None if features is None else grouping_operation(features, idx))
+
+
+class QueryAndGroup(_Grouper):
+    """Ball-query grouper, the role of openpoints/models/layers/group.py:206-255.  normalize_dp divides the
+    relative positions by the radius (inside the fused kernel when that path is taken)."""
 
     def __init__(self, radius: float, nsample: int, relative_xyz=True, normalize_dp=False,
                  normalize_by_std=False, normalize_by_allstd=False, normalize_by_allstd2=False,
                  return_only_idx=False, **kwargs):
         super().__init__()
+        if int(bool(normalize_dp)) + int(bool(normalize_by_std)) + int(bool(normalize_by_allstd)) > 1:
+            raise AssertionError("at most one of normalize_dp / normalize_by_std / normalize_by_allstd")
         self.radius, self.nsample = radius, nsample
+        self.relative_xyz, self.return_only_idx = relative_xyz, return_only_idx
         self.normalize_dp = normalize_dp
-        self.normalize_by_std = normalize_by_std
-        self.normalize_by_allstd = normalize_by_allstd
-        self.normalize_by_allstd2 = normalize_by_allstd2
-        assert self.normalize_dp + self.normalize_by_std + self.normalize_by_allstd < 2
-        self.relative_xyz = relative_xyz
-        self.return_only_idx = return_only_idx
+        # accepted and stored like the reference's constructor; its forward never reads them either
+        self.normalize_by_std, self.normalize_by_allstd, self.normalize_by_allstd2 = \
+            normalize_by_std, normalize_by_allstd, normalize_by_allstd2
 
-    def forward(self, query_xyz, support_xyz, features=None):
-        idx = ball_query(self.radius, self.nsample, support_xyz, query_xyz)
-        if self.return_only_idx:
-            return idx
-        if _fusable(query_xyz, support_xyz):
-            # positions carry no gradient (the usual case): one kernel straight from the (B,N,3) cloud
-            grouped_xyz = F_.group_xyz_relative(support_xyz, query_xyz, idx, relative=self.relative_xyz,
-                                                divisor=self.radius if (self.relative_xyz and self.normalize_dp) else 0.0)
-        else:
-            xyz_trans = support_xyz.transpose(1, 2).contiguous()
-            grouped_xyz = grouping_operation(xyz_trans, idx)  # (B,3,npoint,nsample)
-            if self.relative_xyz:
-                grouped_xyz = grouped_xyz - query_xyz.transpose(1, 2).unsqueeze(-1)
-                if self.normalize_dp:
-                    grouped_xyz /= self.radius
-        grouped_features = grouping_operation(features, idx) if features is not None else None
-        return grouped_xyz, grouped_features
+    def _neighbours(self, query_xyz, support_xyz):
+        return ball_query(self.radius, self.nsample, support_xyz, query_xyz)
+
+    def _fused_divisor(self):
+        return self.radius if (self.relative_xyz and self.normalize_dp) else 0.0
+
+    def _rescale(self, grouped_xyz, fused):
+        if fused or not (self.relative_xyz and self.normalize_dp):
+            return grouped_xyz
+        return grouped_xyz / self.radius
 
 
 class GroupAll(nn.Module):
-    """group.py:258-272."""
+    """One group holding the whole cloud (group.py:258-272): (B,3,1,N) positions, (B,C,1,N) features."""
 
     def forward(self, new_xyz, xyz, features=None):
-        grouped_xyz = xyz.transpose(1, 2).unsqueeze(2)
-        grouped_features = features.unsqueeze(2) if features is not None else None
-        return grouped_xyz, grouped_features
+        return xyz.transpose(1, 2).unsqueeze(2), (None if features is None else features.unsqueeze(2))
 
 
-class KNNGroup(nn.Module):
-    """group.py:275-320."""
+class KNNGroup(_Grouper):
+    """kNN grouper, the role of group.py:275-320.  normalize_dp divides by each cloud's largest neighbour offset."""
 
     def __init__(self, nsample: int, relative_xyz=True, normalize_dp=False, return_only_idx=False, **kwargs):
         super().__init__()
         self.nsample = nsample
         self.knn = GroupKNN(nsample, transpose_mode=True)
-        self.relative_xyz = relative_xyz
-        self.normalize_dp = normalize_dp
-        self.return_only_idx = return_only_idx
+        self.relative_xyz, self.normalize_dp, self.return_only_idx = relative_xyz, normalize_dp, return_only_idx
 
-    def forward(self, query_xyz, support_xyz, features=None):
-        _, idx = self.knn(support_xyz, query_xyz)
-        if self.return_only_idx:
-            return idx
-        idx = idx.int()
-        if _fusable(query_xyz, support_xyz):
-            grouped_xyz = F_.group_xyz_relative(support_xyz, query_xyz, idx.contiguous(), relative=self.relative_xyz)
-        else:
-            xyz_trans = support_xyz.transpose(1, 2).contiguous()
-            grouped_xyz = grouping_operation(xyz_trans, idx)
-            if self.relative_xyz:
-                grouped_xyz -= query_xyz.transpose(1, 2).unsqueeze(-1)
-        if self.normalize_dp:
-            grouped_xyz /= torch.amax(torch.sqrt(torch.sum(grouped_xyz ** 2, dim=1)), dim=(1, 2)).view(-1, 1, 1, 1)
-        if features is not None:
-            return grouped_xyz, grouping_operation(features, idx)
-        return grouped_xyz, None
+    def _neighbours(self, query_xyz, support_xyz):
+        return self.knn(support_xyz, query_xyz)[1]
+
+    def _rescale(self, grouped_xyz, fused):
+        if not self.normalize_dp:
+            return grouped_xyz
+        reach = grouped_xyz.square().sum(dim=1).amax(dim=(1, 2)).sqrt()
+        return grouped_xyz / reach.view(-1, 1, 1, 1)
 
 
 # --------------------------------------------------------------------------------------------------

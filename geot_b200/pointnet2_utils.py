@@ -58,6 +58,24 @@ class BallQuery(Function):
 ball_query = BallQuery.apply
 
 
+def _resample_unique(idx):
+    """sample_uniformly of pointnet2_utils.py:291-373, for all (batch, region) rows at once on the device: each
+    row becomes its distinct ids in ascending order followed by uniform draws (with replacement) from those ids.
+    Same distribution as the reference's per-region torch.unique / torch.randint loop, not the same random stream
+    (the reference draws on the CPU generator, one region at a time).  -> (idx int32, distinct count per row)."""
+    nsample = idx.shape[-1]
+    ordered = idx.sort(dim=-1).values
+    is_first = torch.ones_like(ordered, dtype=torch.bool)
+    is_first[..., 1:] = ordered[..., 1:] != ordered[..., :-1]
+    rank = is_first.cumsum(-1) - 1                               # repeated ids share a rank, so the scatter is race-free
+    distinct = torch.zeros_like(ordered).scatter_(-1, rank, ordered)
+    count = rank[..., -1:] + 1
+    slot = torch.arange(nsample, device=idx.device).expand_as(ordered)
+    draw = (torch.rand(ordered.shape, device=idx.device) * count).long().minimum(count - 1)
+    out = distinct.gather(-1, torch.where(slot < count, slot, draw))
+    return out.to(idx.dtype).contiguous(), count.squeeze(-1).float().cpu()
+
+
 class QueryAndGroup(nn.Module):
     """pointnet2_utils.py:291-373 (argument order xyz, new_xyz — the opposite of openpoints' grouper)."""
 
@@ -69,21 +87,13 @@ class QueryAndGroup(nn.Module):
         self.normalize_xyz = normalize_xyz
         self.sample_uniformly = sample_uniformly
         self.ret_unique_cnt = ret_unique_cnt
-        if self.ret_unique_cnt:
-            assert self.sample_uniformly
+        if ret_unique_cnt and not sample_uniformly:
+            raise AssertionError("ret_unique_cnt needs sample_uniformly")
 
     def forward(self, xyz, new_xyz, features=None):
         idx = ball_query(self.radius, self.nsample, xyz, new_xyz)
         if self.sample_uniformly:
-            unique_cnt = torch.zeros((idx.shape[0], idx.shape[1]))
-            for i_batch in range(idx.shape[0]):
-                for i_region in range(idx.shape[1]):
-                    unique_ind = torch.unique(idx[i_batch, i_region, :])
-                    num_unique = unique_ind.shape[0]
-                    unique_cnt[i_batch, i_region] = num_unique
-                    sample_ind = torch.randint(0, num_unique, (self.nsample - num_unique,), dtype=torch.long)
-                    all_ind = torch.cat((unique_ind, unique_ind[sample_ind]))
-                    idx[i_batch, i_region, :] = all_ind
+            idx, unique_cnt = _resample_unique(idx)
         if _layers._fusable(new_xyz, xyz):  # positions outside autograd: one fused kernel, same bits
             grouped_xyz = F_.group_xyz_relative(xyz, new_xyz, idx, relative=True,
                                                 divisor=self.radius if self.normalize_xyz else 0.0)
@@ -97,7 +107,8 @@ class QueryAndGroup(nn.Module):
             grouped_features = grouping_operation(features, idx)
             new_features = torch.cat([grouped_xyz, grouped_features], dim=1) if self.use_xyz else grouped_features
         else:
-            assert self.use_xyz, "Cannot have not features and not use xyz as a feature!"
+            if not self.use_xyz:
+                raise AssertionError("QueryAndGroup without features needs use_xyz=True")
             new_features = grouped_xyz
         ret = [new_features]
         if self.ret_grouped_xyz:

@@ -175,31 +175,35 @@ class Grouping(Function):
 grouping = Grouping.apply
 
 
+def _neighbour_rows(nsample, xyz, new_xyz, offset, new_offset, radius, query_method):
+    if query_method in ('knn', 'knnquery'):
+        return knnquery(nsample, xyz, new_xyz, offset, new_offset)[0]
+    return ballquery(radius, nsample, xyz, new_xyz, offset, new_offset)
+
+
 def querygroup(nsample, xyz, new_xyz, feat, offset, new_offset, radius=None, query_method='knn',
                normalize_dp=False, idx=None):
-    """openpoints/cpp/pointops/functions/pointops.py:106-147 (kNN or ball query + torch row gathers)."""
-    assert xyz.is_contiguous() and new_xyz.is_contiguous() and feat.is_contiguous()
-    if new_xyz is None:
-        new_xyz = xyz
+    """Neighbour search + relative positions + grouped features, offset format; the role of
+    openpoints/cpp/pointops/functions/pointops.py:106-147.  -> (grouped_xyz (m,nsample,3), grouped_feat (m,nsample,c)).
+
+    Built on the grouping kernel (deterministic backward) rather than fancy indexing.  Differences from the
+    reference function, both supersets: a caller-supplied `idx` is used (the reference falls off the end and returns
+    None in that case), and `feat=None` is accepted (the reference asserts on it before its own None check).
+    normalize_dp divides by the group's largest offset norm (+1e-8) for query_method 'knn' and by `radius` otherwise."""
+    new_xyz = xyz if new_xyz is None else new_xyz
+    for t in (xyz, new_xyz) + (() if feat is None else (feat,)):
+        if not t.is_contiguous():
+            raise AssertionError("querygroup needs contiguous xyz / new_xyz / feat")
+    if nsample is None:                              # group-all: every point of the batch, one group
+        return xyz.transpose(1, 2).unsqueeze(2), (None if feat is None else feat.unsqueeze(2))
     if idx is None:
-        if nsample is not None:
-            if query_method in ['knn', 'knnquery']:
-                idx, _ = knnquery(nsample, xyz, new_xyz, offset, new_offset)
-            else:
-                idx = ballquery(radius, nsample, xyz, new_xyz, offset, new_offset)
-            idx = idx.flatten().long()
-            m, c = new_xyz.shape[0], feat.shape[1]
-            grouped_xyz = xyz[idx, :].view(m, nsample, 3)
-            grouped_xyz -= new_xyz.unsqueeze(1)
-            if normalize_dp:
-                max_dist = grouped_xyz.norm(dim=-1, p=2, keepdim=True).max(dim=-1, keepdim=True)[0] + 1.0e-8 \
-                    if query_method == 'knn' else radius
-                grouped_xyz /= max_dist
-            grouped_feat = feat[idx, :].view(m, nsample, c) if feat is not None else None
-        else:
-            grouped_xyz = xyz.transpose(1, 2).unsqueeze(2)
-            grouped_feat = feat.unsqueeze(2) if feat is not None else None
-        return grouped_xyz, grouped_feat
+        idx = _neighbour_rows(nsample, xyz, new_xyz, offset, new_offset, radius, query_method)
+    idx = idx.view(new_xyz.shape[0], nsample).int().contiguous()
+    rel = grouping(xyz, idx) - new_xyz.unsqueeze(1)
+    if normalize_dp:
+        scale = rel.norm(dim=-1, keepdim=True).amax(dim=1, keepdim=True) + 1.0e-8 if query_method == 'knn' else radius
+        rel = rel / scale
+    return rel, (None if feat is None else grouping(feat, idx))
 
 
 def queryandgroup(nsample, xyz, new_xyz, feat, idx, offset, new_offset, use_xyz=True):

@@ -180,6 +180,57 @@ def test_pointops_offset_autograd(cuda):
     assert up.shape == (n, c)
 
 
+@pytest.mark.parametrize("method,normalize", [("knn", False), ("knn", True), ("ballquery", True)])
+def test_pointops_querygroup_equals_row_gathers(cuda, method, normalize):
+    """querygroup (pointops.py:106-147 role) against the fancy-indexing statement of the same thing, incl. the two
+    normalize_dp branches, a caller-supplied idx, feat=None and the group-all (nsample=None) form."""
+    n, c, ns, r = 3000, 8, 8, 0.2
+    xyz = cu(synth.tooth_cloud(n, 5))
+    off = torch.tensor([1200, 3000], dtype=torch.int32, device="cuda")
+    feat = torch.randn(n, c, device="cuda", requires_grad=True)
+    dp, fj = pointops.querygroup(ns, xyz, xyz, feat, off, off, radius=r, query_method=method, normalize_dp=normalize)
+    idx = pointops.knnquery(ns, xyz, xyz, off, off)[0] if method == "knn" else pointops.ballquery(r, ns, xyz, xyz, off, off)
+    rel = xyz[idx.long().flatten()].view(n, ns, 3) - xyz.unsqueeze(1)
+    if normalize:
+        rel = rel / ((rel.norm(dim=-1, keepdim=True).max(dim=1, keepdim=True)[0] + 1e-8) if method == "knn" else r)
+    assert torch.equal(dp, rel) and torch.equal(fj, feat[idx.long().flatten()].view(n, ns, c))
+    (fj * fj).sum().backward()
+    g = feat.grad.clone(); feat.grad = None
+    feat[idx.long().flatten()].square().sum().backward()
+    torch.testing.assert_close(g, feat.grad, rtol=1e-5, atol=1e-5)
+    dp2, fj2 = pointops.querygroup(ns, xyz, xyz, None, off, off, radius=r, query_method=method, normalize_dp=normalize, idx=idx)
+    assert fj2 is None and torch.equal(dp2, dp)
+    ga_xyz, ga_feat = pointops.querygroup(None, xyz.view(2, 1500, 3), None, feat.detach().view(2, c, 1500), off, off)
+    assert ga_xyz.shape == (2, 3, 1, 1500) and ga_feat.shape == (2, c, 1, 1500)
+
+
+def test_query_and_group_sample_uniformly(cuda):
+    """pointnet2_utils.QueryAndGroup(sample_uniformly=True) (pointnet2_utils.py:291-373 role), vectorised: every row is
+    its distinct ball-query ids ascending, then draws from exactly that set; the count is returned like the reference's."""
+    xyz = cu(synth.tooth_batch(2, 2048))
+    q = xyz[:, ::16].contiguous()
+    ns = 24
+    raw = pointnet2_utils.ball_query(0.12, ns, xyz, q)
+    torch.manual_seed(5)
+    grouper = pointnet2_utils.QueryAndGroup(0.12, ns, use_xyz=True, ret_grouped_xyz=True, sample_uniformly=True, ret_unique_cnt=True)
+    nf, gxyz, cnt = grouper(xyz, q, None)
+    assert nf.shape == (2, 3, 128, ns) and cnt.shape == (2, 128) and cnt.device.type == "cpu"
+    idx, cnt2 = pointnet2_utils._resample_unique(raw)
+    assert idx.dtype == torch.int32 and torch.equal(cnt2, cnt)
+    raw_h, idx_h = raw.cpu(), idx.cpu()
+    some_padding = False
+    for b in range(2):
+        for p in range(128):
+            u = torch.unique(raw_h[b, p])
+            k = u.numel()
+            assert cnt[b, p] == k and torch.equal(idx_h[b, p, :k], u.int())
+            assert set(idx_h[b, p, k:].tolist()) <= set(u.tolist())
+            some_padding |= k < ns
+    assert some_padding
+    with pytest.raises(AssertionError):
+        pointnet2_utils.QueryAndGroup(0.1, 8, ret_unique_cnt=True)
+
+
 def test_facades_have_the_reference_callables(cuda):
     names = ["ball_query_wrapper", "group_points_wrapper", "group_points_grad_wrapper", "gather_points_wrapper",
              "gather_points_grad_wrapper", "furthest_point_sampling_wrapper", "three_nn_wrapper",
