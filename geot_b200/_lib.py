@@ -34,6 +34,7 @@ _SIGNATURES = {
     "geot_furthestsampling": [_i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
     "geot_ball_query_workspace_bytes": [_i, _i],
     "geot_ball_query": [_i, _i, _i, _f, _i, _vp, _vp, _vp, _vp, _sz, _i, _vp],
+    "geot_ball_query_static": [_i, _i, _i, _f, _i, _vp, _vp, _vp, _i, _vp],
     "geot_ballquery_offset": [_i, _i, _f, _i, _vp, _vp, _vp, _vp, _vp, _vp],
     "geot_knnquery_workspace_bytes": [_i, _i, _i],
     "geot_knnquery": [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _sz, _i, _vp],

@@ -28,6 +28,8 @@
 // conservative under fp32 rounding of the cell arithmetic.  bq_build_kernel decides per cloud which path is
 // cheaper (dense balls finish the index-order scan after a few dozen points) and each kernel skips the
 // clouds of the other.
+#include <atomic>
+
 #include "common.cuh"
 
 namespace geot {
@@ -457,6 +459,64 @@ GEOT_API int geot_ball_query(int B, int N, int M, float radius, int nsample, con
   ball_query_shared_kernel<<<grid, 1024, 0, s>>>(N, M, radius, nsample, new_xyz, xyz, idx, aligned16, ws, stride);
   count_launch(1);
   return check_launch("ball_query_shared_kernel");
+}
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free variant: the grid-binning scratch lives in a file-scope device array instead of a caller
+// workspace (for callers that cannot allocate: CUDA graph capture, serving loops).  No counterpart in the
+// reference.  Every call on a device shares the one array: calls that overlap on that GPU race on it.
+// Nothing in it has to start at zero: bq_build_kernel rewrites the header, the cell starts and the sorted
+// points of every cloud it is given before bq_grid_kernel / ball_query_shared_kernel read them, and the
+// counters that do start at zero live in shared memory.
+// ---------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_bq_static_scratch[GEOT_BALL_QUERY_STATIC_SCRATCH_BYTES];
+
+// In host code `g_bq_static_scratch` is only a handle for the runtime; the device address comes from
+// cudaGetSymbolAddress, looked up once per device with that device current.
+static int bq_static_scratch_address(unsigned char** out) {
+  static std::atomic<unsigned char*> per_device[64];
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) {
+    set_error("ball_query_static: cudaGetDevice: %s", cudaGetErrorString(e));
+    return GEOT_ERR_CUDA;
+  }
+  const bool cached = dev >= 0 && dev < 64;
+  unsigned char* p = cached ? per_device[dev].load(std::memory_order_acquire) : nullptr;
+  if (p == nullptr) {
+    void* sym = nullptr;
+    e = cudaGetSymbolAddress(&sym, g_bq_static_scratch);
+    if (e != cudaSuccess || sym == nullptr) {
+      set_error("ball_query_static: cudaGetSymbolAddress(scratch) on device %d: %s", dev, cudaGetErrorString(e));
+      return GEOT_ERR_CUDA;
+    }
+    p = static_cast<unsigned char*>(sym);
+    if (cached) per_device[dev].store(p, std::memory_order_release);
+  }
+  *out = p;
+  return GEOT_OK;
+}
+
+GEOT_API int geot_ball_query_static(int B, int N, int M, float radius, int nsample, const float* new_xyz,
+                                    const float* xyz, int* idx, int flags, geot_stream_t stream) {
+  GEOT_REQUIRE(B >= 0 && N >= 0 && M >= 0 && nsample >= 0, "ball_query_static: bad sizes");
+  if (B == 0 || M == 0 || nsample == 0) return GEOT_OK;
+  GEOT_REQUIRE(N >= 1, "ball_query_static: N=%d (need at least one point per cloud)", N);
+  if (N > kBqMaxN) {
+    set_error("ball_query_static: N=%d exceeds the binned path's limit of %d points per cloud", N, kBqMaxN);
+    return GEOT_ERR_WORKSPACE;
+  }
+  const size_t need = (size_t)B * bq_ws_stride(N);
+  if (need > (size_t)GEOT_BALL_QUERY_STATIC_SCRATCH_BYTES) {
+    set_error("ball_query_static: B=%d x N=%d needs %zu bytes of scratch, the built-in array holds %zu "
+              "(use geot_ball_query with a caller workspace)",
+              B, N, need, (size_t)GEOT_BALL_QUERY_STATIC_SCRATCH_BYTES);
+    return GEOT_ERR_WORKSPACE;
+  }
+  unsigned char* scratch = nullptr;
+  if (int rc = bq_static_scratch_address(&scratch)) return rc;
+  return geot_ball_query(B, N, M, radius, nsample, new_xyz, xyz, idx, scratch, (size_t)GEOT_BALL_QUERY_STATIC_SCRATCH_BYTES,
+                         flags, stream);
 }
 
 GEOT_API int geot_ballquery_offset(int b, int m, float radius, int nsample, const float* xyz,

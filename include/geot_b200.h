@@ -92,6 +92,20 @@ int geot_ball_query(int B, int N, int M, float radius, int nsample, const float*
                     const float* xyz, int* idx, void* workspace, size_t workspace_bytes, int flags,
                     geot_stream_t stream);
 
+/* No counterpart in the reference: added for callers that cannot
+ * allocate device memory (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same result as
+ * geot_ball_query with a workspace, but the grid-binning scratch is a device array built into the library
+ * (GEOT_BALL_QUERY_STATIC_SCRATCH_BYTES, held by every GPU that loads the library until exit); the call
+ * allocates and frees nothing.  Limit: N <= 65536 and geot_ball_query_workspace_bytes(B, N) <=
+ * GEOT_BALL_QUERY_STATIC_SCRATCH_BYTES (e.g. 16 clouds x 16384 points, or 7 x 65536); beyond it the call
+ * returns GEOT_ERR_WORKSPACE with a message and launches nothing.  All calls on one GPU share the array:
+ * calls that can overlap on the GPU (different streams, no ordering between them) race on it — order them.
+ * The array keeps the previous call's contents; nothing in it needs clearing between calls (each call rebuilds
+ * every cloud's bins before reading them). */
+#define GEOT_BALL_QUERY_STATIC_SCRATCH_BYTES (8u << 20)
+int geot_ball_query_static(int B, int N, int M, float radius, int nsample, const float* new_xyz,
+                           const float* xyz, int* idx, int flags, geot_stream_t stream);
+
 /* replaces pointops_cuda.ballquery_cuda(m,radius,nsample,xyz,new_xyz,offset,new_offset,idx)
  * (openpoints/cpp/pointops/src/ballquery/ballquery_cuda_kernel.cu:26-78).  b = number of segments. */
 int geot_ballquery_offset(int b, int m, float radius, int nsample, const float* xyz,
