@@ -26,6 +26,7 @@ void count_launch(int n);
 bool direct_kernels_forced();  // geot_group_points_config(1) (group.cu)
 bool staged_kernels_forced();  // geot_group_points_config(2)
 bool rows4_disabled();         // geot_group_points_config(3)
+bool persistent_interp_disabled();  // geot_group_points_config(4) (or 3)
 int three_interpolate_grad_impl(int B, int C, int n, int m, const float* grad_out, const float* weight,
                                 const void* plan, float* grad_points, cudaStream_t s);
 
@@ -499,6 +500,109 @@ three_interpolate_rows4_kernel(int C, int m, int n, int G, int n_tile, const flo
   }
 }
 
+__device__ __forceinline__ void ti_mbar_wait_phase(uint64_t* bar, unsigned parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAITP_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@!p bra WAITP_%=;\n"
+      "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+
+// Persistent form of the channel-interleaved kernel (default for large launches).  The grid-per-(cloud, channel group)
+// kernel above leaves the 148 SMs unevenly loaded (256 CTAs at the bench shape: 108 SMs get two, 40 get one) and every
+// CTA stages its rows through registers before its first output.  Here the work - (cloud, channel group) PAIRS x quads
+// of 4 consecutive targets - is cut into one contiguous, equally long run per CTA, one CTA per SM.  A pair's G rows are
+// contiguous in memory: they arrive by ONE bulk async copy into a raw buffer, already issued while the previous pair is
+// being computed, and are interleaved smem -> smem (conflict-free LDS.32 x4 + STS.128).  Same FMA order as every
+// other variant: same bits.
+constexpr int kTipThreads = 512;
+// grid (#CTAs), smem = 2 * (G/4) * m * 16 bytes: [interleaved float4 (G/4)*m | raw rows G*m floats]
+__global__ void __launch_bounds__(kTipThreads, 1)
+three_interpolate_persist_kernel(int B, int C, int m, int n, int G, const float* __restrict__ points,
+                                 const int* __restrict__ idx, const float* __restrict__ weight, float* __restrict__ out) {
+  extern __shared__ __align__(128) unsigned char tip_smem[];
+  __shared__ uint64_t bar;
+  float4* inter = reinterpret_cast<float4*>(tip_smem);
+  float* raw = reinterpret_cast<float*>(tip_smem + (size_t)(G / 4) * m * 16);
+  const int t = threadIdx.x;
+  const int NG = (C + G - 1) / G, Q = n >> 2;  // quads per pair (n % 4 == 0)
+  const int64_t W = (int64_t)B * NG * Q;
+  const int64_t lo = W * blockIdx.x / gridDim.x, hi = W * (blockIdx.x + 1) / gridDim.x;
+  if (lo >= hi) return;
+  const int pair_first = (int)(lo / Q), pair_last = (int)((hi - 1) / Q);
+  auto load_rows = [&](int pair) {  // thread 0 only
+    const int b = pair / NG, c0 = (pair - b * NG) * G, gc = min(G, C - c0);
+    ti_bulk_load(raw, points + ((int64_t)b * C + c0) * m, (unsigned)gc * (unsigned)m * 4u, &bar);
+  };
+  if (t == 0) {
+    ti_mbar_init(&bar);
+    load_rows(pair_first);
+  }
+  __syncthreads();  // the barrier init is visible to the waiters
+  unsigned parity = 0;
+  for (int pair = pair_first; pair <= pair_last; pair++) {
+    const int b = pair / NG, c0 = (pair - b * NG) * G, gc = min(G, C - c0), ng = (gc + 3) >> 2;
+    const int q0 = (int)(max(lo, (int64_t)pair * Q) - (int64_t)pair * Q);
+    const int q1 = (int)(min(hi, (int64_t)(pair + 1) * Q) - (int64_t)pair * Q);
+    int4 ia, ib, ic;
+    float4 wa, wb, wc;
+    auto fetch = [&](int q) {
+      const int4* ip = reinterpret_cast<const int4*>(idx + ((int64_t)b * n + 4 * (int64_t)q) * 3);
+      const float4* wp = reinterpret_cast<const float4*>(weight + ((int64_t)b * n + 4 * (int64_t)q) * 3);
+      ia = __ldg(ip); ib = __ldg(ip + 1); ic = __ldg(ip + 2);
+      wa = __ldg(wp); wb = __ldg(wp + 1); wc = __ldg(wp + 2);
+    };
+    int q = q0 + t;
+    if (q < q1) fetch(q);  // the first quad's indices / weights travel while the rows arrive and are interleaved
+    ti_mbar_wait_phase(&bar, parity);
+    parity ^= 1u;
+    for (int g4 = 0; g4 < ng; g4++) {
+      const int live = min(4, gc - 4 * g4);
+      const float* r0 = raw + (size_t)4 * g4 * m;
+      for (int i = t; i < m; i += kTipThreads) {
+        float4 v;
+        v.x = r0[i];
+        v.y = live > 1 ? r0[m + i] : 0.f;
+        v.z = live > 2 ? r0[2 * m + i] : 0.f;
+        v.w = live > 3 ? r0[3 * m + i] : 0.f;
+        inter[(size_t)g4 * m + i] = v;
+      }
+    }
+    __syncthreads();  // interleaved rows complete; the raw buffer is free again
+    if (t == 0 && pair < pair_last) {
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic reads of `raw` before the async write
+      load_rows(pair + 1);
+    }
+    for (; q < q1; q += kTipThreads) {
+      const int id[12] = {ia.x, ia.y, ia.z, ia.w, ib.x, ib.y, ib.z, ib.w, ic.x, ic.y, ic.z, ic.w};
+      const float w[12] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w, wc.x, wc.y, wc.z, wc.w};
+      if (q + kTipThreads < q1) fetch(q + kTipThreads);  // the next quad's indices / weights while this one is computed
+      for (int g4 = 0; g4 < ng; g4++) {
+        const float4* rows = inter + (size_t)g4 * m;
+        float o[4][4];  // [channel][target]
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+          const float4 p0 = rows[id[3 * k]], p1 = rows[id[3 * k + 1]], p2 = rows[id[3 * k + 2]];
+          const float w0 = w[3 * k], w1 = w[3 * k + 1], w2 = w[3 * k + 2];
+          // reference SASS order: FMUL w1*p1 ; FFMA w0*p0 + . ; FFMA w2*p2 + .
+          o[0][k] = __fmaf_rn(w2, p2.x, __fmaf_rn(w0, p0.x, __fmul_rn(w1, p1.x)));
+          o[1][k] = __fmaf_rn(w2, p2.y, __fmaf_rn(w0, p0.y, __fmul_rn(w1, p1.y)));
+          o[2][k] = __fmaf_rn(w2, p2.z, __fmaf_rn(w0, p0.z, __fmul_rn(w1, p1.z)));
+          o[3][k] = __fmaf_rn(w2, p2.w, __fmaf_rn(w0, p0.w, __fmul_rn(w1, p1.w)));
+        }
+        const int live = min(4, gc - 4 * g4);
+        float* ob = out + ((int64_t)b * C + c0 + 4 * g4) * n + 4 * (int64_t)q;
+#pragma unroll
+        for (int ch = 0; ch < 4; ch++)
+          if (ch < live) __stcs(reinterpret_cast<float4*>(ob + (int64_t)ch * n), make_float4(o[ch][0], o[ch][1], o[ch][2], o[ch][3]));
+      }
+    }
+    __syncthreads();  // every thread is done with the interleaved rows before the next pair overwrites them
+  }
+}
+
 }  // namespace geot
 
 using namespace geot;
@@ -561,8 +665,26 @@ GEOT_API int geot_three_interpolate(int B, int C, int m, int n, const float* poi
       (8 * (int64_t)n >= m || staged_kernels_forced()) && !direct_kernels_forced() && !rows4_disabled()) {
     int G = std::max(4, (int)std::min<size_t>(16, ((size_t)64 * 1024) / ((size_t)m * 4)) & ~3);
     G = std::min(G, (C + 3) & ~3);
+    const int NGp = (C + G - 1) / G;
+    const int64_t Wq = (int64_t)B * NGp * (n / 4);
+    // persistent kernel where a pair is long against its staging
+    // (graph-timed A/B, tools/ti_ab.py: 0.079 vs 0.094 ms at the bench shape, 0.023 vs 0.028 at B=16, 0.018 vs 0.027 at
+    // 6 x 128 x 1000 -> 16000; short pairs (n < 4096) lose to the grid kernel's co-resident CTAs: 0.0088 vs 0.0050 ms at
+    // 16 x 128 x 256 -> 1024)
+    if (m % 4 == 0 && (((uintptr_t)points & 15) == 0) && !persistent_interp_disabled() &&
+        ((n >= 4096 && Wq >= 16 * kTipThreads) || staged_kernels_forced())) {
+      const int ctas = (int)std::min<int64_t>((Wq + kTipThreads - 1) / kTipThreads, kNumSMs);
+      const size_t smem = (size_t)2 * (G / 4) * m * 16;
+      static DynSmem dsp;
+      if (int rc = dsp.need(three_interpolate_persist_kernel, 128 * 1024, "three_interpolate", true)) return rc;
+      three_interpolate_persist_kernel<<<ctas, kTipThreads, smem, as_stream(stream)>>>(B, C, m, n, G, points, idx, weight, out);
+      count_launch(1);
+      return check_launch("three_interpolate_persist_kernel");
+    }
     int n_tile = 16384;  // measured: long tiles amortise the register-staged rows (0.120 ms at 4096, 0.093 at 16384; bench shape)
     if (n_tile > n) n_tile = n;
+    // few pairs (measured at 8 x 64 x 1024 -> 16384: 32 CTAs 0.045 ms, the plain row kernel 0.015): shorter tiles until a wave is full
+    while ((int64_t)B * NGp * ((n + n_tile - 1) / n_tile) < kNumSMs && n_tile >= 4096 && n_tile % 8 == 0) n_tile /= 2;
     const size_t smem = (size_t)(G / 4) * m * 16;
     static DynSmem ds4;
     if (int rc = ds4.need(three_interpolate_rows4_kernel, 64 * 1024, "three_interpolate", true)) return rc;

@@ -69,6 +69,12 @@ for (B, N, M, ns, Cc, r) in [(64, 16384, 1024, 32, 64, 0.1), (16, 16384, 4096, 3
     report("gather_operation fwd", tag + " (C=3; 5 us kernels, host call overhead decides)", lambda: F.gather_points(xyz_t, idx, out=cen_t),
            (lambda: R.ref_gather_points(B, 3, N, M, p(xyz_t), p(idx), p(cen_r))) if R else None,
            B * (4 * M + 2 * 12 * M), lambda: (cen_t == cen_r).all())
+    if R:  # the same two kernels, each behind a bare ctypes call (pointers wrapped per call on both sides): what a C/C++ host sees
+        Lg, sp = _lib.lib().geot_gather_points, _lib.stream_ptr
+        report("gather_operation fwd", tag + " (C=3; bare C-ABI call on both sides)",
+               lambda: Lg(B, 3, N, M, xyz_t.data_ptr(), idx.data_ptr(), cen_t.data_ptr(), sp()),
+               lambda: R.ref_gather_points(B, 3, N, M, p(xyz_t), p(idx), p(cen_r)),
+               B * (4 * M + 2 * 12 * M), lambda: (cen_t == cen_r).all())
     fg = torch.empty((B, Cc, M), device=dev); fg_r = torch.empty_like(fg)
     report("gather_operation fwd", tag + f" (C={Cc})", lambda: F.gather_points(feat, idx, out=fg),
            (lambda: R.ref_gather_points(B, Cc, N, M, p(feat), p(idx), p(fg_r))) if R else None,

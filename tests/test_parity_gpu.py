@@ -372,12 +372,14 @@ def test_three_interpolate_fwd_bwd(cuda, oracle, B, C, m, n):
 
 
 @pytest.mark.parametrize("B,C,m,n", [(3, 64, 1024, 16384), (2, 70, 512, 4096), (2, 5, 4096, 8192), (1, 4, 100, 1024), (2, 9, 333, 2000),
-                                     (1, 33, 16000, 100000), (2, 3, 64, 512), (2, 16, 1024, 4098)])
+                                     (1, 33, 16000, 100000), (2, 3, 64, 512), (2, 16, 1024, 4098),
+                                     (40, 24, 256, 2048), (1, 4, 64, 4), (5, 37, 1024, 6148), (64, 64, 1024, 16384), (1, 1100, 128, 512)])
 def test_three_interpolate_interleaved_vs_rows_vs_direct(cuda, oracle, B, C, m, n):
-    """The channel-interleaved forward kernel (default when n % 4 == 0, C >= 4, m <= 4096) against the plain row-staged
-    kernel (mode 3), the direct kernel (mode 1) and the oracle: partial last channel group (C % 4 != 0), partial last
-    CTA group (C % G != 0), m not a multiple of 4, shapes that fall back (m > 4096, C < 4, n % 4 != 0).  Same FMA
-    order in all three kernels: identical bits."""
+    """The persistent channel-interleaved forward kernel (default when n % 4 == 0, C >= 4, m <= 4096, m % 4 == 0) against
+    its grid-per-pair form (mode 4), the plain row-staged kernel (mode 3), the direct kernel (mode 1) and the oracle:
+    partial last channel group (C % 4 != 0), partial last CTA group (C % G != 0), m not a multiple of 4, shapes that
+    fall back (m > 4096, C < 4, n % 4 != 0), more (cloud, channel group) pairs than CTAs, fewer work items than CTAs,
+    a CTA's run starting and ending inside a pair.  Same FMA order in all kernels: identical bits."""
     g = torch.Generator(device="cuda").manual_seed(C * 7 + m)
     feat = torch.randn(B, C, m, device="cuda", generator=g)
     idx = torch.randint(0, m, (B, n, 3), device="cuda", generator=g, dtype=torch.int32)
@@ -386,12 +388,13 @@ def test_three_interpolate_interleaved_vs_rows_vs_direct(cuda, oracle, B, C, m, 
     got = F.three_interpolate(feat, idx, w)
     res = []
     try:
-        for mode in (3, 1):
+        for mode in (2, 4, 3, 1):     # 2: the persistent kernel whatever the launch size
             _lib.lib().geot_group_points_config(mode)
             res.append(F.three_interpolate(feat, idx, w))
     finally:
         _lib.lib().geot_group_points_config(0)
-    assert torch.equal(got, res[0]) and torch.equal(got, res[1])
+    assert all(torch.equal(got, r) for r in res)
+    assert torch.equal(got, F.three_interpolate(feat, idx, w))
     if B * C * n <= 4_000_000:
         exp = oracle.three_interpolate(feat.cpu().numpy(), idx.cpu().numpy(), w.cpu().numpy())
         np.testing.assert_allclose(got.cpu().numpy(), exp, rtol=1e-5, atol=1e-6)
