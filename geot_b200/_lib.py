@@ -21,6 +21,13 @@ GEOT_FPS_FORCE_GENERIC = 4
 GEOT_FPS_NO_PRUNE = 8
 GEOT_FPS_SPEC = 16
 GEOT_BQ_FORCE_GRID = 1
+
+
+def GEOT_BQ_LEVELS(n):
+    """testing / A-B: at most n (1, 2, 4, 8) index levels in the ball-query grid (include/geot_b200.h)."""
+    return (n & 15) << 8
+
+
 GEOT_KNN_NO_GRID = 1
 
 _vp, _i, _f, _i64, _sz = C.c_void_p, C.c_int, C.c_float, C.c_int64, C.c_size_t

@@ -40,7 +40,7 @@ struct BqHeader {  // grid path (below): per-cloud header at the start of the cl
   int use_grid;
   int dx, dy, dz;
   float lox, loy, loz, inv;
-  int nlev, split;  // index levels: points with index < split are binned separately and searched first
+  int nlev, split;  // index levels: points with index in [l*split, (l+1)*split) are binned separately, searched in order
   int pad[6];
 };
 constexpr int kBqHdrBytes = 64;
@@ -148,15 +148,21 @@ ball_query_shared_kernel(int N, int M, float radius, int nsample, const float* _
 constexpr int kBqMaxDim = 32;
 constexpr int kBqMaxCells = kBqMaxDim * kBqMaxDim * kBqMaxDim;
 constexpr int kBqMaxN = 65536;  // bitmap = N bits per warp
+constexpr int kBqMaxLevels = 8;
+constexpr int kBqMinN = 4096;    // at or below: always the index-order scan (GEOT_BQ_FORCE_GRID overrides)
 
 __host__ __device__ inline size_t bq_cells_bytes() { return (((size_t)(kBqMaxCells + 1) * 4) + 15) & ~(size_t)15; }
 static inline size_t bq_ws_stride(int N) { return kBqHdrBytes + bq_cells_bytes() + (size_t)N * 16; }
 
 __device__ __forceinline__ int bq_cell(float p, float lo, float inv) { return __float2int_rd((p - lo) * inv); }
 
+// CACHED: N <= 16 * 1024 - a thread keeps its 16 points in registers after the first pass (the kernel makes four passes
+// over the cloud: bounding box, occupancy, histogram, scatter).
+constexpr int kBqRegPts = 16;
+template <bool CACHED>
 __global__ void __launch_bounds__(1024, 1)
 bq_build_kernel(int N, float radius, int nsample, const float* __restrict__ xyz, unsigned char* __restrict__ ws,
-                size_t ws_stride, int force_grid) {
+                size_t ws_stride, int force_grid, int force_levels) {
   extern __shared__ int bq_hist[];  // kBqMaxCells counters
   __shared__ float s_red[6][32];
   __shared__ int s_scan[32];
@@ -170,14 +176,32 @@ bq_build_kernel(int N, float radius, int nsample, const float* __restrict__ xyz,
   const float kInf = __int_as_float(0x7f800000);
 
   float lo[3] = {kInf, kInf, kInf}, hi[3] = {-kInf, -kInf, -kInf};
-#pragma unroll 4
-  for (int k = t; k < N; k += 1024) {
+  float px[CACHED ? kBqRegPts : 1], py[CACHED ? kBqRegPts : 1], pz[CACHED ? kBqRegPts : 1];
+  if constexpr (CACHED) {
 #pragma unroll
-    for (int a = 0; a < 3; a++) {
-      const float v = src[(int64_t)k * 3 + a];
-      lo[a] = fminf(lo[a], v); hi[a] = fmaxf(hi[a], v);
+    for (int j = 0; j < kBqRegPts; j++) {
+      const int k = t + j * 1024;
+      px[j] = py[j] = pz[j] = 0.f;
+      if (k < N) { px[j] = src[(int64_t)k * 3]; py[j] = src[(int64_t)k * 3 + 1]; pz[j] = src[(int64_t)k * 3 + 2]; }
     }
   }
+  auto for_points = [&](auto&& fn) {  // fn(index, x, y, z) for the points of this thread
+    if constexpr (CACHED) {
+#pragma unroll
+      for (int j = 0; j < kBqRegPts; j++) {
+        const int k = t + j * 1024;
+        if (k < N) fn(k, px[j], py[j], pz[j]);
+      }
+    } else {
+#pragma unroll 4
+      for (int k = t; k < N; k += 1024) fn(k, src[(int64_t)k * 3], src[(int64_t)k * 3 + 1], src[(int64_t)k * 3 + 2]);
+    }
+  };
+  for_points([&](int, float x, float y, float z) {
+    lo[0] = fminf(lo[0], x); hi[0] = fmaxf(hi[0], x);
+    lo[1] = fminf(lo[1], y); hi[1] = fmaxf(hi[1], y);
+    lo[2] = fminf(lo[2], z); hi[2] = fmaxf(hi[2], z);
+  });
 #pragma unroll
   for (int a = 0; a < 3; a++) {
 #pragma unroll
@@ -213,27 +237,65 @@ bq_build_kernel(int N, float radius, int nsample, const float* __restrict__ xyz,
 #pragma unroll
   for (int a = 0; a < 3; a++) dims[a] = min(kBqMaxDim, max(1, bq_cell(hi[a], lo[a], inv) + 1));
   const int ncells1 = dims[0] * dims[1] * dims[2];
-  const int nlev = (2 * ncells1 <= kBqMaxCells && N >= 2048) ? 2 : 1;
-  const int split = nlev == 2 ? ((N / 2 + 31) & ~31) : N;
-  const int ncell = nlev * ncells1;  // sort keys: level-major, then cell
-  auto code_of = [&](float x, float y, float z, int k) -> int {
+  // index levels (1, 2, 4 or 8): level l holds the points with index in [l*split, (l+1)*split), binned separately;
+  // a query walks the levels in order and stops as soon as it has nsample hits.  The histogram is taken at the finest
+  // admissible count; the count actually used follows from the occupancy and the fine levels are merged down to it.
+  int maxlev = 1;
+  while (maxlev < kBqMaxLevels && 2 * maxlev * ncells1 <= kBqMaxCells && N >= 2048 * maxlev) maxlev *= 2;
+  if (force_levels > 0) maxlev = min(maxlev, force_levels);
+  const int split_f = maxlev > 1 ? (((N + maxlev - 1) / maxlev + 31) & ~31) : N;
+  auto cell_of = [&](float x, float y, float z) -> int {
     const int cx = min(max(bq_cell(x, lo[0], inv), 0), dims[0] - 1);
     const int cy = min(max(bq_cell(y, lo[1], inv), 0), dims[1] - 1);
     const int cz = min(max(bq_cell(z, lo[2], inv), 0), dims[2] - 1);
-    return (k >= split ? ncells1 : 0) + (cz * dims[1] + cy) * dims[0] + cx;
+    return (cz * dims[1] + cy) * dims[0] + cx;
   };
-  for (int i = t; i < ncell; i += 1024) bq_hist[i] = 0;
+  // k / d for k < 65536 and d a multiple of 32 up to 65536 as a multiply-high (checked exhaustively)
+  auto level_of = [](int k, unsigned magic) -> int { return (int)__umulhi((unsigned)k, magic); };
+  const unsigned magic_f = 0xFFFFFFFFu / (unsigned)max(split_f, 1) + 1u;
+  for (int i = t; i < maxlev * ncells1; i += 1024) bq_hist[i] = 0;
   __syncthreads();
-#pragma unroll 4
-  for (int k = t; k < N; k += 1024)
-    atomicAdd(&bq_hist[code_of(src[(int64_t)k * 3], src[(int64_t)k * 3 + 1], src[(int64_t)k * 3 + 2], k)], 1);
+  for_points([&](int k, float x, float y, float z) {
+    atomicAdd(&bq_hist[(maxlev > 1 ? level_of(k, magic_f) * ncells1 : 0) + cell_of(x, y, z)], 1);
+  });
   __syncthreads();
-  {  // occupied cells (either level) for the cost model
+  {  // occupied cells (any level) for the cost model and the level count
     int ne1 = 0;
-    for (int i = t; i < ncells1; i += 1024) ne1 += (bq_hist[i] + (nlev == 2 ? bq_hist[i + ncells1] : 0)) > 0;
+    for (int i = t; i < ncells1; i += 1024) {
+      int any = 0;
+      for (int l = 0; l < maxlev; l++) any |= bq_hist[l * ncells1 + i];
+      ne1 += any > 0;
+    }
     ne1 = __reduce_add_sync(0xffffffffu, ne1);
     if (lane == 0 && ne1) atomicAdd(&s_nonempty, ne1);
   }
+  __syncthreads();
+  const float occ = (float)N / (float)max(s_nonempty, 1);
+  const float hits = 3.f * occ;  // points of a ball as the occupancy suggests (a surface: ~pi cells of area)
+  // as many levels as leave ~nsample hits in the first one (measured at 64 x 16384, r = 0.1, nsample = 32:
+  // 1 / 2 / 4 / 8 levels 0.157 / 0.126 / 0.115 / 0.137 ms)
+  int nlev = 1;
+  while (2 * nlev <= maxlev && hits >= (float)(2 * nlev) * (float)nsample) nlev *= 2;
+  if (force_levels > 0) nlev = maxlev;
+  const int ratio = maxlev / nlev;
+  const int split = nlev > 1 ? split_f * ratio : N;
+  const int ncell = nlev * ncells1;  // sort keys: level-major, then cell
+  if (ratio > 1) {  // merge `ratio` consecutive fine levels into one: sums first, then the writes
+    int sums[kBqMaxCells / 1024 / 2];
+    int cnt = 0;
+    for (int i = t; i < ncell; i += 1024, cnt++) {
+      const int l = i / ncells1, c = i - l * ncells1;
+      int v = 0;
+      for (int r = 0; r < ratio; r++) v += bq_hist[(l * ratio + r) * ncells1 + c];
+      sums[cnt] = v;
+    }
+    __syncthreads();
+    cnt = 0;
+    for (int i = t; i < ncell; i += 1024, cnt++) bq_hist[i] = sums[cnt];
+    __syncthreads();
+  }
+  const unsigned magic = 0xFFFFFFFFu / (unsigned)max(split, 1) + 1u;
+  auto code_of = [&](float x, float y, float z, int k) -> int { return (nlev > 1 ? level_of(k, magic) * ncells1 : 0) + cell_of(x, y, z); };
   // exclusive scan over ncell counters, 1024 threads x PER consecutive entries
   {
     const int PER = (ncell + 1023) / 1024;
@@ -264,21 +326,23 @@ bq_build_kernel(int N, float radius, int nsample, const float* __restrict__ xyz,
     if (t == 0) cell_start[ncell] = N;
   }
   __syncthreads();
-#pragma unroll 4
-  for (int k = t; k < N; k += 1024) {
-    const float x = src[(int64_t)k * 3], y = src[(int64_t)k * 3 + 1], z = src[(int64_t)k * 3 + 2];
+  for_points([&](int k, float x, float y, float z) {
     const int pos = atomicAdd(&bq_hist[code_of(x, y, z, k)], 1);
     sorted[pos] = make_float4(x, y, z, __int_as_float(k));
-  }
+  });
   if (t == 0) {
     // cost model in units of "points visited by the index-order scan" (calibrated on B200, tools/bq_ab.py): the
     // 27 cells hold ~34*occ candidate slots (occ = points per occupied cell) at ~1.5x the per-point cost of the
     // scan, plus ~600 for the bitmap read-back; the scan visits ~N*nsample/H points for H ~ 3*occ hits
-    const float occ = (float)N / (float)max(s_nonempty, 1);
-    const float hits = 3.f * occ;
-    const float lower_only = (nlev == 2 && 0.5f * hits >= 1.3f * (float)nsample) ? 0.5f : 1.f;  // upper level rarely needed
-    const float grid_cost = 51.f * occ * lower_only + 600.f;
-    const float scan_cost = (float)N * (float)nsample / fmaxf(hits, (float)nsample);
+    // Cost model, both sides in "points visited by the index-order scan" (0.0023 ns each on B200; tools/bq_ab.py at
+    // 16 x 16384 x 4096 and 64 x 16384 x 1024, r = 0.05 .. 0.2, nsample = 16 .. 64).  The balls hold ~2.5x what the
+    // occupancy suggests (measured 108 / 473 / 1900 points at r = 0.05 / 0.1 / 0.2 against 45 / 177 / 819).  Scan:
+    // 390 fixed + the points visited until nsample hits.  Grid: 400 fixed (bitmap clear and read-back, 9 runs) + ~6 per
+    // point of an occupied cell and walked level.
+    const float per_level = hits / (float)nlev;
+    const float walked = fminf((float)nlev, ceilf(1.3f * (float)nsample / fmaxf(per_level, 1e-3f)));
+    const float grid_cost = 400.f + 6.f * occ * walked / (float)nlev + 60.f * (walked - 1.f);
+    const float scan_cost = 390.f + fminf((float)N, (float)N * (float)nsample / fmaxf(2.5f * hits, (float)nsample));
     hdr->use_grid = (force_grid || grid_cost < scan_cost) ? 1 : 0;
     hdr->dx = dims[0]; hdr->dy = dims[1]; hdr->dz = dims[2];
     hdr->lox = lo[0]; hdr->loy = lo[1]; hdr->loz = lo[2]; hdr->inv = inv;
@@ -309,22 +373,16 @@ bq_grid_kernel(int N, int M, float radius, int nsample, const float* __restrict_
   const float qx = qp[0], qy = qp[1], qz = qp[2];
   const float r2 = __fmul_rn(radius, radius);
   const int cx = bq_cell(qx, hdr.lox, hdr.inv), cy = bq_cell(qy, hdr.loy, hdr.inv), cz = bq_cell(qz, hdr.loz, hdr.inv);
-  // lanes 0..8 (lower index level) and 16..24 (upper level) fetch the 9 runs of their level in one round trip
-  // (3 x-adjacent cells are contiguous in the sorted order)
-  int rs = 0, re = 0;
-  {
-    const int l9 = lane & 15, lev = lane >> 4;
-    if (l9 < 9 && lev < hdr.nlev) {
-      const int z = cz + l9 / 3 - 1, y = cy + l9 % 3 - 1;
-      const int x0 = max(cx - 1, 0), x1 = min(cx + 1, hdr.dx - 1);
-      if (z >= 0 && z < hdr.dz && y >= 0 && y < hdr.dy && x0 <= x1) {
-        const int c0 = lev * hdr.dx * hdr.dy * hdr.dz + (z * hdr.dy + y) * hdr.dx + x0;
-        rs = __ldg(cell_start + c0);
-        re = __ldg(cell_start + c0 + (x1 - x0) + 1);
-      }
-    }
+  // 9 runs per level (3 x-adjacent cells are contiguous in the sorted order); lanes 0..8 fetch the runs of an even
+  // level and lanes 16..24 those of the next one in the same round trip
+  const int l9 = lane & 15;
+  int c9 = -1, w9 = 0;  // first cell of this lane's run (within a level) and its width
+  if (l9 < 9) {
+    const int z = cz + l9 / 3 - 1, y = cy + l9 % 3 - 1;
+    const int x0 = max(cx - 1, 0), x1 = min(cx + 1, hdr.dx - 1);
+    if (z >= 0 && z < hdr.dz && y >= 0 && y < hdr.dy && x0 <= x1) { c9 = (z * hdr.dy + y) * hdr.dx + x0; w9 = x1 - x0 + 1; }
   }
-  __syncwarp();
+  const int ncells1 = hdr.dx * hdr.dy * hdr.dz;
   auto test = [&](const float4& p) {
     const float d2 = dist2_ref(qx, qy, qz, p.x, p.y, p.z);
     if (d2 < r2) {
@@ -332,15 +390,25 @@ bq_grid_kernel(int N, int M, float radius, int nsample, const float* __restrict_
       atomicOr(bmw + (k >> 5), 1u << (k & 31u));
     }
   };
+  int rs = 0, re = 0;
   for (int lev = 0; lev < hdr.nlev; lev++) {
-    if (lev == 1) {  // upper level only if the lower one left the row short
+    if (lev > 0) {  // later levels only if the earlier ones left the row short
+      __syncwarp();
       int c0 = 0;
-      for (int j = 0; (j << 10) < hdr.split; j++) c0 += __popc(bmw[j * 32 + lane]);
+      for (int j = 0; (j << 10) < lev * hdr.split; j++) c0 += __popc(bmw[j * 32 + lane]);
       if (__reduce_add_sync(0xffffffffu, c0) >= nsample) break;
+    }
+    if ((lev & 1) == 0) {
+      const int mine = lev + (lane >> 4);
+      rs = re = 0;
+      if (c9 >= 0 && mine < hdr.nlev) {
+        rs = __ldg(cell_start + mine * ncells1 + c9);
+        re = __ldg(cell_start + mine * ncells1 + c9 + w9);
+      }
     }
 #pragma unroll 1
     for (int r = 0; r < 9; r++) {
-      const int s = __shfl_sync(0xffffffffu, rs, r + 16 * lev), e = __shfl_sync(0xffffffffu, re, r + 16 * lev);
+      const int s = __shfl_sync(0xffffffffu, rs, r + 16 * (lev & 1)), e = __shfl_sync(0xffffffffu, re, r + 16 * (lev & 1));
       int i = s + lane;
       for (; i + 32 < e; i += 64) {  // two candidates per lane in flight
         const float4 p0 = __ldg(sorted + i), p1 = __ldg(sorted + i + 32);
@@ -349,8 +417,8 @@ bq_grid_kernel(int N, int M, float radius, int nsample, const float* __restrict_
       }
       if (i < e) test(__ldg(sorted + i));
     }
-    __syncwarp();
   }
+  __syncwarp();
   // read the set bits back in ascending index order, 1024 indices per step, until nsample are out
   int* row = idx + ((int64_t)b * M + q) * nsample;
   int total = 0, first = 0;
@@ -431,18 +499,26 @@ GEOT_API int geot_ball_query(int B, int N, int M, float radius, int nsample, con
   cudaStream_t s = as_stream(stream);
   const unsigned char* ws = nullptr;
   size_t stride = 0;
-  if (workspace != nullptr && N > 0 && N <= kBqMaxN) {
+  // small clouds: the build (~20 us per launch) costs more than the scan saves (measured at N = 4096, r = 0.2 / 0.4:
+  // scan 0.034 / 0.013 ms, grid 0.045 / 0.046 ms)
+  if (workspace != nullptr && N > 0 && (N > kBqMinN || (flags & GEOT_BQ_FORCE_GRID)) && N <= kBqMaxN) {
     stride = bq_ws_stride(N);
     if (workspace_bytes < (size_t)B * stride) {
       set_error("ball_query: workspace %zu < %zu bytes", workspace_bytes, (size_t)B * stride);
       return GEOT_ERR_WORKSPACE;
     }
     ws = reinterpret_cast<const unsigned char*>(workspace);
-    static DynSmem ds_build, ds_grid;
-    if (int rc = ds_build.need(bq_build_kernel, kBqMaxCells * 4, "ball_query")) return rc;
+    static DynSmem ds_build, ds_build_c, ds_grid;
     if (int rc = ds_grid.need(bq_grid_kernel, 8 * (kBqMaxN / 8), "ball_query")) return rc;
-    bq_build_kernel<<<B, 1024, kBqMaxCells * 4, s>>>(N, radius, nsample, xyz, reinterpret_cast<unsigned char*>(workspace), stride,
-                                                      (flags & GEOT_BQ_FORCE_GRID) ? 1 : 0);
+    unsigned char* wsw = reinterpret_cast<unsigned char*>(workspace);
+    const int force_grid = (flags & GEOT_BQ_FORCE_GRID) ? 1 : 0, force_levels = GEOT_BQ_LEVELS_OF(flags);
+    if (N <= kBqRegPts * 1024) {
+      if (int rc = ds_build_c.need(bq_build_kernel<true>, kBqMaxCells * 4, "ball_query")) return rc;
+      bq_build_kernel<true><<<B, 1024, kBqMaxCells * 4, s>>>(N, radius, nsample, xyz, wsw, stride, force_grid, force_levels);
+    } else {
+      if (int rc = ds_build.need(bq_build_kernel<false>, kBqMaxCells * 4, "ball_query")) return rc;
+      bq_build_kernel<false><<<B, 1024, kBqMaxCells * 4, s>>>(N, radius, nsample, xyz, wsw, stride, force_grid, force_levels);
+    }
     count_launch(1);
     int rc = check_launch("bq_build_kernel");
     if (rc) return rc;

@@ -87,6 +87,10 @@ int geot_furthestsampling(int b, int n_max, const float* xyz, const int* offset,
  * small against the cloud; without one (or N > 65536) every cloud is scanned in index order.  Same result.
  * --------------------------------------------------------------------------------------------- */
 #define GEOT_BQ_FORCE_GRID 1 /* testing: take the grid path for every cloud, whatever the cost model says */
+/* testing / A-B: GEOT_BQ_LEVELS(n), n in {1,2,4,8}: bin the points in (at most) n index levels instead of the count the
+ * occupancy suggests (flags bits 8..11; 0 = automatic).  Same result for every n. */
+#define GEOT_BQ_LEVELS(n) (((n) & 15) << 8)
+#define GEOT_BQ_LEVELS_OF(flags) (((flags) >> 8) & 15)
 size_t geot_ball_query_workspace_bytes(int B, int N);
 int geot_ball_query(int B, int N, int M, float radius, int nsample, const float* new_xyz,
                     const float* xyz, int* idx, void* workspace, size_t workspace_bytes, int flags,

@@ -142,6 +142,26 @@ def test_ball_query_radius_sweep_and_outside_queries(cuda, oracle, r):
         assert np.array_equal(got, exp), f"flags={flags}"
 
 
+@pytest.mark.parametrize("B,N,M,r,ns", [(2, 16384, 700, 0.1, 32), (1, 16384, 512, 0.05, 16), (2, 20000, 300, 0.2, 64), (1, 65536, 256, 0.05, 8),
+                                        (2, 4100, 200, 0.3, 5), (1, 2047, 100, 0.2, 32)])
+def test_ball_query_index_levels(cuda, oracle, B, N, M, r, ns):
+    """The grid path bins the points in 1, 2, 4 or 8 index levels and a query stops after the first level that fills its
+    row: every admissible level count (GEOT_BQ_LEVELS; the kernel caps it by the cell budget and N >= 2048 per level), the
+    automatic choice and the index-order scan give the same rows; sparse queries walk all levels, N not a multiple of
+    the level size, N above the register-cached build's 16384."""
+    xyz = clouds("tooth", B, N)
+    rng = np.random.default_rng(N + ns)
+    q = np.concatenate([xyz[:, rng.choice(N, M - 20, replace=False)], rng.uniform(-1, 1, (B, 20, 3)).astype(np.float32)], 1)
+    scan = F.ball_query(cu(q), cu(xyz), r, ns, use_grid=False)
+    if B * M * N <= 40_000_000:
+        assert np.array_equal(scan.cpu().numpy(), oracle.ball_query(r, ns, xyz, q))
+    assert torch.equal(F.ball_query(cu(q), cu(xyz), r, ns), scan)
+    for lev in (1, 2, 4, 8):
+        out = torch.full((B, M, ns), -7, dtype=torch.int32, device="cuda")
+        F.ball_query(cu(q), cu(xyz), r, ns, out=out, flags=_lib.GEOT_BQ_FORCE_GRID | _lib.GEOT_BQ_LEVELS(lev))
+        assert torch.equal(out, scan), f"levels={lev}: {(out != scan).sum().item()} entries differ"
+
+
 def test_ball_query_offset(cuda, oracle):
     sizes, ms = [3000, 700, 5001], [100, 33, 250]
     xyz = np.concatenate([synth.tooth_cloud(n, 60 + i) for i, n in enumerate(sizes)])
@@ -400,11 +420,13 @@ def test_three_interpolate_interleaved_vs_rows_vs_direct(cuda, oracle, B, C, m, 
         np.testing.assert_allclose(got.cpu().numpy(), exp, rtol=1e-5, atol=1e-6)
 
 
-@pytest.mark.parametrize("B,C,m,n", [(3, 5, 1024, 16384), (2, 64, 700, 4096), (1, 13, 2048, 6002), (2, 7, 4096, 12288)])
+@pytest.mark.parametrize("B,C,m,n", [(3, 5, 1024, 16384), (2, 64, 700, 4096), (1, 13, 2048, 6002), (2, 7, 4096, 12288),
+                                     (2, 4, 1024, 30000), (1, 9, 6000, 8192), (2, 3, 512, 4096), (4, 16, 100, 20000), (1, 6, 8192, 16000)])
 def test_three_interpolate_grad_rows_vs_direct(cuda, oracle, B, C, m, n):
-    """Row-resident backward (gradient rows in shared memory, weights pre-sorted into plan order) against the
-    direct L2-gather kernel and the oracle, on real three_nn indices: skewed segment lengths, targets that no
-    point selects, channel counts that leave a partial last CTA, n % 4 != 0 (falls back to the direct kernel)."""
+    """Row-resident backward (gradient rows in shared memory, packed {source, weight} edges in plan order) against the
+    direct L2-gather kernel (mode 1) and the oracle, on real three_nn indices: skewed segment lengths, targets that no
+    point selects (half of the known points are moved away), channel counts that leave a partial last CTA, rows too
+    long for more than one per CTA, few edges per target (2 lanes per target), n % 4 != 0 (direct kernel)."""
     unknown = clouds("tooth", B, n)
     known = np.ascontiguousarray(unknown[:, :m])
     known[:, m // 2:] += np.float32(5.0)  # half of the known points are far away: empty segments
@@ -424,6 +446,7 @@ def test_three_interpolate_grad_rows_vs_direct(cuda, oracle, B, C, m, n):
     assert_sum_close(direct, exp, terms, what="three_interpolate_grad direct")
     assert_sum_close(got, exp, terms, what="three_interpolate_grad row-resident")
     assert torch.equal(got, F.three_interpolate_grad(g, w, plan, m)), "run-to-run identical"
+    assert torch.equal(got, F.three_interpolate_grad(g, w, F.ScatterPlan(idx, B, m), m)), "a fresh plan gives the same bits"
 
 
 def _check_aggregation(oracle, inp, pos, wt, idn, ga, plan):

@@ -15,7 +15,8 @@ def t(fn, it=20):
     e1.record(); torch.cuda.synchronize()
     return e0.elapsed_time(e1) / it
 
-for (B, N, M, r, ns) in [(64, 16384, 1024, 0.1, 32), (16, 16384, 4096, 0.1, 16), (16, 16384, 4096, 0.2, 64), (16, 4096, 1024, 0.4, 32), (64, 1024, 256, 0.8, 32)]:
+for (B, N, M, r, ns) in [(64, 16384, 1024, 0.1, 32), (16, 16384, 4096, 0.1, 16), (16, 16384, 4096, 0.2, 64), (16, 4096, 1024, 0.4, 32), (64, 1024, 256, 0.8, 32),
+                          (16, 16384, 4096, 0.05, 16), (16, 16384, 4096, 0.1, 32), (16, 16384, 4096, 0.2, 64), (16, 4096, 1024, 0.2, 32), (8, 65536, 4096, 0.05, 32)]:
     xyz = torch.from_numpy(synth.tooth_batch(B, N)).cuda()
     idx = F.furthest_point_sampling(xyz, M)
     q = torch.gather(xyz, 1, idx.long()[..., None].expand(-1, -1, 3)).contiguous()
@@ -27,4 +28,9 @@ for (B, N, M, r, ns) in [(64, 16384, 1024, 0.1, 32), (16, 16384, 4096, 0.1, 16),
     ta = t(lambda: F.ball_query(q, xyz, r, ns, out=out, workspace=ws))
     tb = t(lambda: F.ball_query(q, xyz, r, ns, out=out, use_grid=False))
     tc = t(lambda: F.ball_query(q, xyz, r, ns, out=out, workspace=ws, flags=_lib.GEOT_BQ_FORCE_GRID))
-    print(f"ball B={B} N={N} M={M} r={r} ns={ns}: auto {ta:.3f} ms  scan {tb:.3f} ms  forced-grid {tc:.3f} ms  equal={bool((a==b).all())},{bool((a==c).all())}", flush=True)
+    lv = []
+    for L in (1, 2, 4, 8):
+        fl = _lib.GEOT_BQ_FORCE_GRID | _lib.GEOT_BQ_LEVELS(L)
+        d = F.ball_query(q, xyz, r, ns, flags=fl).clone()
+        lv.append(f"L{L} {t(lambda: F.ball_query(q, xyz, r, ns, out=out, workspace=ws, flags=fl)):.3f}{'' if bool((a == d).all()) else ' MISMATCH'}")
+    print(f"ball B={B} N={N} M={M} r={r} ns={ns}: auto {ta:.3f} ms  scan {tb:.3f} ms  forced-grid {tc:.3f} ms  equal={bool((a==b).all())},{bool((a==c).all())}  | " + "  ".join(lv), flush=True)
