@@ -30,6 +30,7 @@ static thread_local bool g_group_force_direct = false;  // mode 1
 static thread_local bool g_force_staged = false;        // mode 2: ignore the work-size heuristics
 static thread_local bool g_rows4_off = false;           // mode 3: three_interpolate without the channel-interleaved kernel (A/B)
 static thread_local bool g_tip_off = false;             // mode 4: three_interpolate without the persistent interleaved kernel (A/B)
+static thread_local bool g_mtile_off = false;           // mode 6: manifold loss on the warp-per-point kernels (A/B)
 
 // VEC = 4: E % 4 == 0 and 16-byte aligned idx/out.  grid (ceil(E/VEC/256), ceil(C/CCH), B).
 template <int VEC>
@@ -1024,6 +1025,7 @@ bool direct_kernels_forced() { return g_group_force_direct; }
 bool staged_kernels_forced() { return g_force_staged; }
 bool rows4_disabled() { return g_rows4_off; }
 bool persistent_interp_disabled() { return g_tip_off || g_rows4_off; }
+bool manifold_tiles_disabled() { return g_mtile_off; }
 int three_interpolate_grad_impl(int B, int C, int n, int m, const float* grad_out, const float* weight,
                                 const void* plan, float* grad_points, cudaStream_t s) {
   if (B > 0 && C > 0 && m > 0 && n > 0 && grad_out && plan && grad_points && weight) {
@@ -1144,7 +1146,7 @@ GEOT_API int geot_gather_rows(int B, int N, int M, int D, const float* src, cons
 
 /* testing / A-B timing: direct != 0 disables the row-staged forward kernel (process-wide). */
 GEOT_API void geot_group_points_config(int mode) {
-  g_group_force_direct = mode == 1; g_force_staged = mode == 2; g_rows4_off = mode == 3; g_tip_off = mode == 4;
+  g_group_force_direct = mode == 1; g_force_staged = mode == 2; g_rows4_off = mode == 3; g_tip_off = mode == 4; g_mtile_off = mode == 6;
 }
 
 GEOT_API int geot_gather_points(int B, int C, int N, int M, const float* points, const int* idx,

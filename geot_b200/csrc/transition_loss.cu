@@ -102,6 +102,113 @@ spatial_order_kernel(int N, int D, const float* __restrict__ points, int* __rest
   for (int i = t; i < N; i += 1024) ord[atomicAdd(&hist[cell(i)], 1)] = i;
 }
 
+// Fine order for clouds of up to 16384 points: 18-bit Morton keys (64^3 cells) sorted in shared memory by a bitonic
+// network, key << 14 | index as one 32-bit word.  The tile kernels below want consecutive points of the order to be
+// spatial neighbours: with the 16^3 cells above a tile of 32 points touches ~245 distinct matrices, with 64^3 cells
+// ~153, in full 30-bit Morton order ~150 (numpy model of the cfg4 clouds).  A thread owns EPT consecutive keys: the
+// steps of the network that stay inside them run in registers.  Same contract: a permutation, scheduling only.
+__device__ __forceinline__ unsigned spread6(unsigned v) {  // 6 bits -> every third bit
+  v &= 0x3fu;
+  v = (v | (v << 8)) & 0x0000300fu;
+  v = (v | (v << 4)) & 0x000030c3u;
+  v = (v | (v << 2)) & 0x00009249u;
+  return v;
+}
+template <int EPT>
+__global__ void __launch_bounds__(1024)
+spatial_order_fine_kernel(int N, int D, const float* __restrict__ points, int* __restrict__ order) {
+  constexpr int n2 = 1024 * EPT;
+  extern __shared__ __align__(16) unsigned so_keys[];  // n2
+  __shared__ float s_red[6][32];
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const float* __restrict__ p = points + (int64_t)blockIdx.x * N * D;
+  int* __restrict__ ord = order + (int64_t)blockIdx.x * N;
+  const float kInf = __int_as_float(0x7f800000);
+  const int d1 = D > 1 ? 1 : 0, d2 = D > 2 ? 2 : 0;
+  float lo[3] = {kInf, kInf, kInf}, hi[3] = {-kInf, -kInf, -kInf};
+  for (int i = t; i < N; i += 1024) {
+    const float c[3] = {p[(int64_t)i * D], p[(int64_t)i * D + d1], p[(int64_t)i * D + d2]};
+#pragma unroll
+    for (int a = 0; a < 3; a++) { lo[a] = fminf(lo[a], c[a]); hi[a] = fmaxf(hi[a], c[a]); }
+  }
+#pragma unroll
+  for (int a = 0; a < 3; a++) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      lo[a] = fminf(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], o));
+      hi[a] = fmaxf(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], o));
+    }
+    if (lane == 0) { s_red[a][warp] = lo[a]; s_red[3 + a][warp] = hi[a]; }
+  }
+  __syncthreads();
+  float ext = 0.f;
+#pragma unroll
+  for (int a = 0; a < 3; a++) {
+    float l = s_red[a][lane], h = s_red[3 + a][lane];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      l = fminf(l, __shfl_xor_sync(0xffffffffu, l, o));
+      h = fmaxf(h, __shfl_xor_sync(0xffffffffu, h, o));
+    }
+    lo[a] = l;
+    ext = fmaxf(ext, h - l);
+  }
+  const float scale = (ext > 0.f && ext < kInf) ? 64.0f / ext : 0.f;
+  unsigned v[EPT];  // keys 16t .. 16t + EPT - 1
+#pragma unroll
+  for (int e = 0; e < EPT; e++) {
+    const int i = t * EPT + e;
+    unsigned key = ~0u;  // padding sorts last
+    if (i < N) {  // NaN -> cell 0: scheduling only
+      const int qx = min(max(__float2int_rd((p[(int64_t)i * D] - lo[0]) * scale), 0), 63);
+      const int qy = min(max(__float2int_rd((p[(int64_t)i * D + d1] - lo[1]) * scale), 0), 63);
+      const int qz = min(max(__float2int_rd((p[(int64_t)i * D + d2] - lo[2]) * scale), 0), 63);
+      key = ((spread6((unsigned)qx) | (spread6((unsigned)qy) << 1) | (spread6((unsigned)qz) << 2)) << 14) | (unsigned)i;
+    }
+    v[e] = key;
+  }
+  auto local_steps = [&](int k, int jmax) {  // steps j = jmax, jmax/2, .. 1 of merge size k on this thread's keys
+#pragma unroll
+    for (int j = EPT / 2; j > 0; j >>= 1) {
+      if (j <= jmax) {
+#pragma unroll
+        for (int e = 0; e < EPT; e++) {
+          if ((e & j) == 0) {
+            const bool up = ((t * EPT + e) & k) == 0;
+            const unsigned x = v[e], y = v[e | j];
+            if ((x > y) == up) { v[e] = y; v[e | j] = x; }
+          }
+        }
+      }
+    }
+  };
+#pragma unroll
+  for (int k = 2; k <= EPT; k <<= 1) local_steps(k, k >> 1);
+#pragma unroll
+  for (int e = 0; e < EPT; e++) so_keys[t * EPT + e] = v[e];
+  __syncthreads();
+  for (int k = 2 * EPT; k <= n2; k <<= 1) {
+    for (int j = k >> 1; j >= EPT; j >>= 1) {
+      for (int i = t; i < (n2 >> 1); i += 1024) {
+        const int lo_i = ((i & ~(j - 1)) << 1) | (i & (j - 1)), hi_i = lo_i | j;  // the i-th pair of this step
+        const unsigned x = so_keys[lo_i], y = so_keys[hi_i];
+        const bool up = (lo_i & k) == 0;
+        if ((x > y) == up) { so_keys[lo_i] = y; so_keys[hi_i] = x; }
+      }
+      __syncthreads();
+    }
+    if (EPT > 1) {
+#pragma unroll
+      for (int e = 0; e < EPT; e++) v[e] = so_keys[t * EPT + e];
+      local_steps(k, EPT / 2);
+#pragma unroll
+      for (int e = 0; e < EPT; e++) so_keys[t * EPT + e] = v[e];
+      __syncthreads();
+    }
+  }
+  for (int i = t; i < N; i += 1024) ord[i] = (int)(so_keys[i] & 0x3fffu);
+}
+
 // ---------------------------------------------------------------------------------------------
 // Manifold loss forward.  grid-stride over points (in `order` when given), one warp per point.
 // ---------------------------------------------------------------------------------------------
@@ -250,6 +357,385 @@ manifold_bwd_kernel(int B, int N, int C2, int k, const float* __restrict__ insT,
     }
   }
 }
+
+// ---------------------------------------------------------------------------------------------
+// Tile form of the two manifold kernels (default for k <= 32).  The warp-per-point kernels above pull every neighbour
+// matrix from L2 once per PAIR: 32000 points x 32 neighbours x 4.3 KB = 4.4 GB of L2 -> SM traffic in the forward and
+// twice that in the backward, and sit on its latency.  Neighbourhoods of spatially adjacent points overlap: a tile of
+// 32 consecutive points of the Morton order touches 150-250 distinct points, not 1024.  Here a CTA owns such a tile:
+// the distinct points it touches are numbered through a shared-memory hash table, their matrices are staged in shared
+// memory ONE SLICE of the C*C entries at a time (as wide as the number of rows allows: 256 / 128 / 64 / 32 entries),
+// one bulk async copy per row and slice, and every pair is evaluated from shared memory by the warp that owns the
+// point.  Per entry and per pair the arithmetic - and its order - is exactly that of the warp-per-point kernels: same
+// bits, whatever the tiles or the slice width.  A row of C*C floats is not 16-byte aligned when C is odd: the copy
+// starts at the aligned address below the slice and the row's handle carries the 0..3 floats of shift.
+// ---------------------------------------------------------------------------------------------
+constexpr int kMtThreads = 1024;                   // 32 warps, one point of the tile each
+constexpr int kMtTile = 32;
+constexpr int kMtHash = 4096;                      // slots of the id -> row table
+constexpr int kMtRowFloats = 44 * 1024;            // 176 KB of staged matrix slices
+constexpr int kMtRowsMax = kMtRowFloats / 36;      // 1251 rows at the narrowest slice (32 entries + 4 of shift room)
+struct MtTable {
+  int* keys;       // kMtHash, -1 = empty
+  short* rowof;    // kMtHash
+  int* rowid;      // kMtRowsMax: row -> local point id
+  int* nrows;
+  uint64_t* bar;   // completion of a slice's bulk copies
+};
+__device__ __forceinline__ unsigned mt_hash(int id) { return ((unsigned)id * 2654435761u) >> 20; }  // 12 bits
+__device__ __forceinline__ void mt_insert(const MtTable& tb, int id) {
+  unsigned h = mt_hash(id);
+  for (;;) {
+    const int cur = *reinterpret_cast<volatile int*>(tb.keys + h);
+    if (cur == id) return;
+    if (cur == -1) {
+      if (*reinterpret_cast<volatile int*>(tb.nrows) >= kMtRowsMax) return;  // table closed: the id stays a global read
+      const int old = atomicCAS(tb.keys + h, -1, id);
+      if (old == -1) {
+        const int r = atomicAdd(tb.nrows, 1);
+        if (r < kMtRowsMax) { tb.rowof[h] = (short)r; tb.rowid[r] = id; } else tb.rowof[h] = (short)-1;
+        return;
+      }
+      if (old == id) return;
+    }
+    h = (h + 1) & (kMtHash - 1);
+  }
+}
+__device__ __forceinline__ int mt_row(const MtTable& tb, int id) {  // after the inserts (and a barrier); -1 = not staged
+  unsigned h = mt_hash(id);
+  for (;;) {
+    const int cur = tb.keys[h];
+    if (cur == id) return tb.rowof[h];
+    if (cur == -1) return -1;
+    h = (h + 1) & (kMtHash - 1);
+  }
+}
+// offset (in floats) of a point's slice in the row buffer: row * (W + 4) + the shift of its matrix against 16 bytes
+__device__ __forceinline__ int mt_handle(const MtTable& tb, int id, int64_t base, int C2, int Wp) {
+  const int r = mt_row(tb, id);
+  return r < 0 ? -1 : r * Wp + (int)(((base + id) * C2) & 3);
+}
+__device__ __forceinline__ MtTable mt_table(unsigned char* smem) {
+  MtTable tb;
+  tb.keys = reinterpret_cast<int*>(smem + (size_t)kMtRowFloats * 4);
+  tb.rowid = tb.keys + kMtHash;
+  tb.nrows = tb.rowid + kMtRowsMax + 1;
+  tb.bar = reinterpret_cast<uint64_t*>(tb.nrows + 2);  // 8-byte aligned: kMtRowFloats*4 + (4096 + 1252 + 2) * 4
+  tb.rowof = reinterpret_cast<short*>(tb.bar + 1);
+  return tb;
+}
+constexpr size_t kMtSmemBytes = (size_t)kMtRowFloats * 4 + (size_t)(kMtHash + kMtRowsMax + 1 + 2) * 4 + 8 + (size_t)kMtHash * 2;
+static_assert(((size_t)kMtRowFloats * 4 + (size_t)(kMtHash + kMtRowsMax + 1 + 2) * 4) % 8 == 0, "mbarrier alignment");
+
+__device__ __forceinline__ void mt_mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mt_mbar_wait(uint64_t* bar, unsigned parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "MTWAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@!p bra MTWAIT_%=;\n"
+      "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+
+// Stage slice [s0, s0 + 32*NJ) of the first `nr` rows: thread t copies rows t, t + 1024, ... with one bulk copy each and
+// arrives on the barrier with their byte count (threads without a row arrive empty); everyone then waits for the phase.
+// Entries at or beyond C2 are zeroed afterwards (a zero difference adds nothing; the copy may have brought the next
+// matrix's first entries there).  total = number of floats in insT (the copy of the very last matrix is clipped to it).
+template <int NJ>
+__device__ __forceinline__ void mt_fill(float* rows, const MtTable& tb, int nr, const float* __restrict__ insT, int64_t base, int C2,
+                                        int s0, int64_t total, unsigned& parity) {
+  constexpr int W = 32 * NJ, Wp = W + 4;
+  const int t = threadIdx.x;
+  unsigned bytes = 0;
+  if (t < nr) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // earlier generic reads of the rows
+  for (int r = t; r < nr; r += kMtThreads) {
+    const int64_t e0 = (base + tb.rowid[r]) * C2 + s0, ea = e0 & ~(int64_t)3;
+    const int want = min(Wp, (int)(((e0 - ea) + min(W, C2 - s0) + 3) & ~3));  // floats, a multiple of 4
+    const int have = (int)min((int64_t)want, (total - ea) & ~(int64_t)3);
+    float* dst = rows + r * Wp;
+    if (have > 0) {
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   ::"r"(smem_u32(dst)), "l"(insT + ea), "r"((unsigned)have * 4u), "r"(smem_u32(tb.bar)) : "memory");
+      bytes += (unsigned)have * 4u;
+    }
+    for (int i = have; i < want && ea + i < total; i++) dst[i] = __ldg(insT + ea + i);  // the tensor's last 1..3 floats
+  }
+  if (bytes) asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(tb.bar)), "r"(bytes) : "memory");
+  else asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(tb.bar)) : "memory");
+  mt_mbar_wait(tb.bar, parity);
+  parity ^= 1u;
+  if (s0 + W > C2) {  // last slice: zero from the end of the matrix to the end of the row
+    const int lane = t & 31, warp = t >> 5;
+    for (int r = warp; r < nr; r += kMtThreads / 32) {
+      const int first = (int)(((base + tb.rowid[r]) * C2) & 3) + (C2 - s0);
+      for (int i = first + lane; i < Wp; i += 32) rows[r * Wp + i] = 0.f;
+    }
+  }
+}
+
+// the sum of part[q] over the 32 lanes lands in lane q: the xor butterfly (16, 8, 4, 2, 1) of the warp-per-point
+// kernel, each lane keeping only the half of the values it will still need - same additions, 31 shuffles instead of 160
+__device__ __forceinline__ float mt_reduce32(float (&v)[32], int lane) {
+#pragma unroll
+  for (int i = 0; i < 16; i++) {
+    const bool up = lane & 16;
+    const float send = up ? v[i] : v[i + 16], keep = up ? v[i + 16] : v[i];
+    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+  }
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    const bool up = lane & 8;
+    const float send = up ? v[i] : v[i + 8], keep = up ? v[i + 8] : v[i];
+    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+  }
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const bool up = lane & 4;
+    const float send = up ? v[i] : v[i + 4], keep = up ? v[i + 4] : v[i];
+    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+  }
+#pragma unroll
+  for (int i = 0; i < 2; i++) {
+    const bool up = lane & 2;
+    const float send = up ? v[i] : v[i + 2], keep = up ? v[i + 2] : v[i];
+    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+  }
+  {
+    const bool up = lane & 1;
+    const float send = up ? v[0] : v[1], keep = up ? v[1] : v[0];
+    v[0] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
+  }
+  return v[0];
+}
+
+// one slice of the forward: part[q] += sum over this lane's entries of (T_i - T_nbr(q))^2.  Every row is staged: a
+// forward tile touches at most 32 + 32*32 = 1056 <= kMtRowsMax distinct points.
+template <int NJ>
+__device__ __forceinline__ void mt_fwd_slice(const float* rows, int h_i, int h_q, float (&part)[32]) {
+  const int lane = threadIdx.x & 31;
+  float ti[NJ];
+#pragma unroll
+  for (int j = 0; j < NJ; j++) ti[j] = rows[h_i + lane + 32 * j];
+#pragma unroll
+  for (int q = 0; q < 32; q++) {
+    const float* __restrict__ tj = rows + __shfl_sync(0xffffffffu, h_q, q) + lane;
+    float a = part[q];
+#pragma unroll
+    for (int j = 0; j < NJ; j++) {
+      const float d = ti[j] - tj[32 * j];
+      a = __fmaf_rn(d, d, a);
+    }
+    part[q] = a;  // lanes q >= k point at the tile's own row: finite, never read back
+  }
+}
+
+template <int NJ>
+__device__ __forceinline__ void mt_fwd_slices(float* rows, const MtTable& tb, int nr, const float* __restrict__ insT, int64_t base, int C2,
+                                              int64_t total, unsigned& parity, int a, int nbl, bool live, float (&part)[32]) {
+  constexpr int Wp = 32 * NJ + 4;
+  const int h_i = live ? mt_handle(tb, a, base, C2, Wp) : 0, h_q = live ? mt_handle(tb, nbl, base, C2, Wp) : 0;
+  for (int s0 = 0; s0 < C2; s0 += 32 * NJ) {
+    __syncthreads();  // the previous slice is no longer read
+    mt_fill<NJ>(rows, tb, nr, insT, base, C2, s0, total, parity);
+    __syncthreads();
+    if (live) mt_fwd_slice<NJ>(rows, h_i, h_q, part);
+  }
+}
+
+// grid: persistent CTAs over the tiles (B * ceil(N / 32)), kMtThreads threads, kMtSmemBytes dynamic shared memory
+__global__ void __launch_bounds__(kMtThreads, 1)
+manifold_fwd_tile_kernel(int B, int N, int D, int C2, int k, const float* __restrict__ points,
+                         const int64_t* __restrict__ labels, const float* __restrict__ insT,
+                         const int* __restrict__ idx, const int* __restrict__ order, float inv_two_sigma2, int mode,
+                         float* __restrict__ coef, float* __restrict__ per_point) {
+  extern __shared__ __align__(16) unsigned char mt_smem[];
+  float* rows = reinterpret_cast<float*>(mt_smem);
+  const MtTable tb = mt_table(mt_smem);
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int tpc = (N + kMtTile - 1) / kMtTile;
+  const int64_t ntiles = (int64_t)B * tpc, total = (int64_t)B * N * C2;
+  if (t == 0) mt_mbar_init(tb.bar, kMtThreads);
+  unsigned parity = 0;
+  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int64_t b = tile / tpc, base = b * N;
+    const int slot0 = (int)(tile - b * tpc) * kMtTile;
+    const int npts = min(kMtTile, N - slot0);
+    __syncthreads();  // the previous tile's table and rows are no longer read
+    for (int i = t; i < kMtHash; i += kMtThreads) tb.keys[i] = -1;
+    if (t == 0) *tb.nrows = 0;
+    __syncthreads();
+    // the tile's own points first (their rows are read by every pair), then the neighbours
+    if (t < npts) mt_insert(tb, order ? __ldg(order + base + slot0 + t) : slot0 + t);
+    __syncthreads();
+    for (int e = t; e < npts * k; e += kMtThreads) {
+      const int p = e / k, s = e - p * k;
+      const int a = order ? __ldg(order + base + slot0 + p) : slot0 + p;
+      mt_insert(tb, __ldg(idx + (base + a) * k + s));
+    }
+    __syncthreads();
+    const int nr = *tb.nrows;  // <= 1056
+    const bool live = warp < npts;
+    const int a = live ? (order ? __ldg(order + base + slot0 + warp) : slot0 + warp) : 0;
+    const int64_t g = base + a;
+    const int nbl = (live && lane < k) ? __ldg(idx + g * k + lane) : a;
+    float part[32];
+#pragma unroll
+    for (int q = 0; q < 32; q++) part[q] = 0.f;
+    if (nr * 260 <= kMtRowFloats) mt_fwd_slices<8>(rows, tb, nr, insT, base, C2, total, parity, a, nbl, live, part);
+    else if (nr * 132 <= kMtRowFloats) mt_fwd_slices<4>(rows, tb, nr, insT, base, C2, total, parity, a, nbl, live, part);
+    else if (nr * 68 <= kMtRowFloats) mt_fwd_slices<2>(rows, tb, nr, insT, base, C2, total, parity, a, nbl, live, part);
+    else mt_fwd_slices<1>(rows, tb, nr, insT, base, C2, total, parity, a, nbl, live, part);
+    if (live) {  // warp-uniform
+      const float td = mt_reduce32(part, lane);  // lane q: squared distance to neighbour q
+      const int64_t nb = base + nbl;
+      float w = 0.f;
+      if (lane < k) {
+        float d2 = 0.f;
+        for (int c = 0; c < D; c++) {
+          const float d = __ldg(points + g * D + c) - __ldg(points + nb * D + c);
+          d2 = __fmaf_rn(d, d, d2);
+        }
+        const float e = expf(-d2 * inv_two_sigma2);
+        const bool same = labels[nb] == labels[g];
+        w = (mode == GEOT_MANIFOLD_3D) ? (same ? e : 0.f) : (same ? e : -e);
+      }
+      float num = lane < k ? __fmaf_rn(w, td, 0.f) : 0.f, den = 0.f + w;
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) {
+        num += __shfl_xor_sync(0xffffffffu, num, off);
+        den += __shfl_xor_sync(0xffffffffu, den, off);
+      }
+      const float inv = (mode == GEOT_MANIFOLD_3D) ? 1.0f / (den + 0.001f) : 1.0f / (float)k;
+      if (lane < k) coef[g * k + lane] = w * inv;
+      if (lane == 0) per_point[g] = num * inv;
+    }
+  }
+}
+
+// one slice of the backward for one target: acc[j] += c * (T_a - T_other) over the target's own k neighbours (slot
+// order) and then over the points that list it (plan order) - the order of manifold_bwd_kernel.  OVF: the tile touches
+// more distinct points than the table holds (a hub listed by thousands): rows that are not staged come from global.
+template <int NJ, bool OVF>
+__device__ __forceinline__ void mt_bwd_slice(const float* rows, const MtTable& tb, int a, int64_t base,
+                                             const float* __restrict__ insT, const int* __restrict__ idx, const float* __restrict__ coef,
+                                             const int* __restrict__ rp, const int* __restrict__ pm, int C2, int s0, int k, float gs,
+                                             float* __restrict__ grad_insT) {
+  const int lane = threadIdx.x & 31;
+  constexpr int Wp = 32 * NJ + 4;
+  const int64_t g = base + a;
+  const int h_a = mt_handle(tb, a, base, C2, Wp);  // the tile's own points are inserted first: always staged
+  float ta[NJ], acc[NJ];
+#pragma unroll
+  for (int j = 0; j < NJ; j++) {
+    ta[j] = rows[h_a + lane + 32 * j];
+    acc[j] = 0.f;
+  }
+  auto add_terms = [&](int other_l, float c_l, int cnt) {  // lane l holds term l of this batch
+    const int h_l = mt_handle(tb, other_l, base, C2, Wp);
+    for (int q = 0; q < cnt; q++) {
+      const int h = __shfl_sync(0xffffffffu, h_l, q);
+      const float c = __shfl_sync(0xffffffffu, c_l, q);
+      if (!OVF || h >= 0) {
+        const float* __restrict__ to = rows + h + lane;
+#pragma unroll
+        for (int j = 0; j < NJ; j++) acc[j] = __fmaf_rn(c, ta[j] - to[32 * j], acc[j]);
+      } else {
+        const float* __restrict__ to = insT + (base + __shfl_sync(0xffffffffu, other_l, q)) * C2 + s0 + lane;
+#pragma unroll
+        for (int j = 0; j < NJ; j++)
+          if (s0 + lane + 32 * j < C2) acc[j] = __fmaf_rn(c, ta[j] - __ldg(to + 32 * j), acc[j]);
+      }
+    }
+  };
+  for (int q0 = 0; q0 < k; q0 += 32) {
+    const int sl = q0 + lane;
+    add_terms(sl < k ? __ldg(idx + g * k + sl) : a, sl < k ? __ldg(coef + g * k + sl) : 0.f, min(32, k - q0));
+  }
+  const int p0 = __ldg(rp + a), p1 = __ldg(rp + a + 1);
+  for (int pb = p0; pb < p1; pb += 32) {
+    const int pp = pb + lane;
+    int other = a;
+    float c = 0.f;
+    if (pp < p1) {
+      const int e = __ldg(pm + pp);  // e = i*k + s  (local source point i, slot s)
+      other = e / k;
+      c = __ldg(coef + base * k + e);
+    }
+    add_terms(other, c, min(32, p1 - pb));
+  }
+  float* __restrict__ out = grad_insT + g * C2 + s0;
+#pragma unroll
+  for (int j = 0; j < NJ; j++)
+    if (s0 + lane + 32 * j < C2) out[lane + 32 * j] = gs * acc[j];
+}
+
+template <int NJ, bool OVF>
+__device__ __forceinline__ void mt_bwd_slices(float* rows, const MtTable& tb, int nr, bool live, int a, int64_t base, int64_t total,
+                                              unsigned& parity, const float* __restrict__ insT, const int* __restrict__ idx,
+                                              const float* __restrict__ coef, const int* __restrict__ rp, const int* __restrict__ pm,
+                                              int C2, int k, float gs, float* __restrict__ grad_insT) {
+  for (int s0 = 0; s0 < C2; s0 += 32 * NJ) {
+    __syncthreads();  // the previous slice is no longer read
+    mt_fill<NJ>(rows, tb, nr, insT, base, C2, s0, total, parity);
+    __syncthreads();
+    if (live) mt_bwd_slice<NJ, OVF>(rows, tb, a, base, insT, idx, coef, rp, pm, C2, s0, k, gs, grad_insT);
+  }
+}
+
+__global__ void __launch_bounds__(kMtThreads, 1)
+manifold_bwd_tile_kernel(int B, int N, int C2, int k, const float* __restrict__ insT, const int* __restrict__ idx,
+                         const float* __restrict__ coef, const int* __restrict__ row_ptr, const int* __restrict__ perm,
+                         const int* __restrict__ order, const float* __restrict__ grad_loss, float scale,
+                         float* __restrict__ grad_insT) {
+  extern __shared__ __align__(16) unsigned char mt_smem[];
+  float* rows = reinterpret_cast<float*>(mt_smem);
+  const MtTable tb = mt_table(mt_smem);
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int tpc = (N + kMtTile - 1) / kMtTile;
+  const int64_t ntiles = (int64_t)B * tpc, total = (int64_t)B * N * C2;
+  const float gs = 2.0f * scale * __ldg(grad_loss);
+  const int64_t E = (int64_t)N * k;
+  if (t == 0) mt_mbar_init(tb.bar, kMtThreads);
+  unsigned parity = 0;
+  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int64_t b = tile / tpc, base = b * N;
+    const int slot0 = (int)(tile - b * tpc) * kMtTile;
+    const int npts = min(kMtTile, N - slot0);
+    const int* __restrict__ rp = row_ptr + b * (N + 1);
+    const int* __restrict__ pm = perm + b * E;
+    __syncthreads();  // the previous tile's table and rows are no longer read
+    for (int i = t; i < kMtHash; i += kMtThreads) tb.keys[i] = -1;
+    if (t == 0) *tb.nrows = 0;
+    __syncthreads();
+    if (t < npts) mt_insert(tb, order ? __ldg(order + base + slot0 + t) : slot0 + t);
+    __syncthreads();
+    for (int e = t; e < npts * k; e += kMtThreads) {
+      const int p = e / k, s = e - p * k;
+      const int a = order ? __ldg(order + base + slot0 + p) : slot0 + p;
+      mt_insert(tb, __ldg(idx + (base + a) * k + s));
+    }
+    const bool live = warp < npts;
+    const int a = live ? (order ? __ldg(order + base + slot0 + warp) : slot0 + warp) : 0;
+    if (live) {  // the points that list this warp's target
+      const int p0 = __ldg(rp + a), p1 = __ldg(rp + a + 1);
+      for (int pp = p0 + lane; pp < p1; pp += 32) mt_insert(tb, __ldg(pm + pp) / k);
+    }
+    __syncthreads();
+    const int nins = *tb.nrows;
+    const int nr = min(nins, kMtRowsMax);
+    if (nins >= kMtRowsMax) mt_bwd_slices<1, true>(rows, tb, nr, live, a, base, total, parity, insT, idx, coef, rp, pm, C2, k, gs, grad_insT);
+    else if (nr * 260 <= kMtRowFloats) mt_bwd_slices<8, false>(rows, tb, nr, live, a, base, total, parity, insT, idx, coef, rp, pm, C2, k, gs, grad_insT);
+    else if (nr * 132 <= kMtRowFloats) mt_bwd_slices<4, false>(rows, tb, nr, live, a, base, total, parity, insT, idx, coef, rp, pm, C2, k, gs, grad_insT);
+    else if (nr * 68 <= kMtRowFloats) mt_bwd_slices<2, false>(rows, tb, nr, live, a, base, total, parity, insT, idx, coef, rp, pm, C2, k, gs, grad_insT);
+    else mt_bwd_slices<1, false>(rows, tb, nr, live, a, base, total, parity, insT, idx, coef, rp, pm, C2, k, gs, grad_insT);
+  }
+}
+
+bool manifold_tiles_disabled();  // geot_group_points_config(6) (group.cu): A/B against the warp-per-point kernels
 
 // ---------------------------------------------------------------------------------------------
 // Class-level statistics.
@@ -418,6 +904,19 @@ GEOT_API int geot_spatial_order(int B, int N, int D, const float* points, int* o
   GEOT_REQUIRE(B >= 0 && N >= 1 && D >= 1, "spatial_order: bad sizes B=%d N=%d D=%d", B, N, D);
   if (B == 0) return GEOT_OK;
   GEOT_REQUIRE(points && order, "spatial_order: NULL pointer");
+  if (N <= 16384) {
+    cudaStream_t s = as_stream(stream);
+    static DynSmem ds16;
+    if (N > 8192) {
+      if (int rc = ds16.need(spatial_order_fine_kernel<16>, 16384 * 4, "spatial_order")) return rc;
+      spatial_order_fine_kernel<16><<<B, 1024, 16384 * 4, s>>>(N, D, points, order);
+    } else if (N > 4096) spatial_order_fine_kernel<8><<<B, 1024, 8192 * 4, s>>>(N, D, points, order);
+    else if (N > 2048) spatial_order_fine_kernel<4><<<B, 1024, 4096 * 4, s>>>(N, D, points, order);
+    else if (N > 1024) spatial_order_fine_kernel<2><<<B, 1024, 2048 * 4, s>>>(N, D, points, order);
+    else spatial_order_fine_kernel<1><<<B, 1024, 1024 * 4, s>>>(N, D, points, order);
+    count_launch(1);
+    return check_launch("spatial_order_fine_kernel");
+  }
   spatial_order_kernel<<<B, 1024, 0, as_stream(stream)>>>(N, D, points, order);
   count_launch(1);
   return check_launch("spatial_order_kernel");
@@ -438,17 +937,29 @@ GEOT_API int geot_manifold_loss_forward(int B, int N, int D, int C, int k, const
   }
   cudaStream_t s = as_stream(stream);
   float* per_point = reinterpret_cast<float*>(workspace);
-  const int64_t want = (BN + 7) / 8;
-  const int grid = (int)(want < (int64_t)kNumSMs * 8 ? want : (int64_t)kNumSMs * 8);
-  const size_t smem = (size_t)8 * C * C * sizeof(float);
-  if (smem > 48 * 1024) {
-    static DynSmem ds;
-    if (int rc = ds.need(manifold_fwd_kernel, smem, "manifold_loss_forward")) return rc;
+  int rc = GEOT_OK;
+  if (k <= 32 && (((uintptr_t)insT) & 15) == 0 && !manifold_tiles_disabled()) {
+    static DynSmem dst;
+    if (int rcs = dst.need(manifold_fwd_tile_kernel, kMtSmemBytes, "manifold_loss_forward")) return rcs;
+    const int64_t ntiles = (int64_t)B * ((N + kMtTile - 1) / kMtTile);
+    const int grid = (int)(ntiles < kNumSMs ? ntiles : kNumSMs);
+    manifold_fwd_tile_kernel<<<grid, kMtThreads, kMtSmemBytes, s>>>(B, N, D, C * C, k, points, labels, insT, idx, order,
+                                                                     1.0f / (2.0f * (sigma * sigma)), mode, coef, per_point);
+    count_launch(1);
+    rc = check_launch("manifold_fwd_tile_kernel");
+  } else {
+    const int64_t want = (BN + 7) / 8;
+    const int grid = (int)(want < (int64_t)kNumSMs * 8 ? want : (int64_t)kNumSMs * 8);
+    const size_t smem = (size_t)8 * C * C * sizeof(float);
+    if (smem > 48 * 1024) {
+      static DynSmem ds;
+      if (int rcs = ds.need(manifold_fwd_kernel, smem, "manifold_loss_forward")) return rcs;
+    }
+    manifold_fwd_kernel<<<grid, 256, smem, s>>>(B, N, D, C * C, k, points, labels, insT, idx, order,
+                                                1.0f / (2.0f * (sigma * sigma)), mode, coef, per_point);
+    count_launch(1);
+    rc = check_launch("manifold_fwd_kernel");
   }
-  manifold_fwd_kernel<<<grid, 256, smem, s>>>(B, N, D, C * C, k, points, labels, insT, idx, order,
-                                              1.0f / (2.0f * (sigma * sigma)), mode, coef, per_point);
-  count_launch(1);
-  int rc = check_launch("manifold_fwd_kernel");
   if (rc) return rc;
   const double scale = 1.0 / (double)BN;
   sum_scale_kernel<<<1, 1024, 0, s>>>(BN, per_point, scale, loss);
@@ -473,6 +984,16 @@ GEOT_API int geot_manifold_loss_backward(int B, int N, int C, int k, const float
   const int C2 = C * C;
   const int nt = (C2 + 31) / 32;
   const float scale = 1.0f / (float)BN;
+  if ((((uintptr_t)insT) & 15) == 0 && !manifold_tiles_disabled()) {
+    static DynSmem dst;
+    if (int rcs = dst.need(manifold_bwd_tile_kernel, kMtSmemBytes, "manifold_loss_backward")) return rcs;
+    const int64_t ntiles = (int64_t)B * ((N + kMtTile - 1) / kMtTile);
+    const int tgrid = (int)(ntiles < kNumSMs ? ntiles : kNumSMs);
+    manifold_bwd_tile_kernel<<<tgrid, kMtThreads, kMtSmemBytes, s>>>(B, N, C2, k, insT, idx, coef, row_ptr, perm, order, grad_loss,
+                                                                      scale, grad_insT);
+    count_launch(1);
+    return check_launch("manifold_bwd_tile_kernel");
+  }
   auto grid_of = [&](int parts) {
     const int64_t want_w = (BN * parts + 7) / 8;
     return (int)(want_w < (int64_t)kNumSMs * 16 ? want_w : (int64_t)kNumSMs * 16);

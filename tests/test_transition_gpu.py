@@ -439,3 +439,68 @@ def test_manifold_processing_order_changes_no_bit(cuda):
         res.append((loss, coef, grad))
     for r in res[1:]:
         assert all(torch.equal(a, b) for a, b in zip(res[0], r))
+
+
+@pytest.mark.parametrize("case", ["cfg4", "small_k", "ragged_tail", "random_idx", "hub", "feature_mode", "k33"])
+def test_manifold_tile_kernels_equal_warp_kernels(cuda, case):
+    """The tile kernels (32 Morton-consecutive points per CTA, the distinct matrices they touch staged in shared memory
+    slice by slice) against the warp-per-point kernels (mode 6): loss, coefficients and gradient bit for bit - at the
+    cfg4 size (slices of 256 entries), with N % 32 != 0, with random neighbours (1056 distinct rows per tile: slices of
+    32 entries), with one point listed by every other (its in-neighbours overflow the table: global reads), in the
+    feature mode, with and without the processing order; k = 33 stays on the warp-per-point kernels."""
+    from geot_b200 import _lib
+    g = torch.Generator(device="cuda").manual_seed(11)
+    B, N, C, k, mode = {"cfg4": (2, 16000, 33, 32, F_.MANIFOLD_3D), "small_k": (3, 4099, 17, 7, F_.MANIFOLD_3D),
+                        "ragged_tail": (2, 1001, 5, 32, F_.MANIFOLD_3D), "random_idx": (2, 5000, 9, 32, F_.MANIFOLD_3D),
+                        "hub": (1, 6000, 6, 16, F_.MANIFOLD_3D), "feature_mode": (2, 3000, 17, 12, F_.MANIFOLD_FEATURE),
+                        "k33": (1, 2000, 5, 33, F_.MANIFOLD_3D)}[case]
+    pos = torch.from_numpy(synth.tooth_batch(B, N, first_cloud=21)).cuda()
+    labels = torch.randint(0, 3, (B, N), device="cuda", generator=g)
+    insT = torch.softmax(torch.randn((B * N, C, C), device="cuda", generator=g), 2).contiguous()
+    if case == "random_idx":
+        idx = torch.randint(0, N, (B, N, k), device="cuda", generator=g, dtype=torch.int32)
+    else:
+        idx = T._neighbours(k, pos)
+    if case == "hub":
+        idx[:, :, 3] = 77          # every point lists point 77: 6000 in-neighbours in one tile
+        idx[:, 100:200, 5] = 4242  # and a second, smaller hub
+    order = F_.spatial_order(pos)
+    plan = F_.ScatterPlan(idx, B, N)
+    gl = torch.full((1,), 0.7, device="cuda")
+    res = {}
+    try:
+        for name, m in (("tile", 0), ("warp", 6)):
+            _lib.lib().geot_group_points_config(m)
+            for o in (order, None):
+                loss, coef = F_.manifold_loss_forward(pos, labels, insT, idx, 0.8, mode, order=o)
+                grad = F_.manifold_loss_backward(insT, idx, coef, plan, gl, order=o)
+                res[(name, o is None)] = (loss, coef, grad)
+    finally:
+        _lib.lib().geot_group_points_config(0)
+    ref = res[("warp", True)]
+    assert bool(torch.isfinite(ref[2]).all()) and float(ref[2].abs().max()) > 0
+    for key, r in res.items():
+        for what, a, b in zip(("loss", "coef", "grad"), ref, r):
+            assert torch.equal(a, b), f"{key} {what}: {(a != b).sum().item()} of {a.numel()} values differ"
+
+
+@pytest.mark.parametrize("B,N,D", [(1, 1, 3), (3, 5, 3), (2, 1000, 3), (2, 1025, 3), (2, 4096, 3), (2, 6000, 3), (2, 16000, 3), (2, 16384, 3), (1, 16385, 3),
+                                   (2, 40000, 3), (2, 3000, 17), (1, 777, 1)])
+def test_spatial_order_is_a_permutation_and_local(cuda, B, N, D):
+    """geot_spatial_order: a permutation of every cloud (fine 30-bit Morton sort up to 16384 points, 16^3-cell counting
+    sort above), and consecutive points of it are closer to each other than consecutive points of the input."""
+    g = torch.Generator(device="cuda").manual_seed(N + D)
+    if D == 3 and N >= 1000:
+        pos = torch.from_numpy(synth.tooth_batch(B, N, first_cloud=3)).cuda()
+    else:
+        pos = torch.randn((B, N, D), device="cuda", generator=g)
+    order = F_.spatial_order(pos)
+    assert order.dtype == torch.int32 and order.shape == (B, N)
+    assert torch.equal(torch.sort(order.long(), 1).values, torch.arange(N, device="cuda").expand(B, N))
+    if N >= 1000 and D == 3:
+        walk = lambda p: (p[:, 1:] - p[:, :-1]).norm(dim=-1).mean().item()
+        sorted_pos = torch.gather(pos, 1, order.long().unsqueeze(-1).expand(-1, -1, D))
+        assert walk(sorted_pos) < 0.25 * walk(pos)
+    pos[0, 0, 0] = float("nan")          # scheduling only: still a permutation
+    order = F_.spatial_order(pos)
+    assert torch.equal(torch.sort(order.long(), 1).values, torch.arange(N, device="cuda").expand(B, N))
