@@ -85,7 +85,19 @@ __device__ __forceinline__ void sts128(unsigned a, float4 v) {
   asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 
-constexpr int kNumSMs = 148;  // B200
+// SM count of the current device, asked once per device (148 on B200).  It sizes grids and picks kernel variants; no
+// result depends on it.
+inline int num_sms() {
+  static int cached[64] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (cached[dev] == 0) {
+    int v = 0;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+    cached[dev] = v;
+  }
+  return cached[dev];
+}
 
 // cudaFuncAttributeMaxDynamicSharedMemorySize belongs to the function IN ONE DEVICE'S CONTEXT, not to the process: a
 // launcher keeps one static DynSmem per kernel and calls need() before every launch; the attribute is (re)set when the

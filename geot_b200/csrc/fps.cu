@@ -44,7 +44,10 @@ fps_smem_kernel(const float* __restrict__ xyz, const int* __restrict__ offset,
   int n, m, idx_base;
   fps_segment(offset, new_offset, N, M, blockIdx.x, start_n, n, start_m, m, idx_base);
   if (m <= 0) return;
-  if (n > CH * 4096) return;  // caller understated n_max (the Python layer computes it from offset)
+  if (n > CH * 4096) {  // the caller understated n_max (the Python layer computes it from offset): mark, do not leave garbage
+    for (int j = t; j < m; j += blockDim.x) idx[start_m + j] = -1;
+    return;
+  }
   const int q_count = (n + (1 << log2bs) - 1) >> log2bs;
 
   const float* __restrict__ src = xyz + start_n * 3;
@@ -189,7 +192,10 @@ fps_mgr_kernel(const float* __restrict__ xyz, const int* __restrict__ offset,
   int n, m, idx_base;
   fps_segment(offset, new_offset, N, M, blockIdx.x, start_n, n, start_m, m, idx_base);
   if (m <= 0) return;
-  if (n > Cfg::CAP || n <= 0) return;  // caller understated n_max (the Python layer computes it from offset)
+  if (n > Cfg::CAP || n <= 0) {  // the caller understated n_max (the Python layer computes it from offset): mark, do not leave garbage
+    for (int j = t; j < m; j += blockDim.x) idx[start_m + j] = -1;
+    return;
+  }
   const int q_count = (n + (1 << log2bs) - 1) >> log2bs;
   const float* __restrict__ src = xyz + start_n * 3;
   const float kInf = __int_as_float(0x7f800000);

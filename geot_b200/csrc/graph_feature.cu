@@ -117,7 +117,7 @@ GEOT_API int geot_graph_feature_grad_q(int B, int C, int Nq, int k, const float*
   const int64_t total = (int64_t)B * C * Nq;
   if (total == 0) return GEOT_OK;
   GEOT_REQUIRE(grad_out && grad_x_q, "graph_feature_grad_q: NULL pointer");
-  const int grid = (int)std::min<int64_t>((total + kGfThreads - 1) / kGfThreads, (int64_t)kNumSMs * 32);
+  const int grid = (int)std::min<int64_t>((total + kGfThreads - 1) / kGfThreads, (int64_t)num_sms() * 32);
   graph_feature_grad_q_kernel<<<grid, kGfThreads, 0, as_stream(stream)>>>(total, C, Nq, k, grad_out, grad_x_q);
   count_launch(1);
   return check_launch("graph_feature_grad_q_kernel");

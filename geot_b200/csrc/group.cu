@@ -167,7 +167,7 @@ static int launch_group(int B, int C, int N, int64_t E, const float* points, con
   // leaves most SMs without work - halve it until the grid has a few waves
   const int64_t xb = vec ? (E / 4 + 255) / 256 : (E + 255) / 256;
   int cch = kGroupCCH;
-  while (cch > 1 && xb * ((C + cch - 1) / cch) * B < 4 * (int64_t)kNumSMs && (C + cch / 2 - 1) / (cch / 2) <= 65535) cch >>= 1;
+  while (cch > 1 && xb * ((C + cch - 1) / cch) * B < 4 * (int64_t)num_sms() && (C + cch / 2 - 1) / (cch / 2) <= 65535) cch >>= 1;
   // a sparse gather (gather_operation: 1 of 16 points of every row) is bound by DRAM sector fetches, not by the idx
   // loads: one channel per thread keeps the most independent 4-byte gathers in flight (the reference kernel's mapping,
   // sampling_gpu.cu:15-31, plus the int4 idx load and the 16-byte store)
@@ -842,8 +842,8 @@ static int launch_planrow(int B, int C, int N, int E, int Q, const float* g, con
   double best = 0.0;
   for (int k = 4; k <= 8; k++) {
     const double ctas = (double)B * ((C + k - 1) / k);
-    const double waves = std::ceil(ctas / kNumSMs);
-    const double score = ctas / (waves * kNumSMs) * k / (k + 0.8);
+    const double waves = std::ceil(ctas / num_sms());
+    const double score = ctas / (waves * num_sms()) * k / (k + 0.8);
     if (score > best) { best = score; cpc = k; }
   }
   dim3 grid((C + cpc - 1) / cpc, B);
@@ -993,7 +993,7 @@ static int three_interpolate_grad_rows(int B, int C, int n, int m, const float* 
     const int r = kR[i];
     if (smem_of(r) > (size_t)226 * 1024 || (r > 1 && r > C)) continue;
     const double ctas = (double)B * ((C + r - 1) / r);
-    const double eff = ctas / (std::ceil(ctas / kNumSMs) * kNumSMs);
+    const double eff = ctas / (std::ceil(ctas / num_sms()) * num_sms());
     const double score = eff / (24.0 / r + 4.0);
     if (score > best) { best = score; R = r; }
   }
@@ -1182,7 +1182,7 @@ GEOT_API int geot_scatter_plan_build(int B, int N, int64_t E, const int* idx, vo
   // with few clouds, S CTAs per cloud (one target range each): the sort phase - most of the build - divides by S,
   // the two scans of the cloud's sources do not
   int S = 1;
-  while (S < 8 && (int64_t)B * S * 2 <= kNumSMs && N / (S * 2) >= 256) S *= 2;
+  while (S < 8 && (int64_t)B * S * 2 <= num_sms() && N / (S * 2) >= 256) S *= 2;
   const int nmax = (N + S - 1) / S + 1;  // targets per CTA (upper bound)
   // every CTA scans all E sources of its cloud twice: that has to stay small next to the multi-kernel path's launches
   // (measured: B=1, E=524288 on 8 CTAs 0.235 ms against 0.116 ms for the multi-kernel path)
@@ -1239,7 +1239,7 @@ GEOT_API int geot_scatter_plan_build(int B, int N, int64_t E, const int* idx, vo
     static DynSmem ds_heavy;
     if (int rc = ds_heavy.need(plan_sort_heavy_kernel, kPlanHeavyBits / 8, "scatter_plan_build")) return rc;
     const size_t bm_bytes = (size_t)std::min<int64_t>(kPlanHeavyBits, ((E + 32767) / 32768) * 32768) / 8;
-    plan_sort_heavy_kernel<<<2 * kNumSMs, 1024, bm_bytes, s>>>(N, E, row_ptr, tmp, perm, heavy_count, heavy_list, heavy_cap);
+    plan_sort_heavy_kernel<<<2 * num_sms(), 1024, bm_bytes, s>>>(N, E, row_ptr, tmp, perm, heavy_count, heavy_list, heavy_cap);
     count_launch(3);
     rc = check_launch("plan_fill/sort kernels");
   }

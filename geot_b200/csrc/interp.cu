@@ -628,7 +628,7 @@ GEOT_API int geot_three_nn(int B, int n, int m, const float* unknown, const floa
     int cb = 1;
     double best_cost = 1e30;
     for (int k = 1; k <= max_cb; k++) {
-      const double waves = std::ceil((double)k * B / kNumSMs);
+      const double waves = std::ceil((double)k * B / num_sms());
       const double cost = waves * (4.0 + std::ceil((double)n / ((double)k * kNgThreads)));
       if (cost < best_cost) { best_cost = cost; cb = k; }
     }
@@ -673,7 +673,7 @@ GEOT_API int geot_three_interpolate(int B, int C, int m, int n, const float* poi
     // 16 x 128 x 256 -> 1024)
     if (m % 4 == 0 && (((uintptr_t)points & 15) == 0) && !persistent_interp_disabled() &&
         ((n >= 4096 && Wq >= 16 * kTipThreads) || staged_kernels_forced())) {
-      const int ctas = (int)std::min<int64_t>((Wq + kTipThreads - 1) / kTipThreads, kNumSMs);
+      const int ctas = (int)std::min<int64_t>((Wq + kTipThreads - 1) / kTipThreads, num_sms());
       const size_t smem = (size_t)2 * (G / 4) * m * 16;
       static DynSmem dsp;
       if (int rc = dsp.need(three_interpolate_persist_kernel, 128 * 1024, "three_interpolate", true)) return rc;
@@ -684,7 +684,7 @@ GEOT_API int geot_three_interpolate(int B, int C, int m, int n, const float* poi
     int n_tile = 16384;  // measured: long tiles amortise the register-staged rows (0.120 ms at 4096, 0.093 at 16384; bench shape)
     if (n_tile > n) n_tile = n;
     // few pairs (measured at 8 x 64 x 1024 -> 16384: 32 CTAs 0.045 ms, the plain row kernel 0.015): shorter tiles until a wave is full
-    while ((int64_t)B * NGp * ((n + n_tile - 1) / n_tile) < kNumSMs && n_tile >= 4096 && n_tile % 8 == 0) n_tile /= 2;
+    while ((int64_t)B * NGp * ((n + n_tile - 1) / n_tile) < num_sms() && n_tile >= 4096 && n_tile % 8 == 0) n_tile /= 2;
     const size_t smem = (size_t)(G / 4) * m * 16;
     static DynSmem ds4;
     if (int rc = ds4.need(three_interpolate_rows4_kernel, 64 * 1024, "three_interpolate", true)) return rc;

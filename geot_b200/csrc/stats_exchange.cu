@@ -74,7 +74,7 @@ GEOT_API int geot_stats_pack(int C, int64_t P, const float* class_T, const float
   GEOT_REQUIRE(C >= 1 && P >= 0, "stats_pack: bad sizes C=%d P=%lld", C, (long long)P);
   GEOT_REQUIRE(class_T && best_val && cm && c_num && record, "stats_pack: NULL pointer");
   const int64_t L = geot_stats_record_floats(C, P);
-  const int grid = (int)std::min<int64_t>((L + 255) / 256, (int64_t)kNumSMs * 8);
+  const int grid = (int)std::min<int64_t>((L + 255) / 256, (int64_t)num_sms() * 8);
   stats_pack_kernel<<<grid, 256, 0, as_stream(stream)>>>(C, P, class_T, best_val, cm, c_num, grads, record);
   count_launch(1);
   return check_launch("stats_pack_kernel");
@@ -85,7 +85,7 @@ GEOT_API int geot_stats_combine(int W, int C, int64_t P, const float* gathered, 
   GEOT_REQUIRE(W >= 1 && C >= 1 && P >= 0, "stats_combine: bad sizes W=%d C=%d P=%lld", W, C, (long long)P);
   GEOT_REQUIRE(gathered && class_T && cm && c_num, "stats_combine: NULL pointer");
   const int64_t total = 2 * (int64_t)C * C + C + P;
-  const int grid = (int)std::min<int64_t>((total + 255) / 256, (int64_t)kNumSMs * 8);
+  const int grid = (int)std::min<int64_t>((total + 255) / 256, (int64_t)num_sms() * 8);
   stats_combine_kernel<<<grid, 256, 0, as_stream(stream)>>>(W, C, P, gathered, grad_scale, class_T, cm, c_num, grads);
   count_launch(1);
   return check_launch("stats_combine_kernel");

@@ -318,7 +318,7 @@ sigt_gw_final_kernel(int C, int stride, int nparts, const float* __restrict__ pa
 
 static int sigt_grid(int64_t BN) {
   const int64_t tiles = (BN + kSigtTile - 1) / kSigtTile;
-  return (int)(tiles < kNumSMs ? tiles : kNumSMs);
+  return (int)(tiles < num_sms() ? tiles : num_sms());
 }
 
 template <int C, bool BWD>
@@ -345,7 +345,7 @@ static int dispatch_sigt(int B, int C, int N, const float* x, const float* W, in
 static inline size_t align256(size_t b) { return (b + 255) & ~(size_t)255; }
 static inline int gw_parts(int64_t BN) {
   const int64_t p = (BN + 63) / 64;
-  return (int)(p < kNumSMs ? (p < 1 ? 1 : p) : kNumSMs);
+  return (int)(p < num_sms() ? (p < 1 ? 1 : p) : num_sms());
 }
 
 }  // namespace geot

@@ -365,7 +365,7 @@ static int launch_apply_tile(int B, int N, const float* logits, const float* ema
   if (int rc = ds.need(transition_apply_tile_kernel<C, BWD>, TileSmem<C>::kBytes, "transition_apply")) return rc;
   const int64_t tiles = ((int64_t)B * N + kTileP - 1) / kTileP;
   const int per_sm = TileSmem<C>::kBytes > 110 * 1024 ? 1 : (TileSmem<C>::kBytes > 72 * 1024 ? 2 : 3);
-  const int grid = (int)std::min<int64_t>(tiles, (int64_t)kNumSMs * per_sm);
+  const int grid = (int)std::min<int64_t>(tiles, (int64_t)num_sms() * per_sm);
   transition_apply_tile_kernel<C, BWD><<<grid, kTileThreads, TileSmem<C>::kBytes, s>>>(B, N, logits, ema_t, insT, lam, grad_out, out_or_gl, grad_insT);
   count_launch(1);
   return check_launch(BWD ? "transition_apply_tile_kernel<bwd>" : "transition_apply_tile_kernel<fwd>");
@@ -390,7 +390,7 @@ static int launch_apply(int B, int C, int N, const float* logits, const float* e
   if (int rc = ds.need(transition_apply_kernel<BWD>, smem, "transition_apply")) return rc;
   const int64_t tiles = ((int64_t)B * N + kApplyTile - 1) / kApplyTile;
   const int per_sm = smem > 110 * 1024 ? 1 : (smem > 72 * 1024 ? 2 : (smem > 54 * 1024 ? 3 : 4));
-  const int64_t cap = (int64_t)kNumSMs * per_sm;
+  const int64_t cap = (int64_t)num_sms() * per_sm;
   const int grid = (int)(tiles < cap ? tiles : cap);
   transition_apply_kernel<BWD><<<grid, kApplyThreads, smem, s>>>(B, C, N, nbuf, logits, ema_t, insT, lam, grad_out, out_or_gl, grad_insT);
   count_launch(1);

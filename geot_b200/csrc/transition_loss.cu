@@ -942,14 +942,14 @@ GEOT_API int geot_manifold_loss_forward(int B, int N, int D, int C, int k, const
     static DynSmem dst;
     if (int rcs = dst.need(manifold_fwd_tile_kernel, kMtSmemBytes, "manifold_loss_forward")) return rcs;
     const int64_t ntiles = (int64_t)B * ((N + kMtTile - 1) / kMtTile);
-    const int grid = (int)(ntiles < kNumSMs ? ntiles : kNumSMs);
+    const int grid = (int)(ntiles < num_sms() ? ntiles : num_sms());
     manifold_fwd_tile_kernel<<<grid, kMtThreads, kMtSmemBytes, s>>>(B, N, D, C * C, k, points, labels, insT, idx, order,
                                                                      1.0f / (2.0f * (sigma * sigma)), mode, coef, per_point);
     count_launch(1);
     rc = check_launch("manifold_fwd_tile_kernel");
   } else {
     const int64_t want = (BN + 7) / 8;
-    const int grid = (int)(want < (int64_t)kNumSMs * 8 ? want : (int64_t)kNumSMs * 8);
+    const int grid = (int)(want < (int64_t)num_sms() * 8 ? want : (int64_t)num_sms() * 8);
     const size_t smem = (size_t)8 * C * C * sizeof(float);
     if (smem > 48 * 1024) {
       static DynSmem ds;
@@ -978,7 +978,7 @@ GEOT_API int geot_manifold_loss_backward(int B, int N, int C, int k, const float
   const size_t rp_bytes = (((size_t)B * (N + 1) * sizeof(int)) + 255) & ~(size_t)255;
   const int* perm = reinterpret_cast<const int*>(reinterpret_cast<const char*>(plan) + rp_bytes);
   const int64_t want = (BN + 7) / 8;
-  const int grid = (int)(want < (int64_t)kNumSMs * 8 ? want : (int64_t)kNumSMs * 8);
+  const int grid = (int)(want < (int64_t)num_sms() * 8 ? want : (int64_t)num_sms() * 8);
   cudaStream_t s = as_stream(stream);
   // coef holds d(per-point loss)/d(Tdist) for either mode; the mean over points (1/BN) is applied here.
   const int C2 = C * C;
@@ -988,7 +988,7 @@ GEOT_API int geot_manifold_loss_backward(int B, int N, int C, int k, const float
     static DynSmem dst;
     if (int rcs = dst.need(manifold_bwd_tile_kernel, kMtSmemBytes, "manifold_loss_backward")) return rcs;
     const int64_t ntiles = (int64_t)B * ((N + kMtTile - 1) / kMtTile);
-    const int tgrid = (int)(ntiles < kNumSMs ? ntiles : kNumSMs);
+    const int tgrid = (int)(ntiles < num_sms() ? ntiles : num_sms());
     manifold_bwd_tile_kernel<<<tgrid, kMtThreads, kMtSmemBytes, s>>>(B, N, C2, k, insT, idx, coef, row_ptr, perm, order, grad_loss,
                                                                       scale, grad_insT);
     count_launch(1);
@@ -996,7 +996,7 @@ GEOT_API int geot_manifold_loss_backward(int B, int N, int C, int k, const float
   }
   auto grid_of = [&](int parts) {
     const int64_t want_w = (BN * parts + 7) / 8;
-    return (int)(want_w < (int64_t)kNumSMs * 16 ? want_w : (int64_t)kNumSMs * 16);
+    return (int)(want_w < (int64_t)num_sms() * 16 ? want_w : (int64_t)num_sms() * 16);
   };
   if (nt <= 10) manifold_bwd_kernel<10, 1><<<grid_of(1), 256, 0, s>>>(B, N, C2, k, insT, idx, coef, row_ptr, perm, order, grad_loss, scale, grad_insT);
   else if (nt <= 36) manifold_bwd_kernel<18, 2><<<grid_of(2), 256, 0, s>>>(B, N, C2, k, insT, idx, coef, row_ptr, perm, order, grad_loss, scale, grad_insT);

@@ -142,7 +142,7 @@ poly1_bwd_kernel(int B, int C, int N, const float* __restrict__ logits, const in
 
 static int loss_grid(int64_t BN) {
   const int64_t want = (BN + kLossThreads - 1) / kLossThreads;
-  return (int)std::max<int64_t>(1, std::min<int64_t>(want, (int64_t)kNumSMs * 8));
+  return (int)std::max<int64_t>(1, std::min<int64_t>(want, (int64_t)num_sms() * 8));
 }
 
 }  // namespace geot

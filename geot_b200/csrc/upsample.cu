@@ -102,7 +102,7 @@ GEOT_API int geot_interp_weights(int64_t total, const float* dist2, float* dist,
   GEOT_REQUIRE(total >= 0, "interp_weights: bad size %lld", (long long)total);
   if (total == 0) return GEOT_OK;
   GEOT_REQUIRE(dist2 && weight, "interp_weights: NULL pointer");
-  const int grid = (int)std::min<int64_t>((total + kUpThreads - 1) / kUpThreads, (int64_t)kNumSMs * 16);
+  const int grid = (int)std::min<int64_t>((total + kUpThreads - 1) / kUpThreads, (int64_t)num_sms() * 16);
   interp_weights_kernel<<<grid, kUpThreads, 0, as_stream(stream)>>>(total, dist2, dist, weight);
   count_launch(1);
   return check_launch("interp_weights_kernel");
@@ -127,7 +127,7 @@ GEOT_API int geot_seg_counts(int64_t n, int C, const int64_t* pred, const int64_
   cudaError_t e = cudaMemsetAsync(counts, 0, (size_t)(3 * C + 2) * sizeof(int64_t), s);
   if (e != cudaSuccess) { set_error("seg_counts: memset: %s", cudaGetErrorString(e)); return GEOT_ERR_CUDA; }
   if (n == 0) return GEOT_OK;
-  const int grid = (int)std::min<int64_t>((n + kUpThreads * 8 - 1) / (kUpThreads * 8), (int64_t)kNumSMs * 4);
+  const int grid = (int)std::min<int64_t>((n + kUpThreads * 8 - 1) / (kUpThreads * 8), (int64_t)num_sms() * 4);
   seg_counts_kernel<<<std::max(grid, 1), kUpThreads, (size_t)(3 * C + 2) * sizeof(unsigned), s>>>(
       n, C, pred, label, reinterpret_cast<unsigned long long*>(counts));
   count_launch(1);

@@ -162,6 +162,21 @@ def test_ball_query_index_levels(cuda, oracle, B, N, M, r, ns):
         assert torch.equal(out, scan), f"levels={lev}: {(out != scan).sum().item()} entries differ"
 
 
+def test_fps_understated_n_max_marks_the_segment(cuda, oracle):
+    """geot_furthestsampling sizes its kernels from the caller's n_max (pointops_cuda.furthestsampling_cuda takes it as an
+    argument).  A segment longer than promised cannot be sampled by the kernel that was picked: its indices come back as
+    -1 instead of uninitialised memory; the other segments are unaffected."""
+    sizes, ms = [3000, 9000], [50, 64]
+    xyz = np.concatenate([synth.tooth_cloud(n, 5 + i) for i, n in enumerate(sizes)])
+    off, noff = np.cumsum(sizes).astype(np.int32), np.cumsum(ms).astype(np.int32)
+    good = F.furthestsampling(cu(xyz), cu(off), cu(noff))
+    assert np.array_equal(good.cpu().numpy(), oracle.furthestsampling(xyz, off, noff))
+    for flags in (0, _lib.GEOT_FPS_NO_PRUNE):
+        out = torch.full((114,), 7, dtype=torch.int32, device="cuda")
+        F.furthestsampling(cu(xyz), cu(off), cu(noff), n_max=4096, m_total=114, out=out, flags=flags)
+        assert torch.equal(out[:50], good[:50]) and bool((out[50:] == -1).all())
+
+
 def test_ball_query_offset(cuda, oracle):
     sizes, ms = [3000, 700, 5001], [100, 33, 250]
     xyz = np.concatenate([synth.tooth_cloud(n, 60 + i) for i, n in enumerate(sizes)])

@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Dev tool (GPU box): launch ONE op of the bench workload a few times so ncu can capture it.
-usage: python tools/prof_one.py {fps|fps_noprune|ball|group|group3|groupbwd|plan|threenn|tibwd|ti|ti_old|gf|upsample|knn|sigt|apply|manifold} [B]"""
+usage: python tools/prof_one.py {fps|fps_noprune|ball|group|group3|groupxyz|groupbwd|plan|threenn|tibwd|ti|ti_old|gf|upsample|knn|sigt|apply|manifold} [B]"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
@@ -57,6 +57,7 @@ for _ in range(3):
     if what == "fps": F.furthest_point_sampling(xyz, M)
     elif what == "fps_noprune": F.furthest_point_sampling(xyz, M, flags=_lib.GEOT_FPS_NO_PRUNE)
     elif what == "ball": F.ball_query(centres, xyz, 0.1, NS)
+    elif what == "groupxyz": F.group_xyz_relative(xyz, centres, nbr, relative=True, divisor=0.1)
     elif what == "group": F.group_points(feat, nbr)
     elif what == "group3": F.group_points(xyz_t, nbr)
     elif what == "groupbwd": F.group_points_grad(go, plan, N)

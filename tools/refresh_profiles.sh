@@ -12,14 +12,16 @@ python tests/op_sweep.py --out gpurun_out/${tag}_op_sweep.json > gpurun_out/${ta
 python tests/transition_sweep.py --out gpurun_out/${tag}_transition_sweep.json > gpurun_out/${tag}_transition_sweep.log 2>&1
 python tools/fps_ab.py > gpurun_out/${tag}_fps_ab.jsonl 2>&1
 python tools/manifold_ab.py > gpurun_out/${tag}_manifold_ab.log 2>&1
+python tools/ti_ab.py > gpurun_out/${tag}_ti_ab.jsonl 2>&1
+python tools/bq_ab.py > gpurun_out/${tag}_bq_ab.log 2>&1
 B="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-extras"
 $B > gpurun_out/${tag}_launches_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${tag}_launches_bench.csv \
     $B > gpurun_out/${tag}_launches.log 2>&1
 for k in "fps fps_mgr" "ball bq_build" "ball bq_grid" "group group_rows" "groupbwd seg_reduce_planrow" "plan plan_build_fused" \
          "threenn three_nn_grid" "tibwd seg_reduce_wrows" "knn knn_grid" \
-         "sigt sigt_kernel" "apply transition_apply_tile" "manifold manifold_fwd" "manifold manifold_bwd" \
-         "ti three_interpolate_rows4" "gf graph_feature_kernel"; do
+         "sigt sigt_kernel" "apply transition_apply_tile" "manifold manifold_fwd_tile" "manifold manifold_bwd_tile" \
+         "manifold spatial_order_fine" "ti three_interpolate_persist" "gf graph_feature_kernel" "groupxyz group_xyz_rel"; do
   set -- $k
   python tools/prof_one.py $1 > gpurun_out/${tag}_full_$2.plain.log 2>&1 &&
   ncu --set full --clock-control none --import-source on -k regex:$2 -c 1 -f -o gpurun_out/${tag}_full_$2 \
