@@ -1184,9 +1184,12 @@ GEOT_API int geot_scatter_plan_build(int B, int N, int64_t E, const int* idx, vo
   int S = 1;
   while (S < 8 && (int64_t)B * S * 2 <= num_sms() && N / (S * 2) >= 256) S *= 2;
   const int nmax = (N + S - 1) / S + 1;  // targets per CTA (upper bound)
-  // every CTA scans all E sources of its cloud twice: that has to stay small next to the multi-kernel path's launches
-  // (measured: B=1, E=524288 on 8 CTAs 0.235 ms against 0.116 ms for the multi-kernel path)
-  if (N >= 1 && nmax <= kFusedMaxN && E >= 1 && E <= kFusedMaxE && (E <= (1 << 17) || (int64_t)B * S >= 16) && B <= 65535 && !g_force_staged) {
+  // every CTA scans all E sources of its cloud twice: ~0.43 ns per source, whatever the number of clouds (one wave);
+  // the multi-kernel path costs ~0.067 ms of launches + 0.038 ns per source of the WHOLE batch (tools/plan_ab.py on
+  // kNN lists: B=2, E=512000 fused 0.222 ms / multi-kernel 0.105; B=8 0.222 / 0.221; B=16, E=131072 0.064 / 0.200)
+  const double waves = std::ceil((double)B * S / num_sms());
+  const bool fused_pays = 0.43e-6 * (double)E * waves < 0.067 + 0.038e-6 * (double)E * B;
+  if (N >= 1 && nmax <= kFusedMaxN && E >= 1 && E <= kFusedMaxE && fused_pays && B <= 65535 && !g_force_staged) {
     // the whole CSR of a cloud (or of one target range of it) in shared memory (see plan_build_fused_kernel)
     const size_t kBudget = (size_t)220 * 1024;  // + 1.3 KB of static shared memory in the kernel
     const size_t smem = (size_t)(nmax + 1) * 4 + (size_t)((((E + 31) >> 5) + 1023) / 1024) * 1024 * 4;

@@ -554,16 +554,28 @@ knn_heap_kernel(int b, int m, int nsample, const float* __restrict__ xyz,
 // points per step and ballot those below the heap top; lane 0 then applies them in index order (re-checking
 // against the moving top) to a heap kept in shared memory.  Insert sequence and heap layout are exactly the
 // sequential ones, so the result is; only the ~n/32 filter steps and the few hundred heap updates remain serial.
+// The reference's sift-down (knnquery_cuda_kernel.cu:15-37: the larger child, the right one only when strictly
+// larger; stop only when the root is STRICTLY larger, so equal keys swap) with the sinking entry kept in registers:
+// the chain of swaps moves one value down, so writing the children up and the value once at the end leaves the same
+// arrays - three shared-memory round trips per level instead of five.
 __device__ __forceinline__ void heap_reheap_smem(float* dist, int* id, int k) {
   int root = 0, child = 1;
+  const float v = dist[0];
+  const int vi = id[0];
   while (child < k) {
-    if (child + 1 < k && dist[child + 1] > dist[child]) child++;
-    if (dist[root] > dist[child]) return;
-    const float tf = dist[root]; dist[root] = dist[child]; dist[child] = tf;
-    const int ti = id[root]; id[root] = id[child]; id[child] = ti;
+    float dc = dist[child];
+    if (child + 1 < k) {
+      const float dr = dist[child + 1];
+      if (dr > dc) { child++; dc = dr; }
+    }
+    if (v > dc) break;
+    dist[root] = dc;
+    id[root] = id[child];
     root = child;
     child = root * 2 + 1;
   }
+  dist[root] = v;
+  id[root] = vi;
 }
 
 __global__ void __launch_bounds__(256)
@@ -590,20 +602,33 @@ knn_heap_warp_kernel(int b, int m, int nsample, const float* __restrict__ xyz, c
   for (int i = lane; i < nsample; i += 32) { bd[i] = 1e10f; bi[i] = start; }
   __syncwarp();
   float top = 1e10f;
-  for (int i0 = start; i0 < end; i0 += 32) {
-    const int i = i0 + lane;
-    float d2 = 0.f;
-    if (i < end) d2 = dist2_ref(qx, qy, qz, xyz[(int64_t)i * 3 + 0], xyz[(int64_t)i * 3 + 1], xyz[(int64_t)i * 3 + 2]);
-    unsigned mask = __ballot_sync(0xffffffffu, i < end && d2 < top);
-    if (mask == 0) continue;
-    while (mask) {
-      const int src = __ffs(mask) - 1;
-      mask &= mask - 1;
-      const float nd = __shfl_sync(0xffffffffu, d2, src);
-      if (lane == 0 && nd < bd[0]) { bd[0] = nd; bi[0] = i0 + src; heap_reheap_smem(bd, bi, nsample); }
+  // Flagged queries are rare (1 of 32000 on the cfg4 clouds) but each walks its whole segment: with one 32-point chunk per
+  // round trip a single replay took 0.37 ms - longer than the grid search of all the others.  Eight chunks of
+  // distances are in flight; they are then offered to the heap chunk by chunk, in index order, each against the
+  // threshold left by the previous one: the reference's sequence of insertions, unchanged.
+  constexpr int kChunks = 8;
+  for (int i0 = start; i0 < end; i0 += 32 * kChunks) {
+    float d2c[kChunks];
+#pragma unroll
+    for (int c = 0; c < kChunks; c++) {
+      const int i = i0 + 32 * c + lane;
+      d2c[c] = 0.f;
+      if (i < end) d2c[c] = dist2_ref(qx, qy, qz, xyz[(int64_t)i * 3 + 0], xyz[(int64_t)i * 3 + 1], xyz[(int64_t)i * 3 + 2]);
     }
-    __syncwarp();
-    top = bd[0];
+#pragma unroll
+    for (int c = 0; c < kChunks; c++) {
+      const int ib = i0 + 32 * c;
+      unsigned mask = __ballot_sync(0xffffffffu, ib + lane < end && d2c[c] < top);
+      if (mask == 0) continue;
+      while (mask) {
+        const int src = __ffs(mask) - 1;
+        mask &= mask - 1;
+        const float nd = __shfl_sync(0xffffffffu, d2c[c], src);
+        if (lane == 0 && nd < bd[0]) { bd[0] = nd; bi[0] = ib + src; heap_reheap_smem(bd, bi, nsample); }
+      }
+      __syncwarp();
+      top = bd[0];
+    }
   }
   if (lane == 0) {
     for (int i = nsample - 1; i > 0; i--) {  // heap_sort :39-48
