@@ -14,6 +14,9 @@ python tools/fps_ab.py > gpurun_out/${tag}_fps_ab.jsonl 2>&1
 python tools/manifold_ab.py > gpurun_out/${tag}_manifold_ab.log 2>&1
 python tools/ti_ab.py > gpurun_out/${tag}_ti_ab.jsonl 2>&1
 python tools/bq_ab.py > gpurun_out/${tag}_bq_ab.log 2>&1
+python tools/plan_ab.py > gpurun_out/${tag}_plan_ab.log 2>&1
+python tools/manifold_parts.py > gpurun_out/${tag}_manifold_parts.log 2>&1
+[ -n "$NO_NCU" ] && { ls -la gpurun_out/ | tail -30; exit 0; }   # NO_NCU=1: the measurements only, no ncu captures
 B="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-extras"
 $B > gpurun_out/${tag}_launches_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${tag}_launches_bench.csv \
