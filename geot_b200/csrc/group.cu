@@ -31,6 +31,7 @@ static thread_local bool g_force_staged = false;        // mode 2: ignore the wo
 static thread_local bool g_rows4_off = false;           // mode 3: three_interpolate without the channel-interleaved kernel (A/B)
 static thread_local bool g_tip_off = false;             // mode 4: three_interpolate without the persistent interleaved kernel (A/B)
 static thread_local bool g_mtile_off = false;           // mode 6: manifold loss on the warp-per-point kernels (A/B)
+static thread_local bool g_mtile_on = false;            // mode 7: manifold loss on the tile kernels whatever C (tests)
 
 // VEC = 4: E % 4 == 0 and 16-byte aligned idx/out.  grid (ceil(E/VEC/256), ceil(C/CCH), B).
 template <int VEC>
@@ -1026,6 +1027,7 @@ bool staged_kernels_forced() { return g_force_staged; }
 bool rows4_disabled() { return g_rows4_off; }
 bool persistent_interp_disabled() { return g_tip_off || g_rows4_off; }
 bool manifold_tiles_disabled() { return g_mtile_off; }
+bool manifold_tiles_forced() { return g_mtile_on; }
 int three_interpolate_grad_impl(int B, int C, int n, int m, const float* grad_out, const float* weight,
                                 const void* plan, float* grad_points, cudaStream_t s) {
   if (B > 0 && C > 0 && m > 0 && n > 0 && grad_out && plan && grad_points && weight) {
@@ -1146,7 +1148,7 @@ GEOT_API int geot_gather_rows(int B, int N, int M, int D, const float* src, cons
 
 /* testing / A-B timing: direct != 0 disables the row-staged forward kernel (process-wide). */
 GEOT_API void geot_group_points_config(int mode) {
-  g_group_force_direct = mode == 1; g_force_staged = mode == 2; g_rows4_off = mode == 3; g_tip_off = mode == 4; g_mtile_off = mode == 6;
+  g_group_force_direct = mode == 1; g_force_staged = mode == 2; g_rows4_off = mode == 3; g_tip_off = mode == 4; g_mtile_off = mode == 6; g_mtile_on = mode == 7;
 }
 
 GEOT_API int geot_gather_points(int B, int C, int N, int M, const float* points, const int* idx,

@@ -444,7 +444,8 @@ def test_manifold_processing_order_changes_no_bit(cuda):
 @pytest.mark.parametrize("case", ["cfg4", "small_k", "ragged_tail", "random_idx", "hub", "feature_mode", "k33"])
 def test_manifold_tile_kernels_equal_warp_kernels(cuda, case):
     """The tile kernels (32 Morton-consecutive points per CTA, the distinct matrices they touch staged in shared memory
-    slice by slice) against the warp-per-point kernels (mode 6): loss, coefficients and gradient bit for bit - at the
+    slice by slice; mutual neighbours merged in the backward) against the warp-per-point kernels (mode 6): loss,
+    coefficients and gradient bit for bit - at the
     cfg4 size (slices of 256 entries), with N % 32 != 0, with random neighbours (1056 distinct rows per tile: slices of
     32 entries), with one point listed by every other (its in-neighbours overflow the table: global reads), in the
     feature mode, with and without the processing order; k = 33 stays on the warp-per-point kernels."""
@@ -469,7 +470,7 @@ def test_manifold_tile_kernels_equal_warp_kernels(cuda, case):
     gl = torch.full((1,), 0.7, device="cuda")
     res = {}
     try:
-        for name, m in (("tile", 0), ("warp", 6)):
+        for name, m in (("tile", 7), ("warp", 6), ("default", 0)):   # 7: the tile kernels whatever C; 0: chosen by C
             _lib.lib().geot_group_points_config(m)
             for o in (order, None):
                 loss, coef = F_.manifold_loss_forward(pos, labels, insT, idx, 0.8, mode, order=o)

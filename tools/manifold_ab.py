@@ -29,7 +29,7 @@ for (B, N, C, k) in [(2, 16000, 33, 32), (2, 16000, 17, 32), (4, 8000, 33, 16), 
     plan = F.ScatterPlan(idx, B, N)
     gl = torch.ones((1,), device="cuda")
     row = {"B": B, "N": N, "C": C, "k": k, "order_ms": round(timeit(lambda: F.spatial_order(pos)), 4)}
-    for name, m in (("tile", 0), ("warp", 6)):
+    for name, m in (("tile", 7), ("warp", 6)):
         _lib.lib().geot_group_points_config(m)
         try:
             loss, coef = F.manifold_loss_forward(pos, labels, insT, idx, 1.0, F.MANIFOLD_3D, order=order)
