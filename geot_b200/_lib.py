@@ -29,6 +29,7 @@ def GEOT_BQ_LEVELS(n):
 
 
 GEOT_KNN_NO_GRID = 1
+GEOT_KNN_TIES_BY_INDEX = 2
 
 _vp, _i, _f, _i64, _sz = C.c_void_p, C.c_int, C.c_float, C.c_int64, C.c_size_t
 

@@ -20,6 +20,7 @@ import torch
 import torch.nn as nn
 
 from . import backends
+from . import _lib
 from . import functional as F_
 
 
@@ -45,7 +46,7 @@ class KNN(nn.Module):
         B, N, D = ref.shape
         M = query.shape[1]
         assert D == 3, "the sm_100a kNN kernel is 3-D"
-        idx, d2 = F_.knnquery(self.k, ref.view(-1, 3), query.view(-1, 3), None, None, n_per=N, m_per=M)
+        idx, d2 = F_.knnquery(self.k, ref.view(-1, 3), query.view(-1, 3), None, None, n_per=N, m_per=M, flags=_lib.GEOT_KNN_TIES_BY_INDEX)
         base = (torch.arange(B, device=idx.device, dtype=torch.int32) * N).view(B, 1, 1)
         idx = (idx.view(B, M, self.k) - base).long()
         dist = torch.sqrt(d2).view(B, M, self.k)

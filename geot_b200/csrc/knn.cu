@@ -45,6 +45,42 @@ __device__ __forceinline__ void knn_segment(const int* __restrict__ offset, cons
   }
 }
 
+// Sorted-list insertion shared by the two fast kernels.  The list (K1 = k + 1 entries across the lanes, S per lane) is
+// kept in (distance, index) order, so the K1 best it ends with do not depend on the order in which the points are
+// visited: equal distances rank by index.  That IS the result under GEOT_KNN_TIES_BY_INDEX; under the default (the
+// reference's heap semantics) a query whose best K1 contain an exact tie is replayed by knn_heap_warp_kernel.
+// A point is admitted when it ranks before the current last entry (tau, tau_i).
+__device__ __forceinline__ bool knn_admit(float nd, int ni, float tau, int tau_i) { return nd < tau || (nd == tau && ni < tau_i); }
+template <int S>
+__device__ __forceinline__ void knn_list_insert(float (&ld)[S], int (&li)[S], int K1, int lane, float nd, int ni, float& tau, int& tau_i) {
+  int pos = 0;  // entries that rank before the new one
+#pragma unroll
+  for (int s = 0; s < S; s++)
+    pos += __popc(__ballot_sync(0xffffffffu, (s * 32 + lane < K1) && (ld[s] < nd || (ld[s] == nd && li[s] < ni))));
+#pragma unroll
+  for (int s = S - 1; s >= 0; s--) {
+    float pd = __shfl_up_sync(0xffffffffu, ld[s], 1);
+    int pi = __shfl_up_sync(0xffffffffu, li[s], 1);
+    if (s > 0) {
+      const float wd = __shfl_sync(0xffffffffu, ld[s - 1], 31);
+      const int wi = __shfl_sync(0xffffffffu, li[s - 1], 31);
+      if (lane == 0) { pd = wd; pi = wi; }
+    }
+    const int j = s * 32 + lane;
+    if (j > pos) { ld[s] = pd; li[s] = pi; }
+    else if (j == pos) { ld[s] = nd; li[s] = ni; }
+  }
+  float tv = ld[0];
+  int ti = li[0];
+#pragma unroll
+  for (int s = 1; s < S; s++) {
+    tv = (((K1 - 1) >> 5) == s) ? ld[s] : tv;
+    ti = (((K1 - 1) >> 5) == s) ? li[s] : ti;
+  }
+  tau = __shfl_sync(0xffffffffu, tv, (K1 - 1) & 31);
+  tau_i = __shfl_sync(0xffffffffu, ti, (K1 - 1) & 31);
+}
+
 // S slots per lane: list element j = s*32 + lane, ascending.  K1 = nsample + 1 <= 32*S.
 template <int S>
 __global__ void __launch_bounds__(1024, 1)
@@ -68,7 +104,8 @@ knn_warp_kernel(int nsample, const float* __restrict__ xyz, const float* __restr
   int li[S];
 #pragma unroll
   for (int s = 0; s < S; s++) { ld[s] = 1e10f; li[s] = start; }
-  float tau = 1e10f;  // current K1-th best (strict '<' admits, knnquery_cuda_kernel.cu:97)
+  float tau = 1e10f;  // current K1-th best (distance, index)
+  int tau_i = start;
 
   const int n = end - start;
   const float* __restrict__ seg = xyz + (int64_t)start * 3;
@@ -103,34 +140,14 @@ knn_warp_kernel(int nsample, const float* __restrict__ xyz, const float* __restr
       for (int i = 0; i < cnt; i += 32) {
         const int p = i + lane;
         const float d = dist2_ref(qx, qy, qz, sm[3 * p + 0], sm[3 * p + 1], sm[3 * p + 2]);
-        unsigned mask = __ballot_sync(0xffffffffu, (p < cnt) && (d < tau));
+        unsigned mask = __ballot_sync(0xffffffffu, (p < cnt) && (d <= tau));
         while (mask) {
           const int src = __ffs(mask) - 1;
           mask &= mask - 1;
           const float nd = __shfl_sync(0xffffffffu, d, src);
-          if (!(nd < tau)) continue;  // tau shrank while draining this ballot
           const int ni = start + base + i + src;
-          // insertion position = number of list elements <= nd (stable: after equals)
-          int pos = 0;
-#pragma unroll
-          for (int s = 0; s < S; s++) pos += __popc(__ballot_sync(0xffffffffu, (s * 32 + lane < K1) && (ld[s] <= nd)));
-#pragma unroll
-          for (int s = S - 1; s >= 0; s--) {
-            float pd = __shfl_up_sync(0xffffffffu, ld[s], 1);
-            int pi = __shfl_up_sync(0xffffffffu, li[s], 1);
-            if (s > 0) {
-              const float wd = __shfl_sync(0xffffffffu, ld[s - 1], 31);
-              const int wi = __shfl_sync(0xffffffffu, li[s - 1], 31);
-              if (lane == 0) { pd = wd; pi = wi; }
-            }
-            const int j = s * 32 + lane;
-            if (j > pos) { ld[s] = pd; li[s] = pi; }
-            else if (j == pos) { ld[s] = nd; li[s] = ni; }
-          }
-          float tv = ld[0];
-#pragma unroll
-          for (int s = 1; s < S; s++) tv = (((K1 - 1) >> 5) == s) ? ld[s] : tv;
-          tau = __shfl_sync(0xffffffffu, tv, (K1 - 1) & 31);
+          if (!knn_admit(nd, ni, tau, tau_i)) continue;  // the list moved while draining this ballot
+          knn_list_insert<S>(ld, li, K1, lane, nd, ni, tau, tau_i);
         }
       }
     }
@@ -341,31 +358,6 @@ knn_build_kernel(int nsample, float alpha, const float* __restrict__ xyz, const 
   }
 }
 
-// Sorted-list insertion shared by the grid kernel (same operation as the inline code of knn_warp_kernel).
-template <int S>
-__device__ __forceinline__ void knn_list_insert(float (&ld)[S], int (&li)[S], int K1, int lane, float nd, int ni, float& tau) {
-  int pos = 0;
-#pragma unroll
-  for (int s = 0; s < S; s++) pos += __popc(__ballot_sync(0xffffffffu, (s * 32 + lane < K1) && (ld[s] <= nd)));
-#pragma unroll
-  for (int s = S - 1; s >= 0; s--) {
-    float pd = __shfl_up_sync(0xffffffffu, ld[s], 1);
-    int pi = __shfl_up_sync(0xffffffffu, li[s], 1);
-    if (s > 0) {
-      const float wd = __shfl_sync(0xffffffffu, ld[s - 1], 31);
-      const int wi = __shfl_sync(0xffffffffu, li[s - 1], 31);
-      if (lane == 0) { pd = wd; pi = wi; }
-    }
-    const int j = s * 32 + lane;
-    if (j > pos) { ld[s] = pd; li[s] = pi; }
-    else if (j == pos) { ld[s] = nd; li[s] = ni; }
-  }
-  float tv = ld[0];
-#pragma unroll
-  for (int s = 1; s < S; s++) tv = (((K1 - 1) >> 5) == s) ? ld[s] : tv;
-  tau = __shfl_sync(0xffffffffu, tv, (K1 - 1) & 31);
-}
-
 // Warp per query, 8 queries per CTA.
 template <int S>
 __global__ void __launch_bounds__(256)
@@ -400,6 +392,7 @@ knn_grid_kernel(int nsample, const float* __restrict__ new_xyz, const int* __res
 #pragma unroll
   for (int s = 0; s < S; s++) { ld[s] = 1e10f; li[s] = start; }
   float tau = 1e10f;
+  int tau_i = start;
 
   auto scan_run = [&](int s0, int e0) {
     for (int i0 = s0; i0 < e0; i0 += 32) {
@@ -411,14 +404,14 @@ knn_grid_kernel(int nsample, const float* __restrict__ new_xyz, const int* __res
         d = dist2_ref(qx, qy, qz, v.x, v.y, v.z);
         pi = __float_as_int(v.w);
       }
-      unsigned mask = __ballot_sync(0xffffffffu, (p < e0) && (d < tau));
+      unsigned mask = __ballot_sync(0xffffffffu, (p < e0) && (d <= tau));
       while (mask) {
         const int src = __ffs(mask) - 1;
         mask &= mask - 1;
         const float nd = __shfl_sync(0xffffffffu, d, src);
         const int ni = start + __shfl_sync(0xffffffffu, pi, src);
-        if (!(nd < tau)) continue;
-        knn_list_insert<S>(ld, li, K1, lane, nd, ni, tau);
+        if (!knn_admit(nd, ni, tau, tau_i)) continue;
+        knn_list_insert<S>(ld, li, K1, lane, nd, ni, tau, tau_i);
       }
     }
   };
@@ -473,6 +466,7 @@ knn_grid_kernel(int nsample, const float* __restrict__ new_xyz, const int* __res
 #pragma unroll
     for (int s = 0; s < S; s++) { ld[s] = 1e10f; li[s] = start; }
     tau = 1e10f;
+    tau_i = start;
     scan_run(0, end - start);
   }
   bool tie = false;
@@ -607,14 +601,21 @@ knn_heap_warp_kernel(int b, int m, int nsample, const float* __restrict__ xyz, c
   // distances are in flight; they are then offered to the heap chunk by chunk, in index order, each against the
   // threshold left by the previous one: the reference's sequence of insertions, unchanged.
   constexpr int kChunks = 8;
-  for (int i0 = start; i0 < end; i0 += 32 * kChunks) {
-    float d2c[kChunks];
+  auto load_group = [&](int i0, float (&d)[kChunks]) {
 #pragma unroll
     for (int c = 0; c < kChunks; c++) {
       const int i = i0 + 32 * c + lane;
-      d2c[c] = 0.f;
-      if (i < end) d2c[c] = dist2_ref(qx, qy, qz, xyz[(int64_t)i * 3 + 0], xyz[(int64_t)i * 3 + 1], xyz[(int64_t)i * 3 + 2]);
+      d[c] = 0.f;
+      if (i < end) d[c] = dist2_ref(qx, qy, qz, xyz[(int64_t)i * 3 + 0], xyz[(int64_t)i * 3 + 1], xyz[(int64_t)i * 3 + 2]);
     }
+  };
+  float nxt[kChunks];
+  load_group(start, nxt);
+  for (int i0 = start; i0 < end; i0 += 32 * kChunks) {
+    float d2c[kChunks];
+#pragma unroll
+    for (int c = 0; c < kChunks; c++) d2c[c] = nxt[c];
+    load_group(i0 + 32 * kChunks, nxt);  // the next group's loads travel while this one is offered to the heap
 #pragma unroll
     for (int c = 0; c < kChunks; c++) {
       const int ib = i0 + 32 * c;
@@ -692,8 +693,10 @@ GEOT_API int geot_knnquery(int b, int n, int m, int nsample, const float* xyz, c
       static DynSmem ds_build;
       const int smem = kKnnMaxCells * (int)sizeof(int);
       if (int rc = ds_build.need(knn_build_kernel, smem, "knnquery")) return rc;
-      // points per occupied cell = a * (k+1).  Measured optimum: ~0.8 at k = 16, less for longer lists (0.4 at 32, 0.3 at 64)
-      const float a = fminf(fmaxf(13.f / (float)(nsample + 1), 0.3f), 0.8f);
+      // points per occupied cell = a * (k+1).  Measured (self-kNN on tooth clouds, 2 x 16000 and 8 x 16384): flat between
+      // 0.55 and 1.0 at k = 16; 0.55-0.7 at k = 33 (0.40 ms against 0.50 at 0.38: fewer queries need the 5x5x5 shell);
+      // 0.3-0.55 at k = 64
+      const float a = fminf(fmaxf(18.f / (float)(nsample + 1), 0.3f), 0.8f);
       knn_build_kernel<<<b, 1024, smem, s>>>(nsample, a, xyz, offset, n_per, seg_grid, base + w.slots, reinterpret_cast<float4*>(base + w.sorted));
       count_launch(1);
       int rc = check_launch("knn_build_kernel");
@@ -723,6 +726,9 @@ GEOT_API int geot_knnquery(int b, int n, int m, int nsample, const float* xyz, c
       rc = check_launch("knn_grid_kernel");
       if (rc) return rc;
     }
+    // ties by index: the fast kernels' (distance, index) order is the answer; otherwise the queries with an exact tie
+    // among their k + 1 best are replayed with the reference's heap (its order of equal distances depends on the heap's history)
+    if (flags_arg & GEOT_KNN_TIES_BY_INDEX) return GEOT_OK;
     knn_heap_warp_kernel<<<(m + 7) / 8, 256, 0, s>>>(b, m, nsample, xyz, new_xyz, offset, new_offset, n_per, m_per, idx, dist2, flags);
     count_launch(1);
     return check_launch("knn_heap_warp_kernel");

@@ -19,6 +19,7 @@ import torch
 import torch.nn as nn
 from torch.autograd import Function
 
+from . import _lib
 from . import functional as F_
 
 
@@ -201,7 +202,7 @@ def _knn3d(k, query, support):
     N = support.shape[1]
     q = query.contiguous().float().view(-1, 3)
     s = support.contiguous().float().view(-1, 3)
-    idx, d2 = F_.knnquery(k, s, q, None, None, n_per=N, m_per=M)
+    idx, d2 = F_.knnquery(k, s, q, None, None, n_per=N, m_per=M, flags=_lib.GEOT_KNN_TIES_BY_INDEX)
     base = (torch.arange(B, device=idx.device, dtype=torch.int32) * N).view(B, 1, 1)
     return torch.sqrt(d2).view(B, M, k), (idx.view(B, M, k) - base)
 
@@ -387,7 +388,7 @@ def knn_neighbours(k, coor_q, coor_k):
         query = coor_q.transpose(1, 2).contiguous().float()
         B, Nk, _ = ref.shape
         Nq = query.shape[1]
-        idx, _ = F_.knnquery(k, ref.view(-1, 3), query.view(-1, 3), None, None, n_per=Nk, m_per=Nq)
+        idx, _ = F_.knnquery(k, ref.view(-1, 3), query.view(-1, 3), None, None, n_per=Nk, m_per=Nq, flags=_lib.GEOT_KNN_TIES_BY_INDEX)
         base = (torch.arange(B, device=idx.device, dtype=torch.int32) * Nk).view(B, 1, 1)
         return (idx.view(B, Nq, k) - base).contiguous()
 
@@ -421,7 +422,8 @@ class Group(nn.Module):
         xyz = xyz.contiguous().float()
         fps_idx = F_.furthest_point_sampling(xyz, self.num_group, flags=_lib.GEOT_FPS_CAP512 | _lib.GEOT_FPS_MAGSKIP)
         center = F_.gather_rows(xyz, fps_idx)  # B G 3
-        idx, _ = F_.knnquery(self.group_size, xyz.view(-1, 3), center.view(-1, 3), None, None, n_per=num_points, m_per=self.num_group)
+        idx, _ = F_.knnquery(self.group_size, xyz.view(-1, 3), center.view(-1, 3), None, None, n_per=num_points, m_per=self.num_group,
+                             flags=_lib.GEOT_KNN_TIES_BY_INDEX)
         assert idx.shape == (batch_size * self.num_group, self.group_size)
         flat = xyz.view(1, batch_size * num_points, 3)
         neighborhood = F_.gather_rows(flat, idx.view(1, -1)).view(batch_size, self.num_group, self.group_size, 3)

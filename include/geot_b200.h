@@ -129,6 +129,11 @@ int geot_ballquery_offset(int b, int m, float radius, int nsample, const float* 
  * flags: GEOT_KNN_NO_GRID forces the brute-force scan for every segment (testing / A-B timing; same results).
  * --------------------------------------------------------------------------------------------- */
 #define GEOT_KNN_NO_GRID 1
+/* Equal distances rank by index (lowest first) instead of by the reference kernel's heap order: the definition this
+ * project uses for the un-vendored knn_cuda.KNN and for openpoints' torch knn_point (cdist + topk, whose tie order is
+ * unspecified).  Skips the replay of the queries that have an exact tie among their k+1 best (one such query of 32000
+ * costs 0.2 ms: it walks its whole segment through a sequential heap).  Needs nsample <= 127. */
+#define GEOT_KNN_TIES_BY_INDEX 2
 size_t geot_knnquery_workspace_bytes(int b, int n, int m);
 int geot_knnquery(int b, int n, int m, int nsample, const float* xyz, const float* new_xyz,
                   const int* offset, const int* new_offset, int n_per, int m_per, int* idx,

@@ -177,6 +177,33 @@ def test_fps_understated_n_max_marks_the_segment(cuda, oracle):
         assert torch.equal(out[:50], good[:50]) and bool((out[50:] == -1).all())
 
 
+@pytest.mark.parametrize("kind", ["dup", "quant", "tooth"])
+@pytest.mark.parametrize("k", [1, 5, 16, 33, 64])
+def test_knnquery_ties_by_index(cuda, kind, k):
+    """GEOT_KNN_TIES_BY_INDEX (knn_point / knn_cuda.KNN semantics: no heap replay): rows ascending in (distance, index);
+    the same rows from the grid and the brute-force kernels (visiting order does not matter); the k best are a prefix
+    of the k+7 best; the distances are the ones the reference's heap order returns (only the order of equal ones and the
+    choice among equals at the boundary may differ) - on clouds with many exact ties (duplicates, quantised coordinates)."""
+    B, N, M = 2, 6000, 700
+    xyz = torch.from_numpy(clouds(kind, B, N, seed=3)).cuda().view(-1, 3).contiguous()
+    q = xyz.view(B, N, 3)[:, :M].reshape(-1, 3).contiguous()
+    T = _lib.GEOT_KNN_TIES_BY_INDEX
+    idx, d2 = F.knnquery(k, xyz, q, None, None, n_per=N, m_per=M, flags=T)
+    idx_b, d2_b = F.knnquery(k, xyz, q, None, None, n_per=N, m_per=M, flags=T | _lib.GEOT_KNN_NO_GRID)
+    assert torch.equal(idx, idx_b) and torch.equal(d2, d2_b)
+    same = d2[:, 1:] == d2[:, :-1]
+    assert bool((d2[:, 1:] >= d2[:, :-1]).all()) and bool((idx[:, 1:] > idx[:, :-1])[same].all())
+    if kind != "tooth" and k >= 5:
+        assert int(same.sum()) > 0
+    idx7, d27 = F.knnquery(k + 7, xyz, q, None, None, n_per=N, m_per=M, flags=T)
+    assert torch.equal(idx7[:, :k], idx) and torch.equal(d27[:, :k], d2)
+    _, d2_heap = F.knnquery(k, xyz, q, None, None, n_per=N, m_per=M)
+    assert torch.equal(d2_heap, d2)
+    # the distances are exact: recomputed from the returned indices in double they agree to fp32 rounding
+    p, c = xyz[idx.long()].double(), q.double().unsqueeze(1)
+    assert float(((p - c).square().sum(-1) - d2.double()).abs().max()) <= 1e-6 * float(d2.max()) + 1e-12
+
+
 def test_ball_query_offset(cuda, oracle):
     sizes, ms = [3000, 700, 5001], [100, 33, 250]
     xyz = np.concatenate([synth.tooth_cloud(n, 60 + i) for i, n in enumerate(sizes)])
