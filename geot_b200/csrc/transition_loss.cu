@@ -114,6 +114,31 @@ __device__ __forceinline__ unsigned spread6(unsigned v) {  // 6 bits -> every th
   v = (v | (v << 2)) & 0x00009249u;
   return v;
 }
+// R consecutive steps (j, j/2, .. j >> (R-1)) of merge size k in one pass: a thread takes the 2^R keys that differ in
+// those R index bits through registers - a third of the shared-memory round trips and barriers of one step per pass.
+template <int R, int N2>
+__device__ __forceinline__ void so_pass(unsigned* keys, int t, int k, int j) {
+  const int jl = j >> (R - 1);  // the lowest step of this pass
+  for (int gi = t; gi < (N2 >> R); gi += 1024) {
+    const int base = ((gi & ~(jl - 1)) << R) | (gi & (jl - 1));
+    const bool up = (base & k) == 0;
+    unsigned w[1 << R];
+#pragma unroll
+    for (int c = 0; c < (1 << R); c++) w[c] = keys[base + c * jl];
+#pragma unroll
+    for (int st = 1 << (R - 1); st > 0; st >>= 1) {
+#pragma unroll
+      for (int c = 0; c < (1 << R); c++) {
+        if ((c & st) == 0) {
+          const unsigned x = w[c], y = w[c | st];
+          if ((x > y) == up) { w[c] = y; w[c | st] = x; }
+        }
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < (1 << R); c++) keys[base + c * jl] = w[c];
+  }
+}
 template <int EPT>
 __global__ void __launch_bounds__(1024)
 spatial_order_fine_kernel(int N, int D, const float* __restrict__ points, int* __restrict__ order) {
@@ -187,14 +212,15 @@ spatial_order_fine_kernel(int N, int D, const float* __restrict__ points, int* _
 #pragma unroll
   for (int e = 0; e < EPT; e++) so_keys[t * EPT + e] = v[e];
   __syncthreads();
+  constexpr int RMAX = EPT >= 8 ? 3 : (EPT >= 4 ? 2 : 1);  // network steps per pass over shared memory
   for (int k = 2 * EPT; k <= n2; k <<= 1) {
-    for (int j = k >> 1; j >= EPT; j >>= 1) {
-      for (int i = t; i < (n2 >> 1); i += 1024) {
-        const int lo_i = ((i & ~(j - 1)) << 1) | (i & (j - 1)), hi_i = lo_i | j;  // the i-th pair of this step
-        const unsigned x = so_keys[lo_i], y = so_keys[hi_i];
-        const bool up = (lo_i & k) == 0;
-        if ((x > y) == up) { so_keys[lo_i] = y; so_keys[hi_i] = x; }
-      }
+    int j = k >> 1;
+    while (j >= EPT) {
+      int avail = 1;
+      while ((j >> avail) >= EPT) avail++;
+      if (RMAX >= 3 && avail >= 3) { so_pass<3, n2>(so_keys, t, k, j); j >>= 3; }
+      else if (RMAX >= 2 && avail >= 2) { so_pass<2, n2>(so_keys, t, k, j); j >>= 2; }
+      else { so_pass<1, n2>(so_keys, t, k, j); j >>= 1; }
       __syncthreads();
     }
     if (EPT > 1) {
