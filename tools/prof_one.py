@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Dev tool (GPU box): launch ONE op of the bench workload a few times so ncu can capture it.
-usage: python tools/prof_one.py {fps|fps_noprune|ball|group|group3|groupxyz|groupbwd|plan|threenn|tibwd|ti|ti_old|gf|upsample|knn|sigt|apply|manifold} [B]"""
+usage: python tools/prof_one.py {fps|fps_noprune|ball|group|group3|groupxyz|groupbwd|plan|threenn|tibwd|ti|ti_old|gf|upsample|knn|knntie|sigt|apply|manifold} [B]"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
@@ -24,6 +24,8 @@ if what in ("threenn", "tibwd", "ti", "ti_old"):
     w = 1.0 / (d2 + 1e-8); w = (w / w.sum(-1, keepdim=True)).contiguous()
     go3 = torch.randn(B, C, N, device="cuda")
     plan3 = F.ScatterPlan(i3, B, M)
+if what == "knntie":  # self-kNN k=33 on the cfg4 clouds under the reference's heap semantics: one tied query is replayed
+    tx = torch.from_numpy(synth.tooth_batch(2, 16000)).cuda().view(-1, 3).contiguous()
 if what == "knn":
     kb = 8
     kx = xyz[:kb].reshape(-1, 3).contiguous()
@@ -70,6 +72,7 @@ for _ in range(3):
         _lib.lib().geot_group_points_config(3 if what == "ti_old" else 0)
         F.three_interpolate(feat[:, :, :M].contiguous(), i3, w)
     elif what == "knn": F.knnquery(16, kx, kx, koff, koff, m_per=N)
+    elif what == "knntie": F.knnquery(33, tx, tx, None, None, n_per=16000, m_per=16000)
     elif what == "sigt":
         modt.zero_grad(set_to_none=True); modt(pt, cmt).backward(got)
     elif what == "apply":

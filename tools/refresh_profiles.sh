@@ -22,7 +22,7 @@ $B > gpurun_out/${tag}_launches_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${tag}_launches_bench.csv \
     $B > gpurun_out/${tag}_launches.log 2>&1
 for k in "fps fps_mgr" "ball bq_build" "ball bq_grid" "group group_rows" "groupbwd seg_reduce_planrow" "plan plan_build_fused" \
-         "threenn three_nn_grid" "tibwd seg_reduce_wrows" "knn knn_grid" \
+         "threenn three_nn_grid" "tibwd seg_reduce_wrows" "knn knn_grid" "knntie knn_heap_warp" \
          "sigt sigt_kernel" "apply transition_apply_tile" "manifold manifold_fwd_tile" "manifold manifold_bwd_tile" \
          "manifold spatial_order_fine" "ti three_interpolate_persist" "gf graph_feature_kernel" "groupxyz group_xyz_rel"; do
   set -- $k
