@@ -32,6 +32,7 @@ static thread_local bool g_rows4_off = false;           // mode 3: three_interpo
 static thread_local bool g_tip_off = false;             // mode 4: three_interpolate without the persistent interleaved kernel (A/B)
 static thread_local bool g_mtile_off = false;           // mode 6: manifold loss on the warp-per-point kernels (A/B)
 static thread_local bool g_mtile_on = false;            // mode 7: manifold loss on the tile kernels whatever C (tests)
+static thread_local bool g_wrows_nb4 = false;           // mode 8: EXPERIMENT three_interpolate backward with 32-edge rounds
 
 // VEC = 4: E % 4 == 0 and 16-byte aligned idx/out.  grid (ceil(E/VEC/256), ceil(C/CCH), B).
 template <int VEC>
@@ -894,7 +895,7 @@ plan_wsort_kernel(int64_t E, const float* __restrict__ w, const int* __restrict_
 // LPT = lanes per target: 8 for long segments (~48 edges when n/m = 16), 2 when a target has only a handful of
 // edges (n/m = 2: six on average) - then 512 targets are in flight per CTA instead of 128 and the per-target
 // round trip to L2, not the edge count, is what is being hidden.
-template <int R, int LPT>
+template <int R, int LPT, int NB>
 __global__ void __launch_bounds__(1024, 1)
 seg_reduce_wrows_kernel(int C, int n, int m, const float* __restrict__ g, const int* __restrict__ row_ptr,
                         const int2* __restrict__ edges, float* __restrict__ dst) {
@@ -931,15 +932,15 @@ seg_reduce_wrows_kernel(int C, int n, int m, const float* __restrict__ g, const 
     for (int r = 0; r < R; r++) acc[r] = 0.f;
     // up to 64 edges of the segment per round: all 8 {perm, w} pairs of a lane are requested before the first
     // is used, so a typical segment (~48 edges) costs one L2 round trip instead of one per pair
-    for (int p0 = s0 + sub; p0 < e0; p0 += 8 * LPT) {
-      int2 e8[8];
+    for (int p0 = s0 + sub; p0 < e0; p0 += NB * LPT) {
+      int2 e8[NB];
 #pragma unroll
-      for (int j = 0; j < 8; j++) {
+      for (int j = 0; j < NB; j++) {
         const int p = p0 + LPT * j;
         e8[j] = p < e0 ? __ldg(ed + p) : make_int2(0, 0);
       }
 #pragma unroll
-      for (int j = 0; j < 8; j++) {
+      for (int j = 0; j < NB; j++) {
         if (p0 + LPT * j < e0) {
           const float wt = __int_as_float(e8[j].y);
 #pragma unroll
@@ -962,13 +963,13 @@ seg_reduce_wrows_kernel(int C, int n, int m, const float* __restrict__ g, const 
   for (int i = t; i < nc * m; i += 1024) out[i] = outs[i];
 }
 
-template <int R, int LPT>
+template <int R, int LPT, int NB>
 static int launch_wrows_t(int B, int C, int n, int m, size_t smem, const float* g, const PlanView& pv, const int2* wsorted,
                           float* dst, cudaStream_t s) {
   static DynSmem ds;  // per instantiation
-  if (int rc = ds.need(seg_reduce_wrows_kernel<R, LPT>, 226 * 1024, "three_interpolate_grad")) return rc;
+  if (int rc = ds.need(seg_reduce_wrows_kernel<R, LPT, NB>, 226 * 1024, "three_interpolate_grad")) return rc;
   dim3 grid((C + R - 1) / R, B);
-  seg_reduce_wrows_kernel<R, LPT><<<grid, 1024, smem, s>>>(C, n, m, g, pv.row_ptr, wsorted, dst);
+  seg_reduce_wrows_kernel<R, LPT, NB><<<grid, 1024, smem, s>>>(C, n, m, g, pv.row_ptr, wsorted, dst);
   count_launch(1);
   return check_launch("seg_reduce_wrows_kernel");
 }
@@ -976,8 +977,9 @@ template <int R>
 static int launch_wrows(int B, int C, int n, int m, size_t smem, const float* g, const PlanView& pv, const int2* wsorted,
                         float* dst, cudaStream_t s) {
   // average segment = 3n / m edges
-  if ((int64_t)3 * n < (int64_t)24 * m) return launch_wrows_t<R, 2>(B, C, n, m, smem, g, pv, wsorted, dst, s);
-  return launch_wrows_t<R, 8>(B, C, n, m, smem, g, pv, wsorted, dst, s);
+  if ((int64_t)3 * n < (int64_t)24 * m) return launch_wrows_t<R, 2, 8>(B, C, n, m, smem, g, pv, wsorted, dst, s);
+  if (g_wrows_nb4) return launch_wrows_t<R, 8, 4>(B, C, n, m, smem, g, pv, wsorted, dst, s);
+  return launch_wrows_t<R, 8, 8>(B, C, n, m, smem, g, pv, wsorted, dst, s);
 }
 
 static int three_interpolate_grad_rows(int B, int C, int n, int m, const float* g, const float* w, const void* plan,
@@ -1148,7 +1150,7 @@ GEOT_API int geot_gather_rows(int B, int N, int M, int D, const float* src, cons
 
 /* testing / A-B timing: direct != 0 disables the row-staged forward kernel (process-wide). */
 GEOT_API void geot_group_points_config(int mode) {
-  g_group_force_direct = mode == 1; g_force_staged = mode == 2; g_rows4_off = mode == 3; g_tip_off = mode == 4; g_mtile_off = mode == 6; g_mtile_on = mode == 7;
+  g_group_force_direct = mode == 1; g_force_staged = mode == 2; g_rows4_off = mode == 3; g_tip_off = mode == 4; g_mtile_off = mode == 6; g_mtile_on = mode == 7; g_wrows_nb4 = mode == 8;
 }
 
 GEOT_API int geot_gather_points(int B, int C, int N, int M, const float* points, const int* idx,

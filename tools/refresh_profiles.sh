@@ -30,4 +30,8 @@ for k in "fps fps_mgr" "ball bq_build" "ball bq_grid" "group group_rows" "groupb
   ncu --set full --clock-control none --import-source on -k regex:$2 -c 1 -f -o gpurun_out/${tag}_full_$2 \
       python tools/prof_one.py $1 > gpurun_out/${tag}_full_$2.log 2>&1
 done
+# keep the digests, not the reports (gpurun brings back at most 64 MiB)
+python tools/ncu_summary.py gpurun_out/${tag}_ncu_full_summary.csv gpurun_out/${tag}_full_*.ncu-rep > /dev/null 2>&1
+for f in gpurun_out/${tag}_full_*.ncu-rep; do python tools/ncu_brief.py $f > ${f%.ncu-rep}_brief.txt 2>/dev/null; done
+[ -n "$KEEP_REPS" ] || rm -f gpurun_out/${tag}_full_*.ncu-rep
 ls -la gpurun_out/ | tail -50

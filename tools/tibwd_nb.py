@@ -1,0 +1,38 @@
+#!/usr/bin/env python
+"""Dev tool (GPU box): three_interpolate backward (plan cached), 64-edge rounds (default) against 32-edge rounds (mode 8)."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from geot_b200 import _lib, synth
+from geot_b200 import functional as F
+
+
+def timeit(fn, it=20):
+    for _ in range(3): fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(it): fn()
+    e1.record(); torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / it
+
+
+for (B, C, m, n) in [(64, 64, 1024, 16384), (16, 32, 4096, 16384), (16, 128, 1024, 4096), (6, 384, 2048, 8192), (6, 128, 8192, 16000)]:
+    xyz = torch.from_numpy(synth.tooth_batch(B, n)).cuda()
+    cen = torch.gather(xyz, 1, F.furthest_point_sampling(xyz, m).long()[..., None].expand(-1, -1, 3)).contiguous()
+    d2, i3 = F.three_nn(xyz, cen)
+    w = 1.0 / (d2 + 1e-8); w = (w / w.sum(-1, keepdim=True)).contiguous()
+    go = torch.randn(B, C, n, device="cuda")
+    plan = F.ScatterPlan(i3, B, m)
+    out = torch.empty(B, C, m, device="cuda")
+    seg = torch.bincount(i3[0].flatten().long(), minlength=m)
+    res = {}
+    for name, mode in (("nb8", 0), ("nb4", 8)):
+        _lib.lib().geot_group_points_config(mode)
+        try:
+            res[name] = timeit(lambda: F.three_interpolate_grad(go, w, plan, m, out=out))
+            res[name + "_out"] = out.clone()
+        finally:
+            _lib.lib().geot_group_points_config(0)
+    print(f"B={B} C={C} m={m} n={n}: nb8 {res['nb8']:.4f} ms  nb4 {res['nb4']:.4f} ms  max diff {(res['nb8_out'] - res['nb4_out']).abs().max().item():.2e}"
+          f"  segment length mean {seg.float().mean():.1f} p50 {seg.float().median():.0f} max {seg.max().item()}", flush=True)
