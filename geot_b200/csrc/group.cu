@@ -32,7 +32,6 @@ static thread_local bool g_rows4_off = false;           // mode 3: three_interpo
 static thread_local bool g_tip_off = false;             // mode 4: three_interpolate without the persistent interleaved kernel (A/B)
 static thread_local bool g_mtile_off = false;           // mode 6: manifold loss on the warp-per-point kernels (A/B)
 static thread_local bool g_mtile_on = false;            // mode 7: manifold loss on the tile kernels whatever C (tests)
-static thread_local bool g_wrows_nb4 = false;           // mode 8: EXPERIMENT three_interpolate backward with 32-edge rounds
 
 // VEC = 4: E % 4 == 0 and 16-byte aligned idx/out.  grid (ceil(E/VEC/256), ceil(C/CCH), B).
 template <int VEC>
@@ -978,7 +977,6 @@ static int launch_wrows(int B, int C, int n, int m, size_t smem, const float* g,
                         float* dst, cudaStream_t s) {
   // average segment = 3n / m edges
   if ((int64_t)3 * n < (int64_t)24 * m) return launch_wrows_t<R, 2, 8>(B, C, n, m, smem, g, pv, wsorted, dst, s);
-  if (g_wrows_nb4) return launch_wrows_t<R, 8, 4>(B, C, n, m, smem, g, pv, wsorted, dst, s);
   return launch_wrows_t<R, 8, 8>(B, C, n, m, smem, g, pv, wsorted, dst, s);
 }
 
@@ -1150,7 +1148,7 @@ GEOT_API int geot_gather_rows(int B, int N, int M, int D, const float* src, cons
 
 /* testing / A-B timing: direct != 0 disables the row-staged forward kernel (process-wide). */
 GEOT_API void geot_group_points_config(int mode) {
-  g_group_force_direct = mode == 1; g_force_staged = mode == 2; g_rows4_off = mode == 3; g_tip_off = mode == 4; g_mtile_off = mode == 6; g_mtile_on = mode == 7; g_wrows_nb4 = mode == 8;
+  g_group_force_direct = mode == 1; g_force_staged = mode == 2; g_rows4_off = mode == 3; g_tip_off = mode == 4; g_mtile_off = mode == 6; g_mtile_on = mode == 7;
 }
 
 GEOT_API int geot_gather_points(int B, int C, int N, int M, const float* points, const int* idx,
