@@ -211,6 +211,13 @@ sigt_generic_kernel(int B, int C, int N, const float* __restrict__ x, const floa
 constexpr int kGwThreads = 384;
 constexpr int kGwTile = 8;  // points per shared tile
 
+// The g_raw tile of the NEXT 8 points travels (16-byte cp.async: pts_per_cta is a multiple of 8, so a tile starts on a
+// 32-byte boundary) while the current one is multiplied: with a single buffer the kernel alternated between waiting
+// for 35 KB and 1.4 us of FMAs (ncu: 29 % issue-active, 176 us at C=33, BN=32000).
+__device__ __forceinline__ void gw_cp_async16(void* smem, const void* gmem) {
+  const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem) : "memory");
+}
 template <int C>
 __global__ void __launch_bounds__(kGwThreads, 1)
 sigt_gw_partial_kernel(int B, int N, int64_t pts_per_cta, const float* __restrict__ x,
@@ -219,8 +226,10 @@ sigt_gw_partial_kernel(int B, int N, int64_t pts_per_cta, const float* __restric
   constexpr int RPT = (R + kGwThreads - 1) / kGwThreads;
   constexpr int CI = C + 1;
   constexpr int CIP = (CI + 3) & ~3;
-  __shared__ __align__(16) float g_s[kGwTile * R];
-  __shared__ __align__(16) float p_s[kGwTile * CIP];
+  constexpr int GT = (kGwTile * R + 3) & ~3;  // floats per g buffer
+  extern __shared__ __align__(16) float gw_smem[];
+  auto g_of = [&](int b2) { return gw_smem + b2 * GT; };
+  auto p_of = [&](int b2) { return gw_smem + 2 * GT + b2 * (kGwTile * CIP); };
   const int64_t BN = (int64_t)B * N;
   const int64_t first = (int64_t)blockIdx.x * pts_per_cta;
   const int64_t last = min(BN, first + pts_per_cta);
@@ -230,24 +239,52 @@ sigt_gw_partial_kernel(int B, int N, int64_t pts_per_cta, const float* __restric
 #pragma unroll
     for (int i = 0; i < CI; i++) acc[q][i] = 0.f;
 
+  auto issue_g = [&](int buf, int64_t g0, int cnt) {  // g_raw[g0 .. g0 + cnt) -> g_buf[buf]
+    const float* __restrict__ src = g_raw + g0 * R;
+    const int nfl = cnt * R;
+    if (((reinterpret_cast<uintptr_t>(src)) & 15) == 0) {
+      const int n4 = nfl >> 2;
+      for (int e = threadIdx.x; e < n4; e += kGwThreads) gw_cp_async16(g_of(buf) + 4 * e, src + 4 * e);
+      for (int e = (n4 << 2) + threadIdx.x; e < nfl; e += kGwThreads) g_of(buf)[e] = __ldg(src + e);
+    } else {
+      for (int e = threadIdx.x; e < nfl; e += kGwThreads) g_of(buf)[e] = __ldg(src + e);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  auto load_p = [&](int64_t g0, int cnt) -> float {  // this thread's entry of the (8 x CIP) input tile: [p | 1 | 0..]
+    const int e = threadIdx.x;
+    if (e >= kGwTile * CIP) return 0.f;
+    const int pt = e / CIP, i = e - pt * CIP;
+    if (pt >= cnt) return 0.f;
+    if (i < C) {
+      const int64_t g = g0 + pt, b = g / N, n = g - b * N;
+      return __ldg(x + (b * C + i) * N + n);
+    }
+    return i == C ? 1.0f : 0.f;
+  };
+  static_assert(kGwTile * CIP <= kGwThreads, "one input-tile entry per thread");
+
+  int buf = 0;
+  if (first < last) {
+    const int cnt0 = (int)min((int64_t)kGwTile, last - first);
+    issue_g(0, first, cnt0);
+    const float pv0 = load_p(first, cnt0);
+    if (threadIdx.x < kGwTile * CIP) p_of(0)[threadIdx.x] = pv0;
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+  }
+  __syncthreads();
   for (int64_t g0 = first; g0 < last; g0 += kGwTile) {
     const int cnt = (int)min((int64_t)kGwTile, last - g0);
-    __syncthreads();
-    for (int e = threadIdx.x; e < cnt * R; e += kGwThreads) g_s[e] = __ldg(g_raw + g0 * R + e);
-    for (int e = threadIdx.x; e < kGwTile * CIP; e += kGwThreads) {
-      const int pt = e / CIP, i = e - pt * CIP;
-      float v = 0.f;
-      if (pt < cnt) {
-        if (i < C) {
-          const int64_t g = g0 + pt, b = g / N, n = g - b * N;
-          v = __ldg(x + (b * C + i) * N + n);
-        } else if (i == C) {
-          v = 1.0f;
-        }
-      }
-      p_s[e] = v;
+    const int64_t gn = g0 + kGwTile;
+    const bool more = gn < last;
+    const int cntn = more ? (int)min((int64_t)kGwTile, last - gn) : 0;
+    float pvn = 0.f;
+    if (more) {
+      issue_g(buf ^ 1, gn, cntn);
+      pvn = load_p(gn, cntn);
     }
-    __syncthreads();
+    const float* __restrict__ g_s = g_of(buf);
+    const float* __restrict__ p_s = p_of(buf);
     for (int pt = 0; pt < cnt; pt++) {
       float gv[RPT];
 #pragma unroll
@@ -269,6 +306,12 @@ sigt_gw_partial_kernel(int B, int N, int64_t pts_per_cta, const float* __restric
         }
       }
     }
+    if (more) {
+      if (threadIdx.x < kGwTile * CIP) p_of(buf ^ 1)[threadIdx.x] = pvn;
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+    __syncthreads();  // the next tile is complete and everyone is done with this one
+    buf ^= 1;
   }
   float* __restrict__ dst = partial + (size_t)blockIdx.x * R * CI;
 #pragma unroll
@@ -280,6 +323,8 @@ sigt_gw_partial_kernel(int B, int N, int64_t pts_per_cta, const float* __restric
     }
   }
 }
+template <int C>
+constexpr size_t gw_smem_bytes() { return (size_t)(2 * (((kGwTile * C * C) + 3) & ~3) + 2 * kGwTile * (((C + 1) + 3) & ~3)) * sizeof(float); }
 
 // Generic C: one thread per (r, i) column walks its CTA's slice of points.
 __global__ void __launch_bounds__(256)
@@ -412,10 +457,16 @@ GEOT_API int geot_sigt_backward(int B, int C, int N, const float* x, const float
   if (rc) return rc;
   const int64_t BN = (int64_t)B * N;
   const int parts = gw_parts(BN);
-  const int64_t per = (BN + parts - 1) / parts;
-  if (C == 17) sigt_gw_partial_kernel<17><<<parts, kGwThreads, 0, s>>>(B, N, per, x, g_raw, partial);
-  else if (C == 33) sigt_gw_partial_kernel<33><<<parts, kGwThreads, 0, s>>>(B, N, per, x, g_raw, partial);
-  else {
+  const int64_t per = (((BN + parts - 1) / parts) + 7) & ~(int64_t)7;  // whole 8-point tiles per CTA (16-byte aligned tile starts)
+  if (C == 17) {
+    static DynSmem ds17;
+    if (int rcs = ds17.need(sigt_gw_partial_kernel<17>, gw_smem_bytes<17>(), "sigt_backward")) return rcs;
+    sigt_gw_partial_kernel<17><<<parts, kGwThreads, gw_smem_bytes<17>(), s>>>(B, N, per, x, g_raw, partial);
+  } else if (C == 33) {
+    static DynSmem ds33;
+    if (int rcs = ds33.need(sigt_gw_partial_kernel<33>, gw_smem_bytes<33>(), "sigt_backward")) return rcs;
+    sigt_gw_partial_kernel<33><<<parts, kGwThreads, gw_smem_bytes<33>(), s>>>(B, N, per, x, g_raw, partial);
+  } else {
     dim3 grid((C * C * (C + 1) + 255) / 256, parts);
     sigt_gw_partial_generic_kernel<<<grid, 256, 0, s>>>(B, C, N, per, x, g_raw, partial);
   }
