@@ -85,18 +85,17 @@ __device__ __forceinline__ void sts128(unsigned a, float4 v) {
   asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 
-// SM count of the current device, asked once per device (148 on B200).  It sizes grids and picks kernel variants; no
-// result depends on it.
+// SM count, asked from the driver once per process (the device current at the first call; 148 on B200).  It sizes
+// grids and picks kernel variants, no result depends on it; the library is built for sm_100a only, so the devices of
+// one process share it.  (A per-call cudaGetDevice here showed up as +2.5 us on the 8-us gather launches.)
 inline int num_sms() {
-  static int cached[64] = {};
-  int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
-  if (cached[dev] == 0) {
-    int v = 0;
-    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
-    cached[dev] = v;
-  }
-  return cached[dev];
+  static const int cached = [] {
+    int dev = 0, v = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) return 148;
+    return v;
+  }();
+  return cached;
 }
 
 // cudaFuncAttributeMaxDynamicSharedMemorySize belongs to the function IN ONE DEVICE'S CONTEXT, not to the process: a

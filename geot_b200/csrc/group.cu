@@ -350,7 +350,15 @@ constexpr int kFusedMaxE = 1 << 19;        // bitmap: 64 KB
 constexpr int kFusedThread = 2;            // a pair is ordered by its own thread; anything longer goes to the warp sorter
                                            // (an insertion sort in local memory costs ~60 cycles per step and the whole
                                            // warp waits for its longest segment: measured 70 us of the 85 us build)
-constexpr int kFusedWarp = 512;            // up to this length: rank sort by one warp (registers + shuffles); longer: CTA bitmap
+constexpr int kFusedWarp = 512;            // the warp rank sort holds up to this many values (16 per lane)
+#ifndef GEOT_PLAN_WARP_CUT
+#define GEOT_PLAN_WARP_CUT 256
+#endif
+// segments up to this length: rank sort by one warp (L*L/32 shuffle steps); longer: the whole CTA through a bitmap (a
+// few microseconds whatever the length).  Measured (tools/plan_ab.py): 128 / 512 are within 10 % of each other on the
+// grouping plans of ball-query lists (pieces of <= 65535 sources); an UNSPLIT dense-ball list (every query lists the
+// same ~80 lowest indices, ~800 sources each; 16 x 4096, E = 65536) takes 1.89 ms at 512 and 0.42 ms at 128.
+constexpr int kFusedWarpCut = GEOT_PLAN_WARP_CUT;
 
 // Warp-cooperative sort of one segment of L <= kFusedWarp DISTINCT values, in place: every lane holds up to 16 of
 // them, rank(x) = #{y < x} by broadcasting every value to every lane; cost ~ (L/32)^2 * 32 shuffles.
@@ -528,11 +536,11 @@ plan_build_fused_kernel(int Nall, int E, int list_cap, int nmax, const int* __re
       const T x0 = seg[0], x1 = seg[1];
       if (x0 > x1) { seg[0] = x1; seg[1] = x0; }
     }
-    if (L > kFusedWarp) {
+    if (L > kFusedWarpCut) {
       const int slot = atomicAdd(&s_heavy_n, 1);
       if (slot < 256) s_heavy[slot] = k;
     }
-    const bool is16 = L >= 3 && L <= 16, isw = L > 16 && L <= kFusedWarp;
+    const bool is16 = L >= 3 && L <= 16, isw = L > 16 && L <= kFusedWarpCut;
     const unsigned m16 = __ballot_sync(0xffffffffu, is16), mw = __ballot_sync(0xffffffffu, isw);
     int p16 = 0, pw = 0;
     if (lane == 0) {
@@ -581,7 +589,7 @@ plan_build_fused_kernel(int Nall, int E, int list_cap, int nmax, const int* __re
   for (int item = 0; item < items; item++) {
     const int k = heavy_n <= 256 ? s_heavy[item] : item;
     const int s = k ? cnt[k - 1] : 0, L = cnt[k] - s;
-    if (L <= kFusedWarp) continue;  // (only reachable in rescan mode; uniform across the CTA)
+    if (L <= kFusedWarpCut) continue;  // (only reachable in rescan mode; uniform across the CTA)
     T* __restrict__ seg = perm + s;
     for (int i = t; i < wpt * 1024; i += 1024) bm[i] = 0u;
     __syncthreads();

@@ -30,3 +30,19 @@ for (B, N, k) in [(2, 16000, 32), (1, 16000, 32), (4, 8000, 16), (2, 16000, 16),
         finally:
             _lib.lib().geot_group_points_config(0)
     print(f"B={B} N={N} k={k} E={N*k}: default {res['default']:.4f} ms   multi-kernel {res['multi_kernel']:.4f} ms", flush=True)
+
+# ball-query index tensors as the grouping backward builds them (grouping_plan: split into pieces of <= 65535 sources):
+# E = M * ns sources into N targets, most targets empty, the lowest indices of every ball listed by many queries
+for (B, N, M, ns, r) in [(64, 16384, 1024, 32, 0.1), (16, 16384, 4096, 32, 0.1), (16, 4096, 1024, 64, 0.4), (16, 1024, 256, 64, 0.8),
+                          (16, 16384, 4096, 64, 0.2), (16, 4096, 1024, 32, 0.2), (16, 16384, 4096, 16, 0.05)]:
+    xyz = torch.from_numpy(synth.tooth_batch(B, N)).cuda()
+    cen = torch.gather(xyz, 1, F.furthest_point_sampling(xyz, M).long()[..., None].expand(-1, -1, 3)).contiguous()
+    idx = F.ball_query(cen, xyz, r, ns)
+    res = {}
+    for name, mode in (("default", 0), ("multi_kernel", 2)):
+        _lib.lib().geot_group_points_config(mode)
+        try:
+            res[name] = timeit(lambda: F.grouping_plan(idx, B, N))
+        finally:
+            _lib.lib().geot_group_points_config(0)
+    print(f"ball query B={B} N={N} M={M} ns={ns} E={M*ns}: default {res['default']:.4f} ms   multi-kernel {res['multi_kernel']:.4f} ms", flush=True)
