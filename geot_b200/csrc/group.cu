@@ -32,6 +32,7 @@ static thread_local bool g_rows4_off = false;           // mode 3: three_interpo
 static thread_local bool g_tip_off = false;             // mode 4: three_interpolate without the persistent interleaved kernel (A/B)
 static thread_local bool g_mtile_off = false;           // mode 6: manifold loss on the warp-per-point kernels (A/B)
 static thread_local bool g_mtile_on = false;            // mode 7: manifold loss on the tile kernels whatever C (tests)
+static thread_local int g_tib_stream = 0;               // mode 8: three_interpolate backward streamed whatever the launch size (tests); mode 5: never (A/B)
 
 // VEC = 4: E % 4 == 0 and 16-byte aligned idx/out.  grid (ceil(E/VEC/256), ceil(C/CCH), B).
 template <int VEC>
@@ -988,6 +989,108 @@ static int launch_wrows(int B, int C, int n, int m, size_t smem, const float* g,
   return launch_wrows_t<R, 8, 8>(B, C, n, m, smem, g, pv, wsorted, dst, s);
 }
 
+// ---------------------------------------------------------------------------------------------
+// three_interpolate backward, streamed (m <= 1024): a THREAD owns a target and keeps CG channel sums in registers; the
+// CG gradient rows of its CTA pass through shared memory in tiles of TS consecutive source points (bulk async copies,
+// double-buffered), and because the plan lists a target's sources in ascending order every thread simply walks its own
+// segment of packed {source, weight} edges forward, consuming the edges whose source lies in the current tile.  No lane
+// groups, no shuffles, no per-round slot bookkeeping: one edge load and CG x (LDS, FMUL, FADD) per edge.  The sum of a
+// target runs strictly in plan (ascending source) order - the order of the direct kernel: same bits as mode 1.
+// ---------------------------------------------------------------------------------------------
+constexpr int kTsThreads = 1024;
+// smem: [raw tile, 2 buffers of CG x TS floats (bulk copies) | interleaved tile: CG/4 planes of TS float4]
+template <int CG, int TS>
+__global__ void __launch_bounds__(kTsThreads, 1)
+ti_bwd_stream_kernel(int C, int n, int m, const float* __restrict__ g, const int* __restrict__ row_ptr,
+                     const int2* __restrict__ edges, float* __restrict__ dst) {
+  static_assert(CG % 4 == 0 && TS == kTsThreads, "one source column per thread in the interleave pass");
+  extern __shared__ __align__(16) float ts_smem[];
+  __shared__ uint64_t bar[2];
+  float4* inter = reinterpret_cast<float4*>(ts_smem + (size_t)2 * CG * TS);
+  const int t = threadIdx.x;
+  const int b = blockIdx.y, c0 = blockIdx.x * CG;
+  const int nc = min(CG, C - c0);
+  const int64_t E = (int64_t)3 * n;
+  const int ntiles = (n + TS - 1) / TS;
+  const float* __restrict__ g0 = g + ((int64_t)b * C + c0) * n;
+  auto issue = [&](int tile) {  // thread 0: the nc row pieces of this tile
+    const int buf = tile & 1, j0 = tile * TS, len = min(TS, n - j0);
+    mbar_expect_tx(&bar[buf], (unsigned)(nc * len) * 4u);
+    for (int c = 0; c < nc; c++) bulk_g2s(ts_smem + (size_t)buf * CG * TS + (size_t)c * TS, g0 + (int64_t)c * n + j0, (unsigned)len * 4u, &bar[buf]);
+  };
+  if (t == 0) {
+    mbar_init(&bar[0], 1);
+    mbar_init(&bar[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (t == 0) issue(0);
+  const int2* __restrict__ ed = edges + (int64_t)b * E;
+  int cur = 0, end = 0;
+  if (t < m) { cur = __ldg(row_ptr + (int64_t)b * (m + 1) + t); end = __ldg(row_ptr + (int64_t)b * (m + 1) + t + 1); }
+  const int2 kNone = make_int2(0x7fffffff, 0);
+  int2 e = cur < end ? __ldg(ed + cur) : kNone;          // the edge being consumed and the two behind it: loads stay
+  int2 e1 = cur + 1 < end ? __ldg(ed + cur + 1) : kNone;  // two edges ahead of the sums
+  int2 e2 = cur + 2 < end ? __ldg(ed + cur + 2) : kNone;
+  float acc[CG];
+#pragma unroll
+  for (int c = 0; c < CG; c++) acc[c] = 0.f;
+  for (int tile = 0; tile < ntiles; tile++) {
+    const int buf = tile & 1;
+    if (t == 0 && tile + 1 < ntiles) {
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // the other raw buffer was read one tile ago (barriers below)
+      issue(tile + 1);
+    }
+    mbar_wait(&bar[buf], (unsigned)((tile >> 1) & 1));
+    {  // interleave: thread t takes source column t of the raw tile, four channels per float4 (rows beyond nc: zeros)
+      const float* __restrict__ raw = ts_smem + (size_t)buf * CG * TS + t;
+#pragma unroll
+      for (int q = 0; q < CG / 4; q++) {
+        float4 v;
+        v.x = 4 * q + 0 < nc ? raw[(4 * q + 0) * TS] : 0.f;
+        v.y = 4 * q + 1 < nc ? raw[(4 * q + 1) * TS] : 0.f;
+        v.z = 4 * q + 2 < nc ? raw[(4 * q + 2) * TS] : 0.f;
+        v.w = 4 * q + 3 < nc ? raw[(4 * q + 3) * TS] : 0.f;
+        inter[q * TS + t] = v;
+      }
+    }
+    __syncthreads();  // the interleaved tile is complete (and this raw buffer may be refilled from the next iteration on)
+    const int j0 = tile * TS, j1 = j0 + TS;
+    while (e.x < j1) {
+      const float wt = __int_as_float(e.y);
+      const float4* __restrict__ col = inter + (e.x - j0);
+      cur++;
+      const int2 nx = cur + 2 < end ? __ldg(ed + cur + 2) : kNone;
+#pragma unroll
+      for (int q = 0; q < CG / 4; q++) {
+        const float4 v = col[q * TS];
+        acc[4 * q + 0] = __fadd_rn(acc[4 * q + 0], __fmul_rn(v.x, wt));
+        acc[4 * q + 1] = __fadd_rn(acc[4 * q + 1], __fmul_rn(v.y, wt));
+        acc[4 * q + 2] = __fadd_rn(acc[4 * q + 2], __fmul_rn(v.z, wt));
+        acc[4 * q + 3] = __fadd_rn(acc[4 * q + 3], __fmul_rn(v.w, wt));
+      }
+      e = e1; e1 = e2; e2 = nx;
+    }
+    __syncthreads();  // everyone is done with the interleaved tile before the next one overwrites it
+  }
+  if (t < m) {
+#pragma unroll
+    for (int c = 0; c < CG; c++)
+      if (c < nc) dst[((int64_t)b * C + c0 + c) * m + t] = acc[c];
+  }
+}
+
+template <int CG, int TS>
+static int launch_ti_bwd_stream(int B, int C, int n, int m, const float* g, const PlanView& pv, const int2* wsorted, float* dst, cudaStream_t s) {
+  static DynSmem ds;
+  const size_t smem = (size_t)3 * CG * TS * 4;
+  if (int rc = ds.need(ti_bwd_stream_kernel<CG, TS>, smem, "three_interpolate_grad")) return rc;  // no carve-out preference: L1 serves the edge walks
+  dim3 grid((C + CG - 1) / CG, B);
+  ti_bwd_stream_kernel<CG, TS><<<grid, kTsThreads, smem, s>>>(C, n, m, g, pv.row_ptr, wsorted, dst);
+  count_launch(1);
+  return check_launch("ti_bwd_stream_kernel");
+}
+
 static int three_interpolate_grad_rows(int B, int C, int n, int m, const float* g, const float* w, const void* plan,
                                        float* dst, cudaStream_t s, bool* taken) {
   *taken = false;
@@ -1018,6 +1121,13 @@ static int three_interpolate_grad_rows(int B, int C, int n, int m, const float* 
   int rc = check_launch("plan_wsort_kernel");
   if (rc) return rc;
   *taken = true;
+  // streamed kernel (thread per target, 16 channels per CTA): a CTA walks the ceil(n/1024) source tiles one after the
+  // other, so it needs the machine filled by CTAs, not by tiles.  Measured (tools/tibwd_ab.py, row-resident kernel in
+  // brackets): 64 x 64 x 1024 <- 16384 0.242 (0.264) ms, 16 x 128 x 1024 <- 4096 0.033 (0.038), 6 x 384 x 512 <- 2048
+  // 0.021 (0.025); with 32 CTAs (8 x 64 x 1024 <- 16384) 0.111 against 0.045
+  if (m <= kTsThreads && (C + 15) / 16 <= 65535 && g_tib_stream >= 0 &&
+      ((int64_t)B * ((C + 15) / 16) >= 96 || g_tib_stream > 0))
+    return launch_ti_bwd_stream<16, 1024>(B, C, n, m, g, pv, wsorted, dst, s);
   const size_t smem = smem_of(R);
   switch (R) {
     case 1: return launch_wrows<1>(B, C, n, m, smem, g, pv, wsorted, dst, s);
@@ -1156,7 +1266,7 @@ GEOT_API int geot_gather_rows(int B, int N, int M, int D, const float* src, cons
 
 /* testing / A-B timing: direct != 0 disables the row-staged forward kernel (process-wide). */
 GEOT_API void geot_group_points_config(int mode) {
-  g_group_force_direct = mode == 1; g_force_staged = mode == 2; g_rows4_off = mode == 3; g_tip_off = mode == 4; g_mtile_off = mode == 6; g_mtile_on = mode == 7;
+  g_group_force_direct = mode == 1; g_force_staged = mode == 2; g_rows4_off = mode == 3; g_tip_off = mode == 4; g_mtile_off = mode == 6; g_mtile_on = mode == 7; g_tib_stream = mode == 8 ? 1 : (mode == 5 ? -1 : 0);
 }
 
 GEOT_API int geot_gather_points(int B, int C, int N, int M, const float* points, const int* idx,

@@ -463,12 +463,16 @@ def test_three_interpolate_interleaved_vs_rows_vs_direct(cuda, oracle, B, C, m, 
 
 
 @pytest.mark.parametrize("B,C,m,n", [(3, 5, 1024, 16384), (2, 64, 700, 4096), (1, 13, 2048, 6002), (2, 7, 4096, 12288),
-                                     (2, 4, 1024, 30000), (1, 9, 6000, 8192), (2, 3, 512, 4096), (4, 16, 100, 20000), (1, 6, 8192, 16000)])
+                                     (2, 4, 1024, 30000), (1, 9, 6000, 8192), (2, 3, 512, 4096), (4, 16, 100, 20000), (1, 6, 8192, 16000),
+                                     (8, 200, 1024, 5000), (3, 17, 1, 2048), (2, 33, 1000, 1028)])
 def test_three_interpolate_grad_rows_vs_direct(cuda, oracle, B, C, m, n):
-    """Row-resident backward (gradient rows in shared memory, packed {source, weight} edges in plan order) against the
-    direct L2-gather kernel (mode 1) and the oracle, on real three_nn indices: skewed segment lengths, targets that no
-    point selects (half of the known points are moved away), channel counts that leave a partial last CTA, rows too
-    long for more than one per CTA, few edges per target (2 lanes per target), n % 4 != 0 (direct kernel)."""
+    """The backward kernels - streamed (thread per target, source tiles through shared memory; mode 8 forces it, default for
+    m <= 1024 when the launch fills the machine), row-resident (mode 5: gradient rows in shared memory, packed {source,
+    weight} edges, lane groups per target) and direct L2 gather (mode 1) - against the oracle, on real three_nn indices:
+    skewed segment lengths, targets that no point selects (half of the known points are moved away), channel counts that
+    leave a partial last CTA, a last source tile shorter than the others, m > 1024 (no streamed kernel), rows too long
+    for more than one per CTA, few edges per target, n % 4 != 0 (direct kernel).  The streamed kernel sums a target in
+    plan order like the direct one: identical bits."""
     unknown = clouds("tooth", B, n)
     known = np.ascontiguousarray(unknown[:, :m])
     known[:, m // 2:] += np.float32(5.0)  # half of the known points are far away: empty segments
@@ -478,15 +482,20 @@ def test_three_interpolate_grad_rows_vs_direct(cuda, oracle, B, C, m, n):
     g = torch.randn(B, C, n, device="cuda")
     plan = F.ScatterPlan(idx, B, m)
     got = F.three_interpolate_grad(g, w, plan, m)
-    _lib.lib().geot_group_points_config(1)
+    res = {}
     try:
-        direct = F.three_interpolate_grad(g, w, plan, m)
+        for name, mode in (("direct", 1), ("row-resident", 5), ("streamed", 8)):
+            _lib.lib().geot_group_points_config(mode)
+            res[name] = F.three_interpolate_grad(g, w, plan, m)
     finally:
         _lib.lib().geot_group_points_config(0)
     exp = oracle.three_interpolate_grad(g.cpu().numpy(), idx.cpu().numpy(), w.cpu().numpy(), m)
     terms = oracle.three_interpolate_grad(np.abs(g.cpu().numpy()), idx.cpu().numpy(), w.cpu().numpy(), m)
-    assert_sum_close(direct, exp, terms, what="three_interpolate_grad direct")
-    assert_sum_close(got, exp, terms, what="three_interpolate_grad row-resident")
+    for name, r in res.items():
+        assert_sum_close(r, exp, terms, what="three_interpolate_grad " + name)
+    assert_sum_close(got, exp, terms, what="three_interpolate_grad default")
+    if m <= 1024 and n % 4 == 0 and n >= 1024:
+        assert torch.equal(res["streamed"], res["direct"]), "streamed == direct, bit for bit"
     assert torch.equal(got, F.three_interpolate_grad(g, w, plan, m)), "run-to-run identical"
     assert torch.equal(got, F.three_interpolate_grad(g, w, F.ScatterPlan(idx, B, m), m)), "a fresh plan gives the same bits"
 
