@@ -32,6 +32,7 @@ static thread_local bool g_rows4_off = false;           // mode 3: three_interpo
 static thread_local bool g_tip_off = false;             // mode 4: three_interpolate without the persistent interleaved kernel (A/B)
 static thread_local bool g_mtile_off = false;           // mode 6: manifold loss on the warp-per-point kernels (A/B)
 static thread_local bool g_mtile_on = false;            // mode 7: manifold loss on the tile kernels whatever C (tests)
+static thread_local int g_pr_variant = -1;              // grouping backward: bit 0 half-row pipeline, bit 1 L2 prefetch of the next row, bit 2 grid of (channel group, cloud) CTAs instead of one CTA per SM; -1 = chosen per launch; modes 9 / 10 / 11 / 12 / 13 = 4 / 3 / 1 / 6 / 2 (A/B)
 static thread_local int g_tib_stream = 0;               // mode 8: three_interpolate backward streamed whatever the launch size (tests); mode 5: never (A/B)
 
 // VEC = 4: E % 4 == 0 and 16-byte aligned idx/out.  grid (ceil(E/VEC/256), ceil(C/CCH), B).
@@ -98,6 +99,15 @@ __device__ __forceinline__ void bulk_g2s_chunked(float* dst, const float* src, u
   for (unsigned o = 0; o < bytes; o += kPiece)
     bulk_g2s(reinterpret_cast<unsigned char*>(dst) + o, reinterpret_cast<const unsigned char*>(src) + o,
              min(kPiece, bytes - o), bar);
+}
+
+// Ask L2 for a row that a later bulk copy will read (no shared memory, no completion to wait for): the HBM read then
+// overlaps whatever the CTA does meanwhile and the copy itself runs at L2 speed.
+__device__ __forceinline__ void bulk_prefetch_l2(const float* src, unsigned bytes) {
+  constexpr unsigned kPiece = 16384;
+  for (unsigned o = 0; o < bytes; o += kPiece)
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;"
+                 ::"l"(reinterpret_cast<const unsigned char*>(src) + o), "r"(min(kPiece, bytes - o)) : "memory");
 }
 
 constexpr int kRowThreads = 512;
@@ -703,8 +713,8 @@ constexpr int kPrTaskCap = 5456;  // non-empty targets the compact task list can
 #ifndef GEOT_SEG_SUM16
 #define GEOT_SEG_SUM16 1
 #endif
-__device__ __forceinline__ float seg_sum16(const float* __restrict__ row, const unsigned short* __restrict__ perm16, int s0, int e0) {
-  float acc = 0.f;
+__device__ __forceinline__ float seg_sum16(const float* __restrict__ row, const unsigned short* __restrict__ perm16, int s0, int e0,
+                                           float acc = 0.f) {
 #if GEOT_SEG_SUM16
   int p = s0;
   if ((p & 1) && p < e0) { acc = __fadd_rn(acc, row[perm16[p]]); p++; }
@@ -720,46 +730,97 @@ __device__ __forceinline__ float seg_sum16(const float* __restrict__ row, const 
 #endif
   return acc;
 }
+constexpr int kPrSplitCap = 4096;  // tasks the list holds when it also keeps every segment's cut at the half row (8 bytes each)
+constexpr int kPrPerThread = kPrSplitCap / 1024;  // tasks of the split list one of the 1024 threads owns
 __global__ void __launch_bounds__(1024, 1)
-seg_reduce_planrow_kernel(int C, int N, int E, int Q, int cpc, const float* __restrict__ g, const int* __restrict__ row_ptr,
+seg_reduce_planrow_kernel(int B, int C, int N, int E, int Q, int cpc, int variant, const float* __restrict__ g, const int* __restrict__ row_ptr,
                           const int* __restrict__ perm, float* __restrict__ dst) {
   extern __shared__ __align__(16) unsigned char pr_smem[];
-  __shared__ uint64_t bar;
+  __shared__ uint64_t bar[2];
   __shared__ int s_bin[64], s_ne;
   float* row = reinterpret_cast<float*>(pr_smem);                                        // E floats
   unsigned short* perm16 = reinterpret_cast<unsigned short*>(pr_smem + (size_t)E * 4);  // E entries
   // 32 KB that hold EITHER row_ptr as 16-bit (general case) OR the compact task list {target, start, length} of
   // the non-empty targets ordered by descending length (sparse case, see below)
   unsigned short* rp16 = perm16 + ((E + 7) & ~7);
-  unsigned short* t_tgt = rp16;
-  unsigned short* t_start = rp16 + kPrTaskCap;
-  unsigned short* t_len = rp16 + 2 * kPrTaskCap;
   const int t = threadIdx.x, lane = t & 31;
-  const int b = blockIdx.y, c_first = blockIdx.x * cpc;
-  const int nc = min(cpc, C - c_first);
+  // rows (cloud, channel) r0 .. r1 of this CTA, cloud-major.  cpc == 0: one CTA per SM takes an equal share of all B*C
+  // rows, so the plan setup below runs once or twice per CTA (its rows span at most two clouds when the share is below
+  // C) and no wave is left partly filled; cpc > 0: the CTA (x, y) takes cpc channels of cloud y (A/B, mode 12).
+  int r0, r1;
+  if (cpc > 0) {
+    r0 = blockIdx.y * C + blockIdx.x * cpc;
+    r1 = blockIdx.y * C + min(C, (int)(blockIdx.x + 1) * cpc);
+  } else {
+    const int64_t items = (int64_t)B * C;
+    r0 = (int)(items * blockIdx.x / gridDim.x);
+    r1 = (int)(items * (blockIdx.x + 1) / gridDim.x);
+  }
   const int64_t Etot = (int64_t)E * Q;  // a gradient row has Q pieces of E values; the plan has one CSR per (cloud, piece)
+  // A gradient row arrives as two halves on two mbarriers.  The compact path sums a segment's entries below `half` as
+  // soon as the first half is there and lets the next row's first half load while it sums the rest out of the second
+  // half (and the other way round): the copy of a row hides behind the sums of the row before it.  A segment's entries
+  // ascend, so cutting the sum at `half` keeps the order of the additions.
+  const int half = (E / 2) & ~3;
+  const bool halves = variant & 1, prefetch = variant & 2;
   if (t == 0) {
-    mbar_init(&bar, 1);
+    mbar_init(&bar[0], 1);
+    mbar_init(&bar[1], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  unsigned loads = 0;  // bulk copies waited for so far (mbarrier phase parity)
+  unsigned loads = 0;  // rows waited for so far (mbarrier phase parity, the same for both halves)
+#pragma unroll 1
+  for (int r = r0, nc = 0; r < r1; r += nc) {
+  const int b = r / C, c_first = r - b * C;
+  nc = min(C - c_first, r1 - r);
 #pragma unroll 1
   for (int q = 0; q < Q; q++) {
     __syncthreads();  // previous piece: every thread is done with perm16 / the task list / s_bin
     if (t == 0) s_ne = 0;
     if (t < 64) s_bin[t] = 0;
     __syncthreads();
-    if (t == 0) bulk_g2s_chunked(row, g + ((int64_t)b * C + c_first) * Etot + (int64_t)q * E, (unsigned)E * 4u, &bar);
+    if (t == 0) {
+      const float* src = g + ((int64_t)b * C + c_first) * Etot + (int64_t)q * E;
+      bulk_g2s_chunked(row, src, (unsigned)half * 4u, &bar[0]);
+      bulk_g2s_chunked(row + half, src + half, (unsigned)(E - half) * 4u, &bar[1]);
+      if (prefetch && nc > 1) bulk_prefetch_l2(src + Etot, (unsigned)E * 4u);  // the second channel's row, during the setup
+    }
     const int* __restrict__ pm = perm + ((int64_t)b * Q + q) * E;
     const int* __restrict__ rp = row_ptr + ((int64_t)b * Q + q) * (N + 1);
-    for (int i = t; i < E; i += 1024) perm16[i] = (unsigned short)__ldg(pm + i);
+    {  // the cloud's plan entries as 16 bits, four per 16-byte load (perm is 256-byte aligned, E % 4 == 0)
+      const int4* __restrict__ pm4 = reinterpret_cast<const int4*>(pm);
+      uint2* p16 = reinterpret_cast<uint2*>(perm16);
+      for (int i = t; i < E / 4; i += 1024) {
+        const int4 v = __ldg(pm4 + i);
+        p16[i] = make_uint2((unsigned)v.x | ((unsigned)v.y << 16), (unsigned)v.z | ((unsigned)v.w << 16));
+      }
+    }
     // ball_query keeps the LOWEST indices of every ball, so most points are never a neighbour (80 % of the targets
     // are empty at the bench shape) and the rest have ~10 sources.  When the non-empty targets fit the task list
     // they are bucketed by segment length (64 bins, longest first): a warp then works on 32 segments of (almost)
     // equal length - no empty targets, no divergence on the segment loop.
-    for (int k = t; k < N; k += 1024) {
-      const int len = __ldg(rp + k + 1) - __ldg(rp + k);
-      if (len > 0) atomicAdd(&s_bin[63 - min(len, 63)], 1);
+    // A thread reads the row_ptr pairs of its targets once ({start, length} packed in a register each, all loads in
+    // flight together) when the cloud has at most 16 targets per thread; larger clouds re-read them in the second pass.
+    constexpr int kOwn = 16;
+    const bool owned = N <= kOwn * 1024;
+    unsigned sl[kOwn];
+    if (owned) {
+#pragma unroll
+      for (int j = 0; j < kOwn; j++) {
+        const int k = t + j * 1024;
+        const int s0 = k < N ? __ldg(rp + k) : 0, e0 = k < N ? __ldg(rp + k + 1) : 0;
+        sl[j] = (unsigned)s0 | ((unsigned)(e0 - s0) << 16);
+      }
+#pragma unroll
+      for (int j = 0; j < kOwn; j++) {
+        const int len = (int)(sl[j] >> 16);
+        if (len > 0) atomicAdd(&s_bin[63 - min(len, 63)], 1);
+      }
+    } else {
+      for (int k = t; k < N; k += 1024) {
+        const int len = __ldg(rp + k + 1) - __ldg(rp + k);
+        if (len > 0) atomicAdd(&s_bin[63 - min(len, 63)], 1);
+      }
     }
     __syncthreads();
     if (t < 32) {  // exclusive scan of the 64 bins (bin 0 = longest)
@@ -777,26 +838,82 @@ seg_reduce_planrow_kernel(int C, int N, int E, int Q, int cpc, const float* __re
     __syncthreads();
     const int ne = s_ne;
     const bool compact = ne <= kPrTaskCap;
-    if (compact) {
+    const bool split = halves && ne <= kPrSplitCap;  // room for a fourth 16-bit field: where the segment crosses `half`
+    const int cap = split ? kPrSplitCap : kPrTaskCap;
+    unsigned short* t_tgt = rp16;
+    unsigned short* t_start = rp16 + cap;
+    unsigned short* t_len = rp16 + 2 * cap;
+    unsigned short* t_mid = rp16 + 3 * cap;
+    auto add_task = [&](int k, int s0, int len) {
+      const int pos = atomicAdd(&s_bin[63 - min(len, 63)], 1);  // order inside a bin is free: sums do not depend on it
+      t_tgt[pos] = (unsigned short)k; t_start[pos] = (unsigned short)s0; t_len[pos] = (unsigned short)len;
+      if (split) {  // first entry >= half (entries ascend; perm16 is complete since the barrier after the bins)
+        int lo = s0, hi = s0 + len;
+        while (lo < hi) {
+          const int mid = (lo + hi) >> 1;
+          if (perm16[mid] < half) lo = mid + 1; else hi = mid;
+        }
+        t_mid[pos] = (unsigned short)lo;
+      }
+    };
+    if (compact && owned) {
+#pragma unroll
+      for (int j = 0; j < kOwn; j++)
+        if (sl[j] >> 16) add_task(t + j * 1024, (int)(sl[j] & 0xffffu), (int)(sl[j] >> 16));
+    } else if (compact) {
       for (int k = t; k < N; k += 1024) {
         const int s0 = __ldg(rp + k), len = __ldg(rp + k + 1) - s0;
-        if (len > 0) {
-          const int pos = atomicAdd(&s_bin[63 - min(len, 63)], 1);  // order inside a bin is free: sums do not depend on it
-          t_tgt[pos] = (unsigned short)k; t_start[pos] = (unsigned short)s0; t_len[pos] = (unsigned short)len;
-        }
+        if (len > 0) add_task(k, s0, len);
       }
+    } else if (owned) {
+#pragma unroll
+      for (int j = 0; j < kOwn; j++)
+        if (t + j * 1024 < N) rp16[t + j * 1024] = (unsigned short)(sl[j] & 0xffffu);
+      if (t == 0) rp16[N] = (unsigned short)__ldg(rp + N);
     } else {
       for (int i = t; i <= N; i += 1024) rp16[i] = (unsigned short)__ldg(rp + i);
     }
     __syncthreads();
     for (int ci = 0; ci < nc; ci++) {
       float* __restrict__ out = dst + ((int64_t)b * C + c_first + ci) * N;
+      const float* next = g + ((int64_t)b * C + c_first + ci + 1) * Etot + (int64_t)q * E;
       // piece 0 writes every target, later pieces add to it: the same thread order every run, so the sum
       // ((piece 0 + piece 1) + ...) is fixed
-      if (compact) {
+      if (split) {
         if (q == 0)
           for (int k = t; k < N; k += 1024) out[k] = 0.f;  // empty targets; the others are overwritten below
-        mbar_wait(&bar, loads & 1u);
+        float acc[kPrPerThread];
+        mbar_wait(&bar[0], loads & 1u);
+#pragma unroll
+        for (int j = 0; j < kPrPerThread; j++) {
+          const int i = t + j * 1024;
+          acc[j] = i < ne ? seg_sum16(row, perm16, t_start[i], t_mid[i]) : 0.f;
+        }
+        __syncthreads();  // every thread is done with the first half (and the zero fill is ordered before the sums)
+        if (t == 0 && ci + 1 < nc) bulk_g2s_chunked(row, next, (unsigned)half * 4u, &bar[0]);
+        mbar_wait(&bar[1], loads & 1u);
+#pragma unroll
+        for (int j = 0; j < kPrPerThread; j++) {
+          const int i = t + j * 1024;
+          if (i < ne) {
+            const float a = seg_sum16(row, perm16, t_mid[i], t_start[i] + t_len[i], acc[j]);
+            const int k = t_tgt[i];
+            out[k] = q == 0 ? a : __fadd_rn(out[k], a);
+          }
+        }
+        loads++;
+        __syncthreads();  // every thread is done with the second half (and, for later pieces, its writes to out are ordered)
+        if (t == 0 && ci + 1 < nc) {
+          bulk_g2s_chunked(row + half, next + half, (unsigned)(E - half) * 4u, &bar[1]);
+          if (prefetch && ci + 2 < nc) bulk_prefetch_l2(next + Etot, (unsigned)E * 4u);
+        }
+        continue;
+      }
+      if (compact) {
+        if (q == 0)
+          for (int k = t; k < N; k += 1024) out[k] = 0.f;
+        mbar_wait(&bar[0], loads & 1u);
+        mbar_wait(&bar[1], loads & 1u);
         __syncthreads();  // zero fill ordered before the sums of this CTA
         for (int i = t; i < ne; i += 1024) {
           const int s0 = t_start[i], e0 = s0 + t_len[i];
@@ -805,7 +922,8 @@ seg_reduce_planrow_kernel(int C, int N, int E, int Q, int cpc, const float* __re
           out[k] = q == 0 ? acc : __fadd_rn(out[k], acc);
         }
       } else {
-        mbar_wait(&bar, loads & 1u);
+        mbar_wait(&bar[0], loads & 1u);
+        mbar_wait(&bar[1], loads & 1u);
         for (int k = t; k < N; k += 1024) {
           const int s0 = rp16[k], e0 = rp16[k + 1];
           float acc = seg_sum16(row, perm16, s0, e0);
@@ -815,9 +933,12 @@ seg_reduce_planrow_kernel(int C, int N, int E, int Q, int cpc, const float* __re
       loads++;
       __syncthreads();  // every thread is done with the row buffer (and, for later pieces, its writes to out are ordered)
       if (t == 0 && ci + 1 < nc) {
-        bulk_g2s_chunked(row, g + ((int64_t)b * C + c_first + ci + 1) * Etot + (int64_t)q * E, (unsigned)E * 4u, &bar);
+        bulk_g2s_chunked(row, next, (unsigned)half * 4u, &bar[0]);
+        bulk_g2s_chunked(row + half, next + half, (unsigned)(E - half) * 4u, &bar[1]);
+        if (prefetch && ci + 2 < nc) bulk_prefetch_l2(next + Etot, (unsigned)E * 4u);  // lands while this row is copied and summed
       }
     }
+  }
   }
 }
 
@@ -841,23 +962,34 @@ seg_reduce_pieces_direct_kernel(int C, int N, int E, int Q, const float* __restr
 }
 
 static size_t planrow_smem(int N, int64_t E) {
-  return (size_t)E * 4 + (size_t)((E + 7) & ~7) * 2 + std::max((size_t)(N + 1) * 2, (size_t)kPrTaskCap * 6) + 16;
+  return (size_t)E * 4 + (size_t)((E + 7) & ~7) * 2 + std::max((size_t)(N + 1) * 2, std::max((size_t)kPrTaskCap * 6, (size_t)kPrSplitCap * 8)) + 16;
 }
 static int launch_planrow(int B, int C, int N, int E, int Q, const float* g, const int* row_ptr, const int* perm, float* dst,
                           cudaStream_t s, const char* what) {
   static DynSmem ds;
   if (int rc = ds.need(seg_reduce_planrow_kernel, 226 * 1024, what)) return rc;
-  // channels per CTA: amortise the per-CTA plan setup (~0.8 of a row) without leaving the last wave half empty
-  int cpc = 4;
-  double best = 0.0;
-  for (int k = 4; k <= 8; k++) {
-    const double ctas = (double)B * ((C + k - 1) / k);
-    const double waves = std::ceil(ctas / num_sms());
-    const double score = ctas / (waves * num_sms()) * k / (k + 0.8);
-    if (score > best) { best = score; cpc = k; }
+  // default: the next row prefetched into L2 when every SM has rows to pull (it costs a few per cent on a part-filled
+  // machine), the half-row pipeline only for plans in pieces (measured: +5 % there, -7 % on single-piece plans)
+  const int64_t rows = (int64_t)B * C;
+  const int variant = g_pr_variant >= 0 ? (g_pr_variant & 3) : ((rows >= 8 * (int64_t)num_sms() ? 2 : 0) | (Q > 1 ? 1 : 0));
+  if (g_pr_variant < 0 || !(g_pr_variant & 4)) {
+    // one CTA per SM (at least four rows each): the plan setup costs about two rows' worth of time
+    const int64_t items = (int64_t)B * C;
+    const int grid = (int)std::min<int64_t>(num_sms(), (items + 3) / 4);
+    seg_reduce_planrow_kernel<<<grid, 1024, planrow_smem(N, E), s>>>(B, C, N, E, Q, 0, variant, g, row_ptr, perm, dst);
+  } else {
+    // A/B: a grid of (channel group, cloud) CTAs, channels per CTA chosen against the last wave's fill
+    int cpc = 4;
+    double best = 0.0;
+    for (int k = 4; k <= 8; k++) {
+      const double ctas = (double)B * ((C + k - 1) / k);
+      const double waves = std::ceil(ctas / num_sms());
+      const double score = ctas / (waves * num_sms()) * k / (k + 0.8);
+      if (score > best) { best = score; cpc = k; }
+    }
+    dim3 grid((C + cpc - 1) / cpc, B);
+    seg_reduce_planrow_kernel<<<grid, 1024, planrow_smem(N, E), s>>>(B, C, N, E, Q, cpc, variant, g, row_ptr, perm, dst);
   }
-  dim3 grid((C + cpc - 1) / cpc, B);
-  seg_reduce_planrow_kernel<<<grid, 1024, planrow_smem(N, E), s>>>(C, N, E, Q, cpc, g, row_ptr, perm, dst);
   count_launch(1);
   return check_launch(what);
 }
@@ -1266,7 +1398,7 @@ GEOT_API int geot_gather_rows(int B, int N, int M, int D, const float* src, cons
 
 /* testing / A-B timing: direct != 0 disables the row-staged forward kernel (process-wide). */
 GEOT_API void geot_group_points_config(int mode) {
-  g_group_force_direct = mode == 1; g_force_staged = mode == 2; g_rows4_off = mode == 3; g_tip_off = mode == 4; g_mtile_off = mode == 6; g_mtile_on = mode == 7; g_tib_stream = mode == 8 ? 1 : (mode == 5 ? -1 : 0);
+  g_group_force_direct = mode == 1; g_force_staged = mode == 2; g_rows4_off = mode == 3; g_tip_off = mode == 4; g_mtile_off = mode == 6; g_mtile_on = mode == 7; g_pr_variant = mode == 9 ? 4 : (mode == 10 ? 3 : (mode == 11 ? 1 : (mode == 12 ? 6 : (mode == 13 ? 2 : -1)))); g_tib_stream = mode == 8 ? 1 : (mode == 5 ? -1 : 0);
 }
 
 GEOT_API int geot_gather_points(int B, int C, int N, int M, const float* points, const int* idx,

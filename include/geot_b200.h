@@ -161,7 +161,9 @@ int geot_group_xyz_relative(int B, int N, int M, int nsample, const float* xyz, 
  * results are identical): mode 1 = always the direct kernels (L2 gathers,
  * brute-force three_nn, warp-per-point transition_apply, ...), mode 2 = the staged / grid kernels wherever their hard
  * limits allow, ignoring the work-size heuristics, mode 3 = three_interpolate forward without its channel-interleaved
- * kernel (the plain row-staged one instead), mode 0 = default dispatch. */
+ * kernel (the plain row-staged one instead), mode 0 = default dispatch.  Modes 4-9 switch single kernel variants off or
+ * on for A/B runs (4 three_interpolate without the persistent kernel, 5 / 8 its backward never / always streamed,
+ * 6 / 7 manifold loss on the warp / tile kernels, 9 grouping backward waiting for whole gradient rows). */
 void geot_group_points_config(int mode);
 /* replaces pointnet2_batch_cuda.gather_points_wrapper(B,C,N,M,points,idx,out) (sampling_gpu.cu:15-31)
  * and pointnet2._ext.gather_points.  points (B,C,N), idx (B,M) -> out (B,C,M). */

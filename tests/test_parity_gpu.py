@@ -87,23 +87,33 @@ def test_group_points_row_staged_vs_direct(cuda, oracle):
 
 
 def test_group_points_grad_plan_resident_vs_direct(cuda, oracle):
-    """E <= 65535 takes the plan-resident backward (16-bit plan + gradient row in shared memory); the direct kernel
-    sums in the same plan order, so the two must agree bit for bit; both match the oracle's double sum to 1e-5."""
+    """E <= 65535 takes the plan-resident backward (16-bit plan + gradient row in shared memory; one CTA per SM over an
+    equal share of the (cloud, channel) rows, the next row prefetched into L2, for plans in pieces the row summed in two
+    halves as they land); modes 9-13 select the variants one by one (9 = the round-2 kernel: a grid of CTAs, whole rows,
+    no prefetch), mode 1 the direct kernel.  All sum in the same plan order, so they must agree bit for bit; they match
+    the oracle's double sum to 1e-5.
+    Random lists (dense targets: the general path), ball-query lists (few non-empty targets: the compact task list) and
+    a row length that is not a multiple of 8 (the halves differ in length)."""
     rng = np.random.default_rng(4)
-    for (B, C, N, M, ns) in [(2, 6, 4096, 512, 32), (1, 5, 16384, 1024, 32), (2, 3, 1000, 250, 16)]:
-        idx = rng.integers(0, N, (B, M, ns)).astype(np.int32)
-        idx[:, : M // 8] = idx[:, : M // 8, :1]  # padded rows: long segments for a few targets
+    for (B, C, N, M, ns, ball) in [(2, 6, 4096, 512, 32, 0), (1, 5, 16384, 1024, 32, 0), (2, 3, 1000, 250, 16, 0), (2, 3, 1000, 251, 12, 0),
+                                   (2, 9, 16384, 1024, 32, 0.1), (3, 4, 4096, 509, 20, 0.3)]:
+        if ball:
+            xyz = clouds("tooth", B, N)
+            idx = F.ball_query(cu(xyz[:, rng.choice(N, M, replace=False)].copy()), cu(xyz), ball, ns).cpu().numpy()
+        else:
+            idx = rng.integers(0, N, (B, M, ns)).astype(np.int32)
+            idx[:, : M // 8] = idx[:, : M // 8, :1]  # padded rows: long segments for a few targets
         g = rng.standard_normal((B, C, M, ns)).astype(np.float32)
         exp = oracle.grouping_operation_grad(g, idx, N)
         plan = F.ScatterPlan(cu(idx), B, N)
         res = []
         try:
-            for direct in (0, 1):
-                _lib.lib().geot_group_points_config(direct)
+            for mode in (0, 9, 10, 11, 12, 13, 1):
+                _lib.lib().geot_group_points_config(mode)
                 res.append(F.group_points_grad(cu(g), plan, N))
         finally:
             _lib.lib().geot_group_points_config(0)
-        assert torch.equal(res[0], res[1])
+        assert all(torch.equal(r, res[-1]) for r in res[:-1]), (B, C, N, M, ns, ball)
         assert_sum_close(res[0], exp, oracle.grouping_operation_grad(np.abs(g), idx, N), what="group_points_grad")
 
 
