@@ -69,12 +69,30 @@ for (B, N, M, ns, Cc, r) in [(64, 16384, 1024, 32, 64, 0.1), (16, 16384, 4096, 3
     report("gather_operation fwd", tag + " (C=3; 5 us kernels, host call overhead decides)", lambda: F.gather_points(xyz_t, idx, out=cen_t),
            (lambda: R.ref_gather_points(B, 3, N, M, p(xyz_t), p(idx), p(cen_r))) if R else None,
            B * (4 * M + 2 * 12 * M), lambda: (cen_t == cen_r).all())
-    if R:  # the same two kernels, each behind a bare ctypes call (pointers wrapped per call on both sides): what a C/C++ host sees
-        Lg, sp = _lib.lib().geot_gather_points, _lib.stream_ptr
+    if R:  # the same two kernels, each behind a bare ctypes call (pointers wrapped per call on both sides, the stream handle
+        # held by the caller as a C/C++ host holds its cudaStream_t): what a C/C++ host sees
+        Lg, s0 = _lib.lib().geot_gather_points, _lib.stream_ptr()
         report("gather_operation fwd", tag + " (C=3; bare C-ABI call on both sides)",
-               lambda: Lg(B, 3, N, M, xyz_t.data_ptr(), idx.data_ptr(), cen_t.data_ptr(), sp()),
+               lambda: Lg(B, 3, N, M, xyz_t.data_ptr(), idx.data_ptr(), cen_t.data_ptr(), s0),
                lambda: R.ref_gather_points(B, 3, N, M, p(xyz_t), p(idx), p(cen_r)),
                B * (4 * M + 2 * 12 * M), lambda: (cen_t == cen_r).all())
+    # the kernel alone: 200 launches replayed from one CUDA graph, no host between them (the reference launcher uses the
+    # legacy default stream and cannot be captured; tools/gather_ab.py: its one-element-per-thread mapping in our
+    # kernel gives the same 2.3-2.4 us)
+    side = torch.cuda.Stream()
+    with torch.cuda.stream(side):
+        F.gather_points(xyz_t, idx, out=cen_t)
+        cg = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(cg, stream=side):
+            for _ in range(200): F.gather_points(xyz_t, idx, out=cen_t)
+        cg.replay(); torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(side); cg.replay(); e1.record(side); torch.cuda.synchronize()
+    tk = e0.elapsed_time(e1) / 200
+    nb = B * (4 * M + 2 * 12 * M)
+    rows.append({"op": "gather_operation fwd", "shape": tag + " (C=3; kernel alone, CUDA-graph replay of 200 launches)", "ours_ms": tk, "ref_ms": None,
+                 "speedup": None, "algo_bytes": nb, "gbs": nb / tk / 1e6, "hbm_frac": nb / tk / 1e6 / PEAK, "match_ref": None})
+    print(f"gather_operation fwd         {tag} (C=3; kernel alone, graph replay)  ours {tk:8.4f} ms", flush=True)
     fg = torch.empty((B, Cc, M), device=dev); fg_r = torch.empty_like(fg)
     report("gather_operation fwd", tag + f" (C={Cc})", lambda: F.gather_points(feat, idx, out=fg),
            (lambda: R.ref_gather_points(B, Cc, N, M, p(feat), p(idx), p(fg_r))) if R else None,
