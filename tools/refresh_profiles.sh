@@ -16,16 +16,21 @@ python tools/ti_ab.py > gpurun_out/${tag}_ti_ab.jsonl 2>&1
 python tools/bq_ab.py > gpurun_out/${tag}_bq_ab.log 2>&1
 python tools/plan_ab.py > gpurun_out/${tag}_plan_ab.log 2>&1
 python tools/manifold_parts.py > gpurun_out/${tag}_manifold_parts.log 2>&1
+python tools/groupbwd_ab.py > gpurun_out/${tag}_groupbwd_ab.log 2>&1
+python tools/tibwd_ab.py > gpurun_out/${tag}_tibwd_ab.log 2>&1
 [ -n "$NO_NCU" ] && { ls -la gpurun_out/ | tail -30; exit 0; }   # NO_NCU=1: the measurements only, no ncu captures
 B="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-extras"
 $B > gpurun_out/${tag}_launches_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${tag}_launches_bench.csv \
     $B > gpurun_out/${tag}_launches.log 2>&1
-for k in "fps fps_mgr" "ball bq_build" "ball bq_grid" "group group_rows" "groupbwd seg_reduce_planrow" "plan plan_build_fused" \
-         "threenn three_nn_grid" "tibwd seg_reduce_wrows" "knn knn_grid" "knntie knn_heap_warp" \
-         "sigt sigt_kernel" "apply transition_apply_tile" "manifold manifold_fwd_tile" "manifold manifold_bwd_tile" \
-         "manifold spatial_order_fine" "ti three_interpolate_persist" "gf graph_feature_kernel" "groupxyz group_xyz_rel"; do
+ALL=("fps fps_mgr" "ball bq_build" "ball bq_grid" "group group_rows" "groupbwd seg_reduce_planrow" "plan plan_build_fused" \
+     "threenn three_nn_grid" "tibwd ti_bwd_stream" "knn knn_grid" "knntie knn_heap_warp" \
+     "sigt sigt_kernel" "apply transition_apply_tile" "manifold manifold_fwd_tile" "manifold manifold_bwd_tile" \
+     "manifold spatial_order_fine" "ti three_interpolate_persist" "gf graph_feature_kernel" "groupxyz group_xyz_rel")
+# NCU_ONLY="seg_reduce_planrow ti_bwd_stream": capture only the kernels whose name contains one of these words
+for k in "${ALL[@]}"; do
   set -- $k
+  if [ -n "$NCU_ONLY" ]; then hit=; for w in $NCU_ONLY; do [[ "$2" == *$w* ]] && hit=1; done; [ -n "$hit" ] || continue; fi
   python tools/prof_one.py $1 > gpurun_out/${tag}_full_$2.plain.log 2>&1 &&
   ncu --set full --clock-control none --import-source on -k regex:$2 -c 1 -f -o gpurun_out/${tag}_full_$2 \
       python tools/prof_one.py $1 > gpurun_out/${tag}_full_$2.log 2>&1
