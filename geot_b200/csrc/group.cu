@@ -33,6 +33,7 @@ static thread_local bool g_tip_off = false;             // mode 4: three_interpo
 static thread_local bool g_mtile_off = false;           // mode 6: manifold loss on the warp-per-point kernels (A/B)
 static thread_local bool g_mtile_on = false;            // mode 7: manifold loss on the tile kernels whatever C (tests)
 static thread_local int g_pr_variant = -1;              // grouping backward: bit 0 half-row pipeline, bit 1 L2 prefetch of the next row, bit 2 grid of (channel group, cloud) CTAs instead of one CTA per SM; -1 = chosen per launch; modes 9 / 10 / 11 / 12 / 13 = 4 / 3 / 1 / 6 / 2 (A/B)
+static thread_local bool g_nn_queue_off = false;        // mode 14: three_nn grid kernel finishing every query in place (A/B)
 static thread_local int g_tib_stream = 0;               // mode 8: three_interpolate backward streamed whatever the launch size (tests); mode 5: never (A/B)
 
 // VEC = 4: E % 4 == 0 and 16-byte aligned idx/out.  grid (ceil(E/VEC/256), ceil(C/CCH), B).
@@ -1275,6 +1276,7 @@ static int three_interpolate_grad_rows(int B, int C, int n, int m, const float* 
 bool direct_kernels_forced() { return g_group_force_direct; }
 bool staged_kernels_forced() { return g_force_staged; }
 bool rows4_disabled() { return g_rows4_off; }
+bool three_nn_queue_off() { return g_nn_queue_off; }
 bool persistent_interp_disabled() { return g_tip_off || g_rows4_off; }
 bool manifold_tiles_disabled() { return g_mtile_off; }
 bool manifold_tiles_forced() { return g_mtile_on; }
@@ -1398,7 +1400,7 @@ GEOT_API int geot_gather_rows(int B, int N, int M, int D, const float* src, cons
 
 /* testing / A-B timing: direct != 0 disables the row-staged forward kernel (process-wide). */
 GEOT_API void geot_group_points_config(int mode) {
-  g_group_force_direct = mode == 1; g_force_staged = mode == 2; g_rows4_off = mode == 3; g_tip_off = mode == 4; g_mtile_off = mode == 6; g_mtile_on = mode == 7; g_pr_variant = mode == 9 ? 4 : (mode == 10 ? 3 : (mode == 11 ? 1 : (mode == 12 ? 6 : (mode == 13 ? 2 : -1)))); g_tib_stream = mode == 8 ? 1 : (mode == 5 ? -1 : 0);
+  g_group_force_direct = mode == 1; g_force_staged = mode == 2; g_rows4_off = mode == 3; g_tip_off = mode == 4; g_mtile_off = mode == 6; g_mtile_on = mode == 7; g_pr_variant = mode == 9 ? 4 : (mode == 10 ? 3 : (mode == 11 ? 1 : (mode == 12 ? 6 : (mode == 13 ? 2 : -1)))); g_tib_stream = mode == 8 ? 1 : (mode == 5 ? -1 : 0); g_nn_queue_off = mode == 14;
 }
 
 GEOT_API int geot_gather_points(int B, int C, int N, int M, const float* points, const int* idx,

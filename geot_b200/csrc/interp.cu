@@ -26,6 +26,7 @@ void count_launch(int n);
 bool direct_kernels_forced();  // geot_group_points_config(1) (group.cu)
 bool staged_kernels_forced();  // geot_group_points_config(2)
 bool rows4_disabled();         // geot_group_points_config(3)
+bool three_nn_queue_off();     // geot_group_points_config(14)
 bool persistent_interp_disabled();  // geot_group_points_config(4) (or 3)
 int three_interpolate_grad_impl(int B, int C, int n, int m, const float* grad_out, const float* weight,
                                 const void* plan, float* grad_points, cudaStream_t s);
@@ -116,6 +117,8 @@ constexpr int kNgMaxM = 9216;
 constexpr int kNgMaxDim = 64;      // cells per axis
 constexpr int kNgMaxCells = 8000;  // cells in total (one int table of this size lives in shared memory)
 constexpr int kNgThreads = 1024;
+constexpr size_t kNgSmemMax = 226 * 1024;  // dynamic shared memory the grid kernel may ask for
+constexpr int kNgWarpQueue = 64;           // slots of a warp's ring-2 queue
 
 __device__ __forceinline__ bool lex_lt(float d, int k, float D, int K) { return d < D || (d == D && k < K); }
 __device__ __forceinline__ void top3_push_lex(Top3& t, float d, int k) {
@@ -129,7 +132,7 @@ __device__ __forceinline__ void top3_push_lex(Top3& t, float d, int k) {
 __device__ __forceinline__ int ng_cell(float p, float lo, float inv) { return __float2int_rd((p - lo) * inv); }
 
 __global__ void __launch_bounds__(kNgThreads, 1)
-three_nn_grid_kernel(int n, int m, int m_total, int base, int accumulate, const float* __restrict__ unknown,
+three_nn_grid_kernel(int n, int m, int m_total, int base, int accumulate, int use_queue, const float* __restrict__ unknown,
                      const float* __restrict__ known, float* __restrict__ dist2, int* __restrict__ idx) {
   // m = points of THIS part of the known cloud (known[b, base : base + m]); m_total = the cloud's stride.  Known clouds
   // longer than kNgMaxM are searched part by part: a later part starts from the top-3 the earlier parts left in
@@ -142,6 +145,7 @@ three_nn_grid_kernel(int n, int m, int m_total, int base, int accumulate, const 
   float4* sorted = reinterpret_cast<float4*>(ng_smem);               // m entries
   int* cells = reinterpret_cast<int*>(ng_smem + (size_t)m * 16);     // kNgMaxCells + 1: histogram -> cursor
   unsigned* runs = reinterpret_cast<unsigned*>(cells + kNgMaxCells + 1);  // 9 x kNgThreads: {start:16 | length:16}
+  unsigned* queue = runs + 9 * kNgThreads;                            // per warp 7 x kNgWarpQueue: queries waiting for ring 2 {i, d1..d3, i1..i3}
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int b = blockIdx.y;
   const float* __restrict__ kn = known + ((int64_t)b * m_total + base) * 3;
@@ -258,94 +262,148 @@ three_nn_grid_kernel(int n, int m, int m_total, int base, int accumulate, const 
   }
   __syncthreads();
   // ---- one unknown point per thread ----
-  for (int i = blockIdx.x * kNgThreads + t; i < n; i += gridDim.x * kNgThreads) {
-  const float* up = unknown + ((int64_t)b * n + i) * 3;
-  const float qx = up[0], qy = up[1], qz = up[2];
-  Top3 first = Top3{kInf, kInf, kInf, 0, 0, 0};
-  if (accumulate) {
+  // The 3x3x3 block settles about 70 % of the queries on a surface cloud; the rest need the 5x5x5 shell, which costs
+  // three times the first ring.  Left in place, nearly every warp has such a lane and walks the shell at a third of
+  // its width.  So a query that is not settled after ring 1 parks its {index, top-3} in its WARP's shared-memory queue
+  // and whenever that holds 32 entries (and at the end) the warp finishes them, one per lane: no CTA barrier, warps keep
+  // running independently.  Long known clouds that leave no room for the queues finish every query in place.  A
+  // query's result does not depend on who finishes it or when.
+  auto load_first = [&](int i) -> Top3 {
+    if (!accumulate) return Top3{kInf, kInf, kInf, 0, 0, 0};
     const float* pd = dist2 + ((int64_t)b * n + i) * 3;
     const int* pi = idx + ((int64_t)b * n + i) * 3;
-    first = Top3{pd[0], pd[1], pd[2], pi[0], pi[1], pi[2]};
-  }
-  Top3 best = first;
-  auto visit = [&](int p) {
-    const float4 v = sorted[p];
-    top3_push_lex(best, dist2_ref(qx, qy, qz, v.x, v.y, v.z), __float_as_int(v.w));
+    return Top3{pd[0], pd[1], pd[2], pi[0], pi[1], pi[2]};
   };
-  bool done = false;
-  if (!flat) {
-    const int dx = dims[0], dy = dims[1], dz = dims[2];
-    const float ux = (qx - lo[0]) * inv, uy = (qy - lo[1]) * inv, uz = (qz - lo[2]) * inv;
-    const int cx = (int)fminf(fmaxf(floorf(ux), -4.f), (float)dx + 3.f);
-    const int cy = (int)fminf(fmaxf(floorf(uy), -4.f), (float)dy + 3.f);
-    const int cz = (int)fminf(fmaxf(floorf(uz), -4.f), (float)dz + 3.f);
-    // squared distance below which no point outside the (2R+1)^3 block can lie (cell units, margin for the
-    // fp32 binning arithmetic; faces at the grid boundary have nothing behind them)
-    auto safe_d2 = [&](int R) -> float {
-      float rho = kInf;
-      if (cx - R > 0) rho = fminf(rho, ux - (float)(cx - R));
-      if (cx + R + 1 < dx) rho = fminf(rho, (float)(cx + R + 1) - ux);
-      if (cy - R > 0) rho = fminf(rho, uy - (float)(cy - R));
-      if (cy + R + 1 < dy) rho = fminf(rho, (float)(cy + R + 1) - uy);
-      if (cz - R > 0) rho = fminf(rho, uz - (float)(cz - R));
-      if (cz + R + 1 < dz) rho = fminf(rho, (float)(cz + R + 1) - uz);
-      rho = fmaxf(rho - 2e-4f * (1.f + fabsf(ux) + fabsf(uy) + fabsf(uz)) * 0.03125f - 2e-4f, 0.f) * cell;
-      return rho * rho * 0.9999f;
+  auto write_out = [&](int i, const Top3& best) {
+    float* od = dist2 + ((int64_t)b * n + i) * 3;
+    int* oi = idx + ((int64_t)b * n + i) * 3;
+    od[0] = best.d1; od[1] = best.d2; od[2] = best.d3;
+    oi[0] = best.i1; oi[1] = best.i2; oi[2] = best.i3;
+  };
+  // phase 0: ring 1 from `best` (false = not settled yet; degenerate grids scan everything and are settled);
+  // phase 1: ring 2 from the state ring 1 left, then the whole cloud if that does not settle it either
+  auto search = [&](int i, int phase, Top3& best) -> bool {
+    const float* up = unknown + ((int64_t)b * n + i) * 3;
+    const float qx = up[0], qy = up[1], qz = up[2];
+    auto visit = [&](int p) {
+      const float4 v = sorted[p];
+      top3_push_lex(best, dist2_ref(qx, qy, qz, v.x, v.y, v.z), __float_as_int(v.w));
     };
-    auto run_of = [&](int xa, int xb, int y, int z, int& p, int& e) {
-      p = 0; e = 0;
-      if (y < 0 || y >= dy || z < 0 || z >= dz) return;
-      xa = max(xa, 0); xb = min(xb, dx - 1);
-      if (xa > xb) return;
-      const int row = (z * dy + y) * dx;
-      p = (row + xa) ? cells[row + xa - 1] : 0; e = cells[row + xb];
-    };
-    {  // ring 1: the non-empty x-runs of the 3x3 rows go to a per-thread list in shared memory (converged code),
-       // then they are walked as ONE flat candidate sequence: a warp's cost is its longest list, not the sum
-       // over rows of the longest run
-      int nr = 0;
+    bool done = false;
+    if (!flat) {
+      const int dx = dims[0], dy = dims[1], dz = dims[2];
+      const float ux = (qx - lo[0]) * inv, uy = (qy - lo[1]) * inv, uz = (qz - lo[2]) * inv;
+      const int cx = (int)fminf(fmaxf(floorf(ux), -4.f), (float)dx + 3.f);
+      const int cy = (int)fminf(fmaxf(floorf(uy), -4.f), (float)dy + 3.f);
+      const int cz = (int)fminf(fmaxf(floorf(uz), -4.f), (float)dz + 3.f);
+      // squared distance below which no point outside the (2R+1)^3 block can lie (cell units, margin for the
+      // fp32 binning arithmetic; faces at the grid boundary have nothing behind them)
+      auto safe_d2 = [&](int R) -> float {
+        float rho = kInf;
+        if (cx - R > 0) rho = fminf(rho, ux - (float)(cx - R));
+        if (cx + R + 1 < dx) rho = fminf(rho, (float)(cx + R + 1) - ux);
+        if (cy - R > 0) rho = fminf(rho, uy - (float)(cy - R));
+        if (cy + R + 1 < dy) rho = fminf(rho, (float)(cy + R + 1) - uy);
+        if (cz - R > 0) rho = fminf(rho, uz - (float)(cz - R));
+        if (cz + R + 1 < dz) rho = fminf(rho, (float)(cz + R + 1) - uz);
+        rho = fmaxf(rho - 2e-4f * (1.f + fabsf(ux) + fabsf(uy) + fabsf(uz)) * 0.03125f - 2e-4f, 0.f) * cell;
+        return rho * rho * 0.9999f;
+      };
+      auto run_of = [&](int xa, int xb, int y, int z, int& p, int& e) {
+        p = 0; e = 0;
+        if (y < 0 || y >= dy || z < 0 || z >= dz) return;
+        xa = max(xa, 0); xb = min(xb, dx - 1);
+        if (xa > xb) return;
+        const int row = (z * dy + y) * dx;
+        p = (row + xa) ? cells[row + xa - 1] : 0; e = cells[row + xb];
+      };
+      if (phase == 0) {
+        // ring 1: the non-empty x-runs of the 3x3 rows go to a per-thread list in shared memory (converged code),
+        // then they are walked as ONE flat candidate sequence: a warp's cost is its longest list, not the sum
+        // over rows of the longest run
+        int nr = 0;
 #pragma unroll
-      for (int r = 0; r < 9; r++) {
-        int p, e;
-        run_of(cx - 1, cx + 1, cy + r % 3 - 1, cz + r / 3 - 1, p, e);
-        if (e > p) { runs[nr * kNgThreads + t] = ((unsigned)p << 16) | (unsigned)(e - p); nr++; }
-      }
-      int r = 0, p = 0, e = 0;
-      for (;;) {
-        if (p >= e) {
-          if (r >= nr) break;
-          const unsigned u = runs[r * kNgThreads + t];
-          r++;
-          p = (int)(u >> 16); e = p + (int)(u & 0xffffu);
+        for (int r = 0; r < 9; r++) {
+          int p, e;
+          run_of(cx - 1, cx + 1, cy + r % 3 - 1, cz + r / 3 - 1, p, e);
+          if (e > p) { runs[nr * kNgThreads + t] = ((unsigned)p << 16) | (unsigned)(e - p); nr++; }
         }
-        visit(p++);
+        int r = 0, p = 0, e = 0;
+        for (;;) {
+          if (p >= e) {
+            if (r >= nr) break;
+            const unsigned u = runs[r * kNgThreads + t];
+            r++;
+            p = (int)(u >> 16); e = p + (int)(u & 0xffffu);
+          }
+          visit(p++);
+        }
+        return best.d3 < safe_d2(1);
       }
-      done = best.d3 < safe_d2(1);
-    }
-    if (!done) {  // ring 2: border rows are full runs, interior rows contribute their two end cells
-      int r = 0, p = 0, e = 0;
-      for (;;) {
-        if (p < e) { visit(p++); continue; }
-        if (r == 50) break;
-        const int row = r >> 1, half = r & 1;
-        const int oy = row % 5 - 2, oz = row / 5 - 2;
-        const bool border = oy == -2 || oy == 2 || oz == -2 || oz == 2;
-        if (border) { if (half == 0) run_of(cx - 2, cx + 2, cy + oy, cz + oz, p, e); }
-        else run_of(half ? cx + 2 : cx - 2, half ? cx + 2 : cx - 2, cy + oy, cz + oz, p, e);
-        r++;
+      {  // ring 2: border rows are full runs, interior rows contribute their two end cells
+        int r = 0, p = 0, e = 0;
+        for (;;) {
+          if (p < e) { visit(p++); continue; }
+          if (r == 50) break;
+          const int row = r >> 1, half = r & 1;
+          const int oy = row % 5 - 2, oz = row / 5 - 2;
+          const bool border = oy == -2 || oy == 2 || oz == -2 || oz == 2;
+          if (border) { if (half == 0) run_of(cx - 2, cx + 2, cy + oy, cz + oz, p, e); }
+          else run_of(half ? cx + 2 : cx - 2, half ? cx + 2 : cx - 2, cy + oy, cz + oz, p, e);
+          r++;
+        }
+        done = best.d3 < safe_d2(2);
       }
-      done = best.d3 < safe_d2(2);
+    }
+    if (!done) {  // far from the known cloud / degenerate grid: every known point
+      best = load_first(i);
+      for (int p = 0; p < m; p++) visit(p);
+    }
+    return true;
+  };
+  const int stride = gridDim.x * kNgThreads;
+  const int iters = (n + stride - 1) / stride;  // the same for every lane of a warp: the loop holds warp-wide votes
+  unsigned* wq = queue + (size_t)warp * 7 * kNgWarpQueue;  // this warp's queue, one array of kNgWarpQueue slots per field
+  int wqn = 0;                                             // entries in it (warp-uniform)
+  auto finish32 = [&](int first_slot, int count) {  // lanes 0..count-1 finish one queued query each
+    if (lane < count) {
+      const int e = first_slot + lane;
+      const int qi = (int)wq[e];
+      Top3 best = Top3{__uint_as_float(wq[kNgWarpQueue + e]), __uint_as_float(wq[2 * kNgWarpQueue + e]), __uint_as_float(wq[3 * kNgWarpQueue + e]),
+                       (int)wq[4 * kNgWarpQueue + e], (int)wq[5 * kNgWarpQueue + e], (int)wq[6 * kNgWarpQueue + e]};
+      search(qi, 1, best);
+      write_out(qi, best);
+    }
+  };
+#pragma unroll 1
+  for (int it = 0; it < iters; it++) {
+    const int i = it * stride + blockIdx.x * kNgThreads + t;
+    bool parked = false;
+    Top3 best = Top3{kInf, kInf, kInf, 0, 0, 0};
+    if (i < n) {
+      best = load_first(i);
+      if (search(i, 0, best)) write_out(i, best);
+      else if (use_queue) parked = true;
+      else { search(i, 1, best); write_out(i, best); }
+    }
+    if (use_queue) {
+      const unsigned mask = __ballot_sync(0xffffffffu, parked);
+      if (parked) {
+        const int e = wqn + __popc(mask & ((1u << lane) - 1u));
+        wq[e] = (unsigned)i;
+        wq[kNgWarpQueue + e] = __float_as_uint(best.d1); wq[2 * kNgWarpQueue + e] = __float_as_uint(best.d2); wq[3 * kNgWarpQueue + e] = __float_as_uint(best.d3);
+        wq[4 * kNgWarpQueue + e] = (unsigned)best.i1; wq[5 * kNgWarpQueue + e] = (unsigned)best.i2; wq[6 * kNgWarpQueue + e] = (unsigned)best.i3;
+      }
+      wqn += __popc(mask);
+      __syncwarp();
+      if (wqn >= 32) {  // a full warp's worth: take the newest 32 (at most 31 stay behind, so 64 slots always suffice)
+        wqn -= 32;
+        finish32(wqn, 32);
+        __syncwarp();
+      }
     }
   }
-  if (!done) {  // far from the known cloud / degenerate grid: every known point
-    best = first;
-    for (int p = 0; p < m; p++) visit(p);
-  }
-  float* od = dist2 + ((int64_t)b * n + i) * 3;
-  int* oi = idx + ((int64_t)b * n + i) * 3;
-  od[0] = best.d1; od[1] = best.d2; od[2] = best.d3;
-  oi[0] = best.i1; oi[1] = best.i2; oi[2] = best.i3;
-  }
+  if (use_queue && wqn > 0) finish32(0, wqn);
 }
 
 constexpr int kTiCCH = 16;
@@ -621,7 +679,7 @@ GEOT_API int geot_three_nn(int B, int n, int m, const float* unknown, const floa
   if (m >= 64 && P <= 8 && ((double)B * n * m >= 5e7 || staged_kernels_forced()) && !direct_kernels_forced()) {
     const int part = (m + P - 1) / P;
     static DynSmem ds;
-    if (int rc = ds.need(three_nn_grid_kernel, kNgMaxM * 16 + (kNgMaxCells + 1) * 4 + 9 * kNgThreads * 4, "three_nn")) return rc;
+    if (int rc = ds.need(three_nn_grid_kernel, kNgSmemMax, "three_nn")) return rc;
     // CTAs per cloud: every CTA re-bins the known cloud (~4x the cost of one 1024-query sweep), so prefer few
     // CTAs with several sweeps each, in whole waves of the 148 SMs
     const int max_cb = (n + kNgThreads - 1) / kNgThreads;
@@ -636,8 +694,12 @@ GEOT_API int geot_three_nn(int B, int n, int m, const float* unknown, const floa
     for (int p = 0; p < P; p++) {
       const int base = p * part, mp = std::min(part, m - base);
       if (mp <= 0) break;
-      const size_t smem = (size_t)mp * 16 + (size_t)(kNgMaxCells + 1) * 4 + (size_t)9 * kNgThreads * 4;
-      three_nn_grid_kernel<<<gg, kNgThreads, smem, as_stream(stream)>>>(n, mp, m, base, p > 0, unknown, known, dist2, idx);
+      const size_t fixed = (size_t)mp * 16 + (size_t)(kNgMaxCells + 1) * 4 + (size_t)9 * kNgThreads * 4;
+      // the warps' queues of queries waiting for ring 2, when shared memory has room for them next to the known cloud
+      const size_t qbytes = (size_t)(kNgThreads / 32) * 7 * kNgWarpQueue * 4;
+      const int use_queue = !three_nn_queue_off() && fixed + qbytes <= kNgSmemMax;
+      const size_t smem = fixed + (use_queue ? qbytes : 0);
+      three_nn_grid_kernel<<<gg, kNgThreads, smem, as_stream(stream)>>>(n, mp, m, base, p > 0, use_queue, unknown, known, dist2, idx);
       count_launch(1);
       const int rc = check_launch("three_nn_grid_kernel");
       if (rc) return rc;
