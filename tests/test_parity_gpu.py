@@ -96,7 +96,8 @@ def test_group_points_grad_plan_resident_vs_direct(cuda, oracle):
     a row length that is not a multiple of 8 (the halves differ in length)."""
     rng = np.random.default_rng(4)
     for (B, C, N, M, ns, ball) in [(2, 6, 4096, 512, 32, 0), (1, 5, 16384, 1024, 32, 0), (2, 3, 1000, 250, 16, 0), (2, 3, 1000, 251, 12, 0),
-                                   (2, 9, 16384, 1024, 32, 0.1), (3, 4, 4096, 509, 20, 0.3)]:
+                                   (2, 9, 16384, 1024, 32, 0.1), (3, 4, 4096, 509, 20, 0.3),
+                                   (2, 3, 20000, 700, 32, 0), (2, 5, 20000, 700, 32, 0.1), (1, 1, 64, 16, 4, 0)]:  # > 16 targets per thread; one row
         if ball:
             xyz = clouds("tooth", B, N)
             idx = F.ball_query(cu(xyz[:, rng.choice(N, M, replace=False)].copy()), cu(xyz), ball, ns).cpu().numpy()
