@@ -26,6 +26,8 @@ rows = []
 shapes = [(64, 16384, 1024), (8, 16384, 1024), (16, 16384, 4096), (6, 16000, 8192), (16, 4096, 1024), (64, 4096, 1024), (64, 1024, 256), (256, 16384, 1024)]
 if len(sys.argv) > 1 and sys.argv[1] == "quick":
     shapes = shapes[:4]
+if len(sys.argv) > 1 and sys.argv[1] == "small":
+    shapes = [(64, 4096, 1024), (64, 3072, 768), (64, 2048, 512), (64, 1536, 384), (64, 1024, 256), (16, 1024, 256), (64, 512, 128), (64, 256, 64), (64, 128, 32), (64, 64, 16)]
 for (B, N, M) in shapes:
     xyz = torch.from_numpy(synth.tooth_batch(B, N)).cuda()
     variants = {"mgr": 0, "spec": _lib.GEOT_FPS_SPEC, "brute": _lib.GEOT_FPS_NO_PRUNE}
