@@ -34,6 +34,7 @@ static thread_local bool g_mtile_off = false;           // mode 6: manifold loss
 static thread_local bool g_mtile_on = false;            // mode 7: manifold loss on the tile kernels whatever C (tests)
 static thread_local int g_pr_variant = -1;              // grouping backward: bit 0 half-row pipeline, bit 1 L2 prefetch of the next row, bit 2 grid of (channel group, cloud) CTAs instead of one CTA per SM; -1 = chosen per launch; modes 9 / 10 / 11 / 12 / 13 = 4 / 3 / 1 / 6 / 2 (A/B)
 static thread_local bool g_nn_queue_off = false;        // mode 14: three_nn grid kernel finishing every query in place (A/B)
+static thread_local bool g_plan_ordered_off = false;    // mode 15: scatter plan without the ordered builder (A/B)
 static thread_local int g_tib_stream = 0;               // mode 8: three_interpolate backward streamed whatever the launch size (tests); mode 5: never (A/B)
 
 // VEC = 4: E % 4 == 0 and 16-byte aligned idx/out.  grid (ceil(E/VEC/256), ceil(C/CCH), B).
@@ -442,6 +443,182 @@ __device__ __forceinline__ void plan_thread_sort16(T* __restrict__ seg, int L) {
 #pragma unroll
   for (int i = 0; i < 16; i++)
     if (i < L) seg[i] = (T)v[i];
+}
+
+// Chunked builder for FEW targets with LONG source lists (three_interpolate's plan: 1024 coarse points, 48 sources
+// each).  The fused builder below fills every segment through an atomic cursor and sorts it afterwards - one warp per
+// segment, rank sort over shuffles, cost ~ L * ceil(L/32) - which is most of its 0.088 ms at the bench shape.  Here one
+// CTA per cloud cuts the E sources into 32 contiguous chunks, one per warp, and keeps a 16-bit counter per
+// (chunk, target) in shared memory (64 bytes per target), i.e. it counting-sorts by (target, chunk):
+//   1. warp w counts its chunk (shared-memory atomics on packed 16-bit pairs);
+//   2. a thread per target turns the 32 counts of its column into cursors inside the target's segment and the segment
+//      lengths into row_ptr (block scan);
+//   3. warp w fills its chunk's sources through the (w, t) cursors: the pieces of a segment are in chunk order, only
+//      the 1-2 sources inside one piece (48 / 32 on average) are in arbitrary order;
+//   4. a thread per target puts every piece in ascending order (insertion sort, pieces of 0-3 entries) - the segment
+//      is then ascending as a whole: the order the multi-kernel and the fused builder produce, bit for bit;
+//   5. the 16-bit list leaves by one coalesced pass.
+// (A first version ranked equal targets inside a warp with match.any instead of atomics + step 4: correct, but
+// match.any costs ~0.5 us per call with ~20 distinct values in the warp - 0.117 ms, slower than the fused builder.)
+constexpr int kOrdMaxN = 2048;
+constexpr size_t kOrdBudget = (size_t)220 * 1024;
+constexpr int kOrdThreadSort = 16;    // longest (chunk, target) piece a single thread sorts
+constexpr int kOrdBitmapWords = 66;   // a chunk has at most ceil(ceil(65535 / 32) / 32) * 32 = 2048 + 32 positions
+constexpr int kOrdHeavyCap = 4096;    // list of longer pieces (E / (kOrdThreadSort + 1) <= 3855 of them can exist)
+static size_t plan_ordered_smem(int N, int64_t E) {
+  return (size_t)32 * ((N + 1) & ~1) * 2 + (size_t)(N + 1) * 4 + (size_t)((E + 1) / 2) * 4 + (size_t)32 * kOrdBitmapWords * 4 +
+         (size_t)kOrdHeavyCap * 4;
+}
+__global__ void __launch_bounds__(1024, 1)
+plan_build_ordered_kernel(int N, int E, const int* __restrict__ idx_all, int* __restrict__ row_ptr_all, int* __restrict__ perm_all) {
+  extern __shared__ __align__(16) unsigned char po_smem[];
+  __shared__ int s_scan[32];
+  __shared__ int s_heavy;
+  constexpr int heavy_cap = kOrdHeavyCap;
+  const int Np = (N + 1) & ~1;  // counters per chunk row (even: a row is whole 32-bit words)
+  unsigned short* cnt = reinterpret_cast<unsigned short*>(po_smem);               // [32][Np]
+  int* rp = reinterpret_cast<int*>(po_smem + (size_t)32 * Np * 2);                // N + 1
+  unsigned short* perm16 = reinterpret_cast<unsigned short*>(rp + N + 1);         // E
+  unsigned* bitmap = reinterpret_cast<unsigned*>(perm16 + (((size_t)E + 1) & ~(size_t)1));  // 32 x kOrdBitmapWords
+  unsigned* heavy = bitmap + 32 * kOrdBitmapWords;                                // kOrdHeavyCap {chunk:16 | target:16}
+  const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+  const int b = blockIdx.x;
+  const int* __restrict__ idx = idx_all + (int64_t)b * E;
+  const int groups = (E + 31) >> 5, gpw = (groups + 31) >> 5;
+  const int p0 = min(w * gpw * 32, E), p1 = min((w + 1) * gpw * 32, E);  // this warp's chunk of sources
+  unsigned* my = reinterpret_cast<unsigned*>(cnt + (size_t)w * Np);
+  for (int i = t; i < 16 * Np; i += 1024) reinterpret_cast<unsigned*>(cnt)[i] = 0u;
+  __syncthreads();
+  // ---- 1. counts per (chunk, target); an index outside [0, N) is not a target and is left out (the other builders
+  //         require valid indices too)
+#pragma unroll 4
+  for (int p = p0 + lane; p < p1; p += 32) {
+    const int tg = __ldg(idx + p);
+    if ((unsigned)tg < (unsigned)N) atomicAdd(&my[tg >> 1], 1u << ((tg & 1) << 4));
+  }
+  __syncthreads();
+  // ---- 2. column sums -> cursors inside the segment; segment lengths -> row_ptr
+  {
+    const int PER = (N + 1023) >> 10;  // consecutive targets per thread (<= 2)
+    int len[2] = {0, 0}, sum = 0;
+    for (int k = 0; k < PER; k++) {
+      const int tt = t * PER + k;
+      if (tt < N) {
+        int run = 0;
+#pragma unroll 8
+        for (int ww = 0; ww < 32; ww++) {
+          const int c = cnt[(size_t)ww * Np + tt];
+          cnt[(size_t)ww * Np + tt] = (unsigned short)run;
+          run += c;
+        }
+        len[k] = run;
+        sum += run;
+      }
+    }
+    int inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += y;
+    }
+    if (lane == 31) s_scan[w] = inc;
+    __syncthreads();
+    int wtot = s_scan[lane], winc = wtot;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, winc, o);
+      if (lane >= o) winc += y;
+    }
+    int run = __shfl_sync(0xffffffffu, winc - wtot, w) + inc - sum;
+    for (int k = 0; k < PER; k++) {
+      const int tt = t * PER + k;
+      if (tt < N) { rp[tt] = run; run += len[k]; }
+    }
+    if (t == 1023) rp[N] = run;  // = E when every index is a valid target
+  }
+  __syncthreads();
+  int* __restrict__ row_ptr = row_ptr_all + (int64_t)b * (N + 1);
+  for (int i = t; i <= N; i += 1024) row_ptr[i] = rp[i];
+  // ---- 3. fill through the (chunk, target) cursors
+#pragma unroll 4
+  for (int p = p0 + lane; p < p1; p += 32) {
+    const int tg = __ldg(idx + p);
+    if ((unsigned)tg < (unsigned)N) {
+      const int sh = (tg & 1) << 4;
+      const unsigned old = atomicAdd(&my[tg >> 1], 1u << sh);
+      perm16[rp[tg] + (int)((old >> sh) & 0xffffu)] = (unsigned short)p;
+    }
+  }
+  __syncthreads();
+  // ---- 4. every (chunk, target) piece in ascending order: the cursor of chunk w now stands at the start of chunk w+1.
+  //         Pieces of up to kOrdThreadSort entries by the target's thread (insertion sort); longer ones (many sources of
+  //         one chunk on one target: not a three_nn list, but it must not take seconds) go to a list and are sorted by
+  //         a warp each through a bitmap over the chunk's positions: cost ~ piece length + chunk length / 32.
+  if (t == 0) s_heavy = 0;
+  __syncthreads();
+  for (int tt = t; tt < N; tt += 1024) {
+    unsigned short* seg = perm16 + rp[tt];
+    int s0 = 0;
+    for (int ww = 0; ww < 32; ww++) {
+      const int e0 = cnt[(size_t)ww * Np + tt];
+      if (e0 - s0 > kOrdThreadSort) {
+        const int slot = atomicAdd(&s_heavy, 1);
+        if (slot < heavy_cap) { heavy[slot] = ((unsigned)ww << 16) | (unsigned)tt; s0 = e0; continue; }
+      }
+      for (int i = s0 + 1; i < e0; i++) {
+        const unsigned short v = seg[i];
+        int j = i;
+        while (j > s0 && seg[j - 1] > v) { seg[j] = seg[j - 1]; j--; }
+        seg[j] = v;
+      }
+      s0 = e0;
+    }
+  }
+  __syncthreads();
+  {
+    const int nh = min(s_heavy, heavy_cap);
+    unsigned* bm = bitmap + w * kOrdBitmapWords;  // this warp's bitmap over one chunk (gpw * 32 <= 2080 positions)
+    for (int h = w; h < nh; h += 32) {
+      const int ww = (int)(heavy[h] >> 16), tt = (int)(heavy[h] & 0xffffu);
+      const int s0 = ww ? cnt[(size_t)(ww - 1) * Np + tt] : 0, e0 = cnt[(size_t)ww * Np + tt];
+      unsigned short* seg = perm16 + rp[tt];
+      const int cbase = ww * gpw * 32;
+      for (int i = lane; i < kOrdBitmapWords; i += 32) bm[i] = 0u;
+      __syncwarp();
+      for (int i = s0 + lane; i < e0; i += 32) {
+        const int rel = (int)seg[i] - cbase;
+        atomicOr(&bm[rel >> 5], 1u << (rel & 31));
+      }
+      __syncwarp();
+      // lane l owns words [3l, 3l+3): exclusive prefix of their population counts, then the set bits in order
+      unsigned wd[3];
+      int pc = 0;
+#pragma unroll
+      for (int k = 0; k < 3; k++) { wd[k] = 3 * lane + k < kOrdBitmapWords ? bm[3 * lane + k] : 0u; pc += __popc(wd[k]); }
+      int inc = pc;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int y = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += y;
+      }
+      int out = s0 + inc - pc;
+      __syncwarp();  // every lane has read the piece before it is rewritten
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        unsigned m = wd[k];
+        while (m) {
+          const int bit = __ffs(m) - 1;
+          m &= m - 1;
+          seg[out++] = (unsigned short)(cbase + (3 * lane + k) * 32 + bit);
+        }
+      }
+      __syncwarp();
+    }
+  }
+  __syncthreads();
+  // ---- 5. write-out
+  int* __restrict__ perm = perm_all + (int64_t)b * E;
+  for (int i = t; i < E; i += 1024) perm[i] = perm16[i];
 }
 
 // T = unsigned short: the cloud's whole source list lives in shared memory while it is filled and sorted (E <= 65535)
@@ -1400,7 +1577,7 @@ GEOT_API int geot_gather_rows(int B, int N, int M, int D, const float* src, cons
 
 /* testing / A-B timing: direct != 0 disables the row-staged forward kernel (process-wide). */
 GEOT_API void geot_group_points_config(int mode) {
-  g_group_force_direct = mode == 1; g_force_staged = mode == 2; g_rows4_off = mode == 3; g_tip_off = mode == 4; g_mtile_off = mode == 6; g_mtile_on = mode == 7; g_pr_variant = mode == 9 ? 4 : (mode == 10 ? 3 : (mode == 11 ? 1 : (mode == 12 ? 6 : (mode == 13 ? 2 : -1)))); g_tib_stream = mode == 8 ? 1 : (mode == 5 ? -1 : 0); g_nn_queue_off = mode == 14;
+  g_group_force_direct = mode == 1; g_force_staged = mode == 2; g_rows4_off = mode == 3; g_tip_off = mode == 4; g_mtile_off = mode == 6; g_mtile_on = mode == 7; g_pr_variant = mode == 9 ? 4 : (mode == 10 ? 3 : (mode == 11 ? 1 : (mode == 12 ? 6 : (mode == 13 ? 2 : -1)))); g_tib_stream = mode == 8 ? 1 : (mode == 5 ? -1 : 0); g_nn_queue_off = mode == 14; g_plan_ordered_off = mode == 15;
 }
 
 GEOT_API int geot_gather_points(int B, int C, int N, int M, const float* points, const int* idx,
@@ -1443,6 +1620,18 @@ GEOT_API int geot_scatter_plan_build(int B, int N, int64_t E, const int* idx, vo
   // kNN lists: B=2, E=512000 fused 0.222 ms / multi-kernel 0.105; B=8 0.222 / 0.221; B=16, E=131072 0.064 / 0.200)
   const double waves = std::ceil((double)B * S / num_sms());
   const bool fused_pays = 0.43e-6 * (double)E * waves < 0.067 + 0.038e-6 * (double)E * B;
+  // few targets with long source lists (three_interpolate's m = 1024 coarse points, 48 sources each): counting sort by
+  // (target, chunk).  Measured against the fused builder (tools/plan_ab.py): 0.046 vs 0.087 ms at 48 sources per target,
+  // 0.028 vs 0.044 at 48 with 256 targets, but 0.017 vs 0.014 and 0.030 vs 0.015 at 12 (segments the fused builder sorts
+  // in registers)
+  if (N >= 1 && N <= kOrdMaxN && E >= 24 * (int64_t)N && E <= 65535 && plan_ordered_smem(N, E) <= kOrdBudget && !g_force_staged &&
+      !g_plan_ordered_off) {
+    static DynSmem ds_ord;
+    if (int rc = ds_ord.need(plan_build_ordered_kernel, kOrdBudget, "scatter_plan_build")) return rc;
+    plan_build_ordered_kernel<<<B, 1024, plan_ordered_smem(N, E), s>>>(N, (int)E, idx, row_ptr, perm);
+    count_launch(1);
+    return check_launch("plan_build_ordered_kernel");
+  }
   if (N >= 1 && nmax <= kFusedMaxN && E >= 1 && E <= kFusedMaxE && fused_pays && B <= 65535 && !g_force_staged) {
     // the whole CSR of a cloud (or of one target range of it) in shared memory (see plan_build_fused_kernel)
     const size_t kBudget = (size_t)220 * 1024;  // + 1.3 KB of static shared memory in the kernel

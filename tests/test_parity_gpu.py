@@ -580,7 +580,9 @@ def test_aggregation_vector_and_scalar_paths(cuda, oracle, c, wc):
 
 
 @pytest.mark.parametrize("B,N,E_shape", [(4, 16384, (1024, 32)), (2, 4096, (1024, 64)), (3, 1000, (250, 16)), (2, 8192, (16000, 3)),
-                                         (1, 37, (5, 8)), (2, 40000, (4096, 32)), (1, 2048, (16384, 16))])
+                                         (1, 37, (5, 8)), (2, 40000, (4096, 32)), (1, 2048, (16384, 16)),
+                                         # few targets, long lists: the chunked counting-sort builder (E >= 24 N, N <= 2048, E <= 65535)
+                                         (3, 1024, (16384, 3)), (2, 256, (4096, 3)), (1, 2047, (16383, 3)), (2, 100, (1000, 7)), (1, 1, (65535, 1)), (2, 2048, (21845, 3))])
 def test_scatter_plan_fused_builder_equals_multi_kernel_builder(cuda, B, N, E_shape):
     """The one-CTA-per-cloud fused builder (shared-memory counters, in-place segment sort) against the multi-kernel
     builder (mode 2 of the thread-local override forces it): identical row_ptr and perm - ascending sources per target -

@@ -46,3 +46,21 @@ for (B, N, M, ns, r) in [(64, 16384, 1024, 32, 0.1), (16, 16384, 4096, 32, 0.1),
         finally:
             _lib.lib().geot_group_points_config(0)
     print(f"ball query B={B} N={N} M={M} ns={ns} E={M*ns}: default {res['default']:.4f} ms   multi-kernel {res['multi_kernel']:.4f} ms", flush=True)
+
+# three_nn index tensors as three_interpolate's backward builds them: E = 3 n sources into m coarse targets, ~3n/m sources
+# per target - the ordered builder (stable counting sort, default) against the fused builder (mode 15) and the multi-kernel path
+for (B, n, m) in [(64, 16384, 1024), (16, 16384, 1024), (16, 4096, 1024), (16, 4096, 256), (6, 8192, 2048), (16, 1024, 256), (2, 16000, 1000), (16, 16384, 4096)]:
+    xyz = torch.from_numpy(synth.tooth_batch(B, n)).cuda()
+    cen = torch.gather(xyz, 1, F.furthest_point_sampling(xyz, m).long()[..., None].expand(-1, -1, 3)).contiguous()
+    _, i3 = F.three_nn(xyz, cen)
+    res = {}
+    for name, mode in (("default", 0), ("fused", 15), ("multi_kernel", 2)):
+        _lib.lib().geot_group_points_config(mode)
+        try:
+            res[name] = timeit(lambda: F.ScatterPlan(i3, B, m))
+            pl = F.ScatterPlan(i3, B, m)
+            res[name + "_plan"] = (pl.row_ptr().clone(), pl.perm().clone())
+        finally:
+            _lib.lib().geot_group_points_config(0)
+    eq = all(torch.equal(a, b) for a, b in zip(res["default_plan"], res["multi_kernel_plan"])) and all(torch.equal(a, b) for a, b in zip(res["fused_plan"], res["multi_kernel_plan"]))
+    print(f"three_nn B={B} n={n} m={m} E={3*n}: default {res['default']:.4f} ms   fused {res['fused']:.4f} ms   multi-kernel {res['multi_kernel']:.4f} ms   equal={eq}", flush=True)
