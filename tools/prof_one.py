@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Dev tool (GPU box): launch ONE op of the bench workload a few times so ncu can capture it.
-usage: python tools/prof_one.py {fps|fps_noprune|ball|group|group3|groupxyz|groupbwd|plan|threenn|tibwd|ti|ti_old|gf|upsample|knn|knntie|sigt|apply|manifold} [B]"""
+usage: python tools/prof_one.py {fps|fps_noprune|ball|group|group3|groupxyz|groupbwd|plan|plan3|threenn|tibwd|ti|ti_old|gf|upsample|knn|knntie|sigt|apply|manifold} [B]"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
@@ -19,7 +19,7 @@ nbr = F.ball_query(centres, xyz, 0.1, NS)
 if what == "groupbwd":
     go = torch.randn(B, C, M, NS, device="cuda")
     plan = F.ScatterPlan(nbr, B, N)
-if what in ("threenn", "tibwd", "ti", "ti_old"):
+if what in ("threenn", "tibwd", "ti", "ti_old", "plan3"):
     d2, i3 = F.three_nn(xyz, centres)
     w = 1.0 / (d2 + 1e-8); w = (w / w.sum(-1, keepdim=True)).contiguous()
     go3 = torch.randn(B, C, N, device="cuda")
@@ -64,6 +64,7 @@ for _ in range(3):
     elif what == "group3": F.group_points(xyz_t, nbr)
     elif what == "groupbwd": F.group_points_grad(go, plan, N)
     elif what == "plan": F.ScatterPlan(nbr, B, N)
+    elif what == "plan3": F.ScatterPlan(i3, B, M)
     elif what == "threenn": F.three_nn(xyz, centres)
     elif what == "tibwd": F.three_interpolate_grad(go3, w, plan3, M)
     elif what == "gf": F.graph_feature(gx_k, gx_q, gidx)

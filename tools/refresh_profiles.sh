@@ -18,12 +18,13 @@ python tools/plan_ab.py > gpurun_out/${tag}_plan_ab.log 2>&1
 python tools/manifold_parts.py > gpurun_out/${tag}_manifold_parts.log 2>&1
 python tools/groupbwd_ab.py > gpurun_out/${tag}_groupbwd_ab.log 2>&1
 python tools/tibwd_ab.py > gpurun_out/${tag}_tibwd_ab.log 2>&1
+python tools/threenn_ab.py > gpurun_out/${tag}_threenn_ab.log 2>&1
 [ -n "$NO_NCU" ] && { ls -la gpurun_out/ | tail -30; exit 0; }   # NO_NCU=1: the measurements only, no ncu captures
 B="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-extras"
 $B > gpurun_out/${tag}_launches_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${tag}_launches_bench.csv \
     $B > gpurun_out/${tag}_launches.log 2>&1
-ALL=("fps fps_mgr" "ball bq_build" "ball bq_grid" "group group_rows" "groupbwd seg_reduce_planrow" "plan plan_build_fused" \
+ALL=("fps fps_mgr" "ball bq_build" "ball bq_grid" "group group_rows" "groupbwd seg_reduce_planrow" "plan plan_build_fused" "plan3 plan_build_ordered" \
      "threenn three_nn_grid" "tibwd ti_bwd_stream" "knn knn_grid" "knntie knn_heap_warp" \
      "sigt sigt_kernel" "apply transition_apply_tile" "manifold manifold_fwd_tile" "manifold manifold_bwd_tile" \
      "manifold spatial_order_fine" "ti three_interpolate_persist" "gf graph_feature_kernel" "groupxyz group_xyz_rel")
