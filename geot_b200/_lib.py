@@ -21,6 +21,8 @@ GEOT_FPS_FORCE_GENERIC = 4
 GEOT_FPS_NO_PRUNE = 8
 GEOT_FPS_SPEC = 16
 GEOT_BQ_FORCE_GRID = 1
+GEOT_BQ_BUILD_ONLY = 2
+GEOT_BQ_PREBUILT = 4
 
 
 def GEOT_BQ_LEVELS(n):

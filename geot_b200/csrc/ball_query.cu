@@ -493,8 +493,11 @@ GEOT_API int geot_ball_query(int B, int N, int M, float radius, int nsample, con
                              const float* xyz, int* idx, void* workspace, size_t workspace_bytes,
                              int flags, geot_stream_t stream) {
   GEOT_REQUIRE(B >= 0 && N >= 0 && M >= 0 && nsample >= 0, "ball_query: bad sizes");
-  if (B == 0 || M == 0 || nsample == 0) return GEOT_OK;
-  GEOT_REQUIRE(new_xyz && xyz && idx, "ball_query: NULL pointer");
+  const bool build_only = (flags & GEOT_BQ_BUILD_ONLY) != 0, prebuilt = (flags & GEOT_BQ_PREBUILT) != 0;
+  GEOT_REQUIRE(!(build_only && prebuilt), "ball_query: GEOT_BQ_BUILD_ONLY and GEOT_BQ_PREBUILT exclude each other");
+  if (B == 0 || nsample == 0 || (M == 0 && !build_only)) return GEOT_OK;
+  GEOT_REQUIRE(xyz && (build_only || (new_xyz && idx)), "ball_query: NULL pointer");
+  GEOT_REQUIRE(!(build_only || prebuilt) || workspace != nullptr, "ball_query: GEOT_BQ_BUILD_ONLY / GEOT_BQ_PREBUILT need the workspace");
   GEOT_REQUIRE(B <= 65535, "ball_query: B=%d exceeds grid.y", B);
   cudaStream_t s = as_stream(stream);
   const unsigned char* ws = nullptr;
@@ -512,16 +515,20 @@ GEOT_API int geot_ball_query(int B, int N, int M, float radius, int nsample, con
     if (int rc = ds_grid.need(bq_grid_kernel, 8 * (kBqMaxN / 8), "ball_query")) return rc;
     unsigned char* wsw = reinterpret_cast<unsigned char*>(workspace);
     const int force_grid = (flags & GEOT_BQ_FORCE_GRID) ? 1 : 0, force_levels = GEOT_BQ_LEVELS_OF(flags);
-    if (N <= kBqRegPts * 1024) {
-      if (int rc = ds_build_c.need(bq_build_kernel<true>, kBqMaxCells * 4, "ball_query")) return rc;
-      bq_build_kernel<true><<<B, 1024, kBqMaxCells * 4, s>>>(N, radius, nsample, xyz, wsw, stride, force_grid, force_levels);
-    } else {
-      if (int rc = ds_build.need(bq_build_kernel<false>, kBqMaxCells * 4, "ball_query")) return rc;
-      bq_build_kernel<false><<<B, 1024, kBqMaxCells * 4, s>>>(N, radius, nsample, xyz, wsw, stride, force_grid, force_levels);
+    int rc = GEOT_OK;
+    if (!prebuilt) {  // the binning depends on (xyz, radius, nsample) only: a caller may run it ahead of the queries
+      if (N <= kBqRegPts * 1024) {
+        if (int rc2 = ds_build_c.need(bq_build_kernel<true>, kBqMaxCells * 4, "ball_query")) return rc2;
+        bq_build_kernel<true><<<B, 1024, kBqMaxCells * 4, s>>>(N, radius, nsample, xyz, wsw, stride, force_grid, force_levels);
+      } else {
+        if (int rc2 = ds_build.need(bq_build_kernel<false>, kBqMaxCells * 4, "ball_query")) return rc2;
+        bq_build_kernel<false><<<B, 1024, kBqMaxCells * 4, s>>>(N, radius, nsample, xyz, wsw, stride, force_grid, force_levels);
+      }
+      count_launch(1);
+      rc = check_launch("bq_build_kernel");
+      if (rc) return rc;
     }
-    count_launch(1);
-    int rc = check_launch("bq_build_kernel");
-    if (rc) return rc;
+    if (build_only) return GEOT_OK;
     int wpl_log2 = 2;  // words per lane: power of two >= N/1024, at least 4
     while ((1024 << wpl_log2) < N) wpl_log2++;
     dim3 gq((M + 7) / 8, B);
@@ -530,6 +537,7 @@ GEOT_API int geot_ball_query(int B, int N, int M, float radius, int nsample, con
     rc = check_launch("bq_grid_kernel");
     if (rc) return rc;
   }
+  if (build_only) return GEOT_OK;  // a cloud size the grid path does not take: nothing to prepare
   const int aligned16 = (((uintptr_t)xyz & 15) == 0) && ((N * 3) % 4 == 0);
   dim3 grid((M + 31) / 32, B);
   ball_query_shared_kernel<<<grid, 1024, 0, s>>>(N, M, radius, nsample, new_xyz, xyz, idx, aligned16, ws, stride);

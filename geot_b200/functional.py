@@ -89,9 +89,59 @@ def ball_query(new_xyz, xyz, radius, nsample, out=None, workspace=None, use_grid
         ws_bytes = int(_lib.lib().geot_ball_query_workspace_bytes(B, N)) if use_grid else 0
         if ws_bytes and (workspace is None or workspace.numel() < ws_bytes):
             workspace = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        if not ws_bytes:
+            flags &= ~_lib.GEOT_BQ_PREBUILT
         call("geot_ball_query", B, N, M, float(radius), nsample, ptr(new_xyz), ptr(xyz), ptr(out),
              ptr(workspace) if ws_bytes else None, ws_bytes, flags, stream_ptr())
     return out
+
+
+_side_streams = {}
+
+
+def fps_ball_query(xyz, npoint, radius, nsample, fps_flags=0, bq_flags=0, idx=None, centres=None, nbr=None, workspace=None):
+    """The sampling half of a PointNet++ set-abstraction level (pointnet2_modules.py: furthest_point_sample ->
+    gather_operation -> QueryAndGroup's ball_query) with the ball query's binning of the cloud - which needs xyz, radius
+    and nsample but not the centres - running on a side stream while FPS (one CTA per cloud, most SMs idle) computes
+    them.  Returns (fps idx (B,npoint), centres (B,npoint,3), neighbour idx (B,npoint,nsample)): the values of the three
+    separate calls."""
+    dev = check_cuda(xyz)
+    cur = torch.cuda.current_stream(dev)
+    side = _side_streams.get(dev)
+    if side is None:
+        side = _side_streams[dev] = torch.cuda.Stream(device=dev)
+    B, N, _ = xyz.shape
+    ws_bytes = int(_lib.lib().geot_ball_query_workspace_bytes(B, N))
+    if workspace is None or workspace.numel() < ws_bytes:
+        with on_device(dev):
+            workspace = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+    ready, built = torch.cuda.Event(), torch.cuda.Event()
+    ready.record(cur)                      # xyz (and the workspace) as the current stream leaves them
+    side.wait_event(ready)
+    with torch.cuda.stream(side):
+        ball_query_prepare(xyz, radius, nsample, workspace, flags=bq_flags)
+        built.record(side)
+    idx = furthest_point_sampling(xyz, npoint, flags=fps_flags, out=idx)
+    centres = gather_rows(xyz, idx, out=centres)
+    cur.wait_event(built)                  # joined again: nothing of this call is left on the side stream afterwards
+    nbr = ball_query(centres, xyz, radius, nsample, out=nbr, workspace=workspace, flags=bq_flags | _lib.GEOT_BQ_PREBUILT)
+    return idx, centres, nbr
+
+
+def ball_query_prepare(xyz, radius, nsample, workspace=None, flags=0):
+    """Bins the clouds for ball_query(.., radius, nsample) into `workspace` (allocated when None) and returns it.  The
+    binning does not depend on the query centres, so it can run on another stream while they are being computed; the
+    query itself is then ball_query(..., workspace=ws, flags=flags | GEOT_BQ_PREBUILT) with the same xyz."""
+    dev = check_cuda(xyz)
+    B, N, _ = xyz.shape
+    with on_device(dev):
+        ws_bytes = int(_lib.lib().geot_ball_query_workspace_bytes(B, N))
+        if workspace is None or workspace.numel() < ws_bytes:
+            workspace = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        if ws_bytes:  # 0: a cloud size that never takes the binned path - nothing to prepare
+            call("geot_ball_query", B, N, 0, float(radius), nsample, None, ptr(xyz), None, ptr(workspace), ws_bytes,
+                 flags | _lib.GEOT_BQ_BUILD_ONLY, stream_ptr())
+    return workspace
 
 
 def ballquery_offset(radius, nsample, xyz, new_xyz, offset, new_offset, out=None):

@@ -87,6 +87,12 @@ int geot_furthestsampling(int b, int n_max, const float* xyz, const int* offset,
  * small against the cloud; without one (or N > 65536) every cloud is scanned in index order.  Same result.
  * --------------------------------------------------------------------------------------------- */
 #define GEOT_BQ_FORCE_GRID 1 /* testing: take the grid path for every cloud, whatever the cost model says */
+/* The binning of the clouds depends on (xyz, radius, nsample) only, not on the query centres.  A caller that computes the
+ * centres from the same cloud first (PointNet++: furthest_point_sample -> gather -> ball_query) can run it meanwhile on
+ * another stream: call once with GEOT_BQ_BUILD_ONLY (new_xyz / idx may be NULL, M is ignored), order the streams, then
+ * call with GEOT_BQ_PREBUILT, the SAME xyz, N, radius, nsample, workspace and grid flags.  Same indices as one plain call. */
+#define GEOT_BQ_BUILD_ONLY 2
+#define GEOT_BQ_PREBUILT 4
 /* testing / A-B: GEOT_BQ_LEVELS(n), n in {1,2,4,8}: bin the points in (at most) n index levels instead of the count the
  * occupancy suggests (flags bits 8..11; 0 = automatic).  Same result for every n. */
 #define GEOT_BQ_LEVELS(n) (((n) & 15) << 8)

@@ -46,6 +46,26 @@ def test_fps_batched(cuda, oracle, kind, B, N, M, variant):
     assert np.array_equal(got, exp), "pruned kernel, manager in lock-step"
 
 
+def test_ball_query_prebuilt_and_fps_ball_query(cuda):
+    """GEOT_BQ_BUILD_ONLY + GEOT_BQ_PREBUILT (the binning run ahead of the queries) and F.fps_ball_query (the same with
+    the binning on a side stream while FPS runs) give the indices of the plain calls; a workspace that still holds
+    another batch's bins is rebuilt, not reused; small clouds (no binned path) pass through."""
+    ws = None
+    for (B, N, M, r, ns, first, flags) in [(3, 16384, 512, 0.1, 32, 0, 0), (2, 8192, 300, 0.05, 16, 7, _lib.GEOT_BQ_FORCE_GRID),
+                                           (3, 16384, 512, 0.2, 64, 11, 0), (2, 2000, 100, 0.2, 16, 3, 0), (2, 3000, 64, 0.3, 8, 5, _lib.GEOT_BQ_FORCE_GRID)]:
+        xyz = cu(synth.tooth_batch(B, N, first_cloud=first))
+        idx0 = F.furthest_point_sampling(xyz, M)
+        cen0 = F.gather_rows(xyz, idx0)
+        exp = F.ball_query(cen0, xyz, r, ns, flags=flags)
+        ws = F.ball_query_prepare(xyz, r, ns, workspace=ws, flags=flags)
+        got = F.ball_query(cen0, xyz, r, ns, workspace=ws, flags=flags | _lib.GEOT_BQ_PREBUILT)
+        assert torch.equal(got, exp), (B, N, M, r, ns)
+        idx1, cen1, nbr1 = F.fps_ball_query(xyz, M, r, ns, bq_flags=flags, workspace=ws)
+        assert torch.equal(idx1, idx0) and torch.equal(cen1, cen0) and torch.equal(nbr1, exp), (B, N, M, r, ns)
+    with pytest.raises(_lib.GeotError):
+        F.ball_query(cen0, xyz, r, ns, workspace=ws, flags=_lib.GEOT_BQ_PREBUILT | _lib.GEOT_BQ_BUILD_ONLY)
+
+
 def test_fps_large_n_uses_fallback(cuda, oracle):
     xyz = clouds("tooth", 2, 20000)
     assert np.array_equal(F.furthest_point_sampling(cu(xyz), 200).cpu().numpy(), oracle.furthest_point_sample(xyz, 200))
