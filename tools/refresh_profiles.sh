@@ -5,6 +5,7 @@
 tag=${1:-r02}
 mkdir -p gpurun_out
 (time python -m pytest tests/ -q -m gpu -p no:cacheprovider) > gpurun_out/${tag}_pytest_gpu.log 2>&1
+python -c 'import __graft_entry__ as g; g.smoke(); print("smoke ok")' > gpurun_out/${tag}_smoke.log 2>&1
 python bench.py > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err || exit 1
 python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/${tag}_bench_reference.json 2>> gpurun_out/${tag}_bench.err
 for c in cfg2 cfg3 cfg4; do python bench.py --config $c --steps 10 2>/dev/null | tail -1 > gpurun_out/${tag}_$c.json; done
