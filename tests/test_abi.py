@@ -51,6 +51,28 @@ def test_argument_validation_returns_error_not_exit():
     assert rc == -1 and b"nsample" in L.geot_last_error()
 
 
+def test_flag_constants_match_the_header():
+    """Every integer #define GEOT_* of the header that the Python host mirrors has the same value there."""
+    from geot_b200 import _lib
+    src = open(os.path.join(ROOT, "include", "geot_b200.h")).read()
+    defs = dict(re.findall(r"^#define\s+(GEOT_[A-Z0-9_]+)\s+(-?\d+)\b", src, flags=re.M))
+    assert {"GEOT_FPS_CAP512", "GEOT_BQ_FORCE_GRID", "GEOT_BQ_BUILD_ONLY", "GEOT_BQ_PREBUILT", "GEOT_KNN_TIES_BY_INDEX"} <= set(defs)
+    mirrored = [n for n in defs if hasattr(_lib, n) and isinstance(getattr(_lib, n), int)]
+    assert len(mirrored) >= 8
+    for n in mirrored:
+        assert getattr(_lib, n) == int(defs[n]), n
+
+
+def test_ball_query_split_flags_are_validated_before_any_launch():
+    from geot_b200 import _lib
+    L = _lib.lib()
+    both = _lib.GEOT_BQ_BUILD_ONLY | _lib.GEOT_BQ_PREBUILT
+    rc = L.geot_ball_query(1, 8192, 4, ctypes.c_float(0.1), 8, None, None, None, None, 0, both, None)
+    assert rc == -1 and b"exclude" in L.geot_last_error()
+    rc = L.geot_ball_query(1, 8192, 0, ctypes.c_float(0.1), 8, None, ctypes.c_void_p(256), None, None, 0, _lib.GEOT_BQ_BUILD_ONLY, None)
+    assert rc == -1 and b"workspace" in L.geot_last_error()
+
+
 def test_no_cpu_fallback():
     import torch
     from geot_b200 import _lib, layers
