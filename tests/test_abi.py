@@ -80,6 +80,11 @@ def test_no_cpu_fallback():
         layers.furthest_point_sample(torch.zeros(1, 8, 3), 2)
     with pytest.raises(_lib.GeotError):
         layers.ball_query(0.1, 4, torch.zeros(1, 8, 3), torch.zeros(1, 2, 3))
+    from geot_b200 import functional as F
+    with pytest.raises(_lib.GeotError):
+        F.ball_query_prepare(torch.zeros(1, 8, 3), 0.1, 4)
+    with pytest.raises(_lib.GeotError):
+        F.fps_ball_query(torch.zeros(1, 8, 3), 2, 0.1, 4)
 
 
 def test_product_never_imports_oracle():
